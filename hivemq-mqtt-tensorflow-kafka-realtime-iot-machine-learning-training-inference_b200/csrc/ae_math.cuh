@@ -1,0 +1,205 @@
+// Device math of the Dense autoencoder D→14→7→7→D (tanh, relu, tanh, relu).
+//
+// Restates the forward pass built at
+//   python-scripts/AUTOENCODER-TensorFlow-IO-Kafka/cardata-v1.py:161-167 (18-wide)
+//   python-scripts/autoencoder-anomaly-detection/Sensor-Kafka-Consumer-and-TensorFlow-Model-Training.py:16-24 (30-wide)
+// the per-feature scaling of normalize_fn (cardata-v1.py:68-111) and the reconstruction error
+//   mse = np.mean(np.power(x - pred, 2), axis=1)   (nb2.0:1015).
+//
+// B200 specifics: the FP32 pipe only reaches its peak with the packed FFMA2 instruction (two FMAs per lane and
+// issue slot).  Accumulators are packed along the output dimension (h[2p], h[2p+1]); the weight pair arrives
+// through the kernel parameter (constant bank → uniform registers, LDCU.128) and the input is broadcast by
+// FFMA2's .F32 operand form — no shared-memory or register traffic for weights at all.
+#pragma once
+#include "common.cuh"
+
+constexpr int AE_H1 = 14, AE_H2 = 7, AE_H3 = 7;
+constexpr int AE_P1 = 16, AE_P2 = 8, AE_P3 = 8;  // padded row lengths → 16-byte aligned LDCU.128
+
+template <int D>
+struct AeW {  // padded, kernel-parameter resident copy of the weights
+  static constexpr int PD = (D + 3) & ~3;
+  float k1[D][AE_P1];      // [in][out]
+  float b1[AE_P1];
+  float k2[AE_H1][AE_P2];  // [in][out]
+  float b2[AE_P2];
+  float k3[AE_H2][AE_P3];
+  float b3[AE_P3];
+  float k4[AE_H3][PD];     // [in][out]
+  float b4[PD];
+};
+
+template <int D>
+struct NormP {             // normalize_fn table; kind: B2_NORM_*
+  int32_t kind[D];
+  float lo[D];
+  float range[D];
+};
+
+// Pack Keras flat order (kernel0[in,out], bias0, kernel1, ...) into AeW<D>.
+template <int D>
+static inline void ae_pack_weights(const float* w, AeW<D>& o) {
+  memset(&o, 0, sizeof(o));
+  const float* p = w;
+  for (int i = 0; i < D; ++i)
+    for (int j = 0; j < AE_H1; ++j) o.k1[i][j] = *p++;
+  for (int j = 0; j < AE_H1; ++j) o.b1[j] = *p++;
+  for (int i = 0; i < AE_H1; ++i)
+    for (int j = 0; j < AE_H2; ++j) o.k2[i][j] = *p++;
+  for (int j = 0; j < AE_H2; ++j) o.b2[j] = *p++;
+  for (int i = 0; i < AE_H2; ++i)
+    for (int j = 0; j < AE_H3; ++j) o.k3[i][j] = *p++;
+  for (int j = 0; j < AE_H3; ++j) o.b3[j] = *p++;
+  for (int i = 0; i < AE_H3; ++i)
+    for (int j = 0; j < D; ++j) o.k4[i][j] = *p++;
+  for (int j = 0; j < D; ++j) o.b4[j] = *p++;
+}
+
+#ifdef __CUDACC__
+__device__ __forceinline__ float2 splat(float v) { return make_float2(v, v); }
+__device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) { return __ffma2_rn(a, b, c); }
+__device__ __forceinline__ float2 mul2(float2 a, float2 b) { return __fmul2_rn(a, b); }
+__device__ __forceinline__ float2 add2(float2 a, float2 b) { return __fadd2_rn(a, b); }
+__device__ __forceinline__ float2 relu2(float2 a) { return make_float2(fmaxf(a.x, 0.f), fmaxf(a.y, 0.f)); }
+
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float rcp_approx(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// tanh to ≤ ~4 ulp (max abs error ≈ 1.5e-7): odd minimax polynomial below 0.6, 1 - 2/(e^{2|x|}+1) above.
+// tanh.approx.f32 (MUFU.TANH, 2^-11) is far too coarse for the 1e-5 relative MSE contract.
+__device__ __forceinline__ float2 tanh2(float2 x) {
+  const float2 t = mul2(x, x);
+  float2 p = fma2(t, splat(-6.276387590e-03f), splat(2.111621396e-02f));
+  p = fma2(p, t, splat(-5.387513819e-02f));
+  p = fma2(p, t, splat(1.333292401e-01f));
+  p = fma2(p, t, splat(-3.333333043e-01f));
+  p = mul2(p, t);
+  const float2 small = fma2(p, x, x);
+  const float ax = fabsf(x.x), ay = fabsf(x.y);
+  const float ex = ex2_approx(ax * 2.8853900817779268f);  // e^{2|x|}
+  const float ey = ex2_approx(ay * 2.8853900817779268f);
+  const float bx = fmaf(-2.f, rcp_approx(ex + 1.f), 1.f);
+  const float by = fmaf(-2.f, rcp_approx(ey + 1.f), 1.f);
+  float2 r;
+  r.x = ax < 0.6f ? small.x : copysignf(bx, x.x);
+  r.y = ay < 0.6f ? small.y : copysignf(by, x.y);
+  return r;
+}
+__device__ __forceinline__ float tanh1(float x) { return tanh2(make_float2(x, x)).x; }
+
+// scale_fn(v, lo, hi) = (v - lo) / (hi - lo) * 2.0 - 1.0 with the reference's operation order and a true IEEE
+// division (cardata-v1.py:68-69); `*2.0 - 1.0` folds into one FMA because the product is exact.
+__device__ __forceinline__ float norm_feature(float v, int kind, float lo, float range) {
+  if (kind == B2_NORM_SCALE) return fmaf(__fdiv_rn(__fsub_rn(v, lo), range), 2.0f, -1.0f);
+  if (kind == B2_NORM_ZERO) return 0.0f;
+  return v;
+}
+
+// Forward pass for R records living in shared-memory rows row[r] (D floats each, 8-byte aligned).
+//
+// FFMA2 packing is along the OUTPUT dimension: accumulator pair (h[2p], h[2p+1]) += x_i (broadcast, .F32 operand
+// form) * (k[i][2p], k[i][2p+1]) (one 64-bit uniform-register pair).  The input pair (x_i, x_i+1) of one LDS.64 is
+// consumed as-is, so no register shuffling is needed; R = 2 rows per thread share every LDCU.128 weight fetch.
+//   pass 1 streams x (normalising it in place when NORM) into the layer-1 accumulators,
+//   pass 2 produces one output pair at a time, accumulates (x - y)^2 and (RECON) overwrites x with y.
+template <int D, int R, bool NORM, bool RECON>
+__device__ __forceinline__ void ae_forward_rows(const AeW<D>& w, const NormP<D>& nm, float* const (&row)[R], float (&mse)[R]) {
+  static_assert(D % 2 == 0, "feature count must be even (8-byte row alignment)");
+  constexpr int Q1 = AE_H1 / 2, Q2 = AE_P2 / 2, Q3 = AE_P3 / 2;
+  float2 h1[R][Q1];
+#pragma unroll
+  for (int r = 0; r < R; ++r)
+#pragma unroll
+    for (int q = 0; q < Q1; ++q) h1[r][q] = make_float2(w.b1[2 * q], w.b1[2 * q + 1]);
+#pragma unroll
+  for (int i = 0; i < D; i += 2) {
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      float2 xv = *reinterpret_cast<const float2*>(row[r] + i);
+      if (NORM) {
+        xv.x = norm_feature(xv.x, nm.kind[i], nm.lo[i], nm.range[i]);
+        xv.y = norm_feature(xv.y, nm.kind[i + 1], nm.lo[i + 1], nm.range[i + 1]);
+        *reinterpret_cast<float2*>(row[r] + i) = xv;
+      }
+#pragma unroll
+      for (int q = 0; q < Q1; ++q) h1[r][q] = fma2(splat(xv.x), make_float2(w.k1[i][2 * q], w.k1[i][2 * q + 1]), h1[r][q]);
+#pragma unroll
+      for (int q = 0; q < Q1; ++q)
+        h1[r][q] = fma2(splat(xv.y), make_float2(w.k1[i + 1][2 * q], w.k1[i + 1][2 * q + 1]), h1[r][q]);
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < R; ++r)
+#pragma unroll
+    for (int q = 0; q < Q1; ++q) h1[r][q] = tanh2(h1[r][q]);
+
+  float2 h2[R][Q2];  // 7 units padded to 8 (pad lane stays 0: zero weights, zero bias, relu)
+#pragma unroll
+  for (int r = 0; r < R; ++r)
+#pragma unroll
+    for (int q = 0; q < Q2; ++q) h2[r][q] = make_float2(w.b2[2 * q], w.b2[2 * q + 1]);
+#pragma unroll
+  for (int i = 0; i < AE_H1; ++i)
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const float xi = (i & 1) ? h1[r][i / 2].y : h1[r][i / 2].x;
+#pragma unroll
+      for (int q = 0; q < Q2; ++q) h2[r][q] = fma2(splat(xi), make_float2(w.k2[i][2 * q], w.k2[i][2 * q + 1]), h2[r][q]);
+    }
+#pragma unroll
+  for (int r = 0; r < R; ++r)
+#pragma unroll
+    for (int q = 0; q < Q2; ++q) h2[r][q] = relu2(h2[r][q]);
+
+  float2 h3[R][Q3];
+#pragma unroll
+  for (int r = 0; r < R; ++r)
+#pragma unroll
+    for (int q = 0; q < Q3; ++q) h3[r][q] = make_float2(w.b3[2 * q], w.b3[2 * q + 1]);
+#pragma unroll
+  for (int i = 0; i < AE_H2; ++i)
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const float xi = (i & 1) ? h2[r][i / 2].y : h2[r][i / 2].x;
+#pragma unroll
+      for (int q = 0; q < Q3; ++q) h3[r][q] = fma2(splat(xi), make_float2(w.k3[i][2 * q], w.k3[i][2 * q + 1]), h3[r][q]);
+    }
+#pragma unroll
+  for (int r = 0; r < R; ++r)
+#pragma unroll
+    for (int q = 0; q < Q3; ++q) h3[r][q] = tanh2(h3[r][q]);
+
+  // compiler barrier: re-read x from shared memory in pass 2 instead of keeping D values per row live in registers
+  asm volatile("" ::: "memory");
+  float2 se[R];
+#pragma unroll
+  for (int r = 0; r < R; ++r) se[r] = make_float2(0.f, 0.f);
+#pragma unroll
+  for (int j = 0; j < D; j += 2) {
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      float2 y = make_float2(w.b4[j], w.b4[j + 1]);
+#pragma unroll
+      for (int k = 0; k < AE_H3; ++k) {
+        const float hk = (k & 1) ? h3[r][k / 2].y : h3[r][k / 2].x;
+        y = fma2(splat(hk), make_float2(w.k4[k][j], w.k4[k][j + 1]), y);
+      }
+      y = relu2(y);
+      const float2 xv = *reinterpret_cast<const float2*>(row[r] + j);
+      const float2 d = make_float2(xv.x - y.x, xv.y - y.y);
+      se[r] = fma2(d, d, se[r]);
+      if (RECON) *reinterpret_cast<float2*>(row[r] + j) = y;
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < R; ++r) mse[r] = __fdiv_rn(se[r].x + se[r].y, (float)D);
+}
+#endif

@@ -1,0 +1,287 @@
+// K1 — fused normalise → Dense stack → per-record MSE → anomaly flag.
+//
+// Replaces, per batch of pre-decoded rows: normalize_fn (AUTOENCODER-TensorFlow-IO-Kafka/cardata-v1.py:40-131),
+// Model.predict (cardata-v1.py:231, nb2.0:1014), np.mean(np.power(x - pred, 2), axis=1) (nb2.0:1015) and
+// `1 if e > threshold_fixed else 0` (nb2.0:1129,1163).
+//
+// HBM layout: x is the row-major [N, D] f32 matrix exactly as tf.stack(...)/batch() produces it; a tile of
+// 2*NT consecutive rows is one contiguous byte range, so it is fetched with ONE 1-D bulk async copy (TMA engine,
+// cp.async.bulk + mbarrier complete_tx) into a STAGES-deep shared-memory ring by a persistent CTA.  Each thread
+// then owns two rows of the tile (row t and row t+NT: the 120 B / 72 B row stride makes 8-byte LDS conflict-free)
+// and runs the packed-FFMA2 forward pass of ae_math.cuh.  Outputs: mse f32[N] + flag u8[N] (5 B/record), written
+// coalesced; optional reconstruction rows go back through shared memory and a bulk store.
+//
+// Algorithmic bytes/record: 4*D read + 5 written (+ 4*D written with recon).  FLOP/record: 2*(14D+98+49+7D).
+#include "ae_math.cuh"
+
+template <int D>
+struct ScoreArgs {
+  AeW<D> w;
+  NormP<D> nm;
+  const float* x;
+  float* mse;
+  uint8_t* flag;
+  float* recon;
+  unsigned long long* counters;
+  long long n;
+  float threshold;
+  int use_bulk;
+};
+
+template <int D, int NT, int STAGES, bool NORM, bool RECON>
+__global__ void __launch_bounds__(NT) ae_score_kernel(const __grid_constant__ ScoreArgs<D> a) {
+  constexpr int TILE = 2 * NT;
+  constexpr int TILE_FLOATS = TILE * D;
+  constexpr uint32_t TILE_BYTES = TILE_FLOATS * 4;
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)STAGES * TILE_BYTES);
+  const int tid = threadIdx.x;
+  const long long n_tiles = (a.n + TILE - 1) / TILE;
+
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < STAGES; ++s) mbar_init(&full[s], 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  auto issue = [&](long long tile, int s) {  // thread 0 only
+    if (tile < n_tiles && a.use_bulk && (tile + 1) * TILE <= a.n) {
+      mbar_expect_tx(&full[s], TILE_BYTES);
+      bulk_g2s(smem + (size_t)s * TILE_BYTES, a.x + tile * TILE_FLOATS, TILE_BYTES, &full[s]);
+    }
+  };
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < STAGES; ++s) issue((long long)blockIdx.x + (long long)s * gridDim.x, s);
+  }
+
+  uint32_t phase = 0;  // bit s = parity to wait for on stage s
+  unsigned flagged = 0;
+  int s = 0;
+  for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    float* st = reinterpret_cast<float*>(smem + (size_t)s * TILE_BYTES);
+    const long long row0 = tile * TILE;
+    const int rows = (int)min((long long)TILE, a.n - row0);
+    const bool bulk = a.use_bulk && rows == TILE;
+    if (bulk) {
+      mbar_wait(&full[s], (phase >> s) & 1u);
+      phase ^= 1u << s;
+    } else {  // ragged last tile or unaligned input: plain coalesced loads
+      const float* src = a.x + row0 * D;
+      for (int i = tid; i < rows * D; i += NT) st[i] = __ldg(src + i);
+      __syncthreads();
+    }
+    const bool va = tid < rows, vb = tid + NT < rows;
+    // rows tid and tid+NT belong to this thread alone; in a ragged tile the second one may hold stale data that is
+    // computed on but never stored
+    float* const rowp[2] = {st + (size_t)tid * D, st + (size_t)(tid + NT) * D};
+    float mm[2] = {0.f, 0.f};
+    if (va) ae_forward_rows<D, 2, NORM, RECON>(a.w, a.nm, rowp, mm);
+    const float2 m = make_float2(mm[0], mm[1]);
+    const bool fa = m.x > a.threshold, fb = m.y > a.threshold;  // strict, nb2.0:1163
+    if (va) {
+      if (a.mse) a.mse[row0 + tid] = m.x;
+      if (a.flag) a.flag[row0 + tid] = fa ? 1 : 0;
+      flagged += fa;
+    }
+    if (vb) {
+      if (a.mse) a.mse[row0 + tid + NT] = m.y;
+      if (a.flag) a.flag[row0 + tid + NT] = fb ? 1 : 0;
+      flagged += fb;
+    }
+    if (RECON) {
+      if (bulk) {
+        fence_proxy_async();  // my generic-proxy writes of y → visible to the bulk-copy engine
+        __syncthreads();
+        if (tid == 0) {
+          bulk_s2g(a.recon + row0 * D, st, TILE_BYTES);
+          bulk_commit();
+          bulk_wait_read_all();  // stage may be refilled once the engine has read it
+        }
+      } else {
+        __syncthreads();
+        float* dst = a.recon + row0 * D;
+        for (int i = tid; i < rows * D; i += NT) dst[i] = st[i];
+        __syncthreads();
+      }
+    } else {
+      __syncthreads();  // everyone is done reading stage s
+    }
+    if (tid == 0) issue(tile + (long long)STAGES * gridDim.x, s);
+    s = (s + 1 == STAGES) ? 0 : s + 1;
+  }
+  if (RECON && tid == 0) bulk_wait_all();
+
+  if (a.counters) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) flagged += __shfl_xor_sync(0xffffffffu, flagged, o);
+    if ((tid & 31) == 0 && flagged) atomicAdd(&a.counters[1], (unsigned long long)flagged);
+    if (blockIdx.x == 0 && tid == 0) atomicAdd(&a.counters[0], (unsigned long long)a.n);
+  }
+}
+
+// ---- generic fallback: any Dense stack up to 8 layers × 64 units, one thread per record --------------------
+struct GenericArgs {
+  b2_ae_desc desc;
+  b2_norm nm;
+  const float* w;  // device, Keras flat order
+  int n_params;
+  const float* x;
+  float* mse;
+  uint8_t* flag;
+  float* recon;
+  unsigned long long* counters;
+  long long n;
+  float threshold;
+};
+
+__global__ void __launch_bounds__(128) ae_score_generic_kernel(const __grid_constant__ GenericArgs a) {
+  extern __shared__ float wsm[];
+  for (int i = threadIdx.x; i < a.n_params; i += blockDim.x) wsm[i] = a.w[i];
+  __syncthreads();
+  const int D = a.desc.widths[0];
+  unsigned flagged = 0;
+  for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < a.n; r += (long long)gridDim.x * blockDim.x) {
+    float x[B2_MAX_WIDTH], h[B2_MAX_WIDTH], t[B2_MAX_WIDTH];
+    for (int j = 0; j < D; ++j) {
+      float v = a.x[r * D + j];
+      if (a.nm.n) v = norm_feature(v, a.nm.kind[j], a.nm.lo[j], a.nm.range[j]);
+      x[j] = v;
+      h[j] = v;
+    }
+    const float* p = wsm;
+    for (int l = 0; l < a.desc.n_layers; ++l) {
+      const int in = a.desc.widths[l], out = a.desc.widths[l + 1];
+      const float* k = p;
+      const float* b = p + in * out;
+      for (int o = 0; o < out; ++o) {
+        float acc = b[o];
+        for (int i = 0; i < in; ++i) acc = fmaf(h[i], k[i * out + o], acc);
+        if (a.desc.act[l] == B2_ACT_TANH) acc = tanh1(acc);
+        else if (a.desc.act[l] == B2_ACT_RELU) acc = fmaxf(acc, 0.f);
+        t[o] = acc;
+      }
+      for (int o = 0; o < out; ++o) h[o] = t[o];
+      p += in * out + out;
+    }
+    float se = 0.f;
+    for (int j = 0; j < D; ++j) {
+      const float d = x[j] - h[j];
+      se = fmaf(d, d, se);
+      if (a.recon) a.recon[r * D + j] = h[j];
+    }
+    const float m = __fdiv_rn(se, (float)D);
+    const bool f = m > a.threshold;
+    if (a.mse) a.mse[r] = m;
+    if (a.flag) a.flag[r] = f ? 1 : 0;
+    flagged += f;
+  }
+  if (a.counters) {
+    for (int o = 16; o > 0; o >>= 1) flagged += __shfl_xor_sync(0xffffffffu, flagged, o);
+    if ((threadIdx.x & 31) == 0 && flagged) atomicAdd(&a.counters[1], (unsigned long long)flagged);
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&a.counters[0], (unsigned long long)a.n);
+  }
+}
+
+// ---- host side ----------------------------------------------------------------------------------------------
+static int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return v ? atoi(v) : dflt;
+}
+
+template <int D, int NT, int STAGES, bool NORM, bool RECON>
+static int launch_score(b2_ae* ae, const ScoreArgs<D>& args, cudaStream_t stream) {
+  constexpr int TILE = 2 * NT;
+  constexpr size_t smem = (size_t)STAGES * TILE * D * 4 + STAGES * sizeof(uint64_t);
+  auto kern = ae_score_kernel<D, NT, STAGES, NORM, RECON>;
+  static int occ_cache[16] = {0};  // per device
+  int dev = ae->ctx->device;
+  if (occ_cache[dev & 15] == 0) {
+    B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int occ = 0;
+    B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, NT, smem));
+    B2_REQUIRE(occ >= 1, "ae_score: kernel does not fit on an SM (smem %zu)", smem);
+    occ_cache[dev & 15] = occ;
+  }
+  const long long n_tiles = (args.n + TILE - 1) / TILE;
+  long long grid = (long long)ae->ctx->sm_count * occ_cache[dev & 15];
+  if (grid > n_tiles) grid = n_tiles;
+  if (grid < 1) grid = 1;
+  kern<<<(unsigned)grid, NT, smem, stream>>>(args);
+  B2_CUDA(cudaGetLastError());
+  return B2_OK;
+}
+
+template <int D>
+static int score_spec(b2_ae* ae, const float* x, int64_t n, const b2_norm* norm, float threshold, float* mse, uint8_t* flag,
+                      float* recon, unsigned long long* counters, cudaStream_t stream) {
+  ScoreArgs<D> args;
+  ae_pack_weights<D>(ae->h_w.data(), args.w);
+  memset(&args.nm, 0, sizeof(args.nm));
+  const bool has_norm = norm && norm->n > 0;
+  if (has_norm) {
+    for (int j = 0; j < D; ++j) {
+      args.nm.kind[j] = norm->kind[j];
+      args.nm.lo[j] = norm->lo[j];
+      args.nm.range[j] = norm->range[j];
+    }
+  }
+  args.x = x;
+  args.mse = mse;
+  args.flag = flag;
+  args.recon = recon;
+  args.counters = counters;
+  args.n = n;
+  args.threshold = threshold;
+  args.use_bulk = (((uintptr_t)x & 15) == 0) && (!recon || ((uintptr_t)recon & 15) == 0) && !env_int("B2_NO_BULK", 0);
+  constexpr int NT = 128;
+  constexpr int ST = 3;
+  if (has_norm) {
+    if (recon) return launch_score<D, NT, ST, true, true>(ae, args, stream);
+    return launch_score<D, NT, ST, true, false>(ae, args, stream);
+  }
+  if (recon) return launch_score<D, NT, ST, false, true>(ae, args, stream);
+  return launch_score<D, NT, ST, false, false>(ae, args, stream);
+}
+
+extern "C" int b2_ae_score(b2_ae* ae, const float* x_dev, int64_t n, const b2_norm* norm, float threshold, float* mse_dev,
+                           uint8_t* flag_dev, float* recon_dev, unsigned long long* counters_dev, void* stream) {
+  B2_REQUIRE(ae != nullptr, "b2_ae_score: ae is NULL");
+  B2_REQUIRE(n >= 0, "b2_ae_score: n=%lld < 0", (long long)n);
+  if (n == 0) return B2_OK;
+  B2_REQUIRE(x_dev != nullptr, "b2_ae_score: x_dev is NULL");
+  B2_REQUIRE(((uintptr_t)x_dev & 7) == 0, "b2_ae_score: x_dev must be 8-byte aligned");
+  B2_REQUIRE(!norm || norm->n == 0 || norm->n == ae->desc.widths[0], "b2_ae_score: norm table has %d features, model has %d",
+             norm ? norm->n : 0, ae->desc.widths[0]);
+  DeviceGuard g(ae->ctx->device);
+  int rc = b2_ae_sync_host(ae);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (ae->spec_d == 30 && !env_int("B2_FORCE_GENERIC", 0))
+    return score_spec<30>(ae, x_dev, n, norm, threshold, mse_dev, flag_dev, recon_dev, counters_dev, st);
+  if (ae->spec_d == 18 && !env_int("B2_FORCE_GENERIC", 0))
+    return score_spec<18>(ae, x_dev, n, norm, threshold, mse_dev, flag_dev, recon_dev, counters_dev, st);
+  GenericArgs ga;
+  memset(&ga, 0, sizeof(ga));
+  ga.desc = ae->desc;
+  if (norm && norm->n > 0) ga.nm = *norm;
+  ga.w = ae->d_w;
+  ga.n_params = ae->n_params;
+  ga.x = x_dev;
+  ga.mse = mse_dev;
+  ga.flag = flag_dev;
+  ga.recon = recon_dev;
+  ga.counters = counters_dev;
+  ga.n = n;
+  ga.threshold = threshold;
+  const size_t smem = sizeof(float) * ae->n_params;
+  B2_REQUIRE(smem <= (size_t)ae->ctx->smem_optin, "b2_ae_score: %d parameters do not fit in shared memory", ae->n_params);
+  B2_CUDA(cudaFuncSetAttribute(ae_score_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  long long blocks = (n + 127) / 128;
+  long long cap = (long long)ae->ctx->sm_count * 8;
+  if (blocks > cap) blocks = cap;
+  ae_score_generic_kernel<<<(unsigned)blocks, 128, smem, st>>>(ga);
+  B2_CUDA(cudaGetLastError());
+  return B2_OK;
+}

@@ -1,0 +1,115 @@
+// Shared host/device helpers for the b2 sensor-scoring library (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <vector>
+
+#include "../../include/b2_api.h"
+
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
+#error "this library is written for sm_100a (B200) only"
+#endif
+
+// ---- error plumbing ---------------------------------------------------------------------------------------
+void b2_set_error(const char* fmt, ...);
+
+#define B2_CUDA(call)                                                                              \
+  do {                                                                                             \
+    cudaError_t e__ = (call);                                                                      \
+    if (e__ != cudaSuccess) {                                                                      \
+      b2_set_error("%s:%d: %s failed: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__));    \
+      return B2_ECUDA;                                                                             \
+    }                                                                                              \
+  } while (0)
+
+#define B2_REQUIRE(cond, ...)        \
+  do {                               \
+    if (!(cond)) {                   \
+      b2_set_error(__VA_ARGS__);     \
+      return B2_EINVAL;              \
+    }                                \
+  } while (0)
+
+struct b2_ctx {
+  int device;
+  int sm_count;
+  int smem_optin;  // max dynamic shared memory per block (bytes)
+};
+
+// RAII "make this device current for the call" guard (callers may sit on another device)
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) {
+    cudaGetDevice(&prev);
+    if (prev != dev) cudaSetDevice(dev);
+    else prev = -1;
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+// ---- the Dense autoencoder handle (shared by score / decode / train translation units) ---------------------
+struct b2_ae {
+  b2_ctx* ctx;
+  b2_ae_desc desc;
+  int n_params;
+  int spec_d;                  // 18 / 30 when the stack is D-14-7-7-D tanh/relu/tanh/relu (fast kernels), else 0
+  std::vector<float> h_w;      // Keras flat order: kernel0, bias0, kernel1, bias1, ...
+  float* d_w;                  // device copy, same order
+  float* d_m;                  // Adam slots (allocated on first fit)
+  float* d_v;
+  bool host_stale;             // device weights changed by fit; h_w must be refreshed before param-passing
+};
+int b2_ae_sync_host(b2_ae* ae);    // refresh h_w from d_w if stale
+int b2_ae_ensure_adam(b2_ae* ae);  // allocate + zero the Adam slots on first use
+
+// ---- device-side PTX wrappers (mbarrier + 1-D bulk async copy = the TMA engine without a tensor map) -------
+#ifdef __CUDACC__
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  while (!mbar_try_wait(bar, parity)) {
+  }
+}
+// global → shared bulk copy; completion is signalled on `bar` (complete_tx). src/dst 16-byte aligned, bytes % 16 == 0.
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(dst_smem)),
+               "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+// shared → global bulk copy (bulk async-group completion)
+__device__ __forceinline__ void bulk_s2g(void* dst_gmem, const void* src_smem, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst_gmem), "r"(smem_u32(src_smem)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read_all() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+#endif

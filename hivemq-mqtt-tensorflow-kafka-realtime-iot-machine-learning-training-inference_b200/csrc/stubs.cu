@@ -1,0 +1,15 @@
+// Entry points not implemented yet in this build (each is replaced by its own translation unit as it lands).
+#include "common.cuh"
+#define STUB(name) b2_set_error(name ": not implemented in this build"); return B2_EUNSUPPORTED
+extern "C" int b2_decode_csv(b2_ctx*, const uint8_t*, const int32_t*, int64_t, const b2_csv_spec*, float*, int32_t*, int32_t*, void*) { STUB("b2_decode_csv"); }
+extern "C" int b2_decode_avro(b2_ctx*, const uint8_t*, const int32_t*, int64_t, int, const b2_avro_prog*, float*, uint8_t*, int32_t*, void*) { STUB("b2_decode_avro"); }
+extern "C" int b2_decode_score(b2_ae*, const uint8_t*, const int32_t*, int64_t, const b2_csv_spec*, const b2_avro_prog*, int, const b2_norm*, float, float*, uint8_t*, uint8_t*, int32_t*, unsigned long long*, void*) { STUB("b2_decode_score"); }
+extern "C" int b2_ae_fit_steps(b2_ae*, const float*, const int32_t*, int64_t, int, const b2_norm*, b2_adam*, float*, float*, void*) { STUB("b2_ae_fit_steps"); }
+extern "C" int64_t b2_ae_grad_scratch_bytes(const b2_ae*, int64_t) { return 0; }
+extern "C" int b2_ae_grad(b2_ae*, const float*, int64_t, const b2_norm*, float*, void*, int64_t, void*) { STUB("b2_ae_grad"); }
+extern "C" int b2_ae_apply(b2_ae*, const float*, b2_adam*, float*, void*) { STUB("b2_ae_apply"); }
+extern "C" int b2_lstm_create(b2_ctx*, const b2_lstm_desc*, const float*, b2_lstm**) { STUB("b2_lstm_create"); }
+extern "C" void b2_lstm_destroy(b2_lstm*) {}
+extern "C" int b2_lstm_param_count(const b2_lstm*) { return 0; }
+extern "C" int b2_lstm_forward(b2_lstm*, const float*, int64_t, int, float*, void*) { STUB("b2_lstm_forward"); }
+extern "C" int b2_partition_run(b2_ae*, const b2_partition*, int, const b2_csv_spec*, const b2_avro_prog*, int, const b2_norm*, float, int, unsigned long long*, b2_run_stats*) { STUB("b2_partition_run"); }

@@ -1,0 +1,646 @@
+"""The slice of the ``tf.keras`` surface the reference scripts use, running on the B200 kernels.
+
+Mirrors (same names, argument meaning and error behaviour where it matters):
+
+* model building  — ``Input``, ``Dense(units, activation, activity_regularizer=l1(..))``, ``Model(inputs, outputs)``
+  (python-scripts/AUTOENCODER-TensorFlow-IO-Kafka/cardata-v1.py:161-167), ``Sequential().add(LSTM/RepeatVector/
+  TimeDistributed(Dense))`` (python-scripts/LSTM-TensorFlow-IO-Kafka/cardata-v1.py:169-176)
+* ``compile(optimizer='adam', loss='mean_squared_error', metrics=['accuracy'])`` (cardata-v1.py:169-171)
+* ``fit(...).history`` (cardata-v1.py:192-194, nb2.0:871-877), ``predict(x, callbacks=[...])`` (cardata-v1.py:231),
+  ``save(path)`` / ``load_model(path)`` (cardata-v1.py:199-202) on Keras-format ``.h5`` files
+* new conveniences with the notebook's math: ``reconstruction_error(x)`` (nb2.0:1015) and ``score(x, threshold=5)``
+  (nb2.0:1129,1163)
+
+All arithmetic happens in libb2sensor.so; there is no NumPy/CPU compute path here.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import json
+import math
+from typing import Dict, List, Optional, Sequence
+
+import numpy as np
+import torch
+
+from . import _ffi, h5lite
+
+_ctx_cache: Dict[int, int] = {}
+
+
+def get_ctx(device: Optional[int] = None) -> int:
+    """Process-wide b2_ctx per CUDA device (created lazily; raises without a B200)."""
+    if device is None:
+        device = torch.cuda.current_device() if torch.cuda.is_available() else 0
+    if device not in _ctx_cache:
+        l = _ffi.lib()
+        h = C.c_void_p()
+        _ffi.check(l.b2_ctx_create(device, C.byref(h)), "b2_ctx_create")
+        _ctx_cache[device] = h.value
+    return _ctx_cache[device]
+
+
+def _stream_ptr() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+# ----------------------------------------------------------------------------------------------
+# layers / regularisers / callbacks (declarative only)
+# ----------------------------------------------------------------------------------------------
+class L1:
+    def __init__(self, l1: float = 0.01):
+        self.l1 = float(np.float32(l1))
+
+    def get_config(self):
+        return {"class_name": "L1L2", "config": {"l1": self.l1, "l2": 0.0}}
+
+
+class regularizers:
+    @staticmethod
+    def l1(l=0.01):
+        return L1(l)
+
+
+class _Tensor:
+    """Symbolic tensor of the functional API: remembers the chain of layers that produced it."""
+
+    def __init__(self, shape, chain):
+        self.shape, self.chain = shape, chain
+
+
+def Input(shape):
+    return _Tensor(tuple(shape), [InputLayer(shape)])
+
+
+class Layer:
+    _counts: Dict[str, int] = {}
+
+    def __init__(self, name=None):
+        base = type(self).__name__.lower()
+        if name is None:
+            k = Layer._counts.get(base, 0)
+            Layer._counts[base] = k + 1
+            name = base if k == 0 else f"{base}_{k}"
+        self.name = name
+
+    def __call__(self, t: _Tensor) -> _Tensor:
+        return _Tensor(self.output_shape(t.shape), t.chain + [self])
+
+    def output_shape(self, s):
+        return s
+
+
+class InputLayer(Layer):
+    def __init__(self, shape, name=None):
+        super().__init__(name or None)
+        self.shape = tuple(shape)
+
+
+class Dense(Layer):
+    def __init__(self, units, activation=None, activity_regularizer=None, use_bias=True, name=None, **_):
+        super().__init__(name)
+        if not use_bias:
+            raise NotImplementedError("Dense(use_bias=False) is not used by the reference and not supported")
+        act = "linear" if activation is None else activation
+        if act not in _ffi.ACT_CODES:
+            raise ValueError(f"unsupported activation {activation!r} (supported: {sorted(_ffi.ACT_CODES)})")
+        self.units, self.activation, self.activity_regularizer = int(units), act, activity_regularizer
+
+    def output_shape(self, s):
+        return s[:-1] + (self.units,)
+
+
+class LSTM(Layer):
+    def __init__(self, units, activation="tanh", return_sequences=False, input_shape=None, recurrent_activation="sigmoid",
+                 name=None, **_):
+        super().__init__(name)
+        self.units, self.activation, self.return_sequences, self.input_shape = int(units), activation, return_sequences, input_shape
+        self.recurrent_activation = recurrent_activation
+
+
+class RepeatVector(Layer):
+    def __init__(self, n, name=None):
+        super().__init__(name)
+        self.n = int(n)
+
+
+class TimeDistributed(Layer):
+    def __init__(self, layer, name=None):
+        super().__init__(name)
+        self.layer = layer
+
+
+class Callback:
+    """Same hooks the reference's OutputCallback overrides (cardata-v1.py:212-226)."""
+
+    def on_predict_batch_end(self, batch, logs=None):
+        pass
+
+    def on_epoch_end(self, epoch, logs=None):
+        pass
+
+
+class History:
+    def __init__(self):
+        self.history: Dict[str, List[float]] = {}
+
+
+class ModelCheckpoint(Callback):
+    """``ModelCheckpoint(filepath, save_best_only=True)`` on val_loss (nb2.0:862-864)."""
+
+    def __init__(self, filepath, monitor="val_loss", save_best_only=False, verbose=0):
+        self.filepath, self.monitor, self.save_best_only, self.best, self.model = filepath, monitor, save_best_only, math.inf, None
+
+    def on_epoch_end(self, epoch, logs=None):
+        cur = (logs or {}).get(self.monitor)
+        if not self.save_best_only or (cur is not None and cur < self.best):
+            if cur is not None:
+                self.best = cur
+            self.model.save(self.filepath.format(epoch=epoch + 1))
+
+
+# ----------------------------------------------------------------------------------------------
+# initialisers (model_config: GlorotUniform kernels, zero biases; LSTM: orthogonal recurrent, unit_forget_bias)
+# ----------------------------------------------------------------------------------------------
+def _glorot(g: np.random.Generator, shape):
+    lim = math.sqrt(6.0 / (shape[0] + shape[1]))
+    return g.uniform(-lim, lim, size=shape).astype(np.float32)
+
+
+def init_dense_weights(widths: Sequence[int], seed: int = 314) -> np.ndarray:
+    g = np.random.Generator(np.random.PCG64(seed))
+    parts = []
+    for a, b in zip(widths[:-1], widths[1:]):
+        parts += [_glorot(g, (a, b)).ravel(), np.zeros(b, dtype=np.float32)]
+    return np.concatenate(parts)
+
+
+def init_lstm_weights(features: int = 18, units=(32, 16, 16, 32), seed: int = 314) -> np.ndarray:
+    g = np.random.Generator(np.random.PCG64(seed))
+    parts = []
+    inp = features
+    for u in units:
+        parts.append(_glorot(g, (inp, 4 * u)).ravel())
+        q, _ = np.linalg.qr(g.standard_normal((4 * u, u)))
+        parts.append(q.T.astype(np.float32).ravel())
+        b = np.zeros(4 * u, dtype=np.float32)
+        b[u:2 * u] = 1.0
+        parts.append(b)
+        inp = u
+    parts += [_glorot(g, (units[-1], features)).ravel(), np.zeros(features, dtype=np.float32)]
+    return np.concatenate(parts)
+
+
+# ----------------------------------------------------------------------------------------------
+# helpers
+# ----------------------------------------------------------------------------------------------
+def _to_device_f32(x, device) -> torch.Tensor:
+    if isinstance(x, torch.Tensor):
+        t = x
+        if t.dtype != torch.float32:
+            t = t.to(torch.float32)  # Keras casts float64 inputs to float32 on entry
+        if not t.is_cuda:
+            t = t.pin_memory().to(device, non_blocking=True)
+        return t.contiguous()
+    a = np.ascontiguousarray(x, dtype=np.float32)
+    return torch.from_numpy(a).pin_memory().to(device, non_blocking=True)
+
+
+class Model:
+    """Dense autoencoder (any Dense stack ≤ 8 layers × 64 units; the reference's D-14-7-7-D stack gets the fused
+    FFMA2 kernels) or the reference's LSTM stack."""
+
+    def __init__(self, inputs=None, outputs=None, name="model", _layers=None, seed: int = 314, device: Optional[int] = None):
+        self.name = name
+        self.layers: List[Layer] = list(_layers) if _layers is not None else list(outputs.chain)
+        self._device = device
+        self._ae = None
+        self._lstm = None
+        self._compiled = False
+        self._adam = dict(lr=float(np.float32(1e-3)), beta1=float(np.float32(0.9)), beta2=float(np.float32(0.999)),
+                          eps=float(np.float32(1e-7)), iter=0)
+        self._norm = None
+        self._seed = seed
+        self._weights: Optional[np.ndarray] = None
+        self._h5_layer_names: Optional[List[str]] = None
+        self.history = None
+        if self.layers:
+            self._analyse()
+
+    # -- structure ---------------------------------------------------------------------------------
+    def _analyse(self):
+        ls = [l for l in self.layers if not isinstance(l, InputLayer)]
+        self.kind = "lstm" if any(isinstance(l, LSTM) for l in ls) else "dense"
+        if self.kind == "dense":
+            if not all(isinstance(l, Dense) for l in ls):
+                raise NotImplementedError("only stacks of Dense layers (autoencoder) are supported")
+            inp = [l for l in self.layers if isinstance(l, InputLayer)]
+            if not inp:
+                raise ValueError("model has no Input layer")
+            self.widths = [int(inp[0].shape[-1])] + [l.units for l in ls]
+            self.acts = [_ffi.ACT_CODES[l.activation] for l in ls]
+            reg = ls[0].activity_regularizer
+            if any(l.activity_regularizer is not None for l in ls[1:]):
+                raise NotImplementedError("activity regulariser is supported on the first Dense layer only (as in the reference)")
+            self.l1 = float(reg.l1) if reg is not None else 0.0
+            self.n_params = sum(a * b + b for a, b in zip(self.widths[:-1], self.widths[1:]))
+        else:
+            lstm = [l for l in ls if isinstance(l, LSTM)]
+            td = [l for l in ls if isinstance(l, TimeDistributed)]
+            rv = [l for l in ls if isinstance(l, RepeatVector)]
+            ok = (len(lstm) == 4 and len(td) == 1 and len(rv) == 1 and isinstance(td[0].layer, Dense)
+                  and all(l.activation == "relu" and l.recurrent_activation == "sigmoid" for l in lstm)
+                  and [l.return_sequences for l in lstm] == [True, False, True, True]
+                  and td[0].layer.activation == "linear")
+            if not ok:
+                raise NotImplementedError("only the reference LSTM stack (LSTM seq → LSTM → RepeatVector → LSTM seq → LSTM seq "
+                                          "→ TimeDistributed(Dense), relu/sigmoid) is supported")
+            self.units = [l.units for l in lstm]
+            self.look_back = rv[0].n
+            shp = lstm[0].input_shape
+            self.features = int(shp[-1]) if shp else td[0].layer.units
+            if td[0].layer.units != self.features:
+                raise NotImplementedError("TimeDistributed(Dense(n)) must map back to the input feature count")
+            inp = self.features
+            n = 0
+            for u in self.units:
+                n += inp * 4 * u + u * 4 * u + 4 * u
+                inp = u
+            self.n_params = n + self.units[-1] * self.features + self.features
+
+    @property
+    def input_dim(self):
+        return self.widths[0] if self.kind == "dense" else self.features
+
+    def count_params(self):
+        return self.n_params
+
+    def summary(self, print_fn=print):
+        print_fn(f'Model: "{self.name}"')
+        for l in self.layers:
+            print_fn(f"  {l.name:<24}{type(l).__name__}")
+        print_fn(f"Total params: {self.n_params:,}")
+
+    # -- weights -------------------------------------------------------------------------------------
+    def get_flat_weights(self) -> np.ndarray:
+        if self._ae is not None:
+            out = np.empty(self.n_params, dtype=np.float32)
+            _ffi.check(_ffi.lib().b2_ae_get_weights(self._ae, out.ctypes.data), "b2_ae_get_weights")
+            self._weights = out
+        if self._weights is None:
+            self._weights = (init_dense_weights(self.widths, self._seed) if self.kind == "dense"
+                             else init_lstm_weights(self.features, self.units, self._seed))
+        return self._weights.copy()
+
+    def set_flat_weights(self, w: np.ndarray):
+        w = np.ascontiguousarray(w, dtype=np.float32).ravel()
+        if w.size != self.n_params:
+            raise ValueError(f"expected {self.n_params} weights, got {w.size}")
+        self._weights = w.copy()
+        if self._ae is not None:
+            _ffi.check(_ffi.lib().b2_ae_set_weights(self._ae, self._weights.ctypes.data), "b2_ae_set_weights")
+        if self._lstm is not None:
+            _ffi.lib().b2_lstm_destroy(self._lstm)
+            self._lstm = None
+
+    def get_weights(self) -> List[np.ndarray]:
+        flat, out, p = self.get_flat_weights(), [], 0
+        for shp in self._weight_shapes():
+            n = int(np.prod(shp))
+            out.append(flat[p:p + n].reshape(shp))
+            p += n
+        return out
+
+    def set_weights(self, ws: Sequence[np.ndarray]):
+        self.set_flat_weights(np.concatenate([np.asarray(w, dtype=np.float32).ravel() for w in ws]))
+
+    def _weight_shapes(self):
+        if self.kind == "dense":
+            s = []
+            for a, b in zip(self.widths[:-1], self.widths[1:]):
+                s += [(a, b), (b,)]
+            return s
+        s, inp = [], self.features
+        for u in self.units:
+            s += [(inp, 4 * u), (u, 4 * u), (4 * u,)]
+            inp = u
+        return s + [(self.units[-1], self.features), (self.features,)]
+
+    def set_normalization(self, kind, lo, rng):
+        """Fuse ``normalize_fn`` (cardata-v1.py:40-131) into score/predict/fit: raw rows in, normalised inside the kernel."""
+        self._norm = None if kind is None else (list(kind), list(lo), list(rng))
+        return self
+
+    # -- native handles ------------------------------------------------------------------------------
+    def _device_index(self):
+        return self._device if self._device is not None else torch.cuda.current_device()
+
+    def _handle(self):
+        l = _ffi.lib()
+        if self.kind == "dense":
+            if self._ae is None:
+                w = self.get_flat_weights()
+                d = _ffi.AeDesc()
+                d.n_layers = len(self.acts)
+                for i, v in enumerate(self.widths):
+                    d.widths[i] = v
+                for i, v in enumerate(self.acts):
+                    d.act[i] = v
+                d.l1_activity = self.l1
+                h = C.c_void_p()
+                _ffi.check(l.b2_ae_create(get_ctx(self._device_index()), C.byref(d), w.ctypes.data, C.byref(h)), "b2_ae_create")
+                self._ae = h.value
+            return self._ae
+        if self._lstm is None:
+            w = self.get_flat_weights()
+            d = _ffi.LstmDesc()
+            d.features = self.features
+            for i, u in enumerate(self.units):
+                d.units[i] = u
+            h = C.c_void_p()
+            _ffi.check(l.b2_lstm_create(get_ctx(self._device_index()), C.byref(d), w.ctypes.data, C.byref(h)), "b2_lstm_create")
+            self._lstm = h.value
+        return self._lstm
+
+    def __del__(self):
+        try:
+            l = _ffi.lib()
+            if self._ae is not None:
+                l.b2_ae_destroy(self._ae)
+            if self._lstm is not None:
+                l.b2_lstm_destroy(self._lstm)
+        except Exception:
+            pass
+
+    def _norm_struct(self):
+        return _ffi.make_norm(*self._norm) if self._norm is not None else _ffi.make_norm()
+
+    # -- inference -------------------------------------------------------------------------------------
+    def score_device(self, x: torch.Tensor, threshold: float = 5.0, mse: Optional[torch.Tensor] = None,
+                     flag: Optional[torch.Tensor] = None, recon: Optional[torch.Tensor] = None,
+                     counters: Optional[torch.Tensor] = None):
+        """Enqueue the fused kernel on device buffers (no host sync). Returns (mse, flag)."""
+        if self.kind != "dense":
+            raise TypeError("score is defined for the Dense autoencoder")
+        n = x.shape[0]
+        if x.dim() != 2 or x.shape[1] != self.widths[0]:
+            raise ValueError(f"expected input of shape (N, {self.widths[0]}), got {tuple(x.shape)}")
+        if mse is None:
+            mse = torch.empty(n, dtype=torch.float32, device=x.device)
+        if flag is None:
+            flag = torch.empty(n, dtype=torch.uint8, device=x.device)
+        nm = self._norm_struct()
+        _ffi.check(_ffi.lib().b2_ae_score(self._handle(), _ffi.ptr(x), n, C.byref(nm), float(threshold), _ffi.ptr(mse),
+                                          _ffi.ptr(flag), _ffi.ptr(recon), _ffi.ptr(counters), _stream_ptr()), "b2_ae_score")
+        return mse, flag
+
+    def score(self, x, threshold: float = 5.0):
+        """``mse = mean((x - predict(x))**2, axis=1)`` (nb2.0:1015) and ``flag = mse > threshold`` (nb2.0:1163).
+        Returns (mse f32[N], flag u8[N]) as NumPy arrays."""
+        dev = torch.device("cuda", self._device_index())
+        xd = _to_device_f32(x, dev)
+        mse, flag = self.score_device(xd, threshold)
+        return mse.cpu().numpy(), flag.cpu().numpy()
+
+    def reconstruction_error(self, x):
+        return self.score(x, threshold=math.inf)[0]
+
+    def predict(self, x, batch_size: Optional[int] = None, callbacks: Optional[Sequence[Callback]] = None, verbose=0):
+        """Forward pass over all rows; one kernel launch regardless of ``batch_size``.  ``callbacks`` get
+        ``on_predict_batch_end(batch, {'outputs': [rows_of_that_batch]})`` per ``batch_size`` chunk (default 32) exactly as
+        TF 2.0.0's predict loop feeds the reference's OutputCallback (cardata-v1.py:218-224)."""
+        dev = torch.device("cuda", self._device_index())
+        xd = _to_device_f32(x, dev)
+        if self.kind == "dense":
+            if xd.dim() != 2 or xd.shape[1] != self.widths[0]:
+                raise ValueError(f"expected input of shape (N, {self.widths[0]}), got {tuple(xd.shape)}")
+            recon = torch.empty_like(xd)
+            self.score_device(xd, math.inf, recon=recon)
+            out = recon.cpu().numpy()
+        else:
+            if xd.dim() != 3 or xd.shape[2] != self.features:
+                raise ValueError(f"expected input of shape (B, T, {self.features}), got {tuple(xd.shape)}")
+            if xd.shape[1] != self.look_back:
+                raise ValueError(f"model was built with look_back={self.look_back}, got T={xd.shape[1]}")
+            y = torch.empty_like(xd)
+            _ffi.check(_ffi.lib().b2_lstm_forward(self._handle(), _ffi.ptr(xd), xd.shape[0], xd.shape[1], _ffi.ptr(y),
+                                                  _stream_ptr()), "b2_lstm_forward")
+            out = y.cpu().numpy()
+        if callbacks:
+            bs = batch_size or 32
+            for b, s in enumerate(range(0, out.shape[0], bs)):
+                for cb in callbacks:
+                    cb.on_predict_batch_end(b, {"outputs": [out[s:s + bs]]})
+        return out
+
+    # -- training ----------------------------------------------------------------------------------------
+    def compile(self, optimizer="adam", loss="mean_squared_error", metrics=None, **_):
+        if (optimizer if isinstance(optimizer, str) else getattr(optimizer, "name", "")).lower() != "adam":
+            raise NotImplementedError("only optimizer='adam' is supported (the reference's training_config)")
+        if loss not in ("mean_squared_error", "mse"):
+            raise NotImplementedError("only loss='mean_squared_error' is supported")
+        self._metrics = list(metrics or [])
+        self._compiled = True
+
+    def fit(self, x, y=None, epochs=1, batch_size=32, shuffle=True, validation_data=None, verbose=0, callbacks=None,
+            seed: Optional[int] = None):
+        """Mini-batch Adam on MSE(x, AE(x)) + l1·Σ|h1|/B, all steps of an epoch inside ONE kernel launch.
+        ``y`` must be None or ``x`` (autoencoder; the notebooks call ``fit(train_x, train_x)``, nb2.0:871)."""
+        if self.kind != "dense":
+            raise NotImplementedError("fit is implemented for the Dense autoencoder (LSTM training is out of scope, SURVEY §8f.4)")
+        if not self._compiled:
+            raise RuntimeError("You must compile your model before training/testing. Use `model.compile(optimizer, loss)`.")
+        if y is not None and y is not x:
+            if np.shape(y) != np.shape(x) or not np.array_equal(np.asarray(y), np.asarray(x)):
+                raise NotImplementedError("autoencoder training only: y must be x")
+        dev = torch.device("cuda", self._device_index())
+        xd = _to_device_f32(x, dev)
+        n = xd.shape[0]
+        l = _ffi.lib()
+        h = self._handle()
+        steps = (n + batch_size - 1) // batch_size
+        hist = History()
+        hist.history = {"loss": [], "accuracy": []} if "accuracy" in getattr(self, "_metrics", []) else {"loss": []}
+        g = np.random.Generator(np.random.PCG64(self._seed if seed is None else seed))
+        adam = _ffi.Adam(self._adam["lr"], self._adam["beta1"], self._adam["beta2"], self._adam["eps"], self._adam["iter"])
+        nm = self._norm_struct()
+        loss_d = torch.empty(steps, dtype=torch.float32, device=dev)
+        acc_d = torch.empty(steps, dtype=torch.float32, device=dev)
+        sizes = np.full(steps, batch_size, dtype=np.float64)
+        sizes[-1] = n - batch_size * (steps - 1)
+        for cb in callbacks or []:
+            if isinstance(cb, ModelCheckpoint):
+                cb.model = self
+        for ep in range(epochs):
+            order = None
+            if shuffle:
+                order = torch.from_numpy(g.permutation(n).astype(np.int32)).to(dev)
+            _ffi.check(l.b2_ae_fit_steps(h, _ffi.ptr(xd), _ffi.ptr(order), n, batch_size, C.byref(nm), C.byref(adam),
+                                         _ffi.ptr(loss_d), _ffi.ptr(acc_d), _stream_ptr()), "b2_ae_fit_steps")
+            # Keras reports the sample-weighted mean of the per-batch values
+            lo = loss_d.cpu().numpy().astype(np.float64)
+            ac = acc_d.cpu().numpy().astype(np.float64)
+            logs = {"loss": float((lo * sizes).sum() / n)}
+            if "accuracy" in hist.history:
+                logs["accuracy"] = float((ac * sizes).sum() / n)
+            if validation_data is not None:
+                vx = validation_data[0] if isinstance(validation_data, (tuple, list)) else validation_data
+                vm = self.reconstruction_error(vx)
+                logs["val_loss"] = float(np.mean(vm.astype(np.float64)))
+            for k, v in logs.items():
+                hist.history.setdefault(k, []).append(v)
+            if verbose:
+                print(f"Epoch {ep + 1}/{epochs} - " + " - ".join(f"{k}: {v:.4f}" for k, v in logs.items()))
+            for cb in callbacks or []:
+                cb.on_epoch_end(ep, logs)
+        self._adam["iter"] = int(adam.iter)
+        self.history = hist
+        return hist
+
+    # -- persistence -----------------------------------------------------------------------------------------
+    def _model_config(self) -> dict:
+        layers = []
+        for l in self.layers:
+            if isinstance(l, InputLayer):
+                layers.append({"class_name": "InputLayer", "name": l.name, "config": {
+                    "batch_input_shape": [None, *l.shape], "dtype": "float32", "sparse": False, "name": l.name}, "inbound_nodes": []})
+            elif isinstance(l, Dense):
+                layers.append({"class_name": "Dense", "name": l.name, "config": {
+                    "name": l.name, "trainable": True, "dtype": "float32", "units": l.units, "activation": l.activation,
+                    "use_bias": True,
+                    "kernel_initializer": {"class_name": "GlorotUniform", "config": {"seed": None}},
+                    "bias_initializer": {"class_name": "Zeros", "config": {}},
+                    "kernel_regularizer": None, "bias_regularizer": None,
+                    "activity_regularizer": l.activity_regularizer.get_config() if l.activity_regularizer else None,
+                    "kernel_constraint": None, "bias_constraint": None}})
+            else:
+                raise NotImplementedError("save() supports Dense models")
+        for prev, cur in zip(layers[:-1], layers[1:]):
+            cur["inbound_nodes"] = [[[prev["name"], 0, 0, {}]]]
+        return {"class_name": "Model", "config": {"name": self.name, "layers": layers,
+                                                  "input_layers": [[layers[0]["name"], 0, 0]],
+                                                  "output_layers": [[layers[-1]["name"], 0, 0]]}}
+
+    def save(self, path: str):
+        """Write a Keras-2.2.4-tf style ``.h5`` (model_config, training_config, model_weights, optimizer_weights)."""
+        if self.kind != "dense":
+            raise NotImplementedError("save() supports Dense models")
+        ws = self.get_weights()
+        dense = [l for l in self.layers if isinstance(l, Dense)]
+        names = [l.name for l in self.layers]
+        mw: Dict[str, object] = {"@attrs": {"layer_names": np.array(names), "backend": "tensorflow", "keras_version": "2.2.4-tf"}}
+        for l in self.layers:
+            if isinstance(l, InputLayer):
+                mw[l.name] = {"@attrs": {"weight_names": np.array([], dtype="S1")}}
+        for i, l in enumerate(dense):
+            mw[l.name] = {l.name: {"kernel:0": ws[2 * i], "bias:0": ws[2 * i + 1]},
+                          "@attrs": {"weight_names": np.array([f"{l.name}/kernel:0", f"{l.name}/bias:0"])}}
+        tree: Dict[str, object] = {"model_weights": mw}
+        if self._ae is not None and self._adam["iter"] > 0:
+            m = np.empty(self.n_params, dtype=np.float32)
+            v = np.empty(self.n_params, dtype=np.float32)
+            _ffi.check(_ffi.lib().b2_ae_get_adam(self._ae, m.ctypes.data, v.ctypes.data), "b2_ae_get_adam")
+            adam: Dict[str, object] = {"iter:0": np.array(self._adam["iter"], dtype=np.int64)}
+            p = 0
+            wn = ["training/Adam/iter:0"]
+            for i, l in enumerate(dense):
+                kshape, bshape = ws[2 * i].shape, ws[2 * i + 1].shape
+                kn, bn = int(np.prod(kshape)), int(np.prod(bshape))
+                adam[l.name] = {"kernel": {"m:0": m[p:p + kn].reshape(kshape), "v:0": v[p:p + kn].reshape(kshape)},
+                                "bias": {"m:0": m[p + kn:p + kn + bn], "v:0": v[p + kn:p + kn + bn]}}
+                p += kn + bn
+            tree["optimizer_weights"] = {"training": {"Adam": adam}}
+        training_config = {"optimizer_config": {"class_name": "Adam", "config": {
+            "name": "Adam", "learning_rate": self._adam["lr"], "decay": 0.0, "beta_1": self._adam["beta1"],
+            "beta_2": self._adam["beta2"], "epsilon": self._adam["eps"], "amsgrad": False}},
+            "loss": "mean_squared_error", "metrics": ["accuracy"], "weighted_metrics": None, "sample_weight_mode": None,
+            "loss_weights": None}
+        h5lite.write_h5(path, tree, {"keras_version": "2.2.4-tf", "backend": "tensorflow",
+                                     "model_config": json.dumps(self._model_config()),
+                                     "training_config": json.dumps(training_config)})
+
+
+class Sequential(Model):
+    def __init__(self, layers=None, name="sequential", **kw):
+        super().__init__(name=name, _layers=[], **kw)
+        for l in layers or []:
+            self.add(l)
+
+    def add(self, layer: Layer):
+        self.layers.append(layer)
+        try:
+            self._analyse()
+        except (NotImplementedError, ValueError):
+            pass  # stack not complete yet; validated again on first use
+
+    def _handle(self):
+        self._analyse()
+        return super()._handle()
+
+
+def load_model(path: str, device: Optional[int] = None) -> Model:
+    """``tf.keras.models.load_model`` for Keras ``.h5`` files (cardata-v1.py:202, nb2.0:888): rebuilds the Dense stack from
+    ``model_config`` and loads ``model_weights`` (+ Adam ``iter``/``m``/``v`` when present so training can resume)."""
+    f = h5lite.H5File(path)
+    if "model_config" not in f.attrs:
+        raise ValueError(f"{path}: no model_config attribute (not a Keras full-model file)")
+    cfg = json.loads(f.attrs["model_config"])
+    lcfgs = cfg["config"]["layers"] if isinstance(cfg["config"], dict) else cfg["config"]
+    layers: List[Layer] = []
+    for lc in lcfgs:
+        cn, c = lc["class_name"], lc["config"]
+        if cn == "InputLayer":
+            layers.append(InputLayer(tuple(c["batch_input_shape"][1:]), name=c["name"]))
+        elif cn == "Dense":
+            reg = c.get("activity_regularizer")
+            r = L1(reg["config"]["l1"]) if reg and reg["config"].get("l1") else None
+            if reg and reg["config"].get("l2"):
+                raise NotImplementedError("l2 activity regulariser not supported")
+            if "batch_input_shape" in c and not layers:
+                layers.append(InputLayer(tuple(c["batch_input_shape"][1:]), name=c["name"] + "_input"))
+            layers.append(Dense(c["units"], activation=c["activation"], activity_regularizer=r, use_bias=c.get("use_bias", True),
+                                name=c["name"]))
+        else:
+            raise NotImplementedError(f"{path}: layer type {cn} is not supported by load_model")
+    m = Model(_layers=layers, name=cfg["config"].get("name", "model") if isinstance(cfg["config"], dict) else "sequential",
+              device=device)
+    mw = f["model_weights"]
+    parts = []
+    for ln in [str(s) for s in np.atleast_1d(mw.attrs["layer_names"])]:
+        g = mw[ln]
+        wn = [str(s) for s in np.atleast_1d(g.attrs.get("weight_names", []))]
+        if not wn:
+            continue
+        by_kind = {("kernel" if "kernel" in w else "bias"): g[w].read() for w in wn}
+        parts += [by_kind["kernel"].astype(np.float32).ravel(), by_kind["bias"].astype(np.float32).ravel()]
+    m.set_flat_weights(np.concatenate(parts))
+    if "training_config" in f.attrs:
+        tc = json.loads(f.attrs["training_config"])
+        oc = tc.get("optimizer_config", {})
+        if oc.get("class_name") == "Adam":
+            c = oc["config"]
+            m._adam.update(lr=float(c["learning_rate"]), beta1=float(c["beta_1"]), beta2=float(c["beta_2"]), eps=float(c["epsilon"]))
+            m.compile("adam", tc.get("loss", "mean_squared_error"), tc.get("metrics"))
+    m._h5_optimizer = None
+    if "optimizer_weights" in f:
+        ow = f["optimizer_weights"]
+        found: Dict[str, np.ndarray] = {}
+        ow.visit(lambda p, o: found.__setitem__(p, o.read()) if not o.is_group else None)
+        m._h5_optimizer = found
+        for p, v in found.items():
+            if p.endswith("iter:0"):
+                m._adam["iter"] = int(np.asarray(v).ravel()[0])
+    return m
+
+
+class _NS:
+    pass
+
+
+# tf.keras-like namespaces so that scripts can do `keras.layers.Dense`, `keras.models.load_model`, ...
+layers = _NS()
+layers.Input, layers.Dense, layers.LSTM, layers.RepeatVector, layers.TimeDistributed = Input, Dense, LSTM, RepeatVector, TimeDistributed
+models = _NS()
+models.Model, models.Sequential, models.load_model = Model, Sequential, load_model
+callbacks = _NS()
+callbacks.Callback, callbacks.ModelCheckpoint = Callback, ModelCheckpoint

@@ -1,0 +1,198 @@
+/*
+ * b2_api.h — C ABI of the B200 sensor-scoring hot path.
+ *
+ * The reference (uurl/hivemq-mqtt-tensorflow-kafka-realtime-iot-machine-learning-training-inference) has no
+ * FFI of its own: its hot path sits directly behind TensorFlow / tensorflow-io Python calls.  Each entry point
+ * below therefore names the Python call site(s) it replaces (paths relative to the reference root).  All
+ * pointers suffixed _dev are device pointers owned by the caller (e.g. torch.Tensor.data_ptr()); `stream` is
+ * a cudaStream_t passed as void* (NULL = legacy default stream).  Every function returns 0 on success or a
+ * negative B2_E* code; b2_strerror() / b2_last_error() give text.  Functions that take a stream only enqueue
+ * work; nothing here allocates device memory on the hot path (handles own their small parameter blocks).
+ */
+#ifndef B2_API_H
+#define B2_API_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2_OK            0
+#define B2_EINVAL       -1   /* bad argument (null pointer, size out of range, unsupported layer stack) */
+#define B2_ECUDA        -2   /* a CUDA runtime call failed; b2_last_error() has the CUDA message      */
+#define B2_EUNSUPPORTED -3   /* valid request this build does not implement                             */
+#define B2_ENOMEM       -4
+
+#define B2_MAX_WIDTH    64   /* widest Dense layer / input the score + train kernels accept */
+#define B2_MAX_FIELDS   64   /* CSV / Avro fields per record */
+
+/* activations (Keras names: cardata-v1.py:163-166) */
+#define B2_ACT_LINEAR 0
+#define B2_ACT_TANH   1
+#define B2_ACT_RELU   2
+
+/* per-feature normalisation kinds (normalize_fn, cardata-v1.py:68-111) */
+#define B2_NORM_IDENTITY 0
+#define B2_NORM_ZERO     1   /* feature forced to 0.0 (:72,:78,:84,:87) */
+#define B2_NORM_SCALE    2   /* (v - lo) / range * 2.0 - 1.0 with IEEE division (:69) */
+
+/* per-record decode status */
+#define B2_REC_OK          0
+#define B2_REC_FIELD_COUNT 1  /* CSV: wrong number of fields ("Expect N fields but have M") */
+#define B2_REC_BAD_NUMBER  2  /* CSV: "Field i in record j is not a valid float" */
+#define B2_REC_EMPTY_FIELD 3  /* CSV: empty field and the column has no default ("Field i is required") */
+#define B2_REC_BAD_QUOTE   4  /* CSV: quote inside unquoted field / unterminated quoted field */
+#define B2_REC_TRUNCATED   5  /* Avro: record ends inside a field */
+#define B2_REC_BAD_BRANCH  6  /* Avro: union branch index out of range */
+#define B2_REC_TOO_LONG    7  /* CSV: number with > 19 significant digits that cannot be rounded unambiguously */
+
+typedef struct b2_ctx b2_ctx;   /* one per device / rank */
+typedef struct b2_ae b2_ae;     /* Dense autoencoder: weights (+ Adam state once fit is called) */
+typedef struct b2_lstm b2_lstm; /* LSTM stack of LSTM-TensorFlow-IO-Kafka/cardata-v1.py:165-178 */
+
+/* ---- context ------------------------------------------------------------------------------------------ */
+int  b2_ctx_create(int device, b2_ctx** out);
+void b2_ctx_destroy(b2_ctx* ctx);
+int  b2_ctx_sm_count(const b2_ctx* ctx);
+const char* b2_strerror(int code);
+const char* b2_last_error(void);      /* thread-local detail of the last failure */
+const char* b2_version(void);
+
+/* ---- Dense autoencoder -------------------------------------------------------------------------------- */
+typedef struct {
+  int32_t n_layers;                 /* number of Dense layers (4 for the reference models) */
+  int32_t widths[9];                /* widths[0] = input dim D, widths[i+1] = units of layer i */
+  int32_t act[8];                   /* B2_ACT_* per layer */
+  float   l1_activity;              /* L1 activity regulariser on layer 0's output (1e-7; cardata-v1.py:163) */
+} b2_ae_desc;
+
+typedef struct {
+  int32_t n;                        /* number of features (must equal widths[0]) or 0 = no normalisation */
+  int32_t kind[B2_MAX_WIDTH];
+  float   lo[B2_MAX_WIDTH];
+  float   range[B2_MAX_WIDTH];      /* hi - lo */
+} b2_norm;
+
+/* Replaces tf.keras.models.load_model + model construction (cardata-v1.py:153-167,202; nb2.0:888).
+ * host_weights = kernel0[in*out] (row-major [in,out], Keras layout), bias0[out], kernel1, bias1, ... */
+int  b2_ae_create(b2_ctx* ctx, const b2_ae_desc* desc, const float* host_weights, b2_ae** out);
+void b2_ae_destroy(b2_ae* ae);
+int  b2_ae_param_count(const b2_ae* ae);
+int  b2_ae_get_weights(b2_ae* ae, float* host_weights);                  /* after fit: read back */
+int  b2_ae_set_weights(b2_ae* ae, const float* host_weights);
+
+/* Fused normalise → Dense stack → per-record MSE → flag = mse > threshold.
+ * Replaces normalize_fn (cardata-v1.py:40-131) + Model.predict (:231, nb2.0:1014) + np.mean(np.power(x - pred, 2),
+ * axis=1) (nb2.0:1015) + `e > threshold_fixed` (nb2.0:1129,1163).
+ * x_dev [N,D] row-major f32 (16-byte aligned); mse_dev [N] f32; flag_dev [N] u8 (either may be NULL);
+ * recon_dev [N,D] or NULL (predict output); counters_dev u64[4] += {records, flagged, 0, 0} or NULL. */
+int  b2_ae_score(b2_ae* ae, const float* x_dev, int64_t n, const b2_norm* norm, float threshold,
+                 float* mse_dev, uint8_t* flag_dev, float* recon_dev, unsigned long long* counters_dev,
+                 void* stream);
+
+/* ---- record decode -------------------------------------------------------------------------------------- */
+typedef struct {
+  int32_t n_fields;                 /* fields per record (20 sensor CSV, 31 credit-card CSV) */
+  int32_t kind[B2_MAX_FIELDS];      /* 0 skip, 1 float32 → next output column, 2 string (span reported) */
+  int32_t has_default[B2_MAX_FIELDS];
+  float   dflt[B2_MAX_FIELDS];      /* value for an empty field when has_default (record_defaults) */
+  int32_t delim;                    /* ',' */
+  int32_t use_quote_delim;          /* 1: RFC-4180 double quotes honoured (tf.io.decode_csv default) */
+} b2_csv_spec;
+
+/* Replaces tf.io.decode_csv + tf.stack (Sensor-Kafka-Consumer-and-TensorFlow-Model-Training.py:32-39).
+ * bytes_dev: concatenated message payloads; offs_dev int32[N+1]; out_dev f32[N, n_float] row-major;
+ * span_dev int32[N, n_string, 2] (begin,end byte offsets of string fields, NULL to skip);
+ * status_dev int32[N] (B2_REC_*, NULL to skip).  Parsed floats are correctly rounded binary32. */
+int  b2_decode_csv(b2_ctx* ctx, const uint8_t* bytes_dev, const int32_t* offs_dev, int64_t n,
+                   const b2_csv_spec* spec, float* out_dev, int32_t* span_dev, int32_t* status_dev, void* stream);
+
+typedef struct { int8_t type, nullable, out, pad; } b2_avro_field;  /* see avro_schema.py for codes */
+typedef struct {
+  int32_t n_fields;
+  int32_t n_out;
+  b2_avro_field f[B2_MAX_FIELDS];
+} b2_avro_prog;
+
+/* Replaces tf.strings.substr(e, 5, -1) + kafka_io.decode_avro + the int→float casts of normalize_fn
+ * (cardata-v1.py:13-37,61-66).  label_dev u8[N]: 0 "false", 1 "true", 2 null/empty, 3 other (NULL to skip). */
+int  b2_decode_avro(b2_ctx* ctx, const uint8_t* bytes_dev, const int32_t* offs_dev, int64_t n, int skip_prefix,
+                    const b2_avro_prog* prog, float* out_dev, uint8_t* label_dev, int32_t* status_dev, void* stream);
+
+/* Fused decode → normalise → score: the streaming scoring loop of cardata-v1.py:176-231 in one kernel.
+ * Exactly one of csv / avro is non-NULL.  Records whose status != 0 get mse = NaN, flag = 0 and are counted
+ * in counters[2]; counters_dev u64[4] += {records ok, flagged, decode errors, payload bytes}. */
+int  b2_decode_score(b2_ae* ae, const uint8_t* bytes_dev, const int32_t* offs_dev, int64_t n,
+                     const b2_csv_spec* csv, const b2_avro_prog* avro, int skip_prefix, const b2_norm* norm,
+                     float threshold, float* mse_dev, uint8_t* flag_dev, uint8_t* label_dev, int32_t* status_dev,
+                     unsigned long long* counters_dev, void* stream);
+
+/* ---- training ------------------------------------------------------------------------------------------- */
+typedef struct {
+  float lr, beta1, beta2, eps;      /* Adam(1e-3, .9, .999, 1e-7) from the .h5 training_config */
+  int64_t iter;                     /* optimizer step counter (`iter:0`) — in/out */
+} b2_adam;
+
+/* Model.fit hot loop (cardata-v1.py:192-194, cardata-v3.py:220-222, nb2.0:871-877): `steps` consecutive
+ * mini-batch Adam steps on MSE(x, AE(x)) + l1·Σ|h1|/B inside ONE kernel launch.  Step s uses rows
+ * order_dev[s*batch .. s*batch+batch_s) of x_dev (order_dev NULL = sequential), the last step of an epoch may be
+ * short: rows_total rows are consumed in ceil(rows_total/batch) steps.  loss_dev f32[steps] and acc_dev
+ * f32[steps] receive the per-step loss / "accuracy" metric (NULL to skip).  Single CTA, latency-bound path
+ * for the reference's batch sizes (32/100/128). */
+int  b2_ae_fit_steps(b2_ae* ae, const float* x_dev, const int32_t* order_dev, int64_t rows_total, int batch,
+                     const b2_norm* norm, b2_adam* adam, float* loss_dev, float* acc_dev, void* stream);
+
+/* Large-batch / data-parallel step, split so that a gradient all-reduce can sit between the halves:
+ *   b2_ae_grad:  grads_dev f32[P+3] = Σ_rows d(loss)/dθ (un-normalised), then Σ loss, Σ correct, row count.
+ *                scratch_dev must hold b2_ae_grad_scratch_bytes(ae, n) bytes.
+ *   b2_ae_apply: θ ← Adam(θ, grads / total_rows) using grads_dev after the caller's all-reduce. */
+int64_t b2_ae_grad_scratch_bytes(const b2_ae* ae, int64_t n);
+int  b2_ae_grad(b2_ae* ae, const float* x_dev, int64_t n, const b2_norm* norm, float* grads_dev,
+                void* scratch_dev, int64_t scratch_bytes, void* stream);
+int  b2_ae_apply(b2_ae* ae, const float* grads_dev, b2_adam* adam, float* loss_out_dev, void* stream);
+
+/* Adam slots (for .h5 save / resume; layout like the weights) */
+int  b2_ae_get_adam(b2_ae* ae, float* host_m, float* host_v);
+int  b2_ae_set_adam(b2_ae* ae, const float* host_m, const float* host_v);
+
+/* ---- LSTM ---------------------------------------------------------------------------------------------- */
+typedef struct {
+  int32_t features;                 /* 18 */
+  int32_t units[4];                 /* 32, 16, 16, 32 (LSTM-TensorFlow-IO-Kafka/cardata-v1.py:170-175) */
+} b2_lstm_desc;
+
+/* host_weights: per LSTM layer kernel[in,4u], recurrent_kernel[u,4u], bias[4u] (gate order i,f,c,o), then the
+ * TimeDistributed Dense kernel[32,features], bias[features]. */
+int  b2_lstm_create(b2_ctx* ctx, const b2_lstm_desc* desc, const float* host_weights, b2_lstm** out);
+void b2_lstm_destroy(b2_lstm* m);
+int  b2_lstm_param_count(const b2_lstm* m);
+/* Model.predict of the LSTM stack (LSTM-…/cardata-v1.py:226): x_dev f32[B,T,features] → y_dev f32[B,T,features]. */
+int  b2_lstm_forward(b2_lstm* m, const float* x_dev, int64_t batch, int timesteps, float* y_dev, void* stream);
+
+/* ---- per-GPU partition driver --------------------------------------------------------------------------- */
+typedef struct {
+  const uint8_t* bytes_dev;         /* device-resident message payloads of one Kafka partition batch */
+  const int32_t* offs_dev;          /* int32[n+1] */
+  int64_t        n;
+  float*         mse_dev;           /* [n] */
+  uint8_t*       flag_dev;          /* [n] */
+} b2_partition;
+
+typedef struct {
+  unsigned long long records, flagged, decode_errors, bytes;
+  float elapsed_ms;                 /* CUDA-event time of the whole run on this GPU */
+} b2_run_stats;
+
+/* One process per Kafka partition set (cardata-v1.py:10 reads "<topic>:0:<offset>"; 10 partitions per topic,
+ * infrastructure/confluent/01_installConfluentPlatform.sh:180): runs decode+score over this GPU's partitions on
+ * `n_streams` CUDA streams and returns the counters.  The cross-GPU count reduction is the caller's
+ * (torch.distributed / NCCL) because the communicator lives there. counters_dev u64[4] is accumulated too. */
+int  b2_partition_run(b2_ae* ae, const b2_partition* parts, int n_parts, const b2_csv_spec* csv,
+                      const b2_avro_prog* avro, int skip_prefix, const b2_norm* norm, float threshold,
+                      int n_streams, unsigned long long* counters_dev, b2_run_stats* host_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B2_API_H */
