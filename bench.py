@@ -1,0 +1,367 @@
+#!/usr/bin/env python
+"""Benchmark of the sensor-record scoring hot path (BASELINE.json metric: records/s scored, % of HBM roofline).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl reference]
+
+One "step" = one pass of the hot path over one batch of synthetic records that is already resident in HBM
+(`value`), or that starts in pinned HOST memory and whose results end in host memory (`e2e`).  Multi-GPU runs are
+launched by torchrun (one rank per GPU); ranks own disjoint Kafka-partition-like shards (weak scaling, no data-path
+collective; one NCCL all-reduce of the 4 counters per step).  `--impl reference` times the CPU restatement of the
+reference's path (oracle/oracle.c, OpenMP over every host core) on the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+METRIC = "sensor records/sec scored (decode+AE+MSE)"
+UNIT = "records/s"
+W30 = [30, 14, 7, 7, 30]
+W18 = [18, 14, 7, 7, 18]
+ACTS = [1, 2, 1, 2]
+THRESHOLD = 5.0
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def load_traffic(kernel_key):
+    """DRAM bytes/record of the dominant kernel from the committed ncu --set full capture (profiles/traffic.json)."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(p):
+        return json.load(open(p)).get(kernel_key)
+    return None
+
+
+class ClockSampler:
+    """nvidia-smi sampling DURING the timed region (B200_PROFILING.md clocks line)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [t.strip() for t in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------------------
+# workloads
+# ------------------------------------------------------------------------------------------------------------
+def golden_weights():
+    return np.load(os.path.join(ROOT, "tests", "golden", "ae30_5epochs.npz"))["weights"]
+
+
+class ScoreWorkload:
+    """BASELINE.json configs[1]: synthetic pre-decoded float sensor rows, fused AE forward + MSE + flag."""
+
+    def __init__(self, d, rows_log2, e2e_rows_log2):
+        self.d = d
+        self.rows = 1 << rows_log2
+        self.e2e_rows = 1 << e2e_rows_log2
+        self.name = f"score_predecoded_d{d}"
+        self.bytes_per_record = 4 * d + 5
+        self.flop_per_record = 2 * (14 * d + 98 + 49 + 7 * d)
+        self.launches_per_step = 1
+        self.kernel_key = f"ae_score_d{d}"
+
+    def describe(self):
+        return {"workload": self.name, "features": self.d, "model": "Dense AE %d-14-7-7-%d" % (self.d, self.d),
+                "weights": "autoencoder_sensor_anomaly_detection.h5 (shipped)" if self.d == 30 else "Glorot-uniform seed 314 (no 18-wide weights are shipped)",
+                "normalise": self.d == 18, "rows_per_step_per_gpu": self.rows, "threshold": THRESHOLD,
+                "l2_policy": "input per step (%.1f GB) is far larger than the 126 MB L2; offsets rotate" % (self.rows * 4 * self.d / 1e9),
+                "e2e_rows_per_step_per_gpu": self.e2e_rows}
+
+    def weights(self):
+        import b200_sensor as bs
+
+        return golden_weights() if self.d == 30 else bs.keras_compat.init_dense_weights(W18, seed=314)
+
+    def widths(self):
+        return W30 if self.d == 30 else W18
+
+    def norm(self):
+        import b200_sensor as bs
+
+        return bs.schemas.norm_arrays() if self.d == 18 else None
+
+    def model(self):
+        import b200_sensor as bs
+
+        k = bs.keras
+        inp = k.layers.Input(shape=(self.d,))
+        h = k.layers.Dense(14, activation="tanh", activity_regularizer=k.regularizers.l1(1e-7))(inp)
+        h = k.layers.Dense(7, activation="relu")(h)
+        h = k.layers.Dense(7, activation="tanh")(h)
+        h = k.layers.Dense(self.d, activation="relu")(h)
+        m = k.models.Model(inputs=inp, outputs=h)
+        m.set_flat_weights(self.weights())
+        if self.d == 18:
+            m.set_normalization(*self.norm())
+        return m
+
+    def host_rows(self, n, seed):
+        import b200_sensor as bs
+
+        return bs.synth.credit_rows(n, seed=seed) if self.d == 30 else bs.synth.sensor_rows(n, seed=seed)
+
+    def setup(self, dev, rank):
+        import torch
+
+        self.m = self.model()
+        base = torch.from_numpy(self.host_rows(1 << 20, 314 + rank)).to(dev)
+        # tile the seeded 2^20-row block with per-copy jitter so that all rows differ, entirely on the device
+        reps = self.rows // base.shape[0] + 1  # one extra block so that steps can start at rotating offsets
+        self.x = torch.empty((reps * base.shape[0], self.d), dtype=torch.float32, device=dev)
+        g = torch.Generator(device=dev).manual_seed(314 + rank)
+        for r in range(reps):
+            blk = self.x[r * base.shape[0]:(r + 1) * base.shape[0]]
+            blk.copy_(base)
+            if self.d == 30:
+                blk.mul_(1.0 + 0.01 * torch.rand((), device=dev, generator=g))
+        self.mse = torch.empty(self.rows, dtype=torch.float32, device=dev)
+        self.flag = torch.empty(self.rows, dtype=torch.uint8, device=dev)
+        self.counters = torch.zeros(4, dtype=torch.int64, device=dev)
+        self.max_off = self.x.shape[0] - self.rows
+
+    def step(self, i):
+        off = ((i * 104729 * 2) % max(self.max_off, 1)) & ~1  # even row offset keeps the 16-byte alignment of the bulk path
+        self.m.score_device(self.x[off:off + self.rows], THRESHOLD, mse=self.mse, flag=self.flag, counters=self.counters)
+        return self.rows
+
+    def setup_e2e(self, dev, rank):
+        import torch
+
+        self.hx = torch.from_numpy(self.host_rows(self.e2e_rows, 1000 + rank)).pin_memory()
+        self.h2d = self.hx.numel() * 4
+        self.d2h = self.e2e_rows * 5
+
+    def step_e2e(self, i):
+        mse, flag = self.m.score(self.hx, THRESHOLD)  # host in → host out through the public API
+        return self.e2e_rows
+
+    def cpu_sample(self, n, threads=None):
+        from oracle import c_oracle as co
+
+        if threads:
+            co.set_threads(threads)
+        x = self.host_rows(min(n, 1 << 22), 7)
+        w, wd, nm = self.weights(), self.widths(), self.norm()
+        co.score(x[:1024], w, wd, ACTS, norm=nm)
+        done, t0 = 0, time.perf_counter()
+        while done < n:
+            co.score(x, w, wd, ACTS, norm=nm, threshold=THRESHOLD)
+            done += x.shape[0]
+        return done, time.perf_counter() - t0, co.max_threads() if not threads else threads
+
+
+WORKLOADS = {
+    "score30": lambda: ScoreWorkload(30, 27, 22),
+    "score18": lambda: ScoreWorkload(18, 27, 22),
+}
+DEFAULT_WORKLOAD = "score30"
+
+
+# ------------------------------------------------------------------------------------------------------------
+def run_reference(args, wl, rank, world):
+    if rank != 0:
+        return
+    per_step = 1 << 22
+    for _ in range(args.warmup):
+        wl.cpu_sample(per_step // 4)
+    t_tot, n_tot, cores = 0.0, 0, 1
+    for _ in range(args.steps):
+        n, dt, cores = wl.cpu_sample(per_step)
+        t_tot += dt
+        n_tot += n
+    v = n_tot / t_tot
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * t_tot / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": wl.describe(),
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                             "sample": f"{per_step} records/step x {args.steps} steps, oracle/oracle.c (OpenMP, gcc -O3 -march=native); "
+                                       "TensorFlow/Keras is not installable offline, so the reference's predict path is timed as its C restatement"},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=8)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default=os.environ.get("B2_BENCH_WORKLOAD", DEFAULT_WORKLOAD), choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target wall time of the cpu_baseline leg")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    wl = WORKLOADS[args.workload]()
+
+    if args.impl == "reference":
+        run_reference(args, wl, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device visible — the b200 arm has no CPU fallback (use --impl reference for the CPU arm)")
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit(f"bench.py: --gpus {args.gpus} needs torchrun (one rank per GPU); WORLD_SIZE is 1")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    wl.setup(dev, rank)
+    for i in range(args.warmup):
+        wl.step(i)
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.25)
+    wl.counters.zero_()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    recs = 0
+    for i in range(args.steps):
+        recs += wl.step(args.warmup + i)
+    if world > 1:  # the path's only exchange: the final count reduction over NVLink (cardata-style per-partition counters)
+        dist.all_reduce(wl.counters, op=dist.ReduceOp.SUM)
+    e1.record()
+    torch.cuda.synchronize()
+    ms_local = e0.elapsed_time(e1)
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    ms = max_over_ranks(ms_local)
+    total_records = recs * world
+    value = total_records / (ms * 1e-3)
+    counters = wl.counters.cpu().numpy().tolist()
+
+    # end-to-end: pinned host → device → kernel → host, through the public API
+    e2e = None
+    if not args.no_e2e:
+        wl.setup_e2e(dev, rank)
+        for i in range(2):
+            wl.step_e2e(i)
+        barrier()
+        t0 = time.perf_counter()
+        e0.record()
+        n_e2e = 0
+        for i in range(args.steps):
+            n_e2e += wl.step_e2e(i)
+        e1.record()
+        torch.cuda.synchronize()
+        wall = (time.perf_counter() - t0) * 1e3
+        ms_e2e = max_over_ranks(max(e0.elapsed_time(e1), wall))
+        e2e = {"value": n_e2e * world / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": wl.h2d, "d2h_bytes_per_step": wl.d2h,
+               "ms_per_step": ms_e2e / args.steps, "api": "Model.score(pinned host tensor) -> (mse, flag) numpy"}
+
+    if rank == 0:
+        peak, peak_src = load_peaks()
+        per_launch_ms = ms_local / (args.steps * wl.launches_per_step)
+        achieved = wl.bytes_per_record * (recs / args.steps) / (per_launch_ms * 1e-3) / 1e9
+        traffic = load_traffic(wl.kernel_key)
+        roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                    "traffic": None if traffic is None else traffic * (recs / args.steps),
+                    "peak_source": peak_src, "algorithmic_bytes_per_record": wl.bytes_per_record,
+                    "flop_per_record": wl.flop_per_record,
+                    "fp32_tflops_achieved": wl.flop_per_record * (recs / args.steps) / (per_launch_ms * 1e-3) / 1e12,
+                    "kernel_ms_per_launch": per_launch_ms}
+        cpu = None
+        if not args.no_cpu_baseline and world >= 1:
+            n_target = 1 << 22
+            n, dt, cores = wl.cpu_sample(n_target)
+            rate = n / dt
+            n2 = int(min(max(rate * args.cpu_seconds, n_target), 1 << 28))
+            n, dt, cores = wl.cpu_sample(n2)
+            cpu = {"value": n / dt, "unit": UNIT, "cores": cores, "kind": "port",
+                   "sample": f"{n} records of the same workload through oracle/oracle.c (OpenMP, all host threads), {dt:.1f} s"}
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+                "data": "synthetic", "config": wl.describe(), "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
+                "gpu_launches": args.steps * wl.launches_per_step, "clocks": clocks,
+                "counters": {"records": counters[0], "flagged": counters[1], "decode_errors": counters[2], "bytes": counters[3]}}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
