@@ -34,6 +34,7 @@ struct NormP {             // normalize_fn table; kind: B2_NORM_*
   int32_t kind[D];
   float lo[D];
   float range[D];
+  float rinv[D];           // RN(1 / range), filled by the host
 };
 
 // Pack Keras flat order (kernel0[in,out], bias0, kernel1, ...) into AeW<D>.
@@ -95,12 +96,50 @@ __device__ __forceinline__ float2 tanh2(float2 x) {
 }
 __device__ __forceinline__ float tanh1(float x) { return tanh2(make_float2(x, x)).x; }
 
+// Cheaper variant: tanh(x) = 1 - 2/(2^(2x·log2 e) + 1) for every x (3 packed FP32 ops + 4 MUFU per pair, no select).
+// Saturates correctly (2^y → 0 / inf), absolute error ≤ ~2.5e-7 near 0 where 1 - 2r cancels (relative error is
+// unbounded for tiny |x|, which a following Dense layer does not care about).
+__device__ __forceinline__ float2 tanh2_fast(float2 x) {
+  const float2 y = mul2(x, splat(2.8853900817779268f));
+  float2 t = make_float2(ex2_approx(y.x), ex2_approx(y.y));
+  t = add2(t, splat(1.0f));
+  const float2 r = make_float2(rcp_approx(t.x), rcp_approx(t.y));
+  return fma2(r, splat(-2.0f), splat(1.0f));
+}
+template <bool FAST>
+__device__ __forceinline__ float2 tanh2_sel(float2 x) {
+  return FAST ? tanh2_fast(x) : tanh2(x);
+}
+
 // scale_fn(v, lo, hi) = (v - lo) / (hi - lo) * 2.0 - 1.0 with the reference's operation order and a true IEEE
 // division (cardata-v1.py:68-69); `*2.0 - 1.0` folds into one FMA because the product is exact.
 __device__ __forceinline__ float norm_feature(float v, int kind, float lo, float range) {
   if (kind == B2_NORM_SCALE) return fmaf(__fdiv_rn(__fsub_rn(v, lo), range), 2.0f, -1.0f);
   if (kind == B2_NORM_ZERO) return 0.0f;
   return v;
+}
+
+// Packed path for two adjacent features (x_i, x_i+1) of one row, 5 packed FP32 ops instead of two IEEE divisions:
+// with rinv = RN(1/range), q0 = RN(t*rinv), r = RN(t - q0*range) (exact by FMA) and q = RN(q0 + r*rinv) is the
+// correctly rounded quotient t/range (Markstein's theorem) for every finite t whose quotient neither overflows nor
+// lands in the subnormal range.  A subnormal-range slip is absorbed by the final `*2 - 1` (|q| < 2^-25 gives -1 either
+// way); an infinite t or an overflowing quotient shows up as q0 = ±inf, which is then the IEEE result and is selected
+// explicitly (the correction step would turn it into NaN).  NaN propagates.  Hence bit-identical to norm_feature().
+template <int D>
+__device__ __forceinline__ float2 norm_pair_fast(float2 v, const NormP<D>& nm, int i) {
+  const float2 lo = make_float2(nm.lo[i], nm.lo[i + 1]);
+  const float2 rg = make_float2(nm.range[i], nm.range[i + 1]);
+  const float2 ri = make_float2(nm.rinv[i], nm.rinv[i + 1]);
+  const float2 t = fma2(lo, splat(-1.0f), v);  // v - lo (exactly one rounding, like the reference's subtraction)
+  const float2 q0 = mul2(t, ri);
+  const float2 r = fma2(make_float2(-q0.x, -q0.y), rg, t);
+  float2 q = fma2(r, ri, q0);
+  if (fabsf(q0.x) == __int_as_float(0x7F800000)) q.x = q0.x;
+  if (fabsf(q0.y) == __int_as_float(0x7F800000)) q.y = q0.y;
+  float2 o = fma2(q, splat(2.0f), splat(-1.0f));
+  if (nm.kind[i] != B2_NORM_SCALE) o.x = nm.kind[i] == B2_NORM_ZERO ? 0.0f : v.x;
+  if (nm.kind[i + 1] != B2_NORM_SCALE) o.y = nm.kind[i + 1] == B2_NORM_ZERO ? 0.0f : v.y;
+  return o;
 }
 
 // Forward pass for R records living in shared-memory rows row[r] (D floats each, 8-byte aligned).
@@ -110,7 +149,7 @@ __device__ __forceinline__ float norm_feature(float v, int kind, float lo, float
 // consumed as-is, so no register shuffling is needed; R = 2 rows per thread share every LDCU.128 weight fetch.
 //   pass 1 streams x (normalising it in place when NORM) into the layer-1 accumulators,
 //   pass 2 produces one output pair at a time, accumulates (x - y)^2 and (RECON) overwrites x with y.
-template <int D, int R, bool NORM, bool RECON>
+template <int D, int R, bool NORM, bool RECON, bool FAST_TANH>
 __device__ __forceinline__ void ae_forward_rows(const AeW<D>& w, const NormP<D>& nm, float* const (&row)[R], float (&mse)[R]) {
   static_assert(D % 2 == 0, "feature count must be even (8-byte row alignment)");
   constexpr int Q1 = AE_H1 / 2, Q2 = AE_P2 / 2, Q3 = AE_P3 / 2;
@@ -125,8 +164,7 @@ __device__ __forceinline__ void ae_forward_rows(const AeW<D>& w, const NormP<D>&
     for (int r = 0; r < R; ++r) {
       float2 xv = *reinterpret_cast<const float2*>(row[r] + i);
       if (NORM) {
-        xv.x = norm_feature(xv.x, nm.kind[i], nm.lo[i], nm.range[i]);
-        xv.y = norm_feature(xv.y, nm.kind[i + 1], nm.lo[i + 1], nm.range[i + 1]);
+        xv = norm_pair_fast<D>(xv, nm, i);
         *reinterpret_cast<float2*>(row[r] + i) = xv;
       }
 #pragma unroll
@@ -139,7 +177,7 @@ __device__ __forceinline__ void ae_forward_rows(const AeW<D>& w, const NormP<D>&
 #pragma unroll
   for (int r = 0; r < R; ++r)
 #pragma unroll
-    for (int q = 0; q < Q1; ++q) h1[r][q] = tanh2(h1[r][q]);
+    for (int q = 0; q < Q1; ++q) h1[r][q] = tanh2_sel<FAST_TANH>(h1[r][q]);
 
   float2 h2[R][Q2];  // 7 units padded to 8 (pad lane stays 0: zero weights, zero bias, relu)
 #pragma unroll
@@ -175,7 +213,7 @@ __device__ __forceinline__ void ae_forward_rows(const AeW<D>& w, const NormP<D>&
 #pragma unroll
   for (int r = 0; r < R; ++r)
 #pragma unroll
-    for (int q = 0; q < Q3; ++q) h3[r][q] = tanh2(h3[r][q]);
+    for (int q = 0; q < Q3; ++q) h3[r][q] = tanh2_sel<FAST_TANH>(h3[r][q]);
 
   // compiler barrier: re-read x from shared memory in pass 2 instead of keeping D values per row live in registers
   asm volatile("" ::: "memory");
@@ -194,7 +232,7 @@ __device__ __forceinline__ void ae_forward_rows(const AeW<D>& w, const NormP<D>&
       }
       y = relu2(y);
       const float2 xv = *reinterpret_cast<const float2*>(row[r] + j);
-      const float2 d = make_float2(xv.x - y.x, xv.y - y.y);
+      const float2 d = fma2(y, splat(-1.0f), xv);  // x - y, one packed op
       se[r] = fma2(d, d, se[r]);
       if (RECON) *reinterpret_cast<float2*>(row[r] + j) = y;
     }

@@ -28,7 +28,7 @@ struct ScoreArgs {
   int use_bulk;
 };
 
-template <int D, int NT, int STAGES, bool NORM, bool RECON>
+template <int D, int NT, int STAGES, bool NORM, bool RECON, bool FT>
 __global__ void __launch_bounds__(NT) ae_score_kernel(const __grid_constant__ ScoreArgs<D> a) {
   constexpr int TILE = 2 * NT;
   constexpr int TILE_FLOATS = TILE * D;
@@ -77,7 +77,7 @@ __global__ void __launch_bounds__(NT) ae_score_kernel(const __grid_constant__ Sc
     // computed on but never stored
     float* const rowp[2] = {st + (size_t)tid * D, st + (size_t)(tid + NT) * D};
     float mm[2] = {0.f, 0.f};
-    if (va) ae_forward_rows<D, 2, NORM, RECON>(a.w, a.nm, rowp, mm);
+    if (va) ae_forward_rows<D, 2, NORM, RECON, FT>(a.w, a.nm, rowp, mm);
     const float2 m = make_float2(mm[0], mm[1]);
     const bool fa = m.x > a.threshold, fb = m.y > a.threshold;  // strict, nb2.0:1163
     if (va) {
@@ -190,11 +190,11 @@ static int env_int(const char* name, int dflt) {
   return v ? atoi(v) : dflt;
 }
 
-template <int D, int NT, int STAGES, bool NORM, bool RECON>
+template <int D, int NT, int STAGES, bool NORM, bool RECON, bool FT>
 static int launch_score(b2_ae* ae, const ScoreArgs<D>& args, cudaStream_t stream) {
   constexpr int TILE = 2 * NT;
   constexpr size_t smem = (size_t)STAGES * TILE * D * 4 + STAGES * sizeof(uint64_t);
-  auto kern = ae_score_kernel<D, NT, STAGES, NORM, RECON>;
+  auto kern = ae_score_kernel<D, NT, STAGES, NORM, RECON, FT>;
   static int occ_cache[16] = {0};  // per device
   int dev = ae->ctx->device;
   if (occ_cache[dev & 15] == 0) {
@@ -225,6 +225,7 @@ static int score_spec(b2_ae* ae, const float* x, int64_t n, const b2_norm* norm,
       args.nm.kind[j] = norm->kind[j];
       args.nm.lo[j] = norm->lo[j];
       args.nm.range[j] = norm->range[j];
+      args.nm.rinv[j] = 1.0f / norm->range[j];
     }
   }
   args.x = x;
@@ -236,13 +237,16 @@ static int score_spec(b2_ae* ae, const float* x, int64_t n, const b2_norm* norm,
   args.threshold = threshold;
   args.use_bulk = (((uintptr_t)x & 15) == 0) && (!recon || ((uintptr_t)recon & 15) == 0) && !env_int("B2_NO_BULK", 0);
   constexpr int NT = 128;
-  constexpr int ST = 3;
+  constexpr int ST = 2;
+  const bool ft = env_int("B2_FAST_TANH", 0) != 0;
   if (has_norm) {
-    if (recon) return launch_score<D, NT, ST, true, true>(ae, args, stream);
-    return launch_score<D, NT, ST, true, false>(ae, args, stream);
+    if (recon) return launch_score<D, NT, ST, true, true, false>(ae, args, stream);
+    if (ft) return launch_score<D, NT, ST, true, false, true>(ae, args, stream);
+    return launch_score<D, NT, ST, true, false, false>(ae, args, stream);
   }
-  if (recon) return launch_score<D, NT, ST, false, true>(ae, args, stream);
-  return launch_score<D, NT, ST, false, false>(ae, args, stream);
+  if (recon) return launch_score<D, NT, ST, false, true, false>(ae, args, stream);
+  if (ft) return launch_score<D, NT, ST, false, false, true>(ae, args, stream);
+  return launch_score<D, NT, ST, false, false, false>(ae, args, stream);
 }
 
 extern "C" int b2_ae_score(b2_ae* ae, const float* x_dev, int64_t n, const b2_norm* norm, float threshold, float* mse_dev,

@@ -1,9 +1,6 @@
 // Entry points not implemented yet in this build (each is replaced by its own translation unit as it lands).
 #include "common.cuh"
 #define STUB(name) b2_set_error(name ": not implemented in this build"); return B2_EUNSUPPORTED
-extern "C" int b2_decode_csv(b2_ctx*, const uint8_t*, const int32_t*, int64_t, const b2_csv_spec*, float*, int32_t*, int32_t*, void*) { STUB("b2_decode_csv"); }
-extern "C" int b2_decode_avro(b2_ctx*, const uint8_t*, const int32_t*, int64_t, int, const b2_avro_prog*, float*, uint8_t*, int32_t*, void*) { STUB("b2_decode_avro"); }
-extern "C" int b2_decode_score(b2_ae*, const uint8_t*, const int32_t*, int64_t, const b2_csv_spec*, const b2_avro_prog*, int, const b2_norm*, float, float*, uint8_t*, uint8_t*, int32_t*, unsigned long long*, void*) { STUB("b2_decode_score"); }
 extern "C" int b2_ae_fit_steps(b2_ae*, const float*, const int32_t*, int64_t, int, const b2_norm*, b2_adam*, float*, float*, void*) { STUB("b2_ae_fit_steps"); }
 extern "C" int64_t b2_ae_grad_scratch_bytes(const b2_ae*, int64_t) { return 0; }
 extern "C" int b2_ae_grad(b2_ae*, const float*, int64_t, const b2_norm*, float*, void*, int64_t, void*) { STUB("b2_ae_grad"); }

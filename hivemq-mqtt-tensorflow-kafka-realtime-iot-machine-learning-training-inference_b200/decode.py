@@ -1,0 +1,209 @@
+"""Record decode surface: the ``tf.io.decode_csv`` / ``tf.strings.substr`` / ``tensorflow_io.kafka.decode_avro`` calls of the
+reference scripts, running on the CUDA decode kernel (csrc/decode.cu).
+
+Reference call sites:
+  * ``tf.io.decode_csv(entry, [[0.0]]*30 + [[""]])`` + ``tf.stack`` — Sensor-Kafka-Consumer-and-TensorFlow-Model-Training.py:32-39
+  * ``tf.strings.substr(e, 5, -1)`` + ``kafka_io.decode_avro(e, schema=schema, dtype=[...])`` — cardata-v1.py:13-37
+
+A Kafka partition batch is held as ``RecordBatch(data uint8[], offsets int32[n+1])`` on the device (what
+``KafkaDataset(...).batch(n)`` would hand to the decode op, minus the per-element tensor overhead).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional, Sequence, Union
+
+import numpy as np
+import torch
+
+from . import _ffi, avro_schema as av
+from .keras_compat import _stream_ptr, get_ctx
+
+STATUS_TEXT = {1: "wrong number of fields", 2: "field is not a valid float", 3: "empty field without a default (required)",
+               4: "quote inside an unquoted field or unterminated quoted field", 5: "record ends inside a field (truncated Avro)",
+               6: "union branch index out of range", 7: "number too long to round unambiguously / record larger than the stage"}
+
+
+class DecodeError(ValueError):
+    """Counterpart of TF's InvalidArgumentError for a malformed record (decode_csv aborts the whole batch)."""
+
+
+class RecordBatch:
+    def __init__(self, data, offsets, device: Optional[torch.device] = None, skip_prefix: int = 0):
+        dev = device or torch.device("cuda", torch.cuda.current_device())
+        self.data = data if isinstance(data, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(data, dtype=np.uint8))
+        self.offsets = offsets if isinstance(offsets, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(offsets, dtype=np.int32))
+        if self.offsets.dtype != torch.int32 or self.data.dtype != torch.uint8:
+            raise TypeError("RecordBatch wants uint8 data and int32 offsets")
+        self.data = self.data.to(dev, non_blocking=True)
+        self.offsets = self.offsets.to(dev, non_blocking=True)
+        self.n = int(self.offsets.numel()) - 1
+        self.skip_prefix = skip_prefix
+
+    @classmethod
+    def from_messages(cls, msgs: Sequence[Union[bytes, str]], device=None) -> "RecordBatch":
+        bs = [m.encode("utf-8") if isinstance(m, str) else bytes(m) for m in msgs]
+        offs = np.zeros(len(bs) + 1, dtype=np.int64)
+        np.cumsum([len(b) for b in bs], out=offs[1:])
+        return cls(np.frombuffer(b"".join(bs), dtype=np.uint8).copy(), offs.astype(np.int32), device)
+
+    @property
+    def nbytes(self) -> int:
+        return int(self.data.numel())
+
+    def substr(self, pos: int, length: int = -1) -> "RecordBatch":
+        if length != -1:
+            raise NotImplementedError("only substr(e, pos, -1) (drop a fixed prefix) is used by the reference")
+        rb = RecordBatch.__new__(RecordBatch)
+        rb.data, rb.offsets, rb.n, rb.skip_prefix = self.data, self.offsets, self.n, self.skip_prefix + int(pos)
+        return rb
+
+
+def substr(records: RecordBatch, pos: int, length: int = -1) -> RecordBatch:
+    """``tf.strings.substr(e, 5, -1)``: strip the Confluent framing (magic byte + 4-byte schema id), cardata-v1.py:13."""
+    return records.substr(pos, length)
+
+
+def _as_batch(records) -> RecordBatch:
+    return records if isinstance(records, RecordBatch) else RecordBatch.from_messages(records)
+
+
+def _raise_on_status(status: torch.Tensor, what: str):
+    bad = torch.nonzero(status).flatten()
+    if bad.numel():
+        i = int(bad[0])
+        code = int(status[i])
+        raise DecodeError(f"{what}: record {i}: {STATUS_TEXT.get(code, code)} ({bad.numel()} bad record(s) in the batch)")
+
+
+def csv_spec_from_defaults(record_defaults, select_cols=None, field_delim=",", use_quote_delim=True):
+    """TF-style ``record_defaults`` (one per column: [[0.0]] float with default, [] float required via np.float32 dtype
+    array of size 0, [[""]] string) → kernel spec."""
+    kinds, dfl = [], []
+    for d in record_defaults:
+        arr = np.asarray(d)
+        if arr.dtype.kind in "US" or (arr.dtype == object):
+            kinds.append(2)
+            dfl.append(None)
+        elif arr.dtype.kind in "fiu":
+            kinds.append(1)
+            dfl.append(None if arr.size == 0 else float(arr.ravel()[0]))
+        else:
+            raise TypeError(f"unsupported record_default {d!r}")
+    if select_cols is not None:
+        raise NotImplementedError("select_cols: pass kinds with 0 (skip) via decode_csv_matrix instead")
+    return _ffi.make_csv_spec(kinds, dfl, field_delim, use_quote_delim), kinds
+
+
+def decode_csv_matrix(records, kinds, defaults=None, field_delim=",", use_quote_delim=True, raise_on_error=True):
+    """Fused ``decode_csv`` + ``tf.stack(cols, 1)``: device matrix f32[n, n_float] (row-major) + status i32[n]."""
+    rb = _as_batch(records)
+    spec = _ffi.make_csv_spec(kinds, defaults, field_delim, use_quote_delim)
+    nf = sum(1 for k in kinds if k == 1)
+    ns = sum(1 for k in kinds if k == 2)
+    out = torch.empty((rb.n, nf), dtype=torch.float32, device=rb.data.device)
+    span = torch.zeros((rb.n, max(ns, 1), 2), dtype=torch.int32, device=rb.data.device) if ns else None
+    status = torch.empty(rb.n, dtype=torch.int32, device=rb.data.device)
+    _ffi.check(_ffi.lib().b2_decode_csv(get_ctx(rb.data.device.index), _ffi.ptr(rb.data), _ffi.ptr(rb.offsets), rb.n, C.byref(spec),
+                                        _ffi.ptr(out), _ffi.ptr(span), _ffi.ptr(status), _stream_ptr()), "b2_decode_csv")
+    if raise_on_error:
+        _raise_on_status(status, "decode_csv")
+    return out, span, status
+
+
+def decode_csv(records, record_defaults, field_delim=",", use_quote_delim=True, na_value="", select_cols=None) -> List[np.ndarray]:
+    """``tf.io.decode_csv``: one array per column (float32 for numeric defaults, object/bytes for string defaults).
+    A malformed record raises :class:`DecodeError` for the whole batch, like TF's InvalidArgumentError."""
+    if na_value != "":
+        raise NotImplementedError("na_value other than '' is not used by the reference")
+    rb = _as_batch(records)
+    spec, kinds = csv_spec_from_defaults(record_defaults, select_cols, field_delim, use_quote_delim)
+    defaults = [None if not spec.has_default[i] else spec.dflt[i] for i in range(len(kinds))]
+    out, span, _ = decode_csv_matrix(rb, kinds, defaults, field_delim, use_quote_delim)
+    out_h = out.cpu().numpy()
+    cols: List[np.ndarray] = []
+    fi = si = 0
+    raw = None
+    for k in kinds:
+        if k == 1:
+            cols.append(np.ascontiguousarray(out_h[:, fi]))
+            fi += 1
+        else:
+            if raw is None:
+                raw = rb.data.cpu().numpy().tobytes()
+                sp = span.cpu().numpy()
+            cols.append(np.array([raw[b:e].replace(b'""', b'"') for b, e in sp[:, si]], dtype=object))
+            si += 1
+    return cols
+
+
+_NP_DTYPES = {"float32": np.float32, "float64": np.float64, "int32": np.int32, "int64": np.int64, "string": object}
+
+
+def decode_avro_matrix(records, schema, skip_prefix: Optional[int] = None, raise_on_error=True):
+    """Avro records → device matrix f32[n, n_numeric] + label u8[n] (0 "false", 1 "true", 2 null/empty, 3 other) + status."""
+    rb = _as_batch(records)
+    prog = schema if isinstance(schema, av.AvroProgram) else av.compile_schema(schema)
+    p = _ffi.make_avro_prog(prog)
+    out = torch.empty((rb.n, prog.n_out), dtype=torch.float32, device=rb.data.device)
+    label = torch.empty(rb.n, dtype=torch.uint8, device=rb.data.device)
+    status = torch.empty(rb.n, dtype=torch.int32, device=rb.data.device)
+    skip = rb.skip_prefix if skip_prefix is None else skip_prefix
+    _ffi.check(_ffi.lib().b2_decode_avro(get_ctx(rb.data.device.index), _ffi.ptr(rb.data), _ffi.ptr(rb.offsets), rb.n, skip, C.byref(p),
+                                         _ffi.ptr(out), _ffi.ptr(label), _ffi.ptr(status), _stream_ptr()), "b2_decode_avro")
+    if raise_on_error:
+        _raise_on_status(status, "decode_avro")
+    return out, label, status, prog
+
+
+def decode_avro(records, schema, dtype=None) -> List[np.ndarray]:
+    """``kafka_io.decode_avro(e, schema=schema, dtype=[...])``: one array per schema field, cast to the requested dtypes
+    (names or numpy dtypes; default float32 / object).  Apply :func:`substr` first to drop the Confluent framing."""
+    out, label, _, prog = decode_avro_matrix(records, schema)
+    out_h, lab_h = out.cpu().numpy(), label.cpu().numpy()
+    if (lab_h == 3).any():
+        raise NotImplementedError("string field with a value other than 'true'/'false'/'' (only the label semantics of the "
+                                  "reference's FAILURE_OCCURRED field are implemented)")
+    cols = []
+    for i, f in enumerate(prog.fields):
+        want = None if dtype is None else dtype[i]
+        want = _NP_DTYPES.get(getattr(want, "name", want), want) if want is not None else None
+        if f.out >= 0:
+            c = np.ascontiguousarray(out_h[:, f.out])
+            cols.append(c if want in (None, np.float32) else c.astype(want))
+        elif f.out == av.OUT_LABEL:
+            cols.append(np.array([(b"false", b"true", b"")[v] for v in lab_h], dtype=object))
+        else:
+            cols.append(None)
+    return cols
+
+
+def decode_score(model, records, csv_kinds=None, csv_defaults=None, avro_schema=None, threshold: float = 5.0,
+                 mse: Optional[torch.Tensor] = None, flag: Optional[torch.Tensor] = None, label: Optional[torch.Tensor] = None,
+                 status: Optional[torch.Tensor] = None, counters: Optional[torch.Tensor] = None, field_delim=",", use_quote_delim=True):
+    """The streaming scoring loop of cardata-v1.py:176-231 in ONE kernel: decode → normalize_fn → Dense AE → MSE → flag.
+    Everything stays on the device; returns (mse, flag, label, status) tensors.  Bad records get mse = NaN, flag = 0."""
+    rb = _as_batch(records)
+    dev = rb.data.device
+    if mse is None:
+        mse = torch.empty(rb.n, dtype=torch.float32, device=dev)
+    if flag is None:
+        flag = torch.empty(rb.n, dtype=torch.uint8, device=dev)
+    if status is None:
+        status = torch.empty(rb.n, dtype=torch.int32, device=dev)
+    if (csv_kinds is None) == (avro_schema is None):
+        raise ValueError("give exactly one of csv_kinds / avro_schema")
+    spec = p = None
+    if csv_kinds is not None:
+        spec = _ffi.make_csv_spec(csv_kinds, csv_defaults, field_delim, use_quote_delim)
+    else:
+        prog = avro_schema if isinstance(avro_schema, av.AvroProgram) else av.compile_schema(avro_schema)
+        p = _ffi.make_avro_prog(prog)
+        if label is None:
+            label = torch.empty(rb.n, dtype=torch.uint8, device=dev)
+    nm = model._norm_struct()
+    _ffi.check(_ffi.lib().b2_decode_score(model._handle(), _ffi.ptr(rb.data), _ffi.ptr(rb.offsets), rb.n,
+                                          C.byref(spec) if spec is not None else None, C.byref(p) if p is not None else None,
+                                          rb.skip_prefix, C.byref(nm), float(threshold), _ffi.ptr(mse), _ffi.ptr(flag), _ffi.ptr(label),
+                                          _ffi.ptr(status), _ffi.ptr(counters), _stream_ptr()), "b2_decode_score")
+    return mse, flag, label, status

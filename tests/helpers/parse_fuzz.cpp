@@ -1,0 +1,110 @@
+// CPU fuzz of csrc/float_parse.cuh (the exact code the CUDA decode kernel runs) against glibc strtof.
+//   g++ -O2 -std=c++17 -o parse_fuzz parse_fuzz.cpp && ./parse_fuzz <n_random> [token_file]
+// Prints "mismatches=<k> checked=<n>"; exit code 1 when k > 0.
+#include <math.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <random>
+#include <string>
+
+#include "../../hivemq-mqtt-tensorflow-kafka-realtime-iot-machine-learning-training-inference_b200/csrc/float_parse.cuh"
+
+static long long bad = 0, checked = 0;
+
+static void check(const std::string& tok) {
+  uint32_t got = 0;
+  const int st = b2_parse_float((const uint8_t*)tok.data(), (int)tok.size(), &got);
+  // reference: glibc strtof on the token with trailing blanks removed (decode_csv allows them); empty and hex tokens are
+  // invalid by our (and decode_csv's decimal) grammar
+  std::string t = tok;
+  while (!t.empty() && (t.back() == ' ' || t.back() == '\t')) t.pop_back();
+  char* end = nullptr;
+  const float f = strtof(t.c_str(), &end);
+  uint32_t ref;
+  memcpy(&ref, &f, 4);
+  ++checked;
+  if (st == B2_NUM_TOO_LONG) return;  // allowed refusal (counted separately by the caller if needed)
+  const bool hex = t.find('x') != std::string::npos || t.find('X') != std::string::npos;
+  const bool ref_ok = !t.empty() && !hex && end == t.c_str() + t.size() && t.find_first_not_of(" \t") != std::string::npos;
+  if ((st == B2_NUM_OK) != ref_ok || (ref_ok && got != ref && !(isnan(f) && (got & 0x7FFFFFFF) > 0x7F800000))) {
+    if (bad < 20) fprintf(stderr, "MISMATCH '%s' got st=%d 0x%08x ref ok=%d 0x%08x\n", tok.c_str(), st, got, (int)ref_ok, ref);
+    ++bad;
+  }
+}
+
+int main(int argc, char** argv) {
+  const long long n = argc > 1 ? atoll(argv[1]) : 1000000;
+  std::mt19937_64 g(314);
+  char buf[128];
+  // 1. every float that is a rounding boundary neighbour: print random floats with 9 and 17 digits, and midpoints
+  for (long long i = 0; i < n; ++i) {
+    uint32_t bits = (uint32_t)g();
+    if ((bits & 0x7F800000u) == 0x7F800000u) bits &= ~0x00800000u;  // finite
+    float f;
+    memcpy(&f, &bits, 4);
+    snprintf(buf, sizeof buf, "%.9g", (double)f);
+    check(buf);
+    // exact midpoint between f and its successor, printed with many digits (hard round-to-even cases)
+    uint32_t b2 = bits + 1;
+    float f2;
+    memcpy(&f2, &b2, 4);
+    if (isfinite(f2)) {
+      const double mid = ((double)f + (double)f2) / 2;
+      snprintf(buf, sizeof buf, "%.19g", mid);
+      check(buf);
+      snprintf(buf, sizeof buf, "%.17g", nextafter(mid, 1e300));
+      check(buf);
+      snprintf(buf, sizeof buf, "%.17g", nextafter(mid, -1e300));
+      check(buf);
+    }
+  }
+  // 2. random decimal strings: d digits, random point position, optional exponent
+  for (long long i = 0; i < n; ++i) {
+    std::string s;
+    if (g() & 1) s += '-';
+    const int nd = 1 + (int)(g() % 19);
+    const int point = (int)(g() % (nd + 1));
+    for (int k = 0; k < nd; ++k) {
+      if (k == point) s += '.';
+      s += (char)('0' + g() % 10);
+    }
+    const int mode = (int)(g() % 4);
+    if (mode == 1) s += "E" + std::to_string((int)(g() % 12) - 6);
+    else if (mode == 2) s += "e" + std::to_string((int)(g() % 100) - 50);
+    else if (mode == 3) s += "E" + std::to_string((int)(g() % 700) - 350);
+    check(s);
+  }
+  // 3. long digit strings (> 19 significant digits): must either match or be refused, never be wrong
+  for (long long i = 0; i < n / 10; ++i) {
+    std::string s;
+    const int nd = 20 + (int)(g() % 30);
+    const int point = (int)(g() % (nd + 1));
+    for (int k = 0; k < nd; ++k) {
+      if (k == point) s += '.';
+      s += (char)('0' + g() % 10);
+    }
+    check(s);
+  }
+  // 4. syntax corner cases
+  const char* cases[] = {"0", "-0", "0.0", "-0.0", ".5", "5.", "+1.5", "1e5", "1E+5", "1e-5", " 1.5", "1.5 ", "\t2\t", "inf", "-inf",
+                         "INF", "Infinity", "nan", "NaN", "-nan", "", " ", "-", "+", ".", "e5", "1e", "1e+", "1.5x", "x1.5", "1..5",
+                         "1.5.2", "--1", "0x10", "1,5", "1 5", "3.4028235e38", "3.4028236e38", "3.4028235677973366e38", "1e39", "1e-46",
+                         "1.4e-45", "7e-46", "7.0064923216240854e-46", "7.0064923216240853e-46", "1.17549435e-38", "1.17549421e-38",
+                         "000000000000000000000001.5", "0.000000000000000000000000000000000000000000001", "123456789012345678901234567890",
+                         "5.723834E-4", "1567606196", "0.034893095", "2493.487", "1e400", "1e-400", "0e999999999", "1e99999999999"};
+  for (const char* c : cases) check(c);
+  if (argc > 2) {
+    FILE* fp = fopen(argv[2], "r");
+    while (fp && fgets(buf, sizeof buf, fp)) {
+      size_t l = strlen(buf);
+      while (l && (buf[l - 1] == '\n' || buf[l - 1] == '\r')) buf[--l] = 0;
+      check(buf);
+    }
+    if (fp) fclose(fp);
+  }
+  printf("mismatches=%lld checked=%lld\n", bad, checked);
+  return bad ? 1 : 0;
+}

@@ -1,0 +1,235 @@
+"""K2 parity: CSV / Avro decode and the fused decode→score kernel against the CPU oracle, through the C ABI.
+
+Decoded floats must be BIT-exact (glibc strtof / IEEE casts are the oracle); statuses must match the oracle's per record;
+fused decode+score must equal decode followed by score bit for bit, and the oracle's MSE within 1e-5 relative.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import b200_sensor as bs
+from b200_sensor import avro_schema as av, decode as dec, schemas, synth
+from oracle import c_oracle as co, cpu_oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+ACTS = [orc.ACT_TANH, orc.ACT_RELU, orc.ACT_TANH, orc.ACT_RELU]
+SENSOR_KINDS = [0, 0] + [1] * 18
+
+
+def _bits(a):
+    return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+
+
+def _model18(seed=314):
+    k = bs.keras
+    inp = k.layers.Input(shape=(18,))
+    e = k.layers.Dense(14, activation="tanh", activity_regularizer=k.regularizers.l1(1e-7))(inp)
+    e = k.layers.Dense(7, activation="relu")(e)
+    d = k.layers.Dense(7, activation="tanh")(e)
+    d = k.layers.Dense(18, activation="relu")(d)
+    m = k.models.Model(inputs=inp, outputs=d, seed=seed)
+    m.set_normalization(*schemas.norm_arrays())
+    return m
+
+
+def test_csv_reference_sample_bit_exact(cuda_device, golden_dir):
+    lines = open(os.path.join(golden_dir, "car_sensor_sample.csv")).read().strip().split("\n")[1:]
+    rb = dec.RecordBatch.from_messages(lines)
+    out, _, status = dec.decode_csv_matrix(rb, SENSOR_KINDS)
+    ref = np.array([[np.float32(float(t)) for t in ln.split(",")[2:]] for ln in lines], dtype=np.float32)
+    assert int(status.abs().sum()) == 0
+    np.testing.assert_array_equal(_bits(out.cpu().numpy()), _bits(ref))
+
+
+def test_csv_every_reference_token_bit_exact(cuda_device, golden_dir):
+    d = np.load(os.path.join(golden_dir, "csv_tokens.npz"))
+    toks, bits = d["tokens"].tolist(), d["bits"]
+    rb = dec.RecordBatch.from_messages(toks)
+    out, _, status = dec.decode_csv_matrix(rb, [1])
+    assert int(status.abs().sum()) == 0
+    np.testing.assert_array_equal(_bits(out.cpu().numpy()).ravel(), bits)
+
+
+@pytest.mark.parametrize("n", [1, 2, 255, 256, 257, 1000, 100_003])
+def test_csv_synthetic_roundtrip_and_oracle(cuda_device, n):
+    rows = synth.sensor_rows(n, seed=40 + n)
+    data, offs = synth.csv_batch(rows, seed=n)
+    out, _, status = dec.decode_csv_matrix(dec.RecordBatch(data, offs), SENSOR_KINDS)
+    ref, _, st = co.decode_csv(data, offs, SENSOR_KINDS)
+    assert st.sum() == 0 and int(status.abs().sum()) == 0
+    np.testing.assert_array_equal(_bits(out.cpu().numpy()), _bits(ref))
+    exp = rows.copy()
+    exp[:, [9, 10, 11, 12, 17]] = np.rint(exp[:, [9, 10, 11, 12, 17]])
+    np.testing.assert_array_equal(_bits(out.cpu().numpy()), _bits(exp))  # text → float32 round trip is lossless
+
+
+def test_csv_number_grammar_fuzz_vs_strtof(cuda_device):
+    g = np.random.default_rng(99)
+    toks = []
+    f32 = g.integers(0, 2 ** 32, size=60000, dtype=np.uint64).astype(np.uint32).view(np.float32)
+    f32 = f32[np.isfinite(f32)]
+    toks += ["%.9g" % v for v in f32[:20000]]
+    toks += [repr(float(v)) for v in f32[20000:30000]]
+    toks += ["%.17g" % ((float(a) + float(np.nextafter(a, np.float32(np.inf)))) / 2) for a in f32[30000:40000]]  # midpoints
+    toks += ["%.6E" % v for v in f32[40000:45000]]
+    toks += [" %s " % s for s in ["1.5", "-2", "+3e2", ".5", "5.", "1E-4", "inf", "-inf", "nan", "Infinity", "0", "-0.0"]]
+    toks += ["%d.%dE%d" % (g.integers(0, 10 ** 9), g.integers(0, 10 ** 9), g.integers(-60, 40)) for _ in range(5000)]
+    toks += ["1e39", "1e-46", "1.4e-45", "7.0064923216240854e-46", "7.0064923216240853e-46", "3.4028235677973366e38",
+             "123456789012345678901234567890", "0.000000000000000000000000000000000000000000001"]
+    toks = [t for t in toks if "," not in t]
+    rb = dec.RecordBatch.from_messages(toks)
+    out, _, status = dec.decode_csv_matrix(rb, [1], raise_on_error=False)
+    got = _bits(out.cpu().numpy()).ravel()
+    st = status.cpu().numpy()
+    ref = np.array([np.float32(orc.strtof(t.encode())[0]) for t in toks], dtype=np.float32)
+    ok = st == 0
+    assert ok.mean() > 0.999  # only >19-digit ambiguous tokens may be refused (status 7), never wrong
+    assert set(np.unique(st[~ok]).tolist()) <= {7}
+    nan = np.isnan(ref)
+    np.testing.assert_array_equal(got[ok & ~nan], _bits(ref)[ok & ~nan])
+    assert np.isnan(out.cpu().numpy().ravel()[ok & nan]).all()
+
+
+def test_csv_error_semantics_match_oracle(cuda_device):
+    recs = [b"1,2,3", b"1,,3", b"1,x,3", b'1,"2",3', b'1,"2,3', b"1,2", b" 1 ,2.5e0,3", b'1,2"x,3', b"1,2,3,4", b"1,2,", b"",
+            b",,", b'"1","2","3"', b'1,"",3', b"1,2\n,3", b"0x10,1,2", b"1e,2,3", b"1,2,3 "]
+    data, offs = synth.lines_to_batch(recs)
+    ref, _, st_ref = orc.decode_csv(data, offs, [1, 1, 1], defaults=[None, 7.0, None])
+    out, _, st = dec.decode_csv_matrix(dec.RecordBatch(data, offs), [1, 1, 1], defaults=[None, 7.0, None], raise_on_error=False)
+    np.testing.assert_array_equal(st.cpu().numpy(), st_ref)
+    ok = st_ref == 0
+    np.testing.assert_array_equal(_bits(out.cpu().numpy())[ok], _bits(ref)[ok])
+    assert np.isnan(out.cpu().numpy()[~ok]).all()
+    with pytest.raises(dec.DecodeError):
+        dec.decode_csv(dec.RecordBatch(data, offs), [[0.0], [7.0], [0.0]])
+
+
+def test_csv_credit_card_form_subtiles_and_strings(cuda_device):
+    """31 fields (30 full-precision floats + quoted class label, ≈550 B/record → the 48 KB stage holds a sub-tile only)."""
+    x = synth.credit_rows(5000, seed=3).astype(np.float64) * 1.000000123
+    labels = (np.arange(5000) % 7 == 0).astype(np.int64)
+    data, offs = synth.credit_csv_batch(x, labels)
+    assert (offs[1:] - offs[:-1]).mean() > 400
+    cols = dec.decode_csv(dec.RecordBatch(data, offs), [[0.0]] * 30 + [[""]])
+    assert len(cols) == 31 and cols[30].dtype == object
+    ref, _, st = co.decode_csv(data, offs, [1] * 30 + [2])
+    assert st.sum() == 0
+    np.testing.assert_array_equal(_bits(np.stack(cols[:30], 1)), _bits(ref))
+    assert [int(c) for c in cols[30]] == labels.tolist()
+    # tf.stack(entry[0:30], 1) + to_number(entry[30]) — process_x_y of the reference script
+    np.testing.assert_array_equal(np.array([int(c) for c in cols[30]], dtype=np.int32), labels.astype(np.int32))
+
+
+def test_csv_malformed_injection(cuda_device):
+    rows = synth.sensor_rows(50_000, seed=8)
+    data, offs = synth.csv_batch(rows, seed=8)
+    data, offs, bad = synth.corrupt_csv(data, offs, frac=2e-3, seed=8)
+    out, _, status = dec.decode_csv_matrix(dec.RecordBatch(data, offs), SENSOR_KINDS, raise_on_error=False)
+    ref, _, st_ref = co.decode_csv(data, offs, SENSOR_KINDS)
+    np.testing.assert_array_equal(status.cpu().numpy(), st_ref)
+    assert set(np.nonzero(st_ref)[0].tolist()) == set(bad.tolist())
+    ok = st_ref == 0
+    np.testing.assert_array_equal(_bits(out.cpu().numpy())[ok], _bits(ref)[ok])
+
+
+def test_avro_both_schemas_match_oracle(cuda_device):
+    x = synth.sensor_rows(70_001, seed=21)
+    for which in ("a", "b"):
+        if which == "a":
+            data, offs = synth.avro_a_batch(x)
+            labs = None
+            sch = schemas.schema_a_json()
+        else:
+            data, offs, labs = synth.avro_b_batch(x, null_frac=0.03, seed=5)
+            sch = schemas.schema_b_json()
+        prog = av.compile_schema(sch)
+        rb = dec.substr(dec.RecordBatch(data, offs), 5, -1)
+        out, label, status, _ = dec.decode_avro_matrix(rb, prog)
+        ref, lab_ref, st_ref = co.decode_avro(data, offs, [(f.type, f.nullable, f.out) for f in prog.fields], prog.n_out, skip_prefix=5)
+        assert st_ref.sum() == 0 and int(status.abs().sum()) == 0
+        np.testing.assert_array_equal(_bits(out.cpu().numpy()), _bits(ref))
+        np.testing.assert_array_equal(label.cpu().numpy(), lab_ref)
+        if labs is not None:
+            np.testing.assert_array_equal(label.cpu().numpy(), labs)
+    # the drop-in list-of-columns form with the dtype list of cardata-v3.py:56-74
+    cols = dec.decode_avro(rb, sch, dtype=["float64"] * 9 + ["int32"] * 4 + ["float64"] * 4 + ["int32", "string"])
+    assert len(cols) == 19 and cols[9].dtype == np.int32 and cols[0].dtype == np.float64 and cols[18][0] in (b"false", b"true", b"")
+
+
+def test_avro_truncated_and_bad_branch(cuda_device):
+    x = synth.sensor_rows(600, seed=2)
+    data, offs, _ = synth.avro_b_batch(x, seed=2)
+    prog = av.compile_schema(schemas.schema_b_json())
+    fields = [(f.type, f.nullable, f.out) for f in prog.fields]
+    data = data.copy()
+    data[offs[7] + 5] = 0x06  # union branch 3
+    offs2 = offs.copy()
+    cut = offs2[-1] - 9
+    data2, offs2[-1] = data[:cut], cut
+    out, label, status, _ = dec.decode_avro_matrix(dec.RecordBatch(data2, offs2, skip_prefix=5), prog, raise_on_error=False)
+    ref, lab_ref, st_ref = co.decode_avro(data2, offs2, fields, prog.n_out, skip_prefix=5)
+    np.testing.assert_array_equal(status.cpu().numpy(), st_ref)
+    assert st_ref[7] == orc.REC_BAD_BRANCH and st_ref[-1] == orc.REC_TRUNCATED
+    ok = st_ref == 0
+    np.testing.assert_array_equal(_bits(out.cpu().numpy())[ok], _bits(ref)[ok])
+
+
+@pytest.mark.parametrize("fmt", ["csv", "avro_a", "avro_b"])
+def test_fused_decode_score_equals_two_step_and_oracle(cuda_device, fmt):
+    m = _model18()
+    x = synth.sensor_rows(120_007, seed=77)
+    if fmt == "csv":
+        data, offs = synth.csv_batch(x, seed=1)
+        data, offs, bad = synth.corrupt_csv(data, offs, frac=1e-3, seed=1)
+        rb = dec.RecordBatch(data, offs)
+        kw = dict(csv_kinds=SENSOR_KINDS)
+        feats, _, st0 = dec.decode_csv_matrix(rb, SENSOR_KINDS, raise_on_error=False)
+    else:
+        if fmt == "avro_a":
+            data, offs = synth.avro_a_batch(x)
+            sch = schemas.schema_a_json()
+        else:
+            data, offs, _ = synth.avro_b_batch(x, null_frac=0.01, seed=4)
+            sch = schemas.schema_b_json()
+        rb = dec.RecordBatch(data, offs, skip_prefix=5)
+        kw = dict(avro_schema=sch)
+        feats, _, st0, _ = dec.decode_avro_matrix(rb, sch, raise_on_error=False)
+    cnt = torch.zeros(4, dtype=torch.int64, device="cuda")
+    mse, flag, label, status = dec.decode_score(m, rb, threshold=5.0, counters=cnt, **kw)
+    torch.testing.assert_close(status, st0, rtol=0, atol=0)
+    ok = (st0 == 0)
+    mse2, flag2 = m.score_device(feats[ok].contiguous())
+    assert torch.equal(mse[ok], mse2) and torch.equal(flag[ok], flag2)  # fused == decode then score, bit for bit
+    assert torch.isnan(mse[~ok]).all() and int(flag[~ok].sum()) == 0
+    c = cnt.cpu().numpy()
+    assert c[0] == int(ok.sum()) and c[1] == int(flag.sum()) and c[2] == int((~ok).sum()) and c[3] == int(offs[-1])
+    # oracle: the whole CPU streaming loop
+    w = m.get_flat_weights()
+    nm = schemas.norm_arrays()
+    if fmt == "csv":
+        mr, fr, sr, _ = co.decode_score(data, offs, w, [18, 14, 7, 7, 18], ACTS, norm=nm, csv=(SENSOR_KINDS, None, ",", True))
+    else:
+        prog = av.compile_schema(sch)
+        mr, fr, sr, _ = co.decode_score(data, offs, w, [18, 14, 7, 7, 18], ACTS, norm=nm,
+                                        avro=[(f.type, f.nullable, f.out) for f in prog.fields], skip_prefix=5)
+    okh = ok.cpu().numpy()
+    np.testing.assert_array_equal(sr, st0.cpu().numpy())
+    got = mse.cpu().numpy()[okh].astype(np.float64)
+    ref = mr[okh].astype(np.float64)
+    err = np.abs(got - ref)
+    assert (err <= np.maximum(2e-5 * ref, 2e-7)).all()  # oracle.c is float32 itself: twice the 1e-5 budget
+    safe = np.abs(ref - 5.0) > 1e-4
+    np.testing.assert_array_equal(flag.cpu().numpy()[okh][safe], fr[okh][safe])
+
+
+def test_empty_and_oversized_records(cuda_device):
+    out, _, st = dec.decode_csv_matrix(dec.RecordBatch(np.zeros(0, np.uint8), np.zeros(1, np.int32)), [1, 1])
+    assert out.shape == (0, 2)
+    big = b"1," + b"9" * 60000  # one record larger than the 48 KB stage → refused with status 7, neighbours unaffected
+    recs = [b"1,2", big, b"3,4"]
+    out, _, st = dec.decode_csv_matrix(dec.RecordBatch.from_messages(recs), [1, 1], raise_on_error=False)
+    assert st.cpu().numpy().tolist() == [0, 7, 0]
+    assert out.cpu().numpy()[[0, 2]].tolist() == [[1.0, 2.0], [3.0, 4.0]]
