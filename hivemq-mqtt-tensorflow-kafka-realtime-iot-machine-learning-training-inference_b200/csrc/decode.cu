@@ -310,7 +310,9 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
           if (s_stat[r] != B2_REC_OK) continue;
           const int f = a.csv.fidx[k];
           const uint16_t* fb = s_fb + (size_t)r * fb_stride;
-          const int quoted = (int)((s_qm[r] >> f) & 1ull);
+          // a quoted field's payload sits between its quotes: drop its closing quote and, when the NEXT field is quoted
+          // too, that field's opening quote (fb[] holds payload starts)
+          const int quoted = (int)((s_qm[r] >> f) & 1ull) + (int)((s_qm[r] >> (f + 1)) & 1ull);
           const int fbeg = fb[f], fend = (int)fb[f + 1] - 1 - quoted;
           if (a.csv.kind[f] == 1) {
             float v;
@@ -554,7 +556,7 @@ static int decode_score_spec(b2_ae* ae, const uint8_t* bytes, const int32_t* off
   args.mse = mse;
   args.flag = flag;
   args.counters = counters;
-  if (env_int("B2_FAST_TANH", 0)) return launch_decode<D, 1, true>(ae->ctx, args, stream);
+  if (env_int("B2_FAST_TANH", 1)) return launch_decode<D, 1, true>(ae->ctx, args, stream);
   return launch_decode<D, 1, false>(ae->ctx, args, stream);
 }
 

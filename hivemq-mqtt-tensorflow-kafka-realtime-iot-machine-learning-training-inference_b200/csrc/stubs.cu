@@ -1,10 +1,6 @@
 // Entry points not implemented yet in this build (each is replaced by its own translation unit as it lands).
 #include "common.cuh"
 #define STUB(name) b2_set_error(name ": not implemented in this build"); return B2_EUNSUPPORTED
-extern "C" int b2_ae_fit_steps(b2_ae*, const float*, const int32_t*, int64_t, int, const b2_norm*, b2_adam*, float*, float*, void*) { STUB("b2_ae_fit_steps"); }
-extern "C" int64_t b2_ae_grad_scratch_bytes(const b2_ae*, int64_t) { return 0; }
-extern "C" int b2_ae_grad(b2_ae*, const float*, int64_t, const b2_norm*, float*, void*, int64_t, void*) { STUB("b2_ae_grad"); }
-extern "C" int b2_ae_apply(b2_ae*, const float*, b2_adam*, float*, void*) { STUB("b2_ae_apply"); }
 extern "C" int b2_lstm_create(b2_ctx*, const b2_lstm_desc*, const float*, b2_lstm**) { STUB("b2_lstm_create"); }
 extern "C" void b2_lstm_destroy(b2_lstm*) {}
 extern "C" int b2_lstm_param_count(const b2_lstm*) { return 0; }

@@ -443,9 +443,14 @@ class Model:
         self._compiled = True
 
     def fit(self, x, y=None, epochs=1, batch_size=32, shuffle=True, validation_data=None, verbose=0, callbacks=None,
-            seed: Optional[int] = None):
+            seed: Optional[int] = None, data_parallel: bool = False):
         """Mini-batch Adam on MSE(x, AE(x)) + l1·Σ|h1|/B, all steps of an epoch inside ONE kernel launch.
-        ``y`` must be None or ``x`` (autoencoder; the notebooks call ``fit(train_x, train_x)``, nb2.0:871)."""
+        ``y`` must be None or ``x`` (autoencoder; the notebooks call ``fit(train_x, train_x)``, nb2.0:871).
+
+        ``batch_size`` ≤ 256 (the reference uses 32/100/128) runs the single-CTA persistent kernel.  Larger batches, or
+        ``data_parallel=True`` under an initialised ``torch.distributed`` NCCL group (``x`` = this rank's shard,
+        ``batch_size`` = per-rank batch), run the grid-wide gradient kernel, ONE all-reduce of the P+3 floats and the Adam
+        kernel per step."""
         if self.kind != "dense":
             raise NotImplementedError("fit is implemented for the Dense autoencoder (LSTM training is out of scope, SURVEY §8f.4)")
         if not self._compiled:
@@ -458,6 +463,9 @@ class Model:
         n = xd.shape[0]
         l = _ffi.lib()
         h = self._handle()
+        self._restore_adam_slots()
+        if batch_size > 256 or data_parallel:
+            return self._fit_large(xd, epochs, batch_size, shuffle, validation_data, verbose, callbacks, seed, data_parallel)
         steps = (n + batch_size - 1) // batch_size
         hist = History()
         hist.history = {"loss": [], "accuracy": []} if "accuracy" in getattr(self, "_metrics", []) else {"loss": []}
@@ -487,6 +495,75 @@ class Model:
                 vx = validation_data[0] if isinstance(validation_data, (tuple, list)) else validation_data
                 vm = self.reconstruction_error(vx)
                 logs["val_loss"] = float(np.mean(vm.astype(np.float64)))
+            for k, v in logs.items():
+                hist.history.setdefault(k, []).append(v)
+            if verbose:
+                print(f"Epoch {ep + 1}/{epochs} - " + " - ".join(f"{k}: {v:.4f}" for k, v in logs.items()))
+            for cb in callbacks or []:
+                cb.on_epoch_end(ep, logs)
+        self._adam["iter"] = int(adam.iter)
+        self.history = hist
+        return hist
+
+    def _restore_adam_slots(self):
+        """Push Adam m/v loaded from an .h5 (load_model) into the native handle once, so that training resumes."""
+        opt = getattr(self, "_h5_optimizer", None)
+        if not opt or self._ae is None:
+            return
+        dense = [l for l in self.layers if isinstance(l, Dense)]
+        names = getattr(self, "_h5_inner_names", None) or [l.name for l in dense]
+        m_parts, v_parts = [], []
+        try:
+            for nm in names:
+                for kind in ("kernel", "bias"):
+                    m_parts.append([val for k, val in opt.items() if k.endswith(f"Adam/{nm}/{kind}/m:0")][0].ravel())
+                    v_parts.append([val for k, val in opt.items() if k.endswith(f"Adam/{nm}/{kind}/v:0")][0].ravel())
+        except IndexError:
+            self._h5_optimizer = None
+            return
+        m = np.ascontiguousarray(np.concatenate(m_parts), dtype=np.float32)
+        v = np.ascontiguousarray(np.concatenate(v_parts), dtype=np.float32)
+        if m.size == self.n_params:
+            _ffi.check(_ffi.lib().b2_ae_set_adam(self._ae, m.ctypes.data, v.ctypes.data), "b2_ae_set_adam")
+        self._h5_optimizer = None
+
+    def _fit_large(self, xd, epochs, batch_size, shuffle, validation_data, verbose, callbacks, seed, data_parallel):
+        import torch.distributed as dist
+
+        dp = data_parallel and dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+        l, h, dev, n = _ffi.lib(), self._handle(), xd.device, xd.shape[0]
+        P = self.n_params
+        nm = self._norm_struct()
+        adam = _ffi.Adam(self._adam["lr"], self._adam["beta1"], self._adam["beta2"], self._adam["eps"], self._adam["iter"])
+        scratch_bytes = int(l.b2_ae_grad_scratch_bytes(h, min(batch_size, n)))
+        scratch = torch.empty(scratch_bytes, dtype=torch.uint8, device=dev)
+        grads = torch.empty(P + 3, dtype=torch.float32, device=dev)
+        steps = (n + batch_size - 1) // batch_size
+        stats = torch.empty((steps, 2), dtype=torch.float32, device=dev)
+        hist = History()
+        hist.history = {"loss": [], "accuracy": []} if "accuracy" in getattr(self, "_metrics", []) else {"loss": []}
+        g = np.random.Generator(np.random.PCG64(self._seed if seed is None else seed))
+        for cb in callbacks or []:
+            if isinstance(cb, ModelCheckpoint):
+                cb.model = self
+        for ep in range(epochs):
+            xs = xd[torch.from_numpy(g.permutation(n)).to(dev)].contiguous() if shuffle else xd
+            for s in range(steps):
+                xb = xs[s * batch_size:(s + 1) * batch_size]
+                _ffi.check(l.b2_ae_grad(h, _ffi.ptr(xb), xb.shape[0], C.byref(nm), _ffi.ptr(grads), _ffi.ptr(scratch), scratch_bytes,
+                                        _stream_ptr()), "b2_ae_grad")
+                if dp:
+                    dist.all_reduce(grads)  # NCCL over NVLink: P+3 floats (gradient sums, loss sum, correct, rows)
+                _ffi.check(l.b2_ae_apply(h, _ffi.ptr(grads), C.byref(adam), _ffi.ptr(stats[s]), _stream_ptr()), "b2_ae_apply")
+            st = stats.cpu().numpy().astype(np.float64)
+            sizes = np.full(steps, batch_size, dtype=np.float64)
+            sizes[-1] = n - batch_size * (steps - 1)
+            logs = {"loss": float((st[:, 0] * sizes).sum() / n)}
+            if "accuracy" in hist.history:
+                logs["accuracy"] = float((st[:, 1] * sizes).sum() / n)
+            if validation_data is not None:
+                vx = validation_data[0] if isinstance(validation_data, (tuple, list)) else validation_data
+                logs["val_loss"] = float(np.mean(self.reconstruction_error(vx).astype(np.float64)))
             for k, v in logs.items():
                 hist.history.setdefault(k, []).append(v)
             if verbose:
@@ -606,11 +683,13 @@ def load_model(path: str, device: Optional[int] = None) -> Model:
               device=device)
     mw = f["model_weights"]
     parts = []
+    inner_names = []
     for ln in [str(s) for s in np.atleast_1d(mw.attrs["layer_names"])]:
         g = mw[ln]
         wn = [str(s) for s in np.atleast_1d(g.attrs.get("weight_names", []))]
         if not wn:
             continue
+        inner_names.append(wn[0].split("/")[0])
         by_kind = {("kernel" if "kernel" in w else "bias"): g[w].read() for w in wn}
         parts += [by_kind["kernel"].astype(np.float32).ravel(), by_kind["bias"].astype(np.float32).ravel()]
     m.set_flat_weights(np.concatenate(parts))
@@ -622,6 +701,7 @@ def load_model(path: str, device: Optional[int] = None) -> Model:
             m._adam.update(lr=float(c["learning_rate"]), beta1=float(c["beta_1"]), beta2=float(c["beta_2"]), eps=float(c["epsilon"]))
             m.compile("adam", tc.get("loss", "mean_squared_error"), tc.get("metrics"))
     m._h5_optimizer = None
+    m._h5_inner_names = inner_names
     if "optimizer_weights" in f:
         ow = f["optimizer_weights"]
         found: Dict[str, np.ndarray] = {}

@@ -120,7 +120,10 @@ def test_predict_matches_oracle_and_callbacks(cuda_device, ae30, golden_dir):
     cb = Out()
     y = m.predict(x, callbacks=[cb])
     ref = orc.ae_forward(x, ae30["weights"], [30, 14, 7, 7, 30], ACTS, dtype=np.float64)
-    np.testing.assert_allclose(y, ref, rtol=2e-6, atol=2e-6)
+    # reconstruction rows: hold the CUDA result to (a multiple of) the float32 evaluation noise itself — the error of the
+    # float32 NumPy restatement against its own float64 shadow on the same rows — with a floor of 2e-6
+    noise = np.abs(orc.ae_forward(x, ae30["weights"], [30, 14, 7, 7, 30], ACTS, dtype=np.float32).astype(np.float64) - ref).max()
+    assert np.abs(y - ref).max() <= max(4 * noise, 2e-6), (np.abs(y - ref).max(), noise)
     assert [i for i, _ in cb.rows] == list(range(x.shape[0]))
     # float64 input is cast to float32 on entry like Keras does
     y2 = m.predict(x.astype(np.float64))
