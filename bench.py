@@ -209,9 +209,128 @@ class ScoreWorkload:
         return done, time.perf_counter() - t0, co.max_threads() if not threads else threads
 
 
+class DecodeScoreWorkload:
+    """BASELINE.json configs[2]: synthetic Kafka-shaped record batches (CSV lines / Confluent-framed Avro), fused
+    decode → normalize_fn → Dense AE 18-14-7-7-18 → MSE → flag, one kernel launch per partition batch."""
+
+    def __init__(self, fmt, batch_log2=20, batches_per_step=4):
+        self.fmt = fmt
+        self.batch = 1 << batch_log2
+        self.nb = batches_per_step
+        self.name = f"decode_score_{fmt}"
+        self.launches_per_step = batches_per_step
+        self.kernel_key = f"decode_score_{fmt}"
+        self.flop_per_record = 2 * (14 * 18 + 98 + 49 + 7 * 18)
+        self.bytes_per_record = None  # measured from the generated batches in setup()
+        self.rows = self.batch * self.nb
+        self.e2e_rows = self.batch
+
+    def describe(self):
+        return {"workload": self.name, "format": {"csv": "CSV line per message (car-sensor-data.csv layout, 20 fields)",
+                                                  "avro_a": "Confluent-framed Avro, testdata/cardata-v1.avsc (63 B/record)",
+                                                  "avro_b": "Confluent-framed Avro, KSQL cardata-v1.avsc (nullable unions, ~139 B/record)"}[self.fmt],
+                "features": 18, "model": "Dense AE 18-14-7-7-18", "weights": "Glorot-uniform seed 314 (no 18-wide weights are shipped)",
+                "normalise": True, "records_per_batch": self.batch, "batches_per_step_per_gpu": self.nb, "threshold": THRESHOLD,
+                "partitioning": "rank r owns partition batches p with seed 314 + (r * batches_per_step + p); no data-path collective",
+                "l2_policy": "each step streams %d distinct batches (> 126 MB L2 in total for CSV/Avro-B; Avro-A batches rotate so "
+                             "that consecutive launches never touch the same bytes)" % self.nb,
+                "bytes_per_record_payload_plus_offset_plus_out": self.bytes_per_record,
+                "e2e_rows_per_step_per_gpu": self.e2e_rows}
+
+    def weights(self):
+        import b200_sensor as bs
+
+        return bs.keras_compat.init_dense_weights(W18, seed=314)
+
+    def _host_batch(self, seed, n=None):
+        import b200_sensor as bs
+
+        rows = bs.synth.sensor_rows(n or self.batch, seed=seed)
+        if self.fmt == "csv":
+            return bs.synth.csv_batch(rows, seed=seed)
+        if self.fmt == "avro_a":
+            return bs.synth.avro_a_batch(rows)
+        d, o, _ = bs.synth.avro_b_batch(rows, seed=seed)
+        return d, o
+
+    def _kw(self):
+        import b200_sensor as bs
+
+        if self.fmt == "csv":
+            return dict(csv_kinds=[0, 0] + [1] * 18)
+        return dict(avro_schema=bs.schemas.schema_a_json() if self.fmt == "avro_a" else bs.schemas.schema_b_json())
+
+    def setup(self, dev, rank):
+        import torch
+
+        import b200_sensor as bs
+
+        self.m = ScoreWorkload(18, 20, 20).model()
+        self.kw = self._kw()
+        self.batches = []
+        tot_bytes = 0
+        for p in range(self.nb):
+            d, o = self._host_batch(314 + rank * self.nb + p)
+            tot_bytes += int(o[-1])
+            rb = bs.decode.RecordBatch(d, o, dev, skip_prefix=0 if self.fmt == "csv" else 5)
+            rb.mse = torch.empty(rb.n, dtype=torch.float32, device=dev)
+            rb.flag = torch.empty(rb.n, dtype=torch.uint8, device=dev)
+            rb.status = torch.empty(rb.n, dtype=torch.int32, device=dev)
+            self.batches.append(rb)
+        self.bytes_per_record = tot_bytes / (self.nb * self.batch) + 4 + 5
+        self.counters = torch.zeros(4, dtype=torch.int64, device=dev)
+
+    def step(self, i):
+        import b200_sensor as bs
+
+        for rb in self.batches:
+            bs.decode.decode_score(self.m, rb, threshold=THRESHOLD, mse=rb.mse, flag=rb.flag, status=rb.status,
+                                   counters=self.counters, **self.kw)
+        return self.rows
+
+    def setup_e2e(self, dev, rank):
+        import torch
+
+        d, o = self._host_batch(2000 + rank)
+        self.hd = torch.from_numpy(d).pin_memory()
+        self.ho = torch.from_numpy(o).pin_memory()
+        self.h2d = self.hd.numel() + self.ho.numel() * 4
+        self.d2h = self.e2e_rows * 5
+
+    def step_e2e(self, i):
+        import b200_sensor as bs
+
+        bs.decode.decode_score_host(self.m, self.hd, self.ho, threshold=THRESHOLD, skip_prefix=0 if self.fmt == "csv" else 5, **self.kw)
+        return self.e2e_rows
+
+    def cpu_sample(self, n, threads=None):
+        import b200_sensor as bs
+        from oracle import c_oracle as co
+
+        if threads:
+            co.set_threads(threads)
+        d, o = self._host_batch(7, n=min(n, 1 << 20))
+        nrec = len(o) - 1
+        w, nm = self.weights(), bs.schemas.norm_arrays()
+        if self.fmt == "csv":
+            kw = dict(csv=([0, 0] + [1] * 18, None, ",", True))
+        else:
+            prog = bs.avro_schema.compile_schema(self._kw()["avro_schema"])
+            kw = dict(avro=[(f.type, f.nullable, f.out) for f in prog.fields], skip_prefix=5)
+        co.decode_score(d[: o[1024]], o[:1025], w, W18, ACTS, norm=nm, **kw)
+        done, t0 = 0, time.perf_counter()
+        while done < n:
+            co.decode_score(d, o, w, W18, ACTS, norm=nm, threshold=THRESHOLD, **kw)
+            done += nrec
+        return done, time.perf_counter() - t0, co.max_threads() if not threads else threads
+
+
 WORKLOADS = {
     "score30": lambda: ScoreWorkload(30, 27, 22),
     "score18": lambda: ScoreWorkload(18, 27, 22),
+    "csv": lambda: DecodeScoreWorkload("csv"),
+    "avro_a": lambda: DecodeScoreWorkload("avro_a", batches_per_step=8),
+    "avro_b": lambda: DecodeScoreWorkload("avro_b"),
 }
 DEFAULT_WORKLOAD = "score30"
 
@@ -220,7 +339,7 @@ DEFAULT_WORKLOAD = "score30"
 def run_reference(args, wl, rank, world):
     if rank != 0:
         return
-    per_step = 1 << 22
+    per_step = 1 << 22 if isinstance(wl, ScoreWorkload) else 1 << 20
     for _ in range(args.warmup):
         wl.cpu_sample(per_step // 4)
     t_tot, n_tot, cores = 0.0, 0, 1
@@ -336,17 +455,17 @@ def main():
     if rank == 0:
         peak, peak_src = load_peaks()
         per_launch_ms = ms_local / (args.steps * wl.launches_per_step)
-        achieved = wl.bytes_per_record * (recs / args.steps) / (per_launch_ms * 1e-3) / 1e9
+        achieved = wl.bytes_per_record * (recs / args.steps / wl.launches_per_step) / (per_launch_ms * 1e-3) / 1e9
         traffic = load_traffic(wl.kernel_key)
         roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                    "traffic": None if traffic is None else traffic * (recs / args.steps),
+                    "traffic": None if traffic is None else traffic * (recs / args.steps / wl.launches_per_step),
                     "peak_source": peak_src, "algorithmic_bytes_per_record": wl.bytes_per_record,
                     "flop_per_record": wl.flop_per_record,
-                    "fp32_tflops_achieved": wl.flop_per_record * (recs / args.steps) / (per_launch_ms * 1e-3) / 1e12,
+                    "fp32_tflops_achieved": wl.flop_per_record * (recs / args.steps / wl.launches_per_step) / (per_launch_ms * 1e-3) / 1e12,
                     "kernel_ms_per_launch": per_launch_ms}
         cpu = None
         if not args.no_cpu_baseline and world >= 1:
-            n_target = 1 << 22
+            n_target = 1 << 22 if isinstance(wl, ScoreWorkload) else 1 << 20
             n, dt, cores = wl.cpu_sample(n_target)
             rate = n / dt
             n2 = int(min(max(rate * args.cpu_seconds, n_target), 1 << 28))

@@ -207,3 +207,23 @@ def decode_score(model, records, csv_kinds=None, csv_defaults=None, avro_schema=
                                           rb.skip_prefix, C.byref(nm), float(threshold), _ffi.ptr(mse), _ffi.ptr(flag), _ffi.ptr(label),
                                           _ffi.ptr(status), _ffi.ptr(counters), _stream_ptr()), "b2_decode_score")
     return mse, flag, label, status
+
+
+def decode_score_host(model, data, offsets, csv_kinds=None, csv_defaults=None, avro_schema=None, threshold: float = 5.0,
+                      skip_prefix: int = 0):
+    """End-to-end form for HOST buffers (what a Kafka consumer hands over): ``data`` uint8 / ``offsets`` int32 as NumPy arrays
+    or (ideally pinned) CPU tensors → H2D copy → fused kernel → D2H of (mse f32[n], flag u8[n]) as NumPy arrays."""
+    dev = torch.device("cuda", torch.cuda.current_device())
+    d = data if isinstance(data, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(data, dtype=np.uint8))
+    o = offsets if isinstance(offsets, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(offsets, dtype=np.int32))
+    rb = RecordBatch(d, o, dev, skip_prefix=skip_prefix)
+    mse, flag, _, _ = decode_score(model, rb, csv_kinds=csv_kinds, csv_defaults=csv_defaults, avro_schema=avro_schema,
+                                   threshold=threshold)
+    n = rb.n
+    out = torch.empty(n * 5, dtype=torch.uint8).pin_memory() if n else torch.empty(0, dtype=torch.uint8)
+    hm = out[: n * 4].view(torch.float32)
+    hf = out[n * 4:]
+    hm.copy_(mse, non_blocking=True)
+    hf.copy_(flag, non_blocking=True)
+    torch.cuda.current_stream().synchronize()
+    return hm.numpy(), hf.numpy()

@@ -268,6 +268,10 @@ class Model:
                 inp = u
             self.n_params = n + self.units[-1] * self.features + self.features
 
+    def _ensure_built(self):
+        if not hasattr(self, "kind"):
+            self._analyse()  # raises NotImplementedError / ValueError for unsupported or incomplete stacks
+
     @property
     def input_dim(self):
         return self.widths[0] if self.kind == "dense" else self.features
@@ -380,6 +384,7 @@ class Model:
                      flag: Optional[torch.Tensor] = None, recon: Optional[torch.Tensor] = None,
                      counters: Optional[torch.Tensor] = None):
         """Enqueue the fused kernel on device buffers (no host sync). Returns (mse, flag)."""
+        self._ensure_built()
         if self.kind != "dense":
             raise TypeError("score is defined for the Dense autoencoder")
         n = x.shape[0]
@@ -409,6 +414,7 @@ class Model:
         """Forward pass over all rows; one kernel launch regardless of ``batch_size``.  ``callbacks`` get
         ``on_predict_batch_end(batch, {'outputs': [rows_of_that_batch]})`` per ``batch_size`` chunk (default 32) exactly as
         TF 2.0.0's predict loop feeds the reference's OutputCallback (cardata-v1.py:218-224)."""
+        self._ensure_built()
         dev = torch.device("cuda", self._device_index())
         xd = _to_device_f32(x, dev)
         if self.kind == "dense":
@@ -451,6 +457,7 @@ class Model:
         ``data_parallel=True`` under an initialised ``torch.distributed`` NCCL group (``x`` = this rank's shard,
         ``batch_size`` = per-rank batch), run the grid-wide gradient kernel, ONE all-reduce of the P+3 floats and the Adam
         kernel per step."""
+        self._ensure_built()
         if self.kind != "dense":
             raise NotImplementedError("fit is implemented for the Dense autoencoder (LSTM training is out of scope, SURVEY §8f.4)")
         if not self._compiled:

@@ -1,0 +1,66 @@
+"""K4 parity: LSTM stack forward against the CPU oracle (float64 shadow), tolerance 1e-4 (BASELINE.json north_star)."""
+import numpy as np
+import pytest
+
+import b200_sensor as bs
+from oracle import cpu_oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+
+def _lstm_model(look_back, features=18, seed=314):
+    k = bs.keras
+    m = k.models.Sequential(seed=seed)
+    m.add(k.layers.LSTM(32, activation="relu", input_shape=(look_back, features), return_sequences=True))
+    m.add(k.layers.LSTM(16, activation="relu", return_sequences=False))
+    m.add(k.layers.RepeatVector(look_back))
+    m.add(k.layers.LSTM(16, activation="relu", return_sequences=True))
+    m.add(k.layers.LSTM(32, activation="relu", return_sequences=True))
+    m.add(k.layers.TimeDistributed(k.layers.Dense(features)))
+    return m
+
+
+@pytest.mark.parametrize("batch,T", [(1, 1), (200, 1), (127, 4), (129, 16), (5000, 3)])
+def test_lstm_forward_matches_oracle(cuda_device, batch, T):
+    m = _lstm_model(T)
+    assert m.count_params() == 18642
+    w = m.get_flat_weights()
+    # make the recurrent path matter: scale up so that gates are not all near 0.5
+    g = np.random.default_rng(batch + T)
+    w = (w * g.uniform(0.5, 2.0, size=w.shape)).astype(np.float32)
+    m.set_flat_weights(w)
+    x = g.uniform(-1, 1, size=(batch, T, 18)).astype(np.float32)
+    x[:, :, [0, 2, 4, 5]] = 0.0  # the four features normalize_fn zeroes
+    y = m.predict(x)
+    ref = orc.lstm_forward(x, w, dtype=np.float64)
+    assert y.shape == (batch, T, 18)
+    np.testing.assert_allclose(y, ref, rtol=1e-4, atol=1e-4)
+    # and tighter against what float32 itself can do
+    assert np.abs(y - ref).max() < 2e-5
+
+
+def test_lstm_reference_usage_batch1_lookback1_with_callback(cuda_device):
+    """The script's shape: look_back = 1, batch_size = 1, predict 200 windows with the Kafka OutputCallback."""
+    m = _lstm_model(1)
+    x = np.random.default_rng(0).uniform(-1, 1, size=(200, 1, 18)).astype(np.float32)
+    got = []
+
+    class Out(bs.keras.callbacks.Callback):
+        def on_predict_batch_end(self, batch, logs=None):
+            index = batch * 1
+            for outputs in logs["outputs"]:
+                for output in outputs:
+                    got.append((index, np.array2string(output)))
+                    index += 1
+
+    y = m.predict(x, batch_size=1, callbacks=[Out()])
+    assert [i for i, _ in got] == list(range(200))
+    np.testing.assert_allclose(y, orc.lstm_forward(x, m.get_flat_weights(), dtype=np.float64), atol=1e-4)
+
+
+def test_lstm_rejects_other_stacks(cuda_device):
+    k = bs.keras
+    m = k.models.Sequential()
+    m.add(k.layers.LSTM(8, activation="tanh", input_shape=(1, 18)))
+    with pytest.raises(NotImplementedError):
+        m.predict(np.zeros((2, 1, 18), np.float32))
