@@ -229,6 +229,11 @@ class Model:
 
     # -- structure ---------------------------------------------------------------------------------
     def _analyse(self):
+        self._built = False
+        self._analyse_impl()
+        self._built = True
+
+    def _analyse_impl(self):
         ls = [l for l in self.layers if not isinstance(l, InputLayer)]
         self.kind = "lstm" if any(isinstance(l, LSTM) for l in ls) else "dense"
         if self.kind == "dense":
@@ -269,7 +274,7 @@ class Model:
             self.n_params = n + self.units[-1] * self.features + self.features
 
     def _ensure_built(self):
-        if not hasattr(self, "kind"):
+        if not getattr(self, "_built", False):
             self._analyse()  # raises NotImplementedError / ValueError for unsupported or incomplete stacks
 
     @property
