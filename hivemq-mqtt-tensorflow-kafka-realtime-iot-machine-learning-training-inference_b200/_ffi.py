@@ -15,6 +15,7 @@ LIB_PATH = os.path.join(HERE, "libb2sensor.so")
 
 MAX_WIDTH = 64
 MAX_FIELDS = 64
+NOALLOC_SCRATCH_FLOATS = 160 * 840  # B2_NOALLOC_SCRATCH_FLOATS
 
 ACT_CODES = {"linear": 0, "tanh": 1, "relu": 2}
 
@@ -86,6 +87,7 @@ _PROTOTYPES = {
     "b2_ae_grad_scratch_bytes": (C.c_int64, [_P, C.c_int64]),
     "b2_ae_grad": (C.c_int, [_P, _P, C.c_int64, C.POINTER(Norm), _P, _P, C.c_int64, _P]),
     "b2_ae_apply": (C.c_int, [_P, _P, C.POINTER(Adam), _P, _P]),
+    "b2_ae_grad_noalloc": (C.c_int, [_P, _P, C.c_int64, C.POINTER(Norm), _P, _P]),
     "b2_ae_get_adam": (C.c_int, [_P, _P, _P]),
     "b2_ae_set_adam": (C.c_int, [_P, _P, _P]),
     "b2_lstm_create": (C.c_int, [_P, C.POINTER(LstmDesc), _P, C.POINTER(_P)]),

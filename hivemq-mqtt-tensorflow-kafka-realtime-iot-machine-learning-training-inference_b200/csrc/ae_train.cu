@@ -15,6 +15,8 @@
 //  * ae_grad_kernel + ae_reduce_kernel + ae_apply_kernel — large batches / data parallel: a persistent grid computes
 //    per-CTA partial gradient sums (scratch[cta][P+3] in global memory), a second kernel folds the partials, the caller
 //    all-reduces the P+3 floats across ranks (NCCL) and ae_apply_kernel does the Adam step.
+#include <mutex>
+
 #include "ae_math.cuh"
 
 constexpr int FIT_NT = 256;     // threads of the fit CTA = max batch rows
@@ -600,4 +602,59 @@ extern "C" int b2_ae_apply(b2_ae* ae, const float* grads_dev, b2_adam* adam, flo
   adam->iter += 1;
   ae->host_stale = true;
   return B2_OK;
+}
+
+// ---- gradient sums without any allocation ------------------------------------------------------------------------------
+// Some hosts of this library are not allowed to allocate device memory while they run: a consumer loop that has handed
+// its whole memory budget to a pool at start-up, a real-time thread that must not take the driver's allocator lock, a
+// caller sitting inside someone else's memory manager whose cudaMalloc is simply off limits.  b2_ae_grad() needs a scratch
+// buffer from them; this variant brings its own: a fixed array that lives in the library's device image, so every GPU
+// that loads the library carries these B2_NOALLOC_SCRATCH_FLOATS * 4 bytes until the process exits.
+//
+// `g_noalloc_scratch` as spelled in host code is only a host-side handle for the symbol — handing it to a kernel would
+// make the kernel fault (or scribble over host memory where the GPU can reach it).  The real device address is looked up
+// once per device with cudaGetSymbolAddress while that device is current, and that address is what the kernel receives.
+static __device__ __align__(256) float g_noalloc_scratch[B2_NOALLOC_SCRATCH_FLOATS];
+
+static float* g_noalloc_ptr[64];
+static bool g_noalloc_ready[64];
+static std::mutex g_noalloc_mu;  // host threads of different devices may arrive at the same time
+
+static int noalloc_scratch_for_current_device(int device, float** out) {
+  B2_REQUIRE(device >= 0 && device < 64, "b2_ae_grad_noalloc: device index %d not supported", device);
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (!g_noalloc_ready[device]) {
+    float* p = nullptr;
+    B2_CUDA(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));  // device `device` is current here (DeviceGuard)
+    B2_REQUIRE(p != nullptr, "b2_ae_grad_noalloc: scratch symbol resolved to NULL");
+    g_noalloc_ptr[device] = p;
+    g_noalloc_ready[device] = true;
+  }
+  *out = g_noalloc_ptr[device];
+  return B2_OK;
+}
+
+extern "C" int b2_ae_grad_noalloc(b2_ae* ae, const float* x_dev, int64_t n, const b2_norm* norm, float* grads_dev, void* stream) {
+  B2_REQUIRE(ae && x_dev && grads_dev, "b2_ae_grad_noalloc: NULL argument");
+  B2_REQUIRE(n >= 1, "b2_ae_grad_noalloc: n=%lld < 1", (long long)n);
+  B2_REQUIRE(((uintptr_t)x_dev & 7) == 0, "b2_ae_grad_noalloc: x_dev must be 8-byte aligned");
+  B2_REQUIRE(!norm || norm->n == 0 || norm->n == ae->desc.widths[0], "b2_ae_grad_noalloc: norm table size mismatch");
+  if (ae->spec_d == 0) {
+    b2_set_error("b2_ae_grad_noalloc: training is implemented for the D-14-7-7-D autoencoder with D in {18, 30}");
+    return B2_EUNSUPPORTED;
+  }
+  const long long need = (long long)grad_grid(ae, n) * (ae->n_params + 3);
+  B2_REQUIRE(need <= (long long)B2_NOALLOC_SCRATCH_FLOATS,
+             "b2_ae_grad_noalloc: this launch needs %lld scratch floats (%d CTAs x %d), the built-in buffer holds %d; "
+             "use b2_ae_grad with caller-provided scratch",
+             need, grad_grid(ae, n), ae->n_params + 3, (int)B2_NOALLOC_SCRATCH_FLOATS);
+  DeviceGuard g(ae->ctx->device);
+  float* scratch = nullptr;
+  int rc = noalloc_scratch_for_current_device(ae->ctx->device, &scratch);
+  if (rc) return rc;
+  // Nothing in the buffer has to start at zero: every CTA of this launch overwrites its whole row before the fold reads
+  // exactly those rows, so whatever an earlier call left behind is never looked at.
+  cudaStream_t st = (cudaStream_t)stream;
+  if (ae->spec_d == 18) return grad_spec<18>(ae, x_dev, n, norm, grads_dev, scratch, st);
+  return grad_spec<30>(ae, x_dev, n, norm, grads_dev, scratch, st);
 }

@@ -152,6 +152,21 @@ int  b2_ae_grad(b2_ae* ae, const float* x_dev, int64_t n, const b2_norm* norm, f
                 void* scratch_dev, int64_t scratch_bytes, void* stream);
 int  b2_ae_apply(b2_ae* ae, const float* grads_dev, b2_adam* adam, float* loss_out_dev, void* stream);
 
+/* No counterpart in the reference.  Same result as b2_ae_grad for callers that may not allocate device memory while
+ * running (pre-budgeted memory pools, real-time loops that must stay off the allocator lock, hosts whose cudaMalloc is
+ * owned by another component): the per-CTA partial sums go to a fixed buffer inside the library image instead of a
+ * caller-supplied one, and the call itself performs no allocation of any kind.
+ *   - Limit: the launch may need at most B2_NOALLOC_SCRATCH_FLOATS floats (CTAs used x (parameters + 3)); anything larger
+ *     is refused with B2_EINVAL and a message — fall back to b2_ae_grad.  Every GPU that loads the library holds those
+ *     B2_NOALLOC_SCRATCH_FLOATS * 4 bytes until exit.
+ *   - The first call on each device resolves the buffer's device address (cudaGetSymbolAddress); make that first call
+ *     before starting any stream capture.
+ *   - All calls on a device share the one buffer and it keeps whatever the previous call wrote.  Nothing needs clearing
+ *     (each launch overwrites every slot it later reads), but two calls that overlap on the GPU — different streams, or
+ *     different b2_ae handles — race on it: serialise them. */
+#define B2_NOALLOC_SCRATCH_FLOATS (160 * 840)
+int  b2_ae_grad_noalloc(b2_ae* ae, const float* x_dev, int64_t n, const b2_norm* norm, float* grads_dev, void* stream);
+
 /* Adam slots (for .h5 save / resume; layout like the weights) */
 int  b2_ae_get_adam(b2_ae* ae, float* host_m, float* host_v);
 int  b2_ae_set_adam(b2_ae* ae, const float* host_m, const float* host_v);

@@ -1,0 +1,64 @@
+"""b2_ae_grad_noalloc: the gradient-sum entry point for callers that must not allocate device memory while running
+(fixed memory budgets, real-time consumer loops, hosts whose allocator belongs to someone else).  It keeps its scratch in
+a buffer built into the library, so it has to give the same numbers as b2_ae_grad with caller-provided scratch — on a
+first call and again on a second call that finds the first call's leftovers in the buffer.  Collected last on purpose
+(file name) so that a stop-at-first-failure run has already gone through every other test."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import b200_sensor as bs
+from b200_sensor import _ffi, synth
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def _grads_with_caller_scratch(l, h, P, xd, nm):
+    n = xd.shape[0]
+    nbytes = int(l.b2_ae_grad_scratch_bytes(h, n))
+    scratch = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+    g = torch.empty(P + 3, dtype=torch.float32, device="cuda")
+    _ffi.check(l.b2_ae_grad(h, xd.data_ptr(), n, C.byref(nm), g.data_ptr(), scratch.data_ptr(), nbytes, None), "b2_ae_grad")
+    torch.cuda.synchronize()
+    return g.cpu().numpy()
+
+
+def test_noalloc_matches_b2_ae_grad_on_two_calls_in_a_row(cuda_device):
+    l = _ffi.lib()
+    m = bs.keras.models.load_model(os.path.join(GOLDEN, "ae30_5epochs.h5"))
+    h, P = m._handle(), m.n_params
+    nm = _ffi.make_norm()
+    # two different batches: a large one (all 148 CTAs write their slots) then a small one (few CTAs, so most of the
+    # buffer still holds the first call's partial sums and must be ignored)
+    for n, seed in ((200_003, 1), (1_000, 2)):
+        x = synth.credit_rows(n, seed=seed)
+        xd = torch.from_numpy(x).cuda()
+        ref = _grads_with_caller_scratch(l, h, P, xd, nm)
+        got = torch.empty(P + 3, dtype=torch.float32, device="cuda")
+        torch.cuda.synchronize()
+        free_before, _ = torch.cuda.mem_get_info()
+        _ffi.check(l.b2_ae_grad_noalloc(h, xd.data_ptr(), n, C.byref(nm), got.data_ptr(), None), "b2_ae_grad_noalloc")
+        torch.cuda.synchronize()
+        free_after, _ = torch.cuda.mem_get_info()
+        if seed == 2:  # set-up is behind us on the second call: the device's free memory must not have moved
+            assert free_after >= free_before
+        # same tolerance as tests/test_train_gpu.py uses for gradient sums
+        np.testing.assert_allclose(got.cpu().numpy(), ref, rtol=2e-4, atol=2e-7)
+        assert got.cpu().numpy()[P + 2] == n
+
+
+def test_noalloc_refuses_what_does_not_fit(cuda_device):
+    l = _ffi.lib()
+    m = bs.keras.models.load_model(os.path.join(GOLDEN, "ae30_5epochs.h5"))
+    h, P = m._handle(), m.n_params
+    assert 148 * (P + 3) <= _ffi.NOALLOC_SCRATCH_FLOATS  # a B200 launch always fits; the check guards bigger parts
+    nm = _ffi.make_norm()
+    g = torch.empty(P + 3, dtype=torch.float32, device="cuda")
+    x = torch.zeros((4, 30), dtype=torch.float32, device="cuda")
+    assert l.b2_ae_grad_noalloc(h, x.data_ptr(), 0, C.byref(nm), g.data_ptr(), None) == -1   # n < 1
+    assert l.b2_ae_grad_noalloc(h, None, 4, C.byref(nm), g.data_ptr(), None) == -1           # NULL input
+    assert b"b2_ae_grad_noalloc" in l.b2_last_error()
