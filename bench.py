@@ -332,7 +332,7 @@ WORKLOADS = {
     "avro_a": lambda: DecodeScoreWorkload("avro_a", batches_per_step=8),
     "avro_b": lambda: DecodeScoreWorkload("avro_b"),
 }
-DEFAULT_WORKLOAD = "score30"
+DEFAULT_WORKLOAD = "avro_a"   # decode+score on the schema BASELINE.json names (testdata/cardata-v1.avsc)
 
 
 # ------------------------------------------------------------------------------------------------------------
@@ -368,6 +368,8 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target wall time of the cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--also", default=None, help="comma list of further workloads to measure (device-resident value only); "
+                                                 "default: all others at N=1, none under torchrun")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
@@ -454,6 +456,7 @@ def main():
 
     if rank == 0:
         peak, peak_src = load_peaks()
+        config = wl.describe()
         per_launch_ms = ms_local / (args.steps * wl.launches_per_step)
         achieved = wl.bytes_per_record * (recs / args.steps / wl.launches_per_step) / (per_launch_ms * 1e-3) / 1e9
         traffic = load_traffic(wl.kernel_key)
@@ -472,10 +475,37 @@ def main():
             n, dt, cores = wl.cpu_sample(n2)
             cpu = {"value": n / dt, "unit": UNIT, "cores": cores, "kind": "port",
                    "sample": f"{n} records of the same workload through oracle/oracle.c (OpenMP, all host threads), {dt:.1f} s"}
+        launches = args.steps * wl.launches_per_step
+        also = {}
+        names = [w for w in WORKLOADS if w != args.workload] if (args.also is None and world == 1) else \
+            [w for w in (args.also or "").split(",") if w]
+        import gc
+
+        wl = None  # free the headline workload's device buffers before measuring the others
+        for nm in names:
+            gc.collect()
+            torch.cuda.empty_cache()
+            w2 = WORKLOADS[nm]()
+            w2.setup(dev, rank)
+            for i in range(3):
+                w2.step(i)
+            torch.cuda.synchronize()
+            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a0.record()
+            r2 = 0
+            for i in range(args.steps):
+                r2 += w2.step(3 + i)
+            a1.record()
+            torch.cuda.synchronize()
+            t2 = a0.elapsed_time(a1) * 1e-3
+            also[w2.name] = {"value": r2 / t2, "unit": UNIT, "hbm_frac": w2.bytes_per_record * r2 / t2 / 1e9 / peak,
+                             "algorithmic_bytes_per_record": w2.bytes_per_record,
+                             "fp32_tflops": w2.flop_per_record * r2 / t2 / 1e12}
+            w2 = None
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-                "data": "synthetic", "config": wl.describe(), "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
-                "gpu_launches": args.steps * wl.launches_per_step, "clocks": clocks,
+                "data": "synthetic", "config": config, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
+                "gpu_launches": launches, "clocks": clocks, "also": also,
                 "counters": {"records": counters[0], "flagged": counters[1], "decode_errors": counters[2], "bytes": counters[3]}}
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -9,16 +9,17 @@
 // `int32 offsets[n+1]`.  A persistent CTA walks tiles of TILE = 2*NT consecutive records.  The bytes of (a prefix of) the
 // tile are one contiguous range, fetched by ONE 1-D bulk async copy (TMA engine) into shared memory — sub-tiled when
 // the records are long (credit-card CSV ≈ 550 B/record) so that a sub-tile never exceeds STAGE_CAP bytes.
-//   phase A  thread-per-record   CSV: SWAR delimiter scan → field-begin table (u16) in smem;  Avro: the whole varint walk
-//   phase B  thread-per-field    CSV only: Eisel-Lemire parse of one token → f32 tile in smem
-//   phase C  thread-per-2-records  fused normalise → Dense stack → MSE → flag (ae_math.cuh), or coalesced tile write-out
+//   phase A  thread-per-record   CSV: SWAR delimiter scan → field-begin table (u16) in smem;  Avro: the whole walk (uniform
+//                                field type across the warp, unaligned 32-bit loads) → f32 tile
+//   phase B  thread-per-field    CSV only: registers-only digit scan + Eisel-Lemire → f32 tile
+//   phase C  thread-per-record   fused normalise → Dense stack → MSE → flag (ae_math.cuh), or coalesced tile write-out
 // Algorithmic bytes/record: payload + 4 (offset) read, 5 written (fused) or 4*F + 4 written (decode only).
 #include "ae_math.cuh"
 #include "float_parse.cuh"
 
-constexpr int DEC_NT = 128;
-constexpr int DEC_TILE = 2 * DEC_NT;
-constexpr int STAGE_CAP = 48 * 1024;  // bytes of payload staged per sub-tile
+constexpr int DEC_NT = 256;
+constexpr int DEC_TILE = 256;
+constexpr int STAGE_CAP_MAX = 48 * 1024;  // most bytes of payload staged per sub-tile (the launch may choose less)
 
 enum { FMT_CSV = 0, FMT_AVRO = 1 };
 enum { AV_INT = 1, AV_LONG, AV_FLOAT, AV_DOUBLE, AV_STRING, AV_BOOLEAN, AV_BYTES, AV_NULL };
@@ -32,7 +33,7 @@ struct CsvP {
   float dflt[B2_MAX_FIELDS];
 };
 struct AvroP {
-  int32_t n_fields, n_out, skip_prefix, pad;
+  int32_t n_fields, n_out, skip_prefix, all_routed;  // all_routed: every output column is written by some field
   b2_avro_field f[B2_MAX_FIELDS];
 };
 
@@ -43,6 +44,7 @@ struct DecodeArgs {
   long long n;
   int fmt;
   int n_out;            // floats per record produced by the decode (== D when scoring)
+  int stage_cap;        // bytes of the shared-memory byte stage chosen for this launch
   CsvP csv;
   AvroP avro;
   // decode-only outputs
@@ -138,72 +140,159 @@ __device__ __forceinline__ int csv_scan(const uint8_t* base, int b, int e, const
   return B2_REC_OK;
 }
 
-// ---- Avro: one record, thread-sequential -----------------------------------------------------------------------
-__device__ __forceinline__ bool av_varint(const uint8_t* base, int& p, int e, int max_bytes, long long* v) {
+// ---- CSV phase B: one float token, registers only ----------------------------------------------------------------------
+// Fast path for what sensor producers write (Java Float.toString): [-]digits[.digits][E[-]d[d]], at most 16 bytes and 9
+// mantissa digits.  The 16 bytes are pulled into registers with 5 aligned 32-bit loads + funnel shifts and walked by a fully
+// unrolled, branch-free state machine (no per-byte shared-memory round trip, no divergence on token length), then rounded by
+// the same Eisel-Lemire routine as the general parser.  Anything else returns false and takes b2_parse_float().
+__device__ __forceinline__ bool csv_fast_token(const uint8_t* __restrict__ st, int b, int L, uint32_t* bits) {
+  if (L < 1 || L > 16) return false;
+  const uint32_t* wp = reinterpret_cast<const uint32_t*>(st + (b & ~3));
+  const int sh = (b & 3) * 8;
+  const uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2], w3 = wp[3], w4 = wp[4];
+  const uint32_t t[4] = {__funnelshift_r(w0, w1, sh), __funnelshift_r(w1, w2, sh), __funnelshift_r(w2, w3, sh), __funnelshift_r(w3, w4, sh)};
+  uint32_t w = 0;          // mantissa (≤ 9 digits fits 32 bits)
+  int nd = 0;              // mantissa digits seen (leading zeros excluded once w != 0 … counted via w)
+  int q = 0;               // decimal exponent adjustment from fraction digits
+  int ex = 0, exd = 0;     // explicit exponent and its digit count
+  bool ok = true, neg = false, eneg = false, dot = false, in_exp = false, any = false;
+#pragma unroll
+  for (int k = 0; k < 16; ++k) {
+    const uint32_t c = (t[k >> 2] >> ((k & 3) * 8)) & 0xFFu;
+    const bool live = k < L;
+    const uint32_t d = c - '0';
+    const bool isd = d < 10u;
+    if (live) {
+      if (isd) {
+        if (!in_exp) {
+          nd += (w != 0u || d != 0u) ? 1 : 0;
+          w = w * 10u + d;
+          q -= dot ? 1 : 0;
+          any = true;
+        } else {
+          ex = ex * 10 + (int)d;
+          ++exd;
+        }
+      } else if (c == '.') {
+        ok = ok && !dot && !in_exp;
+        dot = true;
+      } else if ((c | 0x20u) == 'e') {
+        ok = ok && !in_exp && any;
+        in_exp = true;
+      } else if (c == '-') {
+        if (k == 0) neg = true;
+        else {
+          ok = ok && in_exp && exd == 0 && !eneg;
+          eneg = true;
+        }
+      } else {
+        ok = false;
+      }
+    }
+  }
+  ok = ok && any && nd <= 9 && (!in_exp || (exd >= 1 && exd <= 2));
+  // a '-' right after 'E' is only legal directly after it: "1E5-" is caught by exd == 0 at that point; "1E-" by exd >= 1
+  if (!ok) return false;
+  q += eneg ? -ex : ex;
+  *bits = (neg ? 0x80000000u : 0u) | b2_eisel_lemire32((uint64_t)w, q);
+  return true;
+}
+
+// ---- Avro: one record per thread, whole walk -------------------------------------------------------------------------------
+// Every thread of a warp is at the same field of its own record, so the field descriptor is a uniform constant-bank read and
+// the type switch does not diverge; values are fetched with two aligned 32-bit loads + a funnel shift instead of byte loads.
+__device__ __forceinline__ uint32_t lds_u32_unaligned(const uint8_t* __restrict__ st, int off) {
+  const uint32_t* wp = reinterpret_cast<const uint32_t*>(st + (off & ~3));
+  return __funnelshift_r(wp[0], wp[1], (off & 3) * 8);
+}
+
+// zig-zag varint of more than two bytes (rare: |value| ≥ 8192)
+__device__ __noinline__ int av_varint_long(const uint8_t* base, int p, int e, int max_bytes, long long* v) {
   unsigned long long u = 0;
   int shift = 0;
   for (int k = 0; k < max_bytes; ++k) {
-    if (p >= e) return false;
+    if (p >= e) return -1;
     const uint8_t b = base[p++];
     u |= (unsigned long long)(b & 0x7F) << shift;
     shift += 7;
     if (!(b & 0x80)) {
       *v = (long long)(u >> 1) ^ -(long long)(u & 1);
-      return true;
+      return p;
     }
   }
-  return false;
+  return -1;
+}
+// returns the new position or -1; *v32 receives the value when it fits two bytes (the common case), else *v64 / wide = true
+__device__ __forceinline__ int av_varint(const uint8_t* base, int p, int e, int max_bytes, int* v32, long long* v64, bool* wide) {
+  *wide = false;
+  const uint32_t w = lds_u32_unaligned(base, p);
+  const uint32_t b0 = w & 0xFFu, b1 = (w >> 8) & 0xFFu;
+  if (b0 < 0x80u) {
+    *v32 = (int)(b0 >> 1) ^ -(int)(b0 & 1u);
+    return p + 1 <= e ? p + 1 : -1;
+  }
+  if (b1 < 0x80u) {
+    const uint32_t u = (b0 & 0x7Fu) | (b1 << 7);
+    *v32 = (int)(u >> 1) ^ -(int)(u & 1u);
+    return p + 2 <= e ? p + 2 : -1;
+  }
+  *wide = true;
+  return av_varint_long(base, p, e, max_bytes, v64);
 }
 
-__device__ __forceinline__ int avro_decode_record(const uint8_t* base, int p, int e, const AvroP& a, float* xrow, uint8_t* label) {
+__device__ __forceinline__ int avro_decode_record(const uint8_t* __restrict__ base, int p, int e, const AvroP& a, float* __restrict__ xrow,
+                                                  uint8_t* label) {
   uint8_t lab_out = 2;
   p += a.skip_prefix;
   if (p > e) return B2_REC_TRUNCATED;
   for (int i = 0; i < a.n_fields; ++i) {
     const int type = a.f[i].type, nullable = a.f[i].nullable, oc = a.f[i].out;
-    bool present = true;
-    long long v;
+    bool present = true, wide;
+    int v32 = 0;
+    long long v64 = 0;
     if (nullable) {
-      if (!av_varint(base, p, e, 10, &v)) return B2_REC_TRUNCATED;
-      if (v != 0 && v != 1) return B2_REC_BAD_BRANCH;
-      present = v != (nullable == 1 ? 0 : 1);
+      p = av_varint(base, p, e, 10, &v32, &v64, &wide);
+      if (p < 0) return B2_REC_TRUNCATED;
+      if (wide || (v32 != 0 && v32 != 1)) return B2_REC_BAD_BRANCH;
+      present = v32 != (nullable == 1 ? 0 : 1);
     }
     float val = 0.0f;
     uint8_t lab = 2;
     if (present) {
       if (type == AV_FLOAT) {
-        if (p + 4 > e) return B2_REC_TRUNCATED;
-        const uint32_t bits = (uint32_t)base[p] | ((uint32_t)base[p + 1] << 8) | ((uint32_t)base[p + 2] << 16) | ((uint32_t)base[p + 3] << 24);
-        val = __uint_as_float(bits);
+        val = __uint_as_float(lds_u32_unaligned(base, p));
         p += 4;
       } else if (type == AV_DOUBLE) {
-        if (p + 8 > e) return B2_REC_TRUNCATED;
-        unsigned long long bits = 0;
-#pragma unroll
-        for (int k = 0; k < 8; ++k) bits |= (unsigned long long)base[p + k] << (8 * k);
+        const unsigned long long bits =
+            (unsigned long long)lds_u32_unaligned(base, p) | ((unsigned long long)lds_u32_unaligned(base, p + 4) << 32);
         val = __double2float_rn(__longlong_as_double((long long)bits));  // one rounding, like Keras' float32 input cast
         p += 8;
-      } else if (type == AV_INT) {
-        if (!av_varint(base, p, e, 5, &v)) return B2_REC_TRUNCATED;
-        val = __int2float_rn((int)v);  // tf.cast(int32 → float32), cardata-v1.py:61-66
-      } else if (type == AV_LONG) {
-        if (!av_varint(base, p, e, 10, &v)) return B2_REC_TRUNCATED;
-        val = __ll2float_rn(v);
+      } else if (type == AV_INT || type == AV_LONG) {
+        p = av_varint(base, p, e, type == AV_INT ? 5 : 10, &v32, &v64, &wide);
+        if (p < 0) return B2_REC_TRUNCATED;
+        // tf.cast(int32 → float32), cardata-v1.py:61-66
+        val = !wide ? __int2float_rn(v32) : (type == AV_INT ? __int2float_rn((int)v64) : __ll2float_rn(v64));
       } else if (type == AV_BOOLEAN) {
-        if (p + 1 > e) return B2_REC_TRUNCATED;
-        val = base[p++] ? 1.0f : 0.0f;
+        val = base[p] ? 1.0f : 0.0f;
+        p += 1;
       } else if (type == AV_STRING || type == AV_BYTES) {
-        if (!av_varint(base, p, e, 10, &v) || v < 0 || (long long)p + v > e) return B2_REC_TRUNCATED;
-        const int L = (int)v;
-        if (L == 5 && base[p] == 'f' && base[p + 1] == 'a' && base[p + 2] == 'l' && base[p + 3] == 's' && base[p + 4] == 'e') lab = 0;
-        else if (L == 4 && base[p] == 't' && base[p + 1] == 'r' && base[p + 2] == 'u' && base[p + 3] == 'e') lab = 1;
+        p = av_varint(base, p, e, 10, &v32, &v64, &wide);
+        if (p < 0) return B2_REC_TRUNCATED;
+        const long long L = wide ? v64 : (long long)v32;
+        if (L < 0 || (long long)p + L > e) return B2_REC_TRUNCATED;
+        const uint32_t c4 = lds_u32_unaligned(base, p);
+        if (L == 5 && c4 == 0x736C6166u && base[p + 4] == 'e') lab = 0;  // "fals" + "e"
+        else if (L == 4 && c4 == 0x65757274u) lab = 1;                   // "true"
         else lab = L == 0 ? 2 : 3;
-        p += L;
+        p += (int)L;
       }
+      // fixed-size fields are not bounds-checked one by one: the walk can overshoot `e` by at most a few hundred bytes
+      // (≤ 10 per field), which stays inside this CTA's shared memory, and the final check below rejects the record
     }
     if (oc >= 0) xrow[oc] = val;
     else if (oc == -2) lab_out = lab;
   }
+  if (p > e) return B2_REC_TRUNCATED;
   *label = lab_out;
   return B2_REC_OK;
 }
@@ -213,15 +302,22 @@ __device__ __forceinline__ int avro_decode_record(const uint8_t* base, int p, in
 template <int D, int MODE, bool FT>
 __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ DecodeArgs<D> a) {
   extern __shared__ __align__(128) uint8_t smem[];
-  // carve: [stage bytes | offsets (TILE+1) | status (TILE) | label (TILE) | qmask (TILE) | fb (TILE*(nf+1)) | xt (TILE*stride)]
+  // carve: [stage bytes | offsets (TILE+1) | status (TILE) | qmask/present (TILE) | label (TILE) | mbarrier | fb | xt]
   uint8_t* stage = smem;
-  int32_t* s_offs = reinterpret_cast<int32_t*>(smem + STAGE_CAP + 64);
+  int32_t* s_offs = reinterpret_cast<int32_t*>(smem + a.stage_cap + 64);
   int32_t* s_stat = s_offs + DEC_TILE + 4;
   unsigned long long* s_qm = reinterpret_cast<unsigned long long*>(s_stat + DEC_TILE);
   uint8_t* s_lab = reinterpret_cast<uint8_t*>(s_qm + DEC_TILE);
   uint64_t* full = reinterpret_cast<uint64_t*>(s_lab + DEC_TILE);
   const int fb_stride = a.fmt == FMT_CSV ? a.csv.n_fields + 1 : 0;
-  uint16_t* s_fb = reinterpret_cast<uint16_t*>(full + 2);
+  // per-field tables re-staged in shared memory: phase B indexes them with a per-thread field number, and a divergent
+  // index into the constant bank (kernel parameters) is serialised address by address
+  uint8_t* t_kind = reinterpret_cast<uint8_t*>(full + 2);  // CSV kind / Avro type
+  uint8_t* t_col = t_kind + 64;                            // output column (Avro: int8 out)
+  uint8_t* t_fidx = t_col + 64;                            // k-th value-producing field → field index
+  uint8_t* t_hasd = t_fidx + 64;                           // CSV has_default
+  float* t_dflt = reinterpret_cast<float*>(t_hasd + 64);   // CSV default value
+  uint16_t* s_fb = reinterpret_cast<uint16_t*>(t_dflt + 64);
   const int xt_stride = MODE == 1 ? D : a.n_out;
   float* s_xt = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(s_fb) + (((size_t)DEC_TILE * fb_stride * 2 + 15) & ~(size_t)15));
 
@@ -229,6 +325,18 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
   if (tid == 0) {
     mbar_init(&full[0], 1);
     mbar_fence_init();
+  }
+  if (tid < 64) {
+    if (a.fmt == FMT_CSV) {
+      t_kind[tid] = a.csv.kind[tid];
+      t_col[tid] = a.csv.col[tid];
+      t_fidx[tid] = a.csv.fidx[tid];
+      t_hasd[tid] = a.csv.has_default[tid];
+      t_dflt[tid] = a.csv.dflt[tid];
+    } else {
+      t_kind[tid] = (uint8_t)a.avro.f[tid].type;
+      t_col[tid] = (uint8_t)a.avro.f[tid].out;
+    }
   }
   __syncthreads();
   uint32_t phase = 0;
@@ -247,13 +355,9 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
       const long long b_abs = s_offs[sub];
       const uintptr_t a0 = (reinterpret_cast<uintptr_t>(a.bytes) + (uintptr_t)b_abs) & ~(uintptr_t)15;
       const int lead = (int)((reinterpret_cast<uintptr_t>(a.bytes) + (uintptr_t)b_abs) - a0);
-      int fit = 0;
-#pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const int r = sub + tid + h * DEC_NT;
-        if (r < rows) fit += (long long)s_offs[r + 1] - b_abs + lead <= (long long)STAGE_CAP;
-      }
-      const int cnt = __syncthreads_count(fit) + __syncthreads_count(fit > 1);  // records are monotone: count of fitting ones
+      const int rr = sub + tid;
+      const int fit = rr < rows && (long long)s_offs[rr + 1] - b_abs + lead <= (long long)a.stage_cap;
+      const int cnt = __syncthreads_count(fit);  // record ends are monotone: this is the number of records that fit
       if (cnt == 0) {  // a single record larger than the stage: refuse it, keep going
         if (tid == 0) {
           const long long r = row0 + sub;
@@ -282,104 +386,98 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
       phase ^= 1u;
       const int rel = lead - (int)b_abs;  // stage offset of absolute byte x is x + rel
 
-      // ---- phase A ----
-#pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const int r = tid + h * DEC_NT;  // index inside the sub-tile
-        if (r < cnt) {
-          const int b = s_offs[sub + r] + rel, e = s_offs[sub + r + 1] + rel;
-          int st;
-          if (a.fmt == FMT_CSV) {
-            st = csv_scan(stage, b, e, a.csv, s_fb + (size_t)r * fb_stride, &s_qm[r]);
-          } else {
-            float* xrow = s_xt + (size_t)r * xt_stride;
-            for (int j = 0; j < xt_stride; ++j) xrow[j] = 0.0f;
-            uint8_t lab = 2;
-            st = avro_decode_record(stage, b, e, a.avro, xrow, &lab);
-            s_lab[r] = lab;
+      // ---- phase A: one record per thread → field-begin table ----
+      if (tid < cnt) {
+        const int b = s_offs[sub + tid] + rel, e = s_offs[sub + tid + 1] + rel;
+        int st;
+        uint8_t lab = 2;
+        if (a.fmt == FMT_CSV) {
+          st = csv_scan(stage, b, e, a.csv, s_fb + (size_t)tid * fb_stride, &s_qm[tid]);
+        } else {
+          float* xrow = s_xt + (size_t)tid * xt_stride;
+          if (!a.avro.all_routed)
+            for (int j = 0; j < xt_stride; ++j) xrow[j] = 0.0f;  // columns no field routes to
+          st = avro_decode_record(stage, b, e, a.avro, xrow, &lab);
+        }
+        s_stat[tid] = st;
+        s_lab[tid] = lab;
+      }
+      __syncthreads();
+      // ---- phase B: one task per (record, value-producing field) ----
+      if (a.fmt == FMT_CSV) {  // (Avro needs no phase B: its walk already produced the values)
+        // flat (record, field) tasks; (r, k) advance incrementally by DEC_NT tasks — no division in the loop
+        const int per_rec = a.csv.n_float + a.csv.n_str;
+        const int dq = DEC_NT / per_rec, dr = DEC_NT - dq * per_rec;
+        int r = tid / per_rec, k = tid - r * per_rec;
+        {
+          for (; r < cnt; r += dq, k += dr, r += (k >= per_rec), k -= (k >= per_rec) ? per_rec : 0) {
+            if (s_stat[r] != B2_REC_OK) continue;
+            const int f = t_fidx[k];
+            const uint16_t* fb = s_fb + (size_t)r * fb_stride;
+            // a quoted field's payload sits between its quotes: drop its closing quote and, when the NEXT field is quoted
+            // too, that field's opening quote (fb[] holds payload starts)
+            const unsigned long long qm = s_qm[r];
+            const int quoted = (int)((qm >> f) & 1ull) + (int)((qm >> (f + 1)) & 1ull);
+            const int fbeg = fb[f], fend = (int)fb[f + 1] - 1 - quoted;
+            if (t_kind[f] == 1) {
+              float v;
+              int st = B2_REC_OK;
+              if (fend <= fbeg) {
+                if (t_hasd[f]) v = t_dflt[f];
+                else st = B2_REC_EMPTY_FIELD, v = 0.f;
+              } else {
+                uint32_t bits = 0;
+                if (!csv_fast_token(stage, fbeg, fend - fbeg, &bits)) {
+                  const int ps = b2_parse_float(stage + fbeg, fend - fbeg, &bits);
+                  if (ps == B2_NUM_BAD) st = B2_REC_BAD_NUMBER;
+                  else if (ps == B2_NUM_TOO_LONG) st = B2_REC_TOO_LONG;
+                }
+                v = __uint_as_float(bits);
+              }
+              if (st != B2_REC_OK) atomicMax(&s_stat[r], st);
+              s_xt[(size_t)r * xt_stride + t_col[f]] = v;
+            } else if (MODE == 0 && a.span) {
+              int32_t* sp = a.span + ((row0 + sub + r) * a.csv.n_str + t_col[f]) * 2;
+              sp[0] = fbeg - rel;
+              sp[1] = fend - rel;
+            }
           }
-          s_stat[r] = st;
         }
       }
       __syncthreads();
-      // ---- phase B (CSV): one task per (record, float/string field) ----
-      if (a.fmt == FMT_CSV) {
-        const int per_rec = a.csv.n_float + a.csv.n_str;
-        for (int t = tid; t < cnt * per_rec; t += DEC_NT) {
-          const int r = t / per_rec, k = t - r * per_rec;
-          if (s_stat[r] != B2_REC_OK) continue;
-          const int f = a.csv.fidx[k];
-          const uint16_t* fb = s_fb + (size_t)r * fb_stride;
-          // a quoted field's payload sits between its quotes: drop its closing quote and, when the NEXT field is quoted
-          // too, that field's opening quote (fb[] holds payload starts)
-          const int quoted = (int)((s_qm[r] >> f) & 1ull) + (int)((s_qm[r] >> (f + 1)) & 1ull);
-          const int fbeg = fb[f], fend = (int)fb[f + 1] - 1 - quoted;
-          if (a.csv.kind[f] == 1) {
-            float v;
-            int st = B2_REC_OK;
-            if (fend <= fbeg) {
-              if (a.csv.has_default[f]) v = a.csv.dflt[f];
-              else st = B2_REC_EMPTY_FIELD, v = 0.f;
-            } else {
-              uint32_t bits = 0;
-              const int ps = b2_parse_float(stage + fbeg, fend - fbeg, &bits);
-              v = __uint_as_float(bits);
-              if (ps == B2_NUM_BAD) st = B2_REC_BAD_NUMBER;
-              else if (ps == B2_NUM_TOO_LONG) st = B2_REC_TOO_LONG;
-            }
-            if (st != B2_REC_OK) atomicMax(&s_stat[r], st);
-            s_xt[(size_t)r * xt_stride + a.csv.col[f]] = v;
-          } else if (MODE == 0 && a.span) {
-            int32_t* sp = a.span + ((row0 + sub + r) * a.csv.n_str + a.csv.col[f]) * 2;
-            sp[0] = fbeg - rel;
-            sp[1] = fend - rel;
-          }
-        }
-        __syncthreads();
-      }
       // ---- phase C ----
       if (MODE == 1) {
-        const bool va = tid < cnt, vb = tid + DEC_NT < cnt;
-        float* const rowp[2] = {s_xt + (size_t)tid * D, s_xt + (size_t)(tid + DEC_NT) * D};
-        float mm[2] = {0.f, 0.f};
+        const bool va = tid < cnt;
+        float* const rowp[1] = {s_xt + (size_t)tid * D};
+        float mm[1] = {0.f};
         if (va) {
-          if (a.has_norm) ae_forward_rows<D, 2, true, false, FT>(a.w, a.nm, rowp, mm);
-          else ae_forward_rows<D, 2, false, false, FT>(a.w, a.nm, rowp, mm);
-        }
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          const int r = tid + h * DEC_NT;
-          if (r < cnt) {
-            const long long gr = row0 + sub + r;
-            const int st = s_stat[r];
-            float m = mm[h];
-            if (st != B2_REC_OK) m = __int_as_float(0x7FC00000);
-            const bool f = m > a.threshold;
-            if (a.mse) a.mse[gr] = m;
-            if (a.flag) a.flag[gr] = f ? 1 : 0;
-            if (a.status) a.status[gr] = st;
-            if (a.label) a.label[gr] = a.fmt == FMT_AVRO && st == B2_REC_OK ? s_lab[r] : 2;
-            flagged += f;
-            n_ok += st == B2_REC_OK;
-            n_err += st != B2_REC_OK;
-          }
+          if (a.has_norm) ae_forward_rows<D, 1, true, false, FT>(a.w, a.nm, rowp, mm);
+          else ae_forward_rows<D, 1, false, false, FT>(a.w, a.nm, rowp, mm);
+          const long long gr = row0 + sub + tid;
+          const int st = s_stat[tid];
+          float m = mm[0];
+          if (st != B2_REC_OK) m = __int_as_float(0x7FC00000);
+          const bool f = m > a.threshold;
+          if (a.mse) a.mse[gr] = m;
+          if (a.flag) a.flag[gr] = f ? 1 : 0;
+          if (a.status) a.status[gr] = st;
+          if (a.label) a.label[gr] = a.fmt == FMT_AVRO && st == B2_REC_OK ? s_lab[tid] : 2;
+          flagged += f;
+          n_ok += st == B2_REC_OK;
+          n_err += st != B2_REC_OK;
         }
       } else {
         for (int i = tid; i < cnt * xt_stride; i += DEC_NT) {
           const int r = i / xt_stride;
           a.out[(row0 + sub) * xt_stride + i] = s_stat[r] == B2_REC_OK ? s_xt[i] : __int_as_float(0x7FC00000);
         }
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          const int r = tid + h * DEC_NT;
-          if (r < cnt) {
-            const long long gr = row0 + sub + r;
-            const int st = s_stat[r];
-            if (a.status) a.status[gr] = st;
-            if (a.label) a.label[gr] = a.fmt == FMT_AVRO && st == B2_REC_OK ? s_lab[r] : 2;
-            n_ok += st == B2_REC_OK;
-            n_err += st != B2_REC_OK;
-          }
+        if (tid < cnt) {
+          const long long gr = row0 + sub + tid;
+          const int st = s_stat[tid];
+          if (a.status) a.status[gr] = st;
+          if (a.label) a.label[gr] = a.fmt == FMT_AVRO && st == B2_REC_OK ? s_lab[tid] : 2;
+          n_ok += st == B2_REC_OK;
+          n_err += st != B2_REC_OK;
         }
       }
       __syncthreads();  // stage, tables and tile are free again
@@ -435,26 +533,56 @@ static int fill_avro(const b2_avro_prog* p, int skip_prefix, AvroP& a) {
     B2_REQUIRE(p->f[i].out < p->n_out, "avro: field %d routed to column %d >= n_out", i, p->f[i].out);
     a.f[i] = p->f[i];
   }
+  unsigned long long routed = 0;
+  for (int i = 0; i < p->n_fields; ++i)
+    if (p->f[i].out >= 0) routed |= 1ull << p->f[i].out;
+  a.all_routed = routed == (p->n_out >= 64 ? ~0ull : ((1ull << p->n_out) - 1));
   return B2_OK;
 }
 
-static size_t decode_smem_bytes(int fb_stride, int xt_stride) {
-  size_t s = STAGE_CAP + 64;
+// Upper bound of an Avro record's size when the schema has no strings/bytes (else 0 = unbounded)
+static int avro_max_record_bytes(const AvroP& a) {
+  int n = a.skip_prefix;
+  for (int i = 0; i < a.n_fields; ++i) {
+    if (a.f[i].nullable) n += 1;
+    switch (a.f[i].type) {
+      case AV_FLOAT: n += 4; break;
+      case AV_DOUBLE: n += 8; break;
+      case AV_BOOLEAN: n += 1; break;
+      case AV_INT: n += 5; break;
+      case AV_LONG: n += 10; break;
+      case AV_NULL: break;
+      default: return 0;
+    }
+  }
+  return n;
+}
+
+static size_t decode_smem_bytes(int stage_cap, int fb_stride, int xt_stride) {
+  size_t s = (size_t)stage_cap + 64;
   s += sizeof(int32_t) * (DEC_TILE + 4);           // offsets
   s += sizeof(int32_t) * DEC_TILE;                 // status
   s += sizeof(unsigned long long) * DEC_TILE;      // qmask
   s += DEC_TILE;                                   // label
   s += 2 * sizeof(uint64_t);                       // mbarrier
+  s += 4 * 64 + 64 * sizeof(float);                // per-field tables
   s += ((size_t)DEC_TILE * fb_stride * 2 + 15) & ~(size_t)15;
   s += (size_t)DEC_TILE * xt_stride * 4;
   return s + 64;
 }
 
 template <int D, int MODE, bool FT>
-static int launch_decode(b2_ctx* ctx, const DecodeArgs<D>& args, cudaStream_t stream) {
+static int launch_decode(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stream) {
   const int fb_stride = args.fmt == FMT_CSV ? args.csv.n_fields + 1 : 0;
   const int xt_stride = MODE == 1 ? D : args.n_out;
-  const size_t smem = decode_smem_bytes(fb_stride, xt_stride);
+  // byte stage: 48 KB unless the schema bounds the record size (Avro without strings) — a smaller stage means more CTAs/SM
+  args.stage_cap = STAGE_CAP_MAX;
+  if (args.fmt == FMT_AVRO) {
+    const int mx = avro_max_record_bytes(args.avro);
+    if (mx > 0) args.stage_cap = min(STAGE_CAP_MAX, ((mx * DEC_TILE + 31) & ~15));
+    else args.stage_cap = 40 * 1024;
+  }
+  const size_t smem = decode_smem_bytes(args.stage_cap, fb_stride, xt_stride);
   B2_REQUIRE(smem <= (size_t)ctx->smem_optin, "decode: tile needs %zu bytes of shared memory (max %d)", smem, ctx->smem_optin);
   auto kern = decode_kernel<D, MODE, FT>;
   B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
