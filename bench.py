@@ -197,8 +197,7 @@ class ScoreWorkload:
     def cpu_sample(self, n, threads=None):
         from oracle import c_oracle as co
 
-        if threads:
-            co.set_threads(threads)
+        co.set_threads(threads or os.cpu_count())  # torchrun exports OMP_NUM_THREADS=1: ask for every host thread explicitly
         x = self.host_rows(min(n, 1 << 22), 7)
         w, wd, nm = self.weights(), self.widths(), self.norm()
         co.score(x[:1024], w, wd, ACTS, norm=nm)
@@ -307,8 +306,7 @@ class DecodeScoreWorkload:
         import b200_sensor as bs
         from oracle import c_oracle as co
 
-        if threads:
-            co.set_threads(threads)
+        co.set_threads(threads or os.cpu_count())
         d, o = self._host_batch(7, n=min(n, 1 << 20))
         nrec = len(o) - 1
         w, nm = self.weights(), bs.schemas.norm_arrays()
@@ -323,6 +321,61 @@ class DecodeScoreWorkload:
             co.decode_score(d, o, w, W18, ACTS, norm=nm, threshold=THRESHOLD, **kw)
             done += nrec
         return done, time.perf_counter() - t0, co.max_threads() if not threads else threads
+
+
+def aux_fit(dev):
+    """BASELINE.json configs[3]: autoencoder training, 227 468 x 30 rows, batch 128 (the notebook's run, nb2.0:653-853)."""
+    import torch
+
+    import b200_sensor as bs
+
+    m = ScoreWorkload(30, 20, 20).model()
+    m.set_flat_weights(bs.keras_compat.init_dense_weights(W30, seed=314))
+    m.compile(optimizer="adam", loss="mean_squared_error", metrics=["accuracy"])
+    x = torch.from_numpy(bs.synth.credit_rows(227468, seed=314, outlier_frac=0.0)).to(dev)
+    m.fit(x, epochs=1, batch_size=128, shuffle=True)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    h = m.fit(x, epochs=3, batch_size=128, shuffle=True)
+    torch.cuda.synchronize()
+    dt = (time.perf_counter() - t0) / 3
+    return {"value": 227468 / dt, "unit": "samples/s", "us_per_sample": dt / 227468 * 1e6, "s_per_epoch": dt, "batch": 128,
+            "loss_after_4_epochs": h.history["loss"][-1], "kernel": "ae_fit_kernel (one persistent CTA per epoch)",
+            "reference_published": {"us_per_sample": 16.0, "source": "nb2.0:653-853 (MacBook CPU, TF 2.0.0-alpha0)"}}
+
+
+def aux_lstm(dev, T):
+    """BASELINE.json configs[4]: LSTM stack forward on synthetic sequences (B = 2^20 / T)."""
+    import torch
+
+    import b200_sensor as bs
+
+    k = bs.keras
+    m = k.models.Sequential()
+    m.add(k.layers.LSTM(32, activation="relu", input_shape=(T, 18), return_sequences=True))
+    m.add(k.layers.LSTM(16, activation="relu", return_sequences=False))
+    m.add(k.layers.RepeatVector(T))
+    m.add(k.layers.LSTM(16, activation="relu", return_sequences=True))
+    m.add(k.layers.LSTM(32, activation="relu", return_sequences=True))
+    m.add(k.layers.TimeDistributed(k.layers.Dense(18)))
+    B = (1 << 20) // T
+    g = torch.Generator(device=dev).manual_seed(314)
+    x = torch.rand((B, T, 18), device=dev, generator=g) * 2 - 1
+    y = torch.empty_like(x)
+    lib = bs._ffi.lib()
+    h = m._handle()
+    st = torch.cuda.current_stream().cuda_stream
+    for _ in range(3):
+        bs._ffi.check(lib.b2_lstm_forward(h, x.data_ptr(), B, T, y.data_ptr(), st))
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(10):
+        bs._ffi.check(lib.b2_lstm_forward(h, x.data_ptr(), B, T, y.data_ptr(), st))
+    e1.record()
+    torch.cuda.synchronize()
+    dt = e0.elapsed_time(e1) * 1e-4
+    return {"value": B * T / dt, "unit": "record-steps/s", "batch": B, "timesteps": T, "fp32_tflops": 36480 * B * T / dt / 1e12,
+            "fp32_frac_of_74.4": 36480 * B * T / dt / 74.4e12}
 
 
 WORKLOADS = {
@@ -467,7 +520,7 @@ def main():
                     "fp32_tflops_achieved": wl.flop_per_record * (recs / args.steps / wl.launches_per_step) / (per_launch_ms * 1e-3) / 1e12,
                     "kernel_ms_per_launch": per_launch_ms}
         cpu = None
-        if not args.no_cpu_baseline and world >= 1:
+        if not args.no_cpu_baseline and world == 1:  # reported at N=1 only
             n_target = 1 << 22 if isinstance(wl, ScoreWorkload) else 1 << 20
             n, dt, cores = wl.cpu_sample(n_target)
             rate = n / dt
@@ -502,6 +555,12 @@ def main():
                              "algorithmic_bytes_per_record": w2.bytes_per_record,
                              "fp32_tflops": w2.flop_per_record * r2 / t2 / 1e12}
             w2 = None
+        if names:
+            gc.collect()
+            torch.cuda.empty_cache()
+            also["fit_d30_batch128"] = aux_fit(dev)
+            also["lstm_forward_T1"] = aux_lstm(dev, 1)
+            also["lstm_forward_T16"] = aux_lstm(dev, 16)
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
                 "data": "synthetic", "config": config, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
