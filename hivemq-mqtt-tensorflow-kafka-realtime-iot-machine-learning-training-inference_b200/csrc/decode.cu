@@ -32,9 +32,14 @@ struct CsvP {
   uint8_t fidx[B2_MAX_FIELDS];       // k-th non-skipped field → field index
   float dflt[B2_MAX_FIELDS];
 };
+struct AvroRun {
+  int8_t type, nullable, count, out0;  // out0: first output column, -1 skip, -2 label
+};
 struct AvroP {
   int32_t n_fields, n_out, skip_prefix, all_routed;  // all_routed: every output column is written by some field
+  int32_t n_runs, pad[3];
   b2_avro_field f[B2_MAX_FIELDS];
+  AvroRun run[B2_MAX_FIELDS];
 };
 
 template <int D>
@@ -120,92 +125,49 @@ __device__ __forceinline__ int csv_scan(const uint8_t* base, int b, int e, const
   uint32_t special = 0;
   fb[0] = (uint16_t)b;
   *qmask = 0;
+  // 32-bit SWAR: exact byte-equality for the delimiter; "any byte below ','" as a cheap superset of quote / CR / LF (blanks
+  // and '+' also trip it — they only cost the careful path, they do not change the result)
   for (int p = b & ~3; p < e; p += 4) {
     const uint32_t wv = *reinterpret_cast<const uint32_t*>(base + p);
-    uint32_t keep = 0xFFFFFFFFu;
-    if (p < b) keep &= 0xFFFFFFFFu << ((b - p) * 8);
-    if (p + 4 > e) keep &= 0xFFFFFFFFu >> ((p + 4 - e) * 8);
-    uint32_t m = __vcmpeq4(wv, d4) & keep;
-    special |= (__vcmpeq4(wv, 0x22222222u) | __vcmpeq4(wv, 0x0A0A0A0Au) | __vcmpeq4(wv, 0x0D0D0D0Du)) & keep;
+    uint32_t keep = 0x80808080u;
+    if (p < b) keep &= 0x80808080u << ((b - p) * 8);
+    if (p + 4 > e) keep &= 0x80808080u >> ((p + 4 - e) * 8);
+    const uint32_t x = wv ^ d4;
+    uint32_t m = ~(((x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | x) & keep;  // 0x80 where byte == delim
+    special |= (wv - 0x2C2C2C2Cu) & ~wv & keep;                     // 0x80 where byte < 0x2C (may also flag a byte after one)
     while (m) {
-      const int k = (__ffs(m) - 1) >> 3;
+      const int k = (__ffs((int)m) - 1) >> 3;
       ++nf;
       if (nf < c.n_fields) fb[nf] = (uint16_t)(p + k + 1);
-      m &= ~(0xFFu << (k * 8));
+      m &= m - 1;
     }
   }
-  if (special) return csv_scan_slow(base, b, e, c, fb, qmask);  // quotes / CR / LF present: careful sequential scan
+  if (special || c.delim < 0x2C) return csv_scan_slow(base, b, e, c, fb, qmask);  // quotes / CR / LF possible: careful sequential scan
   if (nf + 1 != c.n_fields) return B2_REC_FIELD_COUNT;
   fb[c.n_fields] = (uint16_t)(e + 1);
   return B2_REC_OK;
 }
 
 // ---- CSV phase B: one float token, registers only ----------------------------------------------------------------------
-// Fast path for what sensor producers write (Java Float.toString): [-]digits[.digits][E[-]d[d]], at most 16 bytes and 9
-// mantissa digits.  The 16 bytes are pulled into registers with 5 aligned 32-bit loads + funnel shifts and walked by a fully
-// unrolled, branch-free state machine (no per-byte shared-memory round trip, no divergence on token length), then rounded by
-// the same Eisel-Lemire routine as the general parser.  Anything else returns false and takes b2_parse_float().
+// The token's first 16 bytes are pulled into registers with 5 aligned 32-bit loads + funnel shifts, its last 4 bytes with 2
+// more, and handed to the branch-free SWAR parser b2_fast_token16() (float_parse.cuh; fuzzed on the CPU against strtof).
+// Anything that parser declines (long mantissas, '+', blanks, inf/nan, junk) takes the general b2_parse_float().
+__device__ __forceinline__ uint32_t lds_u32_unaligned(const uint8_t* __restrict__ st, int off) {
+  const uint32_t* wp = reinterpret_cast<const uint32_t*>(st + (off & ~3));
+  return __funnelshift_r(wp[0], wp[1], (off & 3) * 8);
+}
 __device__ __forceinline__ bool csv_fast_token(const uint8_t* __restrict__ st, int b, int L, uint32_t* bits) {
-  if (L < 1 || L > 16) return false;
   const uint32_t* wp = reinterpret_cast<const uint32_t*>(st + (b & ~3));
   const int sh = (b & 3) * 8;
   const uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2], w3 = wp[3], w4 = wp[4];
-  const uint32_t t[4] = {__funnelshift_r(w0, w1, sh), __funnelshift_r(w1, w2, sh), __funnelshift_r(w2, w3, sh), __funnelshift_r(w3, w4, sh)};
-  uint32_t w = 0;          // mantissa (≤ 9 digits fits 32 bits)
-  int nd = 0;              // mantissa digits seen (leading zeros excluded once w != 0 … counted via w)
-  int q = 0;               // decimal exponent adjustment from fraction digits
-  int ex = 0, exd = 0;     // explicit exponent and its digit count
-  bool ok = true, neg = false, eneg = false, dot = false, in_exp = false, any = false;
-#pragma unroll
-  for (int k = 0; k < 16; ++k) {
-    const uint32_t c = (t[k >> 2] >> ((k & 3) * 8)) & 0xFFu;
-    const bool live = k < L;
-    const uint32_t d = c - '0';
-    const bool isd = d < 10u;
-    if (live) {
-      if (isd) {
-        if (!in_exp) {
-          nd += (w != 0u || d != 0u) ? 1 : 0;
-          w = w * 10u + d;
-          q -= dot ? 1 : 0;
-          any = true;
-        } else {
-          ex = ex * 10 + (int)d;
-          ++exd;
-        }
-      } else if (c == '.') {
-        ok = ok && !dot && !in_exp;
-        dot = true;
-      } else if ((c | 0x20u) == 'e') {
-        ok = ok && !in_exp && any;
-        in_exp = true;
-      } else if (c == '-') {
-        if (k == 0) neg = true;
-        else {
-          ok = ok && in_exp && exd == 0 && !eneg;
-          eneg = true;
-        }
-      } else {
-        ok = false;
-      }
-    }
-  }
-  ok = ok && any && nd <= 9 && (!in_exp || (exd >= 1 && exd <= 2));
-  // a '-' right after 'E' is only legal directly after it: "1E5-" is caught by exd == 0 at that point; "1E-" by exd >= 1
-  if (!ok) return false;
-  q += eneg ? -ex : ex;
-  *bits = (neg ? 0x80000000u : 0u) | b2_eisel_lemire32((uint64_t)w, q);
-  return true;
+  const uint32_t tail = lds_u32_unaligned(st, b + L - 4);  // may reach ≤ 3 bytes in front of the token: the stage has a 16-byte apron
+  return b2_fast_token16(__funnelshift_r(w0, w1, sh), __funnelshift_r(w1, w2, sh), __funnelshift_r(w2, w3, sh), __funnelshift_r(w3, w4, sh),
+                         tail, L, bits);
 }
 
 // ---- Avro: one record per thread, whole walk -------------------------------------------------------------------------------
 // Every thread of a warp is at the same field of its own record, so the field descriptor is a uniform constant-bank read and
 // the type switch does not diverge; values are fetched with two aligned 32-bit loads + a funnel shift instead of byte loads.
-__device__ __forceinline__ uint32_t lds_u32_unaligned(const uint8_t* __restrict__ st, int off) {
-  const uint32_t* wp = reinterpret_cast<const uint32_t*>(st + (off & ~3));
-  return __funnelshift_r(wp[0], wp[1], (off & 3) * 8);
-}
-
 // zig-zag varint of more than two bytes (rare: |value| ≥ 8192)
 __device__ __noinline__ int av_varint_long(const uint8_t* base, int p, int e, int max_bytes, long long* v) {
   unsigned long long u = 0;
@@ -240,57 +202,108 @@ __device__ __forceinline__ int av_varint(const uint8_t* base, int p, int e, int 
   return av_varint_long(base, p, e, max_bytes, v64);
 }
 
+// one field of any type (strings, booleans, wide varints, nullable anything): the general, slower step
+__device__ __forceinline__ int avro_field(const uint8_t* __restrict__ base, int p, int e, int type, int nullable, float* val,
+                                          uint8_t* lab, int* status) {
+  bool present = true, wide;
+  int v32 = 0;
+  long long v64 = 0;
+  *val = 0.0f;
+  *lab = 2;
+  if (nullable) {
+    p = av_varint(base, p, e, 10, &v32, &v64, &wide);
+    if (p < 0) return *status = B2_REC_TRUNCATED, -1;
+    if (wide || (v32 != 0 && v32 != 1)) return *status = B2_REC_BAD_BRANCH, -1;
+    present = v32 != (nullable == 1 ? 0 : 1);
+  }
+  if (!present) return p;
+  if (type == AV_FLOAT) {
+    *val = __uint_as_float(lds_u32_unaligned(base, p));
+    return p + 4;
+  }
+  if (type == AV_DOUBLE) {
+    const unsigned long long bits = (unsigned long long)lds_u32_unaligned(base, p) | ((unsigned long long)lds_u32_unaligned(base, p + 4) << 32);
+    *val = __double2float_rn(__longlong_as_double((long long)bits));  // one rounding, like Keras' float32 input cast
+    return p + 8;
+  }
+  if (type == AV_INT || type == AV_LONG) {
+    p = av_varint(base, p, e, type == AV_INT ? 5 : 10, &v32, &v64, &wide);
+    if (p < 0) return *status = B2_REC_TRUNCATED, -1;
+    // tf.cast(int32 → float32), cardata-v1.py:61-66
+    *val = !wide ? __int2float_rn(v32) : (type == AV_INT ? __int2float_rn((int)v64) : __ll2float_rn(v64));
+    return p;
+  }
+  if (type == AV_BOOLEAN) {
+    *val = base[p] ? 1.0f : 0.0f;
+    return p + 1;
+  }
+  if (type == AV_STRING || type == AV_BYTES) {
+    p = av_varint(base, p, e, 10, &v32, &v64, &wide);
+    if (p < 0) return *status = B2_REC_TRUNCATED, -1;
+    const long long L = wide ? v64 : (long long)v32;
+    if (L < 0 || (long long)p + L > e) return *status = B2_REC_TRUNCATED, -1;
+    const uint32_t c4 = lds_u32_unaligned(base, p);
+    if (L == 5 && c4 == 0x736C6166u && base[p + 4] == 'e') *lab = 0;  // "fals" + "e"
+    else if (L == 4 && c4 == 0x65757274u) *lab = 1;                   // "true"
+    else *lab = L == 0 ? 2 : 3;
+    return p + (int)L;
+  }
+  return p;  // AV_NULL: no bytes
+}
+
+// The schema program is pre-compiled on the host into RUNS of consecutive fields that share (type, nullable) and go to
+// consecutive output columns; plain float / double / small-int runs get tight type-specialised loops, everything else
+// the general step above.  Fixed-size fields are not bounds-checked one by one: the walk can overshoot `e` by at most a
+// few hundred bytes, which stays inside this CTA's shared memory, and the final check rejects the record.
 __device__ __forceinline__ int avro_decode_record(const uint8_t* __restrict__ base, int p, int e, const AvroP& a, float* __restrict__ xrow,
                                                   uint8_t* label) {
   uint8_t lab_out = 2;
   p += a.skip_prefix;
   if (p > e) return B2_REC_TRUNCATED;
-  for (int i = 0; i < a.n_fields; ++i) {
-    const int type = a.f[i].type, nullable = a.f[i].nullable, oc = a.f[i].out;
-    bool present = true, wide;
-    int v32 = 0;
-    long long v64 = 0;
-    if (nullable) {
-      p = av_varint(base, p, e, 10, &v32, &v64, &wide);
-      if (p < 0) return B2_REC_TRUNCATED;
-      if (wide || (v32 != 0 && v32 != 1)) return B2_REC_BAD_BRANCH;
-      present = v32 != (nullable == 1 ? 0 : 1);
-    }
-    float val = 0.0f;
-    uint8_t lab = 2;
-    if (present) {
-      if (type == AV_FLOAT) {
-        val = __uint_as_float(lds_u32_unaligned(base, p));
-        p += 4;
-      } else if (type == AV_DOUBLE) {
+  for (int ri = 0; ri < a.n_runs; ++ri) {
+    const int type = a.run[ri].type, nullable = a.run[ri].nullable, count = a.run[ri].count, out0 = a.run[ri].out0;
+    if (!nullable && type == AV_FLOAT && out0 >= 0) {
+#pragma unroll 4
+      for (int j = 0; j < count; ++j) xrow[out0 + j] = __uint_as_float(lds_u32_unaligned(base, p + 4 * j));
+      p += 4 * count;
+    } else if (!nullable && type == AV_DOUBLE && out0 >= 0) {
+#pragma unroll 2
+      for (int j = 0; j < count; ++j) {
         const unsigned long long bits =
-            (unsigned long long)lds_u32_unaligned(base, p) | ((unsigned long long)lds_u32_unaligned(base, p + 4) << 32);
-        val = __double2float_rn(__longlong_as_double((long long)bits));  // one rounding, like Keras' float32 input cast
-        p += 8;
-      } else if (type == AV_INT || type == AV_LONG) {
-        p = av_varint(base, p, e, type == AV_INT ? 5 : 10, &v32, &v64, &wide);
-        if (p < 0) return B2_REC_TRUNCATED;
-        // tf.cast(int32 → float32), cardata-v1.py:61-66
-        val = !wide ? __int2float_rn(v32) : (type == AV_INT ? __int2float_rn((int)v64) : __ll2float_rn(v64));
-      } else if (type == AV_BOOLEAN) {
-        val = base[p] ? 1.0f : 0.0f;
-        p += 1;
-      } else if (type == AV_STRING || type == AV_BYTES) {
-        p = av_varint(base, p, e, 10, &v32, &v64, &wide);
-        if (p < 0) return B2_REC_TRUNCATED;
-        const long long L = wide ? v64 : (long long)v32;
-        if (L < 0 || (long long)p + L > e) return B2_REC_TRUNCATED;
-        const uint32_t c4 = lds_u32_unaligned(base, p);
-        if (L == 5 && c4 == 0x736C6166u && base[p + 4] == 'e') lab = 0;  // "fals" + "e"
-        else if (L == 4 && c4 == 0x65757274u) lab = 1;                   // "true"
-        else lab = L == 0 ? 2 : 3;
-        p += (int)L;
+            (unsigned long long)lds_u32_unaligned(base, p + 8 * j) | ((unsigned long long)lds_u32_unaligned(base, p + 8 * j + 4) << 32);
+        xrow[out0 + j] = __double2float_rn(__longlong_as_double((long long)bits));
       }
-      // fixed-size fields are not bounds-checked one by one: the walk can overshoot `e` by at most a few hundred bytes
-      // (≤ 10 per field), which stays inside this CTA's shared memory, and the final check below rejects the record
+      p += 8 * count;
+    } else if (nullable == 1 && type == AV_DOUBLE && out0 >= 0) {  // ["null", "double"]: tag 0x00 = null, 0x02 = value
+      for (int j = 0; j < count; ++j) {
+        const uint32_t tag = base[p];
+        float val = 0.0f;
+        if (tag == 2u) {
+          const unsigned long long bits =
+              (unsigned long long)lds_u32_unaligned(base, p + 1) | ((unsigned long long)lds_u32_unaligned(base, p + 5) << 32);
+          val = __double2float_rn(__longlong_as_double((long long)bits));
+          p += 9;
+        } else if (tag == 0u) {
+          p += 1;
+        } else {  // non-minimal or invalid branch encoding: let the general step decide
+          uint8_t lab;
+          int st = B2_REC_OK;
+          p = avro_field(base, p, e, type, nullable, &val, &lab, &st);
+          if (p < 0) return st;
+        }
+        xrow[out0 + j] = val;
+      }
+    } else {
+      for (int j = 0; j < count; ++j) {
+        float val;
+        uint8_t lab;
+        int st = B2_REC_OK;
+        p = avro_field(base, p, e, type, nullable, &val, &lab, &st);
+        if (p < 0) return st;
+        if (out0 >= 0) xrow[out0 + j] = val;
+        else if (out0 == -2) lab_out = lab;
+      }
     }
-    if (oc >= 0) xrow[oc] = val;
-    else if (oc == -2) lab_out = lab;
   }
   if (p > e) return B2_REC_TRUNCATED;
   *label = lab_out;
@@ -303,7 +316,7 @@ template <int D, int MODE, bool FT>
 __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ DecodeArgs<D> a) {
   extern __shared__ __align__(128) uint8_t smem[];
   // carve: [stage bytes | offsets (TILE+1) | status (TILE) | qmask/present (TILE) | label (TILE) | mbarrier | fb | xt]
-  uint8_t* stage = smem;
+  uint8_t* stage = smem + 16;  // 16-byte apron in front: the token-tail load may start up to 3 bytes before the first token
   int32_t* s_offs = reinterpret_cast<int32_t*>(smem + a.stage_cap + 64);
   int32_t* s_stat = s_offs + DEC_TILE + 4;
   unsigned long long* s_qm = reinterpret_cast<unsigned long long*>(s_stat + DEC_TILE);
@@ -500,6 +513,11 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
   }
 }
 
+static int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return v ? atoi(v) : dflt;
+}
+
 // ---- host side ----------------------------------------------------------------------------------------------------
 static int fill_csv(const b2_csv_spec* s, CsvP& c) {
   B2_REQUIRE(s->n_fields >= 1 && s->n_fields <= 63, "csv: n_fields=%d not in 1..63", s->n_fields);
@@ -532,6 +550,15 @@ static int fill_avro(const b2_avro_prog* p, int skip_prefix, AvroP& a) {
     B2_REQUIRE(p->f[i].type >= AV_INT && p->f[i].type <= AV_NULL, "avro: field %d has unknown type %d", i, p->f[i].type);
     B2_REQUIRE(p->f[i].out < p->n_out, "avro: field %d routed to column %d >= n_out", i, p->f[i].out);
     a.f[i] = p->f[i];
+  }
+  // runs of consecutive fields with the same (type, nullable) and consecutive output columns (or all skipped)
+  for (int i = 0; i < p->n_fields; ++i) {
+    const b2_avro_field& f = p->f[i];
+    AvroRun* last = a.n_runs ? &a.run[a.n_runs - 1] : nullptr;
+    const bool extend = last && last->type == f.type && last->nullable == f.nullable && last->count < 100 &&
+                        ((last->out0 >= 0 && f.out == last->out0 + last->count) || (last->out0 == -1 && f.out == -1));
+    if (extend) ++last->count;
+    else a.run[a.n_runs++] = AvroRun{f.type, f.nullable, 1, f.out};
   }
   unsigned long long routed = 0;
   for (int i = 0; i < p->n_fields; ++i)
@@ -595,11 +622,6 @@ static int launch_decode(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stream) 
   kern<<<(unsigned)grid, DEC_NT, smem, stream>>>(args);
   B2_CUDA(cudaGetLastError());
   return B2_OK;
-}
-
-static int env_int(const char* name, int dflt) {
-  const char* v = getenv(name);
-  return v ? atoi(v) : dflt;
 }
 
 extern "C" int b2_decode_csv(b2_ctx* ctx, const uint8_t* bytes_dev, const int32_t* offs_dev, int64_t n, const b2_csv_spec* spec,

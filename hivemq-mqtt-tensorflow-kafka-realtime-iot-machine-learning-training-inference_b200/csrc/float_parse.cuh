@@ -219,3 +219,89 @@ B2_HD int b2_parse_float(BytePtr s, int n, uint32_t* out) {
   *out = sign | a;
   return B2_NUM_OK;
 }
+
+
+// ---- SWAR fast path for short tokens -----------------------------------------------------------------------------------
+// Handles  [-] digits [. digits] [ E|e [-] d [d] ]  with at most 12 mantissa characters, i.e. everything a sensor producer's
+// Float.toString emits ("39.395103", "0.034893095", "5.723834E-4", "32", "-0.5").  The token's first 16 bytes arrive in four
+// little-endian 32-bit words (byte k of the token = byte k of the 128-bit value; bytes at or beyond L are don't-care) and its
+// last four bytes in `tail`.  No loops, no per-byte branches: the dot is squeezed out with one byte shift + masks, the
+// mantissa is zero-padded on the RIGHT to 12 digits (w × 10^k with the exponent lowered by k is the same number, and the
+// Eisel-Lemire step is exact for any 64-bit w), validated and converted four digits per word.  Returns false for anything
+// else (caller falls back to b2_parse_float); when it returns true the result is bit-identical to b2_parse_float's.
+B2_HD uint32_t b2_fsr(uint32_t lo, uint32_t hi, int s) {  // (hi:lo) >> s, s in [0, 32]
+#if defined(__CUDA_ARCH__)
+  return __funnelshift_rc(lo, hi, s);
+#else
+  return s >= 32 ? hi : (s == 0 ? lo : (lo >> s) | (hi << (32 - s)));
+#endif
+}
+B2_HD uint32_t b2_bytemask(int n) {  // low n bytes set, n clamped to [0, 4]
+  n = n < 0 ? 0 : (n > 4 ? 4 : n);
+  return b2_fsr(0xFFFFFFFFu, 0u, 32 - 8 * n);
+}
+B2_HD uint32_t b2_nondigit(uint32_t x) {  // x = chars ^ 0x30303030: high bit of each byte set iff that byte is not 0..9
+  return ((x + 0x76767676u) | x) & 0x80808080u;
+}
+B2_HD uint32_t b2_eqbyte(uint32_t w, uint32_t splat) {  // 0x80 in every byte of w equal to the splatted byte (exact, no carries)
+  const uint32_t x = w ^ splat;
+  return ~(((x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | x) & 0x80808080u;
+}
+B2_HD int b2_first_byte(uint32_t m) {  // index of the lowest byte whose 0x80 bit is set (m != 0)
+#if defined(__CUDA_ARCH__)
+  return (__ffs((int)m) - 1) >> 3;
+#else
+  return (__builtin_ffs((int)m) - 1) >> 3;
+#endif
+}
+B2_HD uint32_t b2_four_digits(uint32_t x) {  // x = 4 digit values, most significant in the low byte → 0..9999
+  const uint32_t y = x * 10u + (x >> 8);     // byte0 = 10 d0 + d1, byte2 = 10 d2 + d3 (no inter-byte carry: ≤ 99)
+  return (y & 0xFFu) * 100u + ((y >> 16) & 0xFFu);
+}
+
+B2_HD bool b2_fast_token16(uint32_t t0, uint32_t t1, uint32_t t2, uint32_t t3, uint32_t tail, int L, uint32_t* out) {
+  if (L < 1 || L > 16) return false;
+  // sign
+  const bool neg = (t0 & 0xFFu) == '-';
+  const int s8 = neg ? 8 : 0;
+  t0 = b2_fsr(t0, t1, s8);
+  t1 = b2_fsr(t1, t2, s8);
+  t2 = b2_fsr(t2, t3, s8);
+  L -= neg ? 1 : 0;
+  // exponent: E d | E - d | E d d | E - d d at the very end of the token
+  const uint32_t c0 = tail & 0xFFu, c1 = (tail >> 8) & 0xFFu, c2 = (tail >> 16) & 0xFFu, c3 = tail >> 24;
+  const uint32_t d2 = c2 - '0', d3 = c3 - '0';
+  const bool isd2 = d2 < 10u, isd3 = d3 < 10u;
+  const bool E0 = (c0 | 0x20u) == 'e', E1 = (c1 | 0x20u) == 'e', E2 = (c2 | 0x20u) == 'e';
+  const bool e1 = E2 && isd3 && L >= 3;
+  const bool e2 = E1 && c2 == '-' && isd3 && L >= 4;
+  const bool e3 = E1 && isd2 && isd3 && L >= 4;
+  const bool e4 = E0 && c1 == '-' && isd2 && isd3 && L >= 5;
+  const int elen = e1 ? 2 : ((e2 || e3) ? 3 : (e4 ? 4 : 0));
+  int ex = (int)d3 + ((e3 || e4) ? 10 * (int)d2 : 0);
+  ex = elen ? ((e2 || e4) ? -ex : ex) : 0;
+  const int Lm = L - elen;
+  if (Lm < 1 || Lm > 12) return false;
+  // first '.' inside the mantissa
+  const uint32_t m0 = b2_eqbyte(t0, 0x2E2E2E2Eu), m1 = b2_eqbyte(t1, 0x2E2E2E2Eu), m2 = b2_eqbyte(t2, 0x2E2E2E2Eu);
+  int pd = m0 ? b2_first_byte(m0) : (m1 ? 4 + b2_first_byte(m1) : (m2 ? 8 + b2_first_byte(m2) : 12));
+  pd = pd < Lm ? pd : Lm;
+  const int has_dot = pd < Lm ? 1 : 0;
+  const int nd = Lm - has_dot;  // digit characters
+  if (nd < 1) return false;
+  // squeeze the dot out: bytes before it stay, bytes after it move down by one; pad with '0' from byte nd on
+  const uint32_t u0 = b2_fsr(t0, t1, 8), u1 = b2_fsr(t1, t2, 8), u2 = t2 >> 8;
+  const uint32_t a0 = b2_bytemask(pd), a1 = b2_bytemask(pd - 4), a2 = b2_bytemask(pd - 8);
+  const uint32_t k0 = b2_bytemask(nd), k1 = b2_bytemask(nd - 4), k2 = b2_bytemask(nd - 8);
+  uint32_t r0 = (t0 & a0) | (u0 & ~a0), r1 = (t1 & a1) | (u1 & ~a1), r2 = (t2 & a2) | (u2 & ~a2);
+  r0 = (r0 & k0) | (0x30303030u & ~k0);
+  r1 = (r1 & k1) | (0x30303030u & ~k1);
+  r2 = (r2 & k2) | (0x30303030u & ~k2);
+  const uint32_t x0 = r0 ^ 0x30303030u, x1 = r1 ^ 0x30303030u, x2 = r2 ^ 0x30303030u;
+  if (b2_nondigit(x0) | b2_nondigit(x1) | b2_nondigit(x2)) return false;  // anything but digits (second dot, '+', blanks, …)
+  const uint32_t hi8 = b2_four_digits(x0) * 10000u + b2_four_digits(x1);  // ≤ 99 999 999
+  const uint64_t w = (uint64_t)hi8 * 10000u + b2_four_digits(x2);         // 12 digits, < 2^40
+  const int q = ex - (Lm - has_dot - pd) - (12 - nd);                     // fraction digits and the padding zeros
+  *out = (neg ? 0x80000000u : 0u) | b2_eisel_lemire32(w, q);
+  return true;
+}

@@ -12,7 +12,27 @@
 
 #include "../../hivemq-mqtt-tensorflow-kafka-realtime-iot-machine-learning-training-inference_b200/csrc/float_parse.cuh"
 
-static long long bad = 0, checked = 0;
+static long long bad = 0, checked = 0, fast_hits = 0;
+
+// the SWAR fast path sees the token the way the kernel hands it over: 16 bytes + the last 4 bytes, garbage around it
+static void check_fast(const std::string& tok, uint32_t ref_bits, bool ref_ok) {
+  if (tok.empty() || tok.size() > 16) return;
+  unsigned char buf[48];
+  for (int i = 0; i < 48; ++i) buf[i] = (unsigned char)(",x\"9E-.5 "[i % 9]);  // hostile neighbours
+  const int b = 8;
+  memcpy(buf + b, tok.data(), tok.size());
+  uint32_t t[4], tail;
+  memcpy(t, buf + b, 16);
+  memcpy(&tail, buf + b + tok.size() - 4, 4);
+  uint32_t got = 0;
+  if (b2_fast_token16(t[0], t[1], t[2], t[3], tail, (int)tok.size(), &got)) {
+    ++fast_hits;
+    if (!ref_ok || got != ref_bits) {
+      if (bad < 20) fprintf(stderr, "FAST MISMATCH '%s' got 0x%08x ref ok=%d 0x%08x\n", tok.c_str(), got, (int)ref_ok, ref_bits);
+      ++bad;
+    }
+  }
+}
 
 static void check(const std::string& tok) {
   uint32_t got = 0;
@@ -29,6 +49,7 @@ static void check(const std::string& tok) {
   if (st == B2_NUM_TOO_LONG) return;  // allowed refusal (counted separately by the caller if needed)
   const bool hex = t.find('x') != std::string::npos || t.find('X') != std::string::npos;
   const bool ref_ok = !t.empty() && !hex && end == t.c_str() + t.size() && t.find_first_not_of(" \t") != std::string::npos;
+  check_fast(tok, ref, ref_ok && !isnan(f));
   if ((st == B2_NUM_OK) != ref_ok || (ref_ok && got != ref && !(isnan(f) && (got & 0x7FFFFFFF) > 0x7F800000))) {
     if (bad < 20) fprintf(stderr, "MISMATCH '%s' got st=%d 0x%08x ref ok=%d 0x%08x\n", tok.c_str(), st, got, (int)ref_ok, ref);
     ++bad;
@@ -105,6 +126,24 @@ int main(int argc, char** argv) {
     }
     if (fp) fclose(fp);
   }
-  printf("mismatches=%lld checked=%lld\n", bad, checked);
+  // shapes the fast path is meant for: d.dddd with 1..11 digits, optional E[-]d[d], optional sign
+  for (long long i = 0; i < n; ++i) {
+    std::string s;
+    if (g() % 4 == 0) s += '-';
+    const int nd = 1 + (int)(g() % 11);
+    const int point = (int)(g() % (nd + 2)) - 1;  // -1: no dot
+    for (int k = 0; k < nd; ++k) {
+      if (k == point) s += '.';
+      s += (char)('0' + g() % 10);
+    }
+    if (point == nd) s += '.';
+    const int mode = (int)(g() % 6);
+    if (mode == 1) s += "E" + std::to_string((int)(g() % 10));
+    else if (mode == 2) s += "E-" + std::to_string((int)(g() % 10));
+    else if (mode == 3) s += "E" + std::to_string(10 + (int)(g() % 30));
+    else if (mode == 4) s += "e-" + std::to_string(10 + (int)(g() % 36));
+    check(s);
+  }
+  printf("mismatches=%lld checked=%lld fast_path_hits=%lld\n", bad, checked, fast_hits);
   return bad ? 1 : 0;
 }
