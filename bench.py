@@ -531,7 +531,7 @@ def main():
         launches = args.steps * wl.launches_per_step
         also = {}
         names = [w for w in WORKLOADS if w != args.workload] if (args.also is None and world == 1) else \
-            [w for w in (args.also or "").split(",") if w]
+            [w for w in (args.also or "").split(",") if w in WORKLOADS]   # "--also none" → nothing
         import gc
 
         wl = None  # free the headline workload's device buffers before measuring the others
