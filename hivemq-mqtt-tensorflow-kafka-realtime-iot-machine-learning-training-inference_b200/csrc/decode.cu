@@ -263,9 +263,37 @@ __device__ __forceinline__ int avro_decode_record(const uint8_t* __restrict__ ba
   for (int ri = 0; ri < a.n_runs; ++ri) {
     const int type = a.run[ri].type, nullable = a.run[ri].nullable, count = a.run[ri].count, out0 = a.run[ri].out0;
     if (!nullable && type == AV_FLOAT && out0 >= 0) {
+      // consecutive floats share their unaligned words: count + 1 aligned loads, one funnel shift per value
+      const uint32_t* wp = reinterpret_cast<const uint32_t*>(base + (p & ~3));
+      const int sh = (p & 3) * 8;
+      uint32_t w_prev = wp[0];
 #pragma unroll 4
-      for (int j = 0; j < count; ++j) xrow[out0 + j] = __uint_as_float(lds_u32_unaligned(base, p + 4 * j));
+      for (int j = 0; j < count; ++j) {
+        const uint32_t w_next = wp[j + 1];
+        xrow[out0 + j] = __uint_as_float(__funnelshift_r(w_prev, w_next, sh));
+        w_prev = w_next;
+      }
       p += 4 * count;
+    } else if (!nullable && (type == AV_INT || type == AV_LONG) && out0 >= 0) {
+      for (int j = 0; j < count; ++j) {  // one- and two-byte varints inline (tyre pressure, firmware), the rest in the general step
+        const uint32_t w = lds_u32_unaligned(base, p);
+        const uint32_t b0 = w & 0xFFu, b1 = (w >> 8) & 0xFFu;
+        if (b0 < 0x80u) {
+          xrow[out0 + j] = __int2float_rn((int)(b0 >> 1) ^ -(int)(b0 & 1u));  // tf.cast(int32 → float32), cardata-v1.py:61-66
+          p += 1;
+        } else if (b1 < 0x80u) {
+          const uint32_t u = (b0 & 0x7Fu) | (b1 << 7);
+          xrow[out0 + j] = __int2float_rn((int)(u >> 1) ^ -(int)(u & 1u));
+          p += 2;
+        } else {
+          float val;
+          uint8_t lab;
+          int st = B2_REC_OK;
+          p = avro_field(base, p, e, type, 0, &val, &lab, &st);
+          if (p < 0) return st;
+          xrow[out0 + j] = val;
+        }
+      }
     } else if (!nullable && type == AV_DOUBLE && out0 >= 0) {
 #pragma unroll 2
       for (int j = 0; j < count; ++j) {
@@ -318,7 +346,8 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
   // carve: [stage bytes | offsets (TILE+1) | status (TILE) | qmask/present (TILE) | label (TILE) | mbarrier | fb | xt]
   uint8_t* stage = smem + 16;  // 16-byte apron in front: the token-tail load may start up to 3 bytes before the first token
   int32_t* s_offs = reinterpret_cast<int32_t*>(smem + a.stage_cap + 64);
-  int32_t* s_stat = s_offs + DEC_TILE + 4;
+  int32_t* s_offs2 = s_offs + DEC_TILE + 4;
+  int32_t* s_stat = s_offs2 + DEC_TILE + 4;
   unsigned long long* s_qm = reinterpret_cast<unsigned long long*>(s_stat + DEC_TILE);
   uint8_t* s_lab = reinterpret_cast<uint8_t*>(s_qm + DEC_TILE);
   uint64_t* full = reinterpret_cast<uint64_t*>(s_lab + DEC_TILE);
@@ -356,52 +385,83 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
   unsigned flagged = 0, n_ok = 0, n_err = 0;
   unsigned long long n_bytes = 0;
   const long long n_tiles = (a.n + DEC_TILE - 1) / DEC_TILE;
+  int32_t* const offs_buf[2] = {s_offs, s_offs2};
 
-  for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    const long long row0 = tile * DEC_TILE;
-    const int rows = (int)min((long long)DEC_TILE, a.n - row0);
-    for (int i = tid; i <= rows; i += DEC_NT) s_offs[i] = a.offs[row0 + i];
-    __syncthreads();
-    int sub = 0;
+  // Work items are sub-tiles: (tile row0, rows, first record `sub`, record count `cnt`).  The byte stage is single: as soon as
+  // phase A/B have consumed it, the NEXT item is planned (how many records fit) and its bulk copy issued, so the copy runs
+  // under the current item's score phase; the next tile's offsets were fetched into registers one item earlier.
+  auto oversize = [&](long long row) {  // a single record larger than the stage: refuse it, keep going (thread 0)
+    if (a.status) a.status[row] = B2_REC_TOO_LONG;
+    if (MODE == 1) {
+      if (a.mse) a.mse[row] = __int_as_float(0x7FC00000);
+      if (a.flag) a.flag[row] = 0;
+    } else {
+      for (int j = 0; j < a.n_out; ++j) a.out[row * a.n_out + j] = __int_as_float(0x7FC00000);
+    }
+    if (a.label) a.label[row] = 2;
+    ++n_err;
+  };
+  // plan the item starting at record `sub` of the tile whose offsets sit in `so`: returns cnt (0 = tile exhausted) and
+  // issues its bulk copy; every thread must call it (block-wide count)
+  auto plan = [&](const int32_t* so, long long row0, int rows, int& sub, int& rel) -> int {
     while (sub < rows) {
-      // how many records starting at `sub` fit in the stage (byte range is 16-byte aligned outwards)
-      const long long b_abs = s_offs[sub];
+      const long long b_abs = so[sub];
       const uintptr_t a0 = (reinterpret_cast<uintptr_t>(a.bytes) + (uintptr_t)b_abs) & ~(uintptr_t)15;
       const int lead = (int)((reinterpret_cast<uintptr_t>(a.bytes) + (uintptr_t)b_abs) - a0);
       const int rr = sub + tid;
-      const int fit = rr < rows && (long long)s_offs[rr + 1] - b_abs + lead <= (long long)a.stage_cap;
+      const int fit = rr < rows && (long long)so[rr + 1] - b_abs + lead <= (long long)a.stage_cap;
       const int cnt = __syncthreads_count(fit);  // record ends are monotone: this is the number of records that fit
-      if (cnt == 0) {  // a single record larger than the stage: refuse it, keep going
-        if (tid == 0) {
-          const long long r = row0 + sub;
-          if (a.status) a.status[r] = B2_REC_TOO_LONG;
-          if (MODE == 1) {
-            if (a.mse) a.mse[r] = __int_as_float(0x7FC00000);
-            if (a.flag) a.flag[r] = 0;
-          } else {
-            for (int j = 0; j < a.n_out; ++j) a.out[r * a.n_out + j] = __int_as_float(0x7FC00000);
-          }
-          if (a.label) a.label[r] = 2;
-          ++n_err;
-        }
+      if (cnt == 0) {
+        if (tid == 0) oversize(row0 + sub);
         sub += 1;
-        __syncthreads();
         continue;
       }
-      const long long e_abs = s_offs[sub + cnt];
+      const long long e_abs = so[sub + cnt];
       const uint32_t nbytes = (uint32_t)(((e_abs - b_abs + lead) + 15) & ~15ll);
       if (tid == 0) {
         mbar_expect_tx(&full[0], nbytes);
         bulk_g2s(stage, reinterpret_cast<const void*>(a0), nbytes, &full[0]);
         n_bytes += (unsigned long long)(e_abs - b_abs);
       }
-      mbar_wait(&full[0], phase);
-      phase ^= 1u;
-      const int rel = lead - (int)b_abs;  // stage offset of absolute byte x is x + rel
+      rel = lead - (int)b_abs;  // stage offset of absolute byte x is x + rel
+      return cnt;
+    }
+    return 0;
+  };
 
-      // ---- phase A: one record per thread → field-begin table ----
+  long long tile = blockIdx.x;
+  if (tile < n_tiles) {
+    int buf = 0;
+    long long row0 = tile * DEC_TILE;
+    int rows = (int)min((long long)DEC_TILE, a.n - row0);
+    for (int i = tid; i <= rows; i += DEC_NT) offs_buf[0][i] = a.offs[row0 + i];
+    __syncthreads();
+    // offsets of the following tile → registers
+    long long ntile = tile + gridDim.x;
+    int pre0 = 0, pre1 = 0;
+    auto prefetch = [&](long long t) {
+      if (t < n_tiles) {
+        const long long r0 = t * DEC_TILE;
+        const long long last = min((long long)DEC_TILE, a.n - r0);
+        if (tid <= last) pre0 = a.offs[r0 + tid];
+        if (tid == 0 && last == DEC_TILE) pre1 = a.offs[r0 + DEC_TILE];
+      }
+    };
+    prefetch(ntile);
+    int sub = 0, rel = 0;
+    int cnt = plan(offs_buf[0], row0, rows, sub, rel);
+    while (true) {
+      // next tile's offsets: registers → the other offsets buffer (visible after the barrier below)
+      if (ntile < n_tiles) {
+        offs_buf[buf ^ 1][tid] = pre0;
+        if (tid == 0) offs_buf[buf ^ 1][DEC_TILE] = pre1;
+      }
+      if (cnt > 0) {
+        mbar_wait(&full[0], phase);
+        phase ^= 1u;
+        // ---- phase A: one record per thread → field-begin table ----
       if (tid < cnt) {
-        const int b = s_offs[sub + tid] + rel, e = s_offs[sub + tid + 1] + rel;
+        const int b = offs_buf[buf][sub + tid] + rel, e = offs_buf[buf][sub + tid + 1] + rel;
         int st;
         uint8_t lab = 2;
         if (a.fmt == FMT_CSV) {
@@ -457,16 +517,50 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
           }
         }
       }
-      __syncthreads();
+      }
+      __syncthreads();  // stage consumed (and the next tile's offsets are in place)
+      // ---- plan the next item and start its copy ----
+      const long long c_row0 = row0;
+      const int c_sub = sub, c_cnt = cnt;
+      bool more = true, staged = true;
+      sub += cnt;
+      int n_rel = 0, n_cnt = 0;
+      for (;;) {
+        if (sub < rows) {
+          n_cnt = plan(offs_buf[buf], row0, rows, sub, n_rel);
+          if (n_cnt > 0) break;
+        }
+        if (ntile >= n_tiles) {
+          more = false;
+          break;
+        }
+        if (!staged) {  // rare: a whole tile had no record that fits; its successor's offsets are still in registers
+          offs_buf[buf ^ 1][tid] = pre0;
+          if (tid == 0) offs_buf[buf ^ 1][DEC_TILE] = pre1;
+          __syncthreads();
+        }
+        buf ^= 1;  // move on to the next tile (its offsets were staged at the top of the loop)
+        tile = ntile;
+        row0 = tile * DEC_TILE;
+        rows = (int)min((long long)DEC_TILE, a.n - row0);
+        sub = 0;
+        ntile = tile + gridDim.x;
+        prefetch(ntile);
+        staged = false;
+      }
+      // ---- phase C on the CURRENT item ----
+      if (c_cnt > 0) {
+        const long long row0_c = c_row0;
+        const int sub_c = c_sub, cnt_c = c_cnt;
       // ---- phase C ----
       if (MODE == 1) {
-        const bool va = tid < cnt;
+        const bool va = tid < cnt_c;
         float* const rowp[1] = {s_xt + (size_t)tid * D};
         float mm[1] = {0.f};
         if (va) {
           if (a.has_norm) ae_forward_rows<D, 1, true, false, FT>(a.w, a.nm, rowp, mm);
           else ae_forward_rows<D, 1, false, false, FT>(a.w, a.nm, rowp, mm);
-          const long long gr = row0 + sub + tid;
+          const long long gr = row0_c + sub_c + tid;
           const int st = s_stat[tid];
           float m = mm[0];
           if (st != B2_REC_OK) m = __int_as_float(0x7FC00000);
@@ -480,12 +574,12 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
           n_err += st != B2_REC_OK;
         }
       } else {
-        for (int i = tid; i < cnt * xt_stride; i += DEC_NT) {
+        for (int i = tid; i < cnt_c * xt_stride; i += DEC_NT) {
           const int r = i / xt_stride;
-          a.out[(row0 + sub) * xt_stride + i] = s_stat[r] == B2_REC_OK ? s_xt[i] : __int_as_float(0x7FC00000);
+          a.out[(row0_c + sub_c) * xt_stride + i] = s_stat[r] == B2_REC_OK ? s_xt[i] : __int_as_float(0x7FC00000);
         }
-        if (tid < cnt) {
-          const long long gr = row0 + sub + tid;
+        if (tid < cnt_c) {
+          const long long gr = row0_c + sub_c + tid;
           const int st = s_stat[tid];
           if (a.status) a.status[gr] = st;
           if (a.label) a.label[gr] = a.fmt == FMT_AVRO && st == B2_REC_OK ? s_lab[tid] : 2;
@@ -493,8 +587,11 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
           n_err += st != B2_REC_OK;
         }
       }
-      __syncthreads();  // stage, tables and tile are free again
-      sub += cnt;
+      }
+      __syncthreads();  // tile tables free again
+      if (!more) break;
+      cnt = n_cnt;
+      rel = n_rel;
     }
   }
   if (a.counters) {
@@ -587,7 +684,7 @@ static int avro_max_record_bytes(const AvroP& a) {
 
 static size_t decode_smem_bytes(int stage_cap, int fb_stride, int xt_stride) {
   size_t s = (size_t)stage_cap + 64;
-  s += sizeof(int32_t) * (DEC_TILE + 4);           // offsets
+  s += 2 * sizeof(int32_t) * (DEC_TILE + 4);       // offsets (double-buffered)
   s += sizeof(int32_t) * DEC_TILE;                 // status
   s += sizeof(unsigned long long) * DEC_TILE;      // qmask
   s += DEC_TILE;                                   // label
