@@ -11,7 +11,7 @@
 // and the matching cell states in registers; the gate non-linearities are the GEMM epilogue.  Because consecutive layers'
 // inputs are adjacent activation rows, every layer's GEMM reads ONE contiguous [K, 128] panel.
 // Algorithmic bytes per record-step: 4F read + 4F written (weights are read once per CTA).
-#include "common.cuh"
+#include "lstm_tc.h"
 
 constexpr int LS_SEQ = 128;   // sequences per CTA
 constexpr int LS_NT = 256;    // threads: 16 (sequence groups of 8) x 16 (column groups)
@@ -23,6 +23,10 @@ struct b2_lstm {
   int n_params;
   float* d_packed;  // device: per layer [K][N] (gate-interleaved columns) + bias[N], then dense [K][32] + bias[32]
   int packed_floats;
+  // tensor-core path (lstm_tc.cu): canonical-layout (hi, lo) weights; tc_floats == 0 when the stack does not fit it
+  float* d_packed_tc;
+  int tc_floats;
+  TcLayer tc_layers[5];
 };
 
 struct LstmArgs {
@@ -247,11 +251,20 @@ extern "C" int b2_lstm_create(b2_ctx* ctx, const b2_lstm_desc* desc, const float
   m->n_params = lstm_param_count(*desc);
   m->packed_floats = (int)packed.size();
   m->d_packed = nullptr;
+  m->d_packed_tc = nullptr;
+  m->tc_floats = 0;
   cudaError_t e = cudaMalloc(&m->d_packed, sizeof(float) * packed.size());
   if (e == cudaSuccess) e = cudaMemcpy(m->d_packed, packed.data(), sizeof(float) * packed.size(), cudaMemcpyHostToDevice);
+  std::vector<float> tc_packed;
+  if (e == cudaSuccess && b2_lstm_tc_pack(desc, host_weights, tc_packed, m->tc_layers) == 0) {
+    e = cudaMalloc(&m->d_packed_tc, sizeof(float) * tc_packed.size());
+    if (e == cudaSuccess) e = cudaMemcpy(m->d_packed_tc, tc_packed.data(), sizeof(float) * tc_packed.size(), cudaMemcpyHostToDevice);
+    m->tc_floats = (int)tc_packed.size();
+  }
   if (e != cudaSuccess) {
     b2_set_error("b2_lstm_create: weight upload failed: %s", cudaGetErrorString(e));
     if (m->d_packed) cudaFree(m->d_packed);
+    if (m->d_packed_tc) cudaFree(m->d_packed_tc);
     delete m;
     return B2_ECUDA;
   }
@@ -263,6 +276,7 @@ extern "C" void b2_lstm_destroy(b2_lstm* m) {
   if (!m) return;
   DeviceGuard g(m->ctx->device);
   if (m->d_packed) cudaFree(m->d_packed);
+  if (m->d_packed_tc) cudaFree(m->d_packed_tc);
   delete m;
 }
 
@@ -273,6 +287,14 @@ extern "C" int b2_lstm_forward(b2_lstm* m, const float* x_dev, int64_t batch, in
   B2_REQUIRE(batch >= 0 && timesteps >= 1, "b2_lstm_forward: batch=%lld timesteps=%d", (long long)batch, timesteps);
   if (batch == 0) return B2_OK;
   DeviceGuard g(m->ctx->device);
+  {
+    // default: tensor-core kernel (tcgen05, split-precision TF32, within the 1e-4 parity budget); B2_LSTM_TC=0 → FP32 FMA kernel
+    const char* env = getenv("B2_LSTM_TC");
+    const bool want_tc = !(env && env[0] == '0');
+    if (want_tc && m->tc_floats > 0)
+      return b2_lstm_tc_launch(m->ctx, m->d_packed_tc, m->tc_floats, m->tc_layers, m->desc.features, x_dev, batch, timesteps, y_dev,
+                               (cudaStream_t)stream);
+  }
   LstmArgs a;
   a.x = x_dev;
   a.y = y_dev;
