@@ -209,21 +209,61 @@ def decode_score(model, records, csv_kinds=None, csv_defaults=None, avro_schema=
     return mse, flag, label, status
 
 
+_pinned_out = {}   # n → pinned uint8[5n] result buffer (reuse_output=True)
+_side_stream = {}  # device index → copy stream
+
+
 def decode_score_host(model, data, offsets, csv_kinds=None, csv_defaults=None, avro_schema=None, threshold: float = 5.0,
-                      skip_prefix: int = 0):
+                      skip_prefix: int = 0, chunks: int = 4, reuse_output: bool = False):
     """End-to-end form for HOST buffers (what a Kafka consumer hands over): ``data`` uint8 / ``offsets`` int32 as NumPy arrays
-    or (ideally pinned) CPU tensors → H2D copy → fused kernel → D2H of (mse f32[n], flag u8[n]) as NumPy arrays."""
+    or (ideally pinned) CPU tensors → H2D copy → fused kernel → D2H of (mse f32[n], flag u8[n]) as NumPy arrays.
+
+    The batch is cut into ``chunks`` record ranges: the payload bytes of range c+1 cross PCIe on a copy stream while range c is
+    decoded + scored and its 5 B/record results travel back (PCIe is full duplex).  With ``reuse_output`` the returned arrays
+    are views of a per-size pinned buffer that the next call of the same size overwrites (no pinned allocation per call)."""
     dev = torch.device("cuda", torch.cuda.current_device())
     d = data if isinstance(data, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(data, dtype=np.uint8))
     o = offsets if isinstance(offsets, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(offsets, dtype=np.int32))
-    rb = RecordBatch(d, o, dev, skip_prefix=skip_prefix)
-    mse, flag, _, _ = decode_score(model, rb, csv_kinds=csv_kinds, csv_defaults=csv_defaults, avro_schema=avro_schema,
-                                   threshold=threshold)
-    n = rb.n
-    out = torch.empty(n * 5, dtype=torch.uint8).pin_memory() if n else torch.empty(0, dtype=torch.uint8)
+    n = int(o.numel()) - 1
+    if n <= 0:
+        return np.zeros(0, np.float32), np.zeros(0, np.uint8)
+    if reuse_output and n in _pinned_out:
+        out = _pinned_out[n]
+    else:
+        out = torch.empty(n * 5, dtype=torch.uint8).pin_memory()
+        if reuse_output:
+            _pinned_out[n] = out
     hm = out[: n * 4].view(torch.float32)
     hf = out[n * 4:]
-    hm.copy_(mse, non_blocking=True)
-    hf.copy_(flag, non_blocking=True)
-    torch.cuda.current_stream().synchronize()
+    main = torch.cuda.current_stream()
+    side = _side_stream.setdefault(dev.index, torch.cuda.Stream(device=dev))
+    d_dev = torch.empty(d.numel(), dtype=torch.uint8, device=dev)
+    o_dev = o.to(dev, non_blocking=True)
+    mse = torch.empty(n, dtype=torch.float32, device=dev)
+    flag = torch.empty(n, dtype=torch.uint8, device=dev)
+    status = torch.empty(n, dtype=torch.int32, device=dev)
+    label = torch.empty(n, dtype=torch.uint8, device=dev) if avro_schema is not None else None
+    side.wait_stream(main)  # the fresh device buffers are ordered after whatever the caller queued
+    bounds = [n * c // chunks for c in range(chunks + 1)]
+    bounds = sorted(set(bounds))
+    oh = o.numpy() if not o.is_cuda else o.cpu().numpy()
+    events = []
+    with torch.cuda.stream(side):
+        for c0, c1 in zip(bounds[:-1], bounds[1:]):
+            b0, b1 = int(oh[c0]), int(oh[c1])
+            if b1 > b0:
+                d_dev[b0:b1].copy_(d[b0:b1], non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(side)
+            events.append(ev)
+    for (c0, c1), ev in zip(zip(bounds[:-1], bounds[1:]), events):
+        main.wait_event(ev)
+        rb = RecordBatch.__new__(RecordBatch)
+        rb.data, rb.offsets, rb.n, rb.skip_prefix = d_dev, o_dev[c0:c1 + 1], c1 - c0, skip_prefix
+        decode_score(model, rb, csv_kinds=csv_kinds, csv_defaults=csv_defaults, avro_schema=avro_schema, threshold=threshold,
+                     mse=mse[c0:c1], flag=flag[c0:c1], status=status[c0:c1], label=None if label is None else label[c0:c1])
+        hm[c0:c1].copy_(mse[c0:c1], non_blocking=True)
+        hf[c0:c1].copy_(flag[c0:c1], non_blocking=True)
+    main.synchronize()
+    d_dev.record_stream(side)
     return hm.numpy(), hf.numpy()

@@ -233,3 +233,24 @@ def test_empty_and_oversized_records(cuda_device):
     out, _, st = dec.decode_csv_matrix(dec.RecordBatch.from_messages(recs), [1, 1], raise_on_error=False)
     assert st.cpu().numpy().tolist() == [0, 7, 0]
     assert out.cpu().numpy()[[0, 2]].tolist() == [[1.0, 2.0], [3.0, 4.0]]
+
+
+@pytest.mark.parametrize("fmt", ["csv", "avro_a"])
+def test_host_end_to_end_path_matches_device_path(cuda_device, fmt):
+    """decode_score_host (pinned host buffers → chunked H2D overlapped with decode+score → D2H) == the device-resident call."""
+    m = _model18()
+    x = synth.sensor_rows(50_003, seed=123)
+    if fmt == "csv":
+        data, offs = synth.csv_batch(x, seed=3)
+        kw, skip = dict(csv_kinds=SENSOR_KINDS), 0
+    else:
+        data, offs = synth.avro_a_batch(x)
+        kw, skip = dict(avro_schema=schemas.schema_a_json()), 5
+    mse_d, flag_d, _, _ = dec.decode_score(m, dec.RecordBatch(data, offs, skip_prefix=skip), **kw)
+    hd, ho = torch.from_numpy(data).pin_memory(), torch.from_numpy(offs).pin_memory()
+    for reuse in (False, True, True):
+        mse_h, flag_h = dec.decode_score_host(m, hd, ho, skip_prefix=skip, reuse_output=reuse, **kw)
+        np.testing.assert_array_equal(mse_h, mse_d.cpu().numpy())
+        np.testing.assert_array_equal(flag_h, flag_d.cpu().numpy())
+    mse_h, flag_h = dec.decode_score_host(m, data[: offs[7]], offs[:8], skip_prefix=skip, chunks=16, **kw)  # more chunks than records/4
+    np.testing.assert_array_equal(mse_h, mse_d.cpu().numpy()[:7])
