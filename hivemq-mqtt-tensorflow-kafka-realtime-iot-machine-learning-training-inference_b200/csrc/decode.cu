@@ -127,11 +127,9 @@ __device__ __forceinline__ int csv_scan(const uint8_t* base, int b, int e, const
   *qmask = 0;
   // 32-bit SWAR: exact byte-equality for the delimiter; "any byte below ','" as a cheap superset of quote / CR / LF (blanks
   // and '+' also trip it — they only cost the careful path, they do not change the result)
-  for (int p = b & ~3; p < e; p += 4) {
+  // first and last word carry a byte mask for the record's edges; the words in between run the bare loop
+  auto word = [&](int p, uint32_t keep) {
     const uint32_t wv = *reinterpret_cast<const uint32_t*>(base + p);
-    uint32_t keep = 0x80808080u;
-    if (p < b) keep &= 0x80808080u << ((b - p) * 8);
-    if (p + 4 > e) keep &= 0x80808080u >> ((p + 4 - e) * 8);
     const uint32_t x = wv ^ d4;
     uint32_t m = ~(((x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | x) & keep;  // 0x80 where byte == delim
     special |= (wv - 0x2C2C2C2Cu) & ~wv & keep;                     // 0x80 where byte < 0x2C (may also flag a byte after one)
@@ -141,7 +139,18 @@ __device__ __forceinline__ int csv_scan(const uint8_t* base, int b, int e, const
       if (nf < c.n_fields) fb[nf] = (uint16_t)(p + k + 1);
       m &= m - 1;
     }
+  };
+  int p = b & ~3;
+  if (p < e) {
+    uint32_t keep = 0x80808080u << ((b - p) * 8);
+    if (p + 4 > e) keep &= 0x80808080u >> ((p + 4 - e) * 8);
+    word(p, keep);
+    p += 4;
   }
+  const int e4 = e & ~3;
+#pragma unroll 1
+  for (; p < e4; p += 4) word(p, 0x80808080u);
+  if (p < e) word(p, 0x80808080u >> ((p + 4 - e) * 8));
   if (special || c.delim < 0x2C) return csv_scan_slow(base, b, e, c, fb, qmask);  // quotes / CR / LF possible: careful sequential scan
   if (nf + 1 != c.n_fields) return B2_REC_FIELD_COUNT;
   fb[c.n_fields] = (uint16_t)(e + 1);
@@ -155,6 +164,12 @@ __device__ __forceinline__ int csv_scan(const uint8_t* base, int b, int e, const
 __device__ __forceinline__ uint32_t lds_u32_unaligned(const uint8_t* __restrict__ st, int off) {
   const uint32_t* wp = reinterpret_cast<const uint32_t*>(st + (off & ~3));
   return __funnelshift_r(wp[0], wp[1], (off & 3) * 8);
+}
+__device__ __forceinline__ unsigned long long lds_u64_unaligned(const uint8_t* __restrict__ st, int off) {
+  const uint32_t* wp = reinterpret_cast<const uint32_t*>(st + (off & ~3));
+  const uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2];
+  const int sh = (off & 3) * 8;
+  return (unsigned long long)__funnelshift_r(w0, w1, sh) | ((unsigned long long)__funnelshift_r(w1, w2, sh) << 32);
 }
 __device__ __forceinline__ bool csv_fast_token(const uint8_t* __restrict__ st, int b, int L, uint32_t* bits) {
   const uint32_t* wp = reinterpret_cast<const uint32_t*>(st + (b & ~3));
@@ -275,11 +290,22 @@ __device__ __forceinline__ int avro_decode_record(const uint8_t* __restrict__ ba
       }
       p += 4 * count;
     } else if (!nullable && (type == AV_INT || type == AV_LONG) && out0 >= 0) {
-      for (int j = 0; j < count; ++j) {  // one- and two-byte varints inline (tyre pressure, firmware), the rest in the general step
+      int j = 0;
+      for (; count - j >= 4; j += 4) {  // four one-byte varints (tyre pressures) in one word: no per-value loads or branches
+        const uint32_t w4 = lds_u32_unaligned(base, p);
+        if (w4 & 0x80808080u) break;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const uint32_t u = (w4 >> (8 * q)) & 0xFFu;
+          xrow[out0 + j + q] = __int2float_rn((int)(u >> 1) ^ -(int)(u & 1u));  // tf.cast(int32 → float32), cardata-v1.py:61-66
+        }
+        p += 4;
+      }
+      for (; j < count; ++j) {  // one- and two-byte varints inline (firmware), the rest in the general step
         const uint32_t w = lds_u32_unaligned(base, p);
         const uint32_t b0 = w & 0xFFu, b1 = (w >> 8) & 0xFFu;
         if (b0 < 0x80u) {
-          xrow[out0 + j] = __int2float_rn((int)(b0 >> 1) ^ -(int)(b0 & 1u));  // tf.cast(int32 → float32), cardata-v1.py:61-66
+          xrow[out0 + j] = __int2float_rn((int)(b0 >> 1) ^ -(int)(b0 & 1u));
           p += 1;
         } else if (b1 < 0x80u) {
           const uint32_t u = (b0 & 0x7Fu) | (b1 << 7);

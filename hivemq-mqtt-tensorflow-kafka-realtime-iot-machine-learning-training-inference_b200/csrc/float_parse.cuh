@@ -3,7 +3,9 @@
 // Replaces the per-field `safe_strtof` inside tf.io.decode_csv (reference call site:
 // python-scripts/autoencoder-anomaly-detection/Sensor-Kafka-Consumer-and-TensorFlow-Model-Training.py:32-34).
 // "Bit-exact to tf.io.decode_csv" means correctly rounded (round-to-nearest-even) binary32, which is also what
-// glibc strtof produces — the oracle.  A decimal→double→float shortcut double-rounds and is NOT used.
+// glibc strtof produces — the oracle.  A plain decimal→double→float shortcut double-rounds and is NOT used; the
+// double-precision step below (b2_dec32) is taken only when the double lands provably clear of every binary32 rounding
+// midpoint, and hands everything else to the Eisel-Lemire product.
 //
 // Method: scan digits into a 64-bit significand w (≤ 19 digits) and a decimal exponent q, then the Eisel-Lemire
 // product w × 5^q against a 128-bit table (pow5_table.inc) with the Mushtak-Lemire proof that no fallback is needed
@@ -30,15 +32,27 @@ namespace b2dev {
 #undef B2_POW5_DECL
 #define B2_POW5_DECL static __device__ const
 #include "pow5_table.inc"
+// 10^q as binary64, q = -22..22 (exact for q >= 0, correctly rounded reciprocals below)
+B2_POW5_DECL double b2_p10d[45] = {1e-22, 1e-21, 1e-20, 1e-19, 1e-18, 1e-17, 1e-16, 1e-15, 1e-14, 1e-13, 1e-12, 1e-11, 1e-10, 1e-9, 1e-8,
+                                   1e-7,  1e-6,  1e-5,  1e-4,  1e-3,  1e-2,  1e-1,  1e0,   1e1,   1e2,   1e3,   1e4,   1e5,   1e6,  1e7,
+                                   1e8,   1e9,   1e10,  1e11,  1e12,  1e13,  1e14,  1e15,  1e16,  1e17,  1e18,  1e19,  1e20,  1e21, 1e22};
 }  // namespace b2dev
 namespace b2host {
 #undef B2_POW5_DECL
 #define B2_POW5_DECL static const
 #include "pow5_table.inc"
+// 10^q as binary64, q = -22..22 (exact for q >= 0, correctly rounded reciprocals below)
+B2_POW5_DECL double b2_p10d[45] = {1e-22, 1e-21, 1e-20, 1e-19, 1e-18, 1e-17, 1e-16, 1e-15, 1e-14, 1e-13, 1e-12, 1e-11, 1e-10, 1e-9, 1e-8,
+                                   1e-7,  1e-6,  1e-5,  1e-4,  1e-3,  1e-2,  1e-1,  1e0,   1e1,   1e2,   1e3,   1e4,   1e5,   1e6,  1e7,
+                                   1e8,   1e9,   1e10,  1e11,  1e12,  1e13,  1e14,  1e15,  1e16,  1e17,  1e18,  1e19,  1e20,  1e21, 1e22};
 }  // namespace b2host
 #else
 namespace b2host {
 #include "pow5_table.inc"
+// 10^q as binary64, q = -22..22 (exact for q >= 0, correctly rounded reciprocals below)
+B2_POW5_DECL double b2_p10d[45] = {1e-22, 1e-21, 1e-20, 1e-19, 1e-18, 1e-17, 1e-16, 1e-15, 1e-14, 1e-13, 1e-12, 1e-11, 1e-10, 1e-9, 1e-8,
+                                   1e-7,  1e-6,  1e-5,  1e-4,  1e-3,  1e-2,  1e-1,  1e0,   1e1,   1e2,   1e3,   1e4,   1e5,   1e6,  1e7,
+                                   1e8,   1e9,   1e10,  1e11,  1e12,  1e13,  1e14,  1e15,  1e16,  1e17,  1e18,  1e19,  1e20,  1e21, 1e22};
 }
 #endif
 
@@ -110,6 +124,34 @@ B2_HD uint32_t b2_eisel_lemire32(uint64_t w, int q) {
   m &= ~(1ull << 23);
   if (p2 >= 0xFF) return 0x7F800000u;
   return ((uint32_t)p2 << 23) | (uint32_t)m;
+}
+
+// w × 10^q → binary32 bits, correctly rounded, with a binary64 short cut for the common case (w < 2^53, |q| ≤ 22):
+// d = RN(w · RN(10^q)) is within 2 ulp53 of the exact value v (one rounding in the table entry for q < 0, one in the product),
+// so RN32(d) = RN32(v) unless a binary32 midpoint lies within 2 ulp53 of d.  Midpoints in d's binade are the doubles whose low
+// 29 fraction bits read 0x10000000; when d's low bits are more than 4 away from that, the conversion of d is the answer.  With
+// w ≥ 1 and |q| ≤ 22 the result is a normal binary32 (1e-22 ≤ v < 2^53·1e22 < 2^127), so no range cases arise.
+B2_HD uint32_t b2_dec32(uint64_t w, int q) {
+  if (w < (1ull << 53) && q >= -22 && q <= 22) {
+#if defined(__CUDA_ARCH__)
+    const double d = __dmul_rn((double)w, b2dev::b2_p10d[q + 22]);
+    const uint32_t low = (uint32_t)__double2loint(d) & 0x1FFFFFFFu;
+    if (low - 0x0FFFFFFCu > 8u) return __float_as_uint(__double2float_rn(d));
+#else
+    volatile double dv = (double)w * b2host::b2_p10d[q + 22];
+    const double d = dv;
+    uint64_t bits;
+    __builtin_memcpy(&bits, &d, 8);
+    const uint32_t low = (uint32_t)bits & 0x1FFFFFFFu;
+    if (low - 0x0FFFFFFCu > 8u) {
+      const float f = (float)d;
+      uint32_t fb;
+      __builtin_memcpy(&fb, &f, 4);
+      return fb;
+    }
+#endif
+  }
+  return b2_eisel_lemire32(w, q);
 }
 
 B2_HD bool b2_is_digit(uint8_t c) { return (uint8_t)(c - '0') < 10; }
@@ -211,7 +253,7 @@ B2_HD int b2_parse_float(BytePtr s, int n, uint32_t* out) {
   }
   if (q < -400) q = -400;
   if (q > 400) q = 400;
-  const uint32_t a = b2_eisel_lemire32(w, q);
+  const uint32_t a = truncated ? b2_eisel_lemire32(w, q) : b2_dec32(w, q);
   if (truncated) {
     const uint32_t b = b2_eisel_lemire32(w + 1, q);
     if (a != b) return B2_NUM_TOO_LONG;
@@ -302,6 +344,6 @@ B2_HD bool b2_fast_token16(uint32_t t0, uint32_t t1, uint32_t t2, uint32_t t3, u
   const uint32_t hi8 = b2_four_digits(x0) * 10000u + b2_four_digits(x1);  // ≤ 99 999 999
   const uint64_t w = (uint64_t)hi8 * 10000u + b2_four_digits(x2);         // 12 digits, < 2^40
   const int q = ex - (Lm - has_dot - pd) - (12 - nd);                     // fraction digits and the padding zeros
-  *out = (neg ? 0x80000000u : 0u) | b2_eisel_lemire32(w, q);
+  *out = (neg ? 0x80000000u : 0u) | b2_dec32(w, q);
   return true;
 }

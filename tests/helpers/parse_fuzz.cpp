@@ -98,6 +98,29 @@ int main(int argc, char** argv) {
     else if (mode == 3) s += "E" + std::to_string((int)(g() % 700) - 350);
     check(s);
   }
+  // 2b. short tokens that ARE binary32 rounding midpoints (odd integers above 2^24, x.5 above 2^23, …) and their neighbours:
+  //     the binary64 short cut must hand exactly these to the Eisel-Lemire step
+  for (long long i = 0; i < n; ++i) {
+    const int e = 24 + (int)(g() % 10);                    // floats in [2^e, 2^(e+1)) are spaced 2^(e-23) apart
+    const uint64_t step = 1ull << (e - 23);
+    const uint64_t base = (1ull << e) + (g() % (1ull << 23)) * step;
+    const uint64_t mid = base + step / 2;
+    for (int dlt = -1; dlt <= 1; ++dlt) {
+      snprintf(buf, sizeof buf, "%llu", (unsigned long long)(mid + dlt));
+      check(buf);
+      snprintf(buf, sizeof buf, "%llu.0", (unsigned long long)(mid + dlt));
+      check(buf);
+    }
+    const uint64_t k = (1ull << 23) + (g() % (1ull << 23));  // 2^23 ≤ k < 2^24: spacing 1, k + 0.5 is a midpoint
+    snprintf(buf, sizeof buf, "%llu.5", (unsigned long long)k);
+    check(buf);
+    snprintf(buf, sizeof buf, "%llu.25", (unsigned long long)(k >> 1));  // spacing 0.5 → .25 is a midpoint
+    check(buf);
+    snprintf(buf, sizeof buf, "%llu.5E-1", (unsigned long long)(k * 10 + g() % 10));
+    check(buf);
+    snprintf(buf, sizeof buf, "%llu.125", (unsigned long long)(k >> 2));
+    check(buf);
+  }
   // 3. long digit strings (> 19 significant digits): must either match or be refused, never be wrong
   for (long long i = 0; i < n / 10; ++i) {
     std::string s;
