@@ -180,6 +180,99 @@ __device__ __forceinline__ bool csv_fast_token(const uint8_t* __restrict__ st, i
                          tail, L, bits);
 }
 
+// ---- CSV, common case: lock-step field walk --------------------------------------------------------------------------------
+// One record per thread; all lanes of a warp are at field f of their own record, so the field's kind / column / default are
+// uniform constant-bank reads.  A numeric field is parsed straight from the 16 bytes at the cursor (b2_csv_num16: the same byte
+// classification finds the field's end, so there is no separate delimiter scan); a skipped / string field is stepped over by
+// a delimiter search.  Returns B2_REC_OK, or -1 as soon as anything is not the plain grammar (quotes, blanks, '+', long tokens,
+// missing or surplus fields, an empty field without default): the caller then runs csv_record_careful on the record.
+__device__ __forceinline__ int csv_walk(const uint8_t* __restrict__ stage, int b, int e, const CsvP& c, float* __restrict__ xrow,
+                                        int32_t* __restrict__ span, int rel) {
+  if (c.delim < 0x2C) return -1;  // the "byte below ','" test for quotes / CR / LF below needs the delimiter above them
+  const uint32_t delim = (uint32_t)c.delim, d4 = delim * 0x01010101u;
+  int pos = b;
+  for (int f = 0; f < c.n_fields; ++f) {
+    int rem = e - pos;
+    if (rem < 0) return -1;  // the record ended with the previous field
+    const int kind = c.kind[f];
+    if (kind == 1) {
+      const uint32_t* wp = reinterpret_cast<const uint32_t*>(stage + (pos & ~3));
+      uint32_t bits = 0;
+      const int r = b2_csv_num16(wp[0], wp[1], wp[2], wp[3], wp[4], (pos & 3) * 8, rem, delim, &bits);
+      if (r < 0) return -1;
+      float v = __uint_as_float(bits);
+      if (r == 0) {
+        if (!c.has_default[f]) return -1;
+        v = c.dflt[f];
+      }
+      xrow[c.col[f]] = v;
+      pos += r + 1;
+    } else {
+      const int beg = pos;
+      for (;;) {
+        const uint32_t* wp = reinterpret_cast<const uint32_t*>(stage + (pos & ~3));
+        const int sh = (pos & 3) * 8;
+        const uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2], w3 = wp[3], w4 = wp[4];
+        const uint32_t t0 = __funnelshift_r(w0, w1, sh), t1 = __funnelshift_r(w1, w2, sh), t2 = __funnelshift_r(w2, w3, sh),
+                       t3 = __funnelshift_r(w3, w4, sh);
+        uint32_t m = b2_flagmap16(b2_eqbyte(t0, d4), b2_eqbyte(t1, d4), b2_eqbyte(t2, d4), b2_eqbyte(t3, d4)) | 0x10000u;
+        if (rem < 16) m |= 0xFFFFFFFFu << rem;
+        const int pz = __ffs((int)m) - 1;  // delimiter, record end, or 16 = keep looking
+        // bytes below ',' in front of it (quote, CR, LF, blank, …; a borrow may flag one byte too many — that only costs time)
+        const uint32_t sp = b2_flagmap16((t0 - 0x2C2C2C2Cu) & ~t0 & 0x80808080u, (t1 - 0x2C2C2C2Cu) & ~t1 & 0x80808080u,
+                                         (t2 - 0x2C2C2C2Cu) & ~t2 & 0x80808080u, (t3 - 0x2C2C2C2Cu) & ~t3 & 0x80808080u);
+        if (sp & ((1u << pz) - 1u)) return -1;
+        pos += pz;
+        if (pz < 16) break;
+        rem -= 16;
+      }
+      if (kind == 2 && span) {
+        span[2 * c.col[f]] = beg - rel;
+        span[2 * c.col[f] + 1] = pos - rel;
+      }
+      pos += 1;
+    }
+  }
+  return pos == e + 1 ? B2_REC_OK : -1;
+}
+
+// ---- CSV, everything else: full decode_csv grammar for one record ------------------------------------------------------------
+// Delimiter scan with RFC-4180 quotes (csv_scan), then field by field through the SWAR token parser or the general one.
+__device__ __noinline__ int csv_record_careful(const uint8_t* __restrict__ stage, int b, int e, const CsvP& c, float* __restrict__ xrow,
+                                               int32_t* __restrict__ span, int rel) {
+  uint16_t fb[B2_MAX_FIELDS + 1];
+  unsigned long long qm = 0;
+  int st = csv_scan(stage, b, e, c, fb, &qm);
+  if (st != B2_REC_OK) return st;
+  for (int f = 0; f < c.n_fields; ++f) {
+    if (c.kind[f] == 0) continue;
+    // a quoted field's payload sits between its quotes: drop its closing quote and, when the NEXT field is quoted too, that
+    // field's opening quote (fb[] holds payload starts)
+    const int quoted = (int)((qm >> f) & 1ull) + (int)((qm >> (f + 1)) & 1ull);
+    const int fbeg = fb[f], fend = (int)fb[f + 1] - 1 - quoted;
+    if (c.kind[f] == 1) {
+      float v = 0.f;
+      if (fend <= fbeg) {
+        if (c.has_default[f]) v = c.dflt[f];
+        else st = max(st, (int)B2_REC_EMPTY_FIELD);
+      } else {
+        uint32_t bits = 0;
+        if (!csv_fast_token(stage, fbeg, fend - fbeg, &bits)) {
+          const int ps = b2_parse_float(stage + fbeg, fend - fbeg, &bits);
+          if (ps == B2_NUM_BAD) st = max(st, (int)B2_REC_BAD_NUMBER);
+          else if (ps == B2_NUM_TOO_LONG) st = max(st, (int)B2_REC_TOO_LONG);
+        }
+        v = __uint_as_float(bits);
+      }
+      xrow[c.col[f]] = v;
+    } else if (span) {
+      span[2 * c.col[f]] = fbeg - rel;
+      span[2 * c.col[f] + 1] = fend - rel;
+    }
+  }
+  return st;
+}
+
 // ---- Avro: one record per thread, whole walk -------------------------------------------------------------------------------
 // Every thread of a warp is at the same field of its own record, so the field descriptor is a uniform constant-bank read and
 // the type switch does not diverge; values are fetched with two aligned 32-bit loads + a funnel shift instead of byte loads.
@@ -369,42 +462,20 @@ __device__ __forceinline__ int avro_decode_record(const uint8_t* __restrict__ ba
 template <int D, int MODE, bool FT>
 __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ DecodeArgs<D> a) {
   extern __shared__ __align__(128) uint8_t smem[];
-  // carve: [stage bytes | offsets (TILE+1) | status (TILE) | qmask/present (TILE) | label (TILE) | mbarrier | fb | xt]
+  // carve: [stage bytes | offsets (TILE+1) x2 | status (TILE) | label (TILE) | mbarrier | xt]
   uint8_t* stage = smem + 16;  // 16-byte apron in front: the token-tail load may start up to 3 bytes before the first token
   int32_t* s_offs = reinterpret_cast<int32_t*>(smem + a.stage_cap + 64);
   int32_t* s_offs2 = s_offs + DEC_TILE + 4;
   int32_t* s_stat = s_offs2 + DEC_TILE + 4;
-  unsigned long long* s_qm = reinterpret_cast<unsigned long long*>(s_stat + DEC_TILE);
-  uint8_t* s_lab = reinterpret_cast<uint8_t*>(s_qm + DEC_TILE);
+  uint8_t* s_lab = reinterpret_cast<uint8_t*>(s_stat + DEC_TILE);
   uint64_t* full = reinterpret_cast<uint64_t*>(s_lab + DEC_TILE);
-  const int fb_stride = a.fmt == FMT_CSV ? a.csv.n_fields + 1 : 0;
-  // per-field tables re-staged in shared memory: phase B indexes them with a per-thread field number, and a divergent
-  // index into the constant bank (kernel parameters) is serialised address by address
-  uint8_t* t_kind = reinterpret_cast<uint8_t*>(full + 2);  // CSV kind / Avro type
-  uint8_t* t_col = t_kind + 64;                            // output column (Avro: int8 out)
-  uint8_t* t_fidx = t_col + 64;                            // k-th value-producing field → field index
-  uint8_t* t_hasd = t_fidx + 64;                           // CSV has_default
-  float* t_dflt = reinterpret_cast<float*>(t_hasd + 64);   // CSV default value
-  uint16_t* s_fb = reinterpret_cast<uint16_t*>(t_dflt + 64);
   const int xt_stride = MODE == 1 ? D : a.n_out;
-  float* s_xt = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(s_fb) + (((size_t)DEC_TILE * fb_stride * 2 + 15) & ~(size_t)15));
+  float* s_xt = reinterpret_cast<float*>(full + 2);
 
   const int tid = threadIdx.x;
   if (tid == 0) {
     mbar_init(&full[0], 1);
     mbar_fence_init();
-  }
-  if (tid < 64) {
-    if (a.fmt == FMT_CSV) {
-      t_kind[tid] = a.csv.kind[tid];
-      t_col[tid] = a.csv.col[tid];
-      t_fidx[tid] = a.csv.fidx[tid];
-      t_hasd[tid] = a.csv.has_default[tid];
-      t_dflt[tid] = a.csv.dflt[tid];
-    } else {
-      t_kind[tid] = (uint8_t)a.avro.f[tid].type;
-      t_col[tid] = (uint8_t)a.avro.f[tid].out;
-    }
   }
   __syncthreads();
   uint32_t phase = 0;
@@ -491,7 +562,10 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
         int st;
         uint8_t lab = 2;
         if (a.fmt == FMT_CSV) {
-          st = csv_scan(stage, b, e, a.csv, s_fb + (size_t)tid * fb_stride, &s_qm[tid]);
+          float* xrow = s_xt + (size_t)tid * xt_stride;
+          int32_t* sp = (MODE == 0 && a.span) ? a.span + (row0 + sub + tid) * a.csv.n_str * 2 : nullptr;
+          st = csv_walk(stage, b, e, a.csv, xrow, sp, rel);
+          if (st < 0) st = csv_record_careful(stage, b, e, a.csv, xrow, sp, rel);
         } else {
           float* xrow = s_xt + (size_t)tid * xt_stride;
           if (!a.avro.all_routed)
@@ -500,48 +574,6 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
         }
         s_stat[tid] = st;
         s_lab[tid] = lab;
-      }
-      __syncthreads();
-      // ---- phase B: one task per (record, value-producing field) ----
-      if (a.fmt == FMT_CSV) {  // (Avro needs no phase B: its walk already produced the values)
-        // flat (record, field) tasks; (r, k) advance incrementally by DEC_NT tasks — no division in the loop
-        const int per_rec = a.csv.n_float + a.csv.n_str;
-        const int dq = DEC_NT / per_rec, dr = DEC_NT - dq * per_rec;
-        int r = tid / per_rec, k = tid - r * per_rec;
-        {
-          for (; r < cnt; r += dq, k += dr, r += (k >= per_rec), k -= (k >= per_rec) ? per_rec : 0) {
-            if (s_stat[r] != B2_REC_OK) continue;
-            const int f = t_fidx[k];
-            const uint16_t* fb = s_fb + (size_t)r * fb_stride;
-            // a quoted field's payload sits between its quotes: drop its closing quote and, when the NEXT field is quoted
-            // too, that field's opening quote (fb[] holds payload starts)
-            const unsigned long long qm = s_qm[r];
-            const int quoted = (int)((qm >> f) & 1ull) + (int)((qm >> (f + 1)) & 1ull);
-            const int fbeg = fb[f], fend = (int)fb[f + 1] - 1 - quoted;
-            if (t_kind[f] == 1) {
-              float v;
-              int st = B2_REC_OK;
-              if (fend <= fbeg) {
-                if (t_hasd[f]) v = t_dflt[f];
-                else st = B2_REC_EMPTY_FIELD, v = 0.f;
-              } else {
-                uint32_t bits = 0;
-                if (!csv_fast_token(stage, fbeg, fend - fbeg, &bits)) {
-                  const int ps = b2_parse_float(stage + fbeg, fend - fbeg, &bits);
-                  if (ps == B2_NUM_BAD) st = B2_REC_BAD_NUMBER;
-                  else if (ps == B2_NUM_TOO_LONG) st = B2_REC_TOO_LONG;
-                }
-                v = __uint_as_float(bits);
-              }
-              if (st != B2_REC_OK) atomicMax(&s_stat[r], st);
-              s_xt[(size_t)r * xt_stride + t_col[f]] = v;
-            } else if (MODE == 0 && a.span) {
-              int32_t* sp = a.span + ((row0 + sub + r) * a.csv.n_str + t_col[f]) * 2;
-              sp[0] = fbeg - rel;
-              sp[1] = fend - rel;
-            }
-          }
-        }
       }
       }
       __syncthreads();  // stage consumed (and the next tile's offsets are in place)
@@ -708,22 +740,18 @@ static int avro_max_record_bytes(const AvroP& a) {
   return n;
 }
 
-static size_t decode_smem_bytes(int stage_cap, int fb_stride, int xt_stride) {
+static size_t decode_smem_bytes(int stage_cap, int xt_stride) {
   size_t s = (size_t)stage_cap + 64;
   s += 2 * sizeof(int32_t) * (DEC_TILE + 4);       // offsets (double-buffered)
   s += sizeof(int32_t) * DEC_TILE;                 // status
-  s += sizeof(unsigned long long) * DEC_TILE;      // qmask
   s += DEC_TILE;                                   // label
   s += 2 * sizeof(uint64_t);                       // mbarrier
-  s += 4 * 64 + 64 * sizeof(float);                // per-field tables
-  s += ((size_t)DEC_TILE * fb_stride * 2 + 15) & ~(size_t)15;
   s += (size_t)DEC_TILE * xt_stride * 4;
   return s + 64;
 }
 
 template <int D, int MODE, bool FT>
 static int launch_decode(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stream) {
-  const int fb_stride = args.fmt == FMT_CSV ? args.csv.n_fields + 1 : 0;
   const int xt_stride = MODE == 1 ? D : args.n_out;
   // byte stage: 48 KB unless the schema bounds the record size (Avro without strings) — a smaller stage means more CTAs/SM
   args.stage_cap = STAGE_CAP_MAX;
@@ -732,7 +760,7 @@ static int launch_decode(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stream) 
     if (mx > 0) args.stage_cap = min(STAGE_CAP_MAX, ((mx * DEC_TILE + 31) & ~15));
     else args.stage_cap = 40 * 1024;
   }
-  const size_t smem = decode_smem_bytes(args.stage_cap, fb_stride, xt_stride);
+  const size_t smem = decode_smem_bytes(args.stage_cap, xt_stride);
   B2_REQUIRE(smem <= (size_t)ctx->smem_optin, "decode: tile needs %zu bytes of shared memory (max %d)", smem, ctx->smem_optin);
   auto kern = decode_kernel<D, MODE, FT>;
   B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -347,3 +347,118 @@ B2_HD bool b2_fast_token16(uint32_t t0, uint32_t t1, uint32_t t2, uint32_t t3, u
   *out = (neg ? 0x80000000u : 0u) | b2_dec32(w, q);
   return true;
 }
+
+// ---- CSV numeric field straight from the byte stream (the decode kernel's lock-step field walk) ---------------------------
+// The 16 bytes starting at a field's first byte arrive as five aligned little-endian words + the byte shift `sh` ((pos & 3) * 8);
+// `rem` is the number of bytes left in the record from that position, `delim` the field delimiter.  One pass classifies every
+// byte as digit / not-a-digit (a 16-bit map), so the field's end, the decimal point and an exponent are found with bit tricks
+// instead of a separate delimiter scan, and only a strict grammar is accepted:
+//      [-] digits [. digits] [ E|e [-] d [d] ]   followed by the delimiter or the record's end, at most 12 mantissa characters.
+// Returns the number of characters in the field (sign included; the caller steps over them and the delimiter) with *bits set;
+// 0 for an empty field; -1 for anything else ('+', blanks, quotes, inf/nan, long tokens, …) — the caller then re-does the whole
+// record on the careful path, which applies the full decode_csv grammar.  When it accepts, the value is bit-identical to
+// b2_parse_float's (same digits → same b2_dec32).
+B2_HD uint32_t b2_byte16(uint32_t t0, uint32_t t1, uint32_t t2, uint32_t t3, int k) {  // byte k (0..15) of t3:t2:t1:t0
+#if defined(__CUDA_ARCH__)
+  const uint32_t lo = (k & 8) ? t2 : t0, hi = (k & 8) ? t3 : t1;
+  return __byte_perm(lo, hi, (uint32_t)(k & 7)) & 0xFFu;
+#else
+  const uint32_t w = k < 4 ? t0 : (k < 8 ? t1 : (k < 12 ? t2 : t3));
+  return (w >> ((k & 3) * 8)) & 0xFFu;
+#endif
+}
+B2_HD uint32_t b2_flagmap16(uint32_t f0, uint32_t f1, uint32_t f2, uint32_t f3) {  // 0x80-per-byte flags of 4 words → 16-bit map
+#if defined(__CUDA_ARCH__)
+  const uint32_t lo = __dp4a(f1 >> 7, 0x80402010u, __dp4a(f0 >> 7, 0x08040201u, 0u));
+  const uint32_t hi = __dp4a(f3 >> 7, 0x80402010u, __dp4a(f2 >> 7, 0x08040201u, 0u));
+  return lo | (hi << 8);
+#else
+  const uint32_t M = 0x00204081u;
+  return ((((f0 >> 7) * M) >> 21) & 0xFu) | ((((f1 >> 7) * M) >> 17) & 0xF0u) | ((((f2 >> 7) * M) >> 13) & 0xF00u) |
+         ((((f3 >> 7) * M) >> 9) & 0xF000u);
+#endif
+}
+B2_HD int b2_ffs32(uint32_t m) {  // 1-based index of the lowest set bit, 0 for m == 0
+#if defined(__CUDA_ARCH__)
+  return __ffs((int)m);
+#else
+  return __builtin_ffs((int)m);
+#endif
+}
+B2_HD uint32_t b2_four_digits_fast(uint32_t x) {  // like b2_four_digits; two byte-dot-products on the device
+#if defined(__CUDA_ARCH__)
+  return __dp4a(x, 0x0000010Au, 0u) * 100u + __dp4a(x, 0x010A0000u, 0u);
+#else
+  return b2_four_digits(x);
+#endif
+}
+
+B2_HD int b2_csv_num16(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, uint32_t w4, int sh, int rem, uint32_t delim, uint32_t* out) {
+  const int neg = (((w0 >> sh) & 0xFFu) == '-' && rem > 0) ? 1 : 0;
+  const int s = sh + 8 * neg;  // ≤ 32: the clamped funnel shift returns the upper word for 32
+  const uint32_t t0 = b2_fsr(w0, w1, s), t1 = b2_fsr(w1, w2, s), t2 = b2_fsr(w2, w3, s), t3 = b2_fsr(w3, w4, s);
+  rem -= neg;
+  const uint32_t x0 = t0 ^ 0x30303030u, x1 = t1 ^ 0x30303030u, x2 = t2 ^ 0x30303030u, x3 = t3 ^ 0x30303030u;
+  // not-a-digit flags; a byte ≥ 0xBA may carry a false flag into its successor, which only ever sends a record to the careful path
+  uint32_t B = b2_flagmap16(b2_nondigit(x0), b2_nondigit(x1), b2_nondigit(x2), b2_nondigit(x3)) | 0x10000u;
+  if (rem < 16) B |= 0xFFFFFFFFu << rem;  // everything from the record's end on terminates the field
+  const int p1 = b2_ffs32(B) - 1;
+  if (p1 >= 16) return -1;
+  const uint32_t c1 = b2_byte16(t0, t1, t2, t3, p1);
+  int Lm, pd, has_dot, ex = 0, L;
+  if (p1 >= rem || c1 == delim) {
+    if (p1 == 0) return neg ? -1 : 0;  // empty field ("-" alone is not a number)
+    Lm = pd = L = p1;
+    has_dot = 0;
+  } else {
+    int pe = -1;
+    if (c1 == '.') {
+      B &= B - 1;
+      const int p2 = b2_ffs32(B) - 1;
+      if (p2 >= 16) return -1;
+      const uint32_t c2 = b2_byte16(t0, t1, t2, t3, p2);
+      pd = p1;
+      has_dot = 1;
+      Lm = L = p2;
+      if (!(p2 >= rem || c2 == delim)) {
+        if ((c2 | 0x20u) != 'e') return -1;
+        pe = p2;
+      }
+    } else if ((c1 | 0x20u) == 'e') {
+      pe = Lm = pd = p1;
+      has_dot = 0;
+    } else {
+      return -1;
+    }
+    if (pe >= 0) {  // exponent (rare for sensor values: Float.toString switches to E notation below 1e-3 and from 1e7)
+      uint32_t Be = B & (B - 1);  // flags after the 'E'
+      int es = pe + 1;
+      if (es >= 16) return -1;
+      const bool eneg = es < rem && b2_byte16(t0, t1, t2, t3, es) == '-';
+      if (eneg) {
+        Be &= Be - 1;
+        ++es;
+      }
+      const int p3 = b2_ffs32(Be) - 1;
+      const int ne = p3 - es;
+      if (p3 >= 16 || ne < 1 || ne > 2) return -1;
+      if (!(p3 >= rem || b2_byte16(t0, t1, t2, t3, p3) == delim)) return -1;
+      ex = (int)b2_byte16(t0, t1, t2, t3, es) - '0';
+      if (ne == 2) ex = ex * 10 + (int)b2_byte16(t0, t1, t2, t3, es + 1) - '0';
+      if (eneg) ex = -ex;
+      L = p3;
+    }
+  }
+  const int nd = Lm - has_dot;  // digit characters
+  if (nd < 1 || Lm > 12) return -1;
+  // squeeze the dot out (bytes after it move down by one) and zero everything from digit nd on: 12 digits, zero-padded on the right
+  const uint32_t u0 = b2_fsr(x0, x1, 8), u1 = b2_fsr(x1, x2, 8), u2 = x2 >> 8;
+  const uint32_t a0 = b2_bytemask(pd), a1 = b2_bytemask(pd - 4), a2 = b2_bytemask(pd - 8);
+  const uint32_t k0 = b2_bytemask(nd), k1 = b2_bytemask(nd - 4), k2 = b2_bytemask(nd - 8);
+  const uint32_t r0 = ((x0 & a0) | (u0 & ~a0)) & k0, r1 = ((x1 & a1) | (u1 & ~a1)) & k1, r2 = ((x2 & a2) | (u2 & ~a2)) & k2;
+  const uint32_t hi8 = b2_four_digits_fast(r0) * 10000u + b2_four_digits_fast(r1);
+  const uint64_t w = (uint64_t)hi8 * 10000u + b2_four_digits_fast(r2);
+  const int q = ex - (nd - pd) - (12 - nd);  // fraction digits and the padding zeros
+  *out = (neg ? 0x80000000u : 0u) | b2_dec32(w, q);
+  return L + neg;
+}

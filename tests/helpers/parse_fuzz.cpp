@@ -34,6 +34,33 @@ static void check_fast(const std::string& tok, uint32_t ref_bits, bool ref_ok) {
   }
 }
 
+// the lock-step field walk's parser sees the raw byte stream: token at any alignment, then either the delimiter and more
+// bytes, or the record's end with foreign bytes behind it
+static long long num16_hits = 0;
+static void check_num16(const std::string& tok, uint32_t ref_bits, bool ref_ok) {
+  if (tok.find(',') != std::string::npos) return;  // a delimiter inside the token is a different field split, not a parse question
+  static unsigned variant = 0;
+  ++variant;
+  alignas(4) unsigned char buf[96];
+  for (int i = 0; i < 96; ++i) buf[i] = (unsigned char)("7,-\"9E-.5 \xC3"[(i + variant) % 11]);  // hostile neighbours
+  const int b = 4 + (int)(variant % 4);
+  memcpy(buf + b, tok.data(), tok.size());
+  const bool at_end = (variant / 4) % 2;
+  if (!at_end) buf[b + tok.size()] = ',';
+  const int rem = at_end ? (int)tok.size() : (int)tok.size() + 1 + (int)(variant % 7);
+  uint32_t w[5];
+  memcpy(w, buf + (b & ~3), 20);
+  uint32_t got = 0;
+  const int r = b2_csv_num16(w[0], w[1], w[2], w[3], w[4], (b & 3) * 8, rem, ',', &got);
+  if (r < 0) return;
+  ++num16_hits;
+  const bool good = tok.empty() ? r == 0 : (r == (int)tok.size() && ref_ok && got == ref_bits);
+  if (!good) {
+    if (bad < 20) fprintf(stderr, "NUM16 MISMATCH '%s' r=%d got 0x%08x ref ok=%d 0x%08x\n", tok.c_str(), r, got, (int)ref_ok, ref_bits);
+    ++bad;
+  }
+}
+
 static void check(const std::string& tok) {
   uint32_t got = 0;
   const int st = b2_parse_float((const uint8_t*)tok.data(), (int)tok.size(), &got);
@@ -50,6 +77,7 @@ static void check(const std::string& tok) {
   const bool hex = t.find('x') != std::string::npos || t.find('X') != std::string::npos;
   const bool ref_ok = !t.empty() && !hex && end == t.c_str() + t.size() && t.find_first_not_of(" \t") != std::string::npos;
   check_fast(tok, ref, ref_ok && !isnan(f));
+  check_num16(tok, ref, ref_ok && !isnan(f));
   if ((st == B2_NUM_OK) != ref_ok || (ref_ok && got != ref && !(isnan(f) && (got & 0x7FFFFFFF) > 0x7F800000))) {
     if (bad < 20) fprintf(stderr, "MISMATCH '%s' got st=%d 0x%08x ref ok=%d 0x%08x\n", tok.c_str(), st, got, (int)ref_ok, ref);
     ++bad;
@@ -167,6 +195,6 @@ int main(int argc, char** argv) {
     else if (mode == 4) s += "e-" + std::to_string(10 + (int)(g() % 36));
     check(s);
   }
-  printf("mismatches=%lld checked=%lld fast_path_hits=%lld\n", bad, checked, fast_hits);
+  printf("mismatches=%lld checked=%lld fast_path_hits=%lld num16_hits=%lld\n", bad, checked, fast_hits, num16_hits);
   return bad ? 1 : 0;
 }
