@@ -345,6 +345,49 @@ def aux_fit(dev):
             "reference_published": {"us_per_sample": 16.0, "source": "nb2.0:653-853 (MacBook CPU, TF 2.0.0-alpha0)"}}
 
 
+def aux_format_rows(dev):
+    """SURVEY §8 a12 / f1: np.array2string(row) for 2^20 reconstruction-like rows (relu outputs, 18 wide), device resident;
+    the reference does this per row in Python (cardata-v1.py:218-224) — NumPy timed on a bounded sample beside it."""
+    import numpy as np
+    import torch
+
+    import b200_sensor as bs
+
+    n, d = 1 << 20, 18
+    g = torch.Generator(device=dev).manual_seed(314)
+    x = torch.relu(torch.randn((n, d), device=dev, generator=g) * 0.5 + 0.3)
+    lib = bs._ffi.lib()
+    bound = int(lib.b2_format_rows_bound(d))
+    text = torch.empty(n * bound, dtype=torch.uint8, device=dev)
+    offs = torch.empty(n, dtype=torch.int64, device=dev)
+    lens = torch.empty(n, dtype=torch.int32, device=dev)
+    cur = torch.zeros(2, dtype=torch.int64, device=dev)
+    ctx, st = bs.keras_compat.get_ctx(dev.index), torch.cuda.current_stream().cuda_stream
+    compat = bs.sink.installed_numpy_compat()
+
+    def launch():
+        cur.zero_()
+        bs._ffi.check(lib.b2_format_rows(ctx, x.data_ptr(), n, d, compat, text.data_ptr(), text.numel(), offs.data_ptr(),
+                                         lens.data_ptr(), cur.data_ptr(), st))
+
+    for _ in range(3):
+        launch()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(10):
+        launch()
+    e1.record()
+    torch.cuda.synchronize()
+    dt = e0.elapsed_time(e1) * 1e-3 / 10
+    used = int(cur[0].item())
+    xs = x[:20000].cpu().numpy()
+    t0 = time.perf_counter()
+    ref = [np.array2string(r) for r in xs]
+    t_np = time.perf_counter() - t0
+    return {"value": n / dt, "unit": "rows/s", "text_bytes_per_row": used / n, "gb_per_s_out": used / dt / 1e9,
+            "kernel": "format_rows_kernel", "numpy_array2string_rows_per_s_1core": len(ref) / t_np, "numpy": np.__version__}
+
+
 def aux_lstm(dev, T):
     """BASELINE.json configs[4]: LSTM stack forward on synthetic sequences (B = 2^20 / T)."""
     import torch
@@ -564,6 +607,7 @@ def main():
             also["fit_d30_batch128"] = aux_fit(dev)
             also["lstm_forward_T1"] = aux_lstm(dev, 1)
             also["lstm_forward_T16"] = aux_lstm(dev, 16)
+            also["format_rows_d18"] = aux_format_rows(dev)
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
                 "data": "synthetic", "config": config, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,

@@ -33,6 +33,7 @@ struct LstmArgs {
   const float* x;
   float* y;
   long long batch;
+  long long seq_stride;  // rows between sequence starts (T, or the window shift)
   int T, F;
   int u1, u2, u3, u4;
   const float* packed;
@@ -143,7 +144,7 @@ __global__ void __launch_bounds__(LS_NT, 1) lstm_forward_kernel(const __grid_con
     auto load_x = [&](int t) {
       for (int i = tid; i < LS_SEQ * F; i += LS_NT) {
         const int seq = i / F, f = i - seq * F;
-        xr[f * LS_SEQ + seq] = seq < nseq ? __ldg(a.x + ((b0 + seq) * a.T + t) * F + f) : 0.f;
+        xr[f * LS_SEQ + seq] = seq < nseq ? __ldg(a.x + ((b0 + seq) * a.seq_stride + t) * F + f) : 0.f;
       }
     };
     // ---- phase 1: encoder LSTMs over the whole sequence ----
@@ -282,23 +283,21 @@ extern "C" void b2_lstm_destroy(b2_lstm* m) {
 
 extern "C" int b2_lstm_param_count(const b2_lstm* m) { return m ? m->n_params : 0; }
 
-extern "C" int b2_lstm_forward(b2_lstm* m, const float* x_dev, int64_t batch, int timesteps, float* y_dev, void* stream) {
-  B2_REQUIRE(m && x_dev && y_dev, "b2_lstm_forward: NULL argument");
-  B2_REQUIRE(batch >= 0 && timesteps >= 1, "b2_lstm_forward: batch=%lld timesteps=%d", (long long)batch, timesteps);
-  if (batch == 0) return B2_OK;
+static int lstm_launch(b2_lstm* m, const float* x_dev, int64_t batch, int timesteps, int64_t seq_stride, float* y_dev, void* stream) {
   DeviceGuard g(m->ctx->device);
   {
     // default: tensor-core kernel (tcgen05, split-precision TF32, within the 1e-4 parity budget); B2_LSTM_TC=0 → FP32 FMA kernel
     const char* env = getenv("B2_LSTM_TC");
     const bool want_tc = !(env && env[0] == '0');
     if (want_tc && m->tc_floats > 0)
-      return b2_lstm_tc_launch(m->ctx, m->d_packed_tc, m->tc_floats, m->tc_layers, m->desc.features, x_dev, batch, timesteps, y_dev,
-                               (cudaStream_t)stream);
+      return b2_lstm_tc_launch(m->ctx, m->d_packed_tc, m->tc_floats, m->tc_layers, m->desc.features, x_dev, batch, timesteps, seq_stride,
+                               y_dev, (cudaStream_t)stream);
   }
   LstmArgs a;
   a.x = x_dev;
   a.y = y_dev;
   a.batch = batch;
+  a.seq_stride = seq_stride;
   a.T = timesteps;
   a.F = m->desc.features;
   a.u1 = 32, a.u2 = 16, a.u3 = 16, a.u4 = 32;
@@ -313,4 +312,27 @@ extern "C" int b2_lstm_forward(b2_lstm* m, const float* x_dev, int64_t batch, in
   lstm_forward_kernel<<<(unsigned)grid, LS_NT, smem, (cudaStream_t)stream>>>(a);
   B2_CUDA(cudaGetLastError());
   return B2_OK;
+}
+
+extern "C" int b2_lstm_forward(b2_lstm* m, const float* x_dev, int64_t batch, int timesteps, float* y_dev, void* stream) {
+  B2_REQUIRE(m && x_dev && y_dev, "b2_lstm_forward: NULL argument");
+  B2_REQUIRE(batch >= 0 && timesteps >= 1, "b2_lstm_forward: batch=%lld timesteps=%d", (long long)batch, timesteps);
+  if (batch == 0) return B2_OK;
+  return lstm_launch(m, x_dev, batch, timesteps, timesteps, y_dev, stream);
+}
+
+extern "C" int64_t b2_lstm_window_count(int64_t n_rows, int look_back, int shift) {
+  if (look_back < 1 || shift < 1 || n_rows < look_back) return 0;
+  return (n_rows - look_back) / shift + 1;
+}
+
+extern "C" int b2_lstm_forward_windows(b2_lstm* m, const float* rows_dev, int64_t n_rows, int look_back, int shift, float* y_dev,
+                                       void* stream) {
+  B2_REQUIRE(m, "b2_lstm_forward_windows: NULL model");
+  B2_REQUIRE(n_rows >= 0 && look_back >= 1 && shift >= 1, "b2_lstm_forward_windows: n_rows=%lld look_back=%d shift=%d", (long long)n_rows,
+             look_back, shift);
+  const int64_t nw = b2_lstm_window_count(n_rows, look_back, shift);
+  if (nw == 0) return B2_OK;  // fewer rows than one window (drop_remainder)
+  B2_REQUIRE(rows_dev && y_dev, "b2_lstm_forward_windows: NULL device pointer");
+  return lstm_launch(m, rows_dev, nw, look_back, shift, y_dev, stream);
 }

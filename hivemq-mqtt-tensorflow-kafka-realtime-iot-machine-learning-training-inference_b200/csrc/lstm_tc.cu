@@ -26,6 +26,7 @@ struct LstmTcArgs {
   const float* x;
   float* y;
   long long batch;
+  long long seq_stride;  // rows between the starts of consecutive sequences: T for [B,T,F] input, `shift` for sliding windows
   int T, F;
   const float* packed;  // [Σ 2·N·K] canonical-layout weights (hi, lo) for L1, L2, L3, L4, Dense
   int packed_floats;
@@ -220,7 +221,7 @@ __global__ void __launch_bounds__(TC_NT, 1) lstm_forward_tc_kernel(const __grid_
       for (int i = 0; i < 24; ++i) xv[i] = 0.f;
       xv[0] = 1.0f;
       if (live) {
-        const float* xp = a.x + (seq * a.T + t) * F;
+        const float* xp = a.x + (seq * a.seq_stride + t) * F;
         for (int f = 0; f < F; ++f) xv[6 + f] = __ldg(xp + f);
       }
       a_store<16>(lane_base, 0, xv);
@@ -335,11 +336,12 @@ int b2_lstm_tc_pack(const b2_lstm_desc* desc, const float* w, std::vector<float>
 }
 
 int b2_lstm_tc_launch(b2_ctx* ctx, const float* d_packed, int packed_floats, const TcLayer (&layers)[5], int F, const float* x, int64_t batch,
-                      int T, float* y, cudaStream_t stream) {
+                      int T, int64_t seq_stride, float* y, cudaStream_t stream) {
   LstmTcArgs a;
   a.x = x;
   a.y = y;
   a.batch = batch;
+  a.seq_stride = seq_stride;
   a.T = T;
   a.F = F;
   a.packed = d_packed;

@@ -13,4 +13,4 @@ struct TcLayer {
 // returns 0 and fills `packed` / `layers` when the stack fits the tensor-core kernel (features ≤ 18, units 32-16-16-32)
 int b2_lstm_tc_pack(const b2_lstm_desc* desc, const float* host_weights, std::vector<float>& packed, TcLayer (&layers)[5]);
 int b2_lstm_tc_launch(b2_ctx* ctx, const float* d_packed, int packed_floats, const TcLayer (&layers)[5], int F, const float* x, int64_t batch,
-                      int T, float* y, cudaStream_t stream);
+                      int T, int64_t seq_stride, float* y, cudaStream_t stream);

@@ -145,6 +145,33 @@ class History:
         self.history: Dict[str, List[float]] = {}
 
 
+
+class Windows:
+    """``dataset.window(look_back, shift=1, drop_remainder=True).flat_map(lambda w: w.batch(look_back))``
+    (LSTM-…/cardata-v1.py:184-185) as a *view*: it keeps the row stream ``rows[N, features]`` and the window geometry;
+    ``Model.predict(Windows(...))`` hands both to ``b2_lstm_forward_windows`` so the kernel reads every window in place.
+    ``targets()`` is the script's ``dataset.skip(look_back)`` (:189), truncated like ``Dataset.zip``; ``numpy()`` materialises
+    the windows (for tests and small inputs)."""
+
+    def __init__(self, rows, look_back: int, shift: int = 1):
+        if look_back < 1 or shift < 1:
+            raise ValueError("look_back and shift must be >= 1")
+        self.rows, self.look_back, self.shift = rows, int(look_back), int(shift)
+
+    def __len__(self):
+        n = int(self.rows.shape[0])
+        return 0 if n < self.look_back else (n - self.look_back) // self.shift + 1
+
+    def numpy(self):
+        r = self.rows.detach().cpu().numpy() if isinstance(self.rows, torch.Tensor) else np.asarray(self.rows)
+        idx = np.arange(len(self))[:, None] * self.shift + np.arange(self.look_back)[None, :]
+        return r[idx]
+
+    def targets(self):
+        r = self.rows.detach().cpu().numpy() if isinstance(self.rows, torch.Tensor) else np.asarray(self.rows)
+        y = r[self.look_back:]
+        return y[:min(len(y), len(self))][:, None, :]
+
 class ModelCheckpoint(Callback):
     """``ModelCheckpoint(filepath, save_best_only=True)`` on val_loss (nb2.0:862-864)."""
 
@@ -421,6 +448,21 @@ class Model:
         TF 2.0.0's predict loop feeds the reference's OutputCallback (cardata-v1.py:218-224)."""
         self._ensure_built()
         dev = torch.device("cuda", self._device_index())
+        if isinstance(x, Windows):
+            if self.kind == "dense":
+                raise ValueError("Windows input is for the LSTM model")
+            if x.look_back != self.look_back:
+                raise ValueError(f"model was built with look_back={self.look_back}, got windows of {x.look_back}")
+            rows = _to_device_f32(x.rows, dev)
+            if rows.dim() != 2 or rows.shape[1] != self.features:
+                raise ValueError(f"expected a row stream of shape (N, {self.features}), got {tuple(rows.shape)}")
+            y = torch.empty((len(x), x.look_back, self.features), dtype=torch.float32, device=dev)
+            if len(x) == 0:
+                return y.cpu().numpy()
+            _ffi.check(_ffi.lib().b2_lstm_forward_windows(self._handle(), _ffi.ptr(rows), rows.shape[0], x.look_back, x.shift,
+                                                          _ffi.ptr(y), _stream_ptr()), "b2_lstm_forward_windows")
+            out = y.cpu().numpy()
+            return self._predict_callbacks(out, batch_size, callbacks)
         xd = _to_device_f32(x, dev)
         if self.kind == "dense":
             if xd.dim() != 2 or xd.shape[1] != self.widths[0]:
@@ -428,6 +470,12 @@ class Model:
             recon = torch.empty_like(xd)
             self.score_device(xd, math.inf, recon=recon)
             out = recon.cpu().numpy()
+            if callbacks and any(hasattr(cb, "consume_rows") for cb in callbacks):
+                # result sinks that format on the GPU (sink.OutputCallback) take every row in one launch, from device memory
+                for cb in callbacks:
+                    if hasattr(cb, "consume_rows"):
+                        cb.consume_rows(recon)
+                callbacks = [cb for cb in callbacks if not hasattr(cb, "consume_rows")]
         else:
             if xd.dim() != 3 or xd.shape[2] != self.features:
                 raise ValueError(f"expected input of shape (B, T, {self.features}), got {tuple(xd.shape)}")
@@ -437,6 +485,10 @@ class Model:
             _ffi.check(_ffi.lib().b2_lstm_forward(self._handle(), _ffi.ptr(xd), xd.shape[0], xd.shape[1], _ffi.ptr(y),
                                                   _stream_ptr()), "b2_lstm_forward")
             out = y.cpu().numpy()
+        return self._predict_callbacks(out, batch_size, callbacks)
+
+    @staticmethod
+    def _predict_callbacks(out, batch_size, callbacks):
         if callbacks:
             bs = batch_size or 32
             for b, s in enumerate(range(0, out.shape[0], bs)):

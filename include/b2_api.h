@@ -184,6 +184,26 @@ void b2_lstm_destroy(b2_lstm* m);
 int  b2_lstm_param_count(const b2_lstm* m);
 /* Model.predict of the LSTM stack (LSTM-…/cardata-v1.py:226): x_dev f32[B,T,features] → y_dev f32[B,T,features]. */
 int  b2_lstm_forward(b2_lstm* m, const float* x_dev, int64_t batch, int timesteps, float* y_dev, void* stream);
+/* The script's input pipeline fused into the forward pass (LSTM-…/cardata-v1.py:184-185:
+ * dataset.window(look_back, shift=1, drop_remainder=True).flat_map(lambda w: w.batch(look_back))): window i is rows
+ * [i*shift, i*shift + look_back) of rows_dev f32[n_rows, features]; the kernel reads them in place, nothing is materialised.
+ * y_dev f32[b2_lstm_window_count(...), look_back, features]. */
+int64_t b2_lstm_window_count(int64_t n_rows, int look_back, int shift);
+int  b2_lstm_forward_windows(b2_lstm* m, const float* rows_dev, int64_t n_rows, int look_back, int shift, float* y_dev, void* stream);
+
+/* ---- result sink: rows → text ------------------------------------------------------------------------------
+ * Replaces the formatting half of OutputCallback.on_predict_batch_end (cardata-v1.py:218-224:
+ * `message = np.array2string(output)` per reconstructed row, then KafkaOutputSequence.setitem(index, message)).
+ * x_dev f32[n, n_cols] (n_cols ≤ 64) → the exact text NumPy's array2string gives for each row with default print options.
+ * numpy_compat picks the NumPy generation to reproduce: 0 = NumPy ≥ 2.3, 1 = NumPy 1.21 … 2.2, 2 = NumPy 1.14 … 1.20 (the
+ * generation the reference's tensorflow:2.0.0 images carried; differs only in rows printed in scientific notation and for
+ * integers ≥ 2^24).  Texts are packed back to back into text_dev (capacity text_cap bytes; b2_format_rows_bound(n_cols) per
+ * row always suffices) in tile order, NOT row order: row i is text_dev[offs_dev[i] : offs_dev[i] + len_dev[i]].
+ * cursor_dev: uint64[2], zeroed by the caller; [0] receives the bytes used, [1] the number of rows dropped because the arena
+ * was full (their len_dev is -1). */
+int64_t b2_format_rows_bound(int n_cols);
+int  b2_format_rows(b2_ctx* ctx, const float* x_dev, int64_t n, int n_cols, int numpy_compat, uint8_t* text_dev, int64_t text_cap,
+                    int64_t* offs_dev, int32_t* len_dev, unsigned long long* cursor_dev, void* stream);
 
 /* ---- per-GPU partition driver --------------------------------------------------------------------------- */
 typedef struct {

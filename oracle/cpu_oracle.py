@@ -487,3 +487,77 @@ def init_lstm_weights(features: int = 18, units=(32, 16, 16, 32), seed: int = 31
         inp = u
     parts += [glorot_uniform(g, (units[-1], features)).ravel(), np.zeros(features, dtype=np.float32)]
     return np.concatenate(parts)
+
+
+# ---- result sink: np.array2string(row) (cardata-v1.py:218-224) ---------------------------------------------------------------
+# PINNED: the arithmetic owner of this row of SURVEY §8 (a12) is NumPy itself, which IS installed here, so the oracle for the
+# two current generations is the library call; only the NumPy 1.14-1.20 generation (what the reference's tensorflow:2.0.0
+# images carried) has to be restated, from the Dragon4 primitives NumPy still exposes (they did not change).
+def array2string_rows(x: np.ndarray, compat: int = 0) -> List[str]:
+    """compat 0: NumPy >= 2.3 (the installed one), 1: NumPy 1.21 .. 2.2 (printoptions legacy='2.2'), 2: NumPy 1.14 .. 1.20."""
+    x = np.asarray(x, dtype=np.float32)
+    if compat == 0:
+        if tuple(int(v) for v in np.__version__.split(".")[:2]) < (2, 3):
+            raise RuntimeError("compat 0 needs NumPy >= 2.3 as the oracle")
+        return [np.array2string(r) for r in x]
+    if compat == 1:
+        with np.printoptions(legacy="2.2"):
+            return [np.array2string(r) for r in x]
+    return [_array2string_np114(r) for r in x]
+
+
+def _array2string_np114(row: np.ndarray) -> str:
+    """numpy/core/arrayprint.py FloatingFormat + _formatArray of NumPy 1.14-1.20 for a 1-D float32 row, default options:
+    like today's except (a) no min_digits, i.e. elements shorter than the row's precision are zero-filled and integer parts
+    beyond the shortest form are zero-filled, (b) scalar comparisons against Python floats ran in float64, (c) the scientific
+    threshold is 1e8 for every dtype."""
+    fin = row[np.isfinite(row)]
+    nz = np.abs(fin[fin != 0])
+    sci = False
+    if len(nz):
+        mx, mn = nz.max(), nz.min()
+        with np.errstate(over="ignore"):
+            sci = bool(float(mx) >= 1e8 or float(mn) < 0.0001 or float(mx / mn) > 1000.0)
+    if len(fin) == 0:
+        pad_left = pad_right = 0
+        prec = exp_size = 0
+    elif sci:
+        strs = [np.format_float_scientific(v, precision=8, unique=True, trim=".", sign=False) for v in fin]
+        fracs, exps = zip(*((s.partition("e")[0], s.partition("e")[2]) for s in strs))
+        ints, fr = zip(*(s.split(".") for s in fracs))
+        exp_size = max(len(s) for s in exps) - 1
+        prec = max(len(s) for s in fr)
+        pad_left = max(len(s) for s in ints)
+        pad_right = exp_size + 2 + prec
+    else:
+        strs = [np.format_float_positional(v, precision=8, fractional=True, unique=True, trim=".", sign=False) for v in fin]
+        ints, fr = zip(*(s.split(".") for s in strs))
+        pad_left = max(len(s) for s in ints)
+        pad_right = max(len(s) for s in fr)
+    if len(fin) != len(row):
+        neginf = bool(np.any(row[np.isinf(row)] < 0))
+        offset = pad_right + 1
+        pad_left = max(pad_left, 3 - offset, 3 + neginf - offset)
+
+    def fmt(v):
+        if not np.isfinite(v):
+            s = "nan" if np.isnan(v) else ("-inf" if v < 0 else "inf")
+            return " " * (pad_left + pad_right + 1 - len(s)) + s
+        if sci:  # trim='k' of that generation zero-filled the shortest digits up to `precision`; today that takes min_digits
+            m, _, e = np.format_float_scientific(v, precision=prec, unique=True, trim=".", sign=False, exp_digits=exp_size).partition("e")
+            ip, _, fp = m.partition(".")
+            return " " * (pad_left - len(ip)) + ip + "." + fp + "0" * (prec - len(fp)) + "e" + e
+        return np.format_float_positional(v, precision=8, unique=True, fractional=True, trim=".", sign=False, pad_left=pad_left,
+                                          pad_right=pad_right)
+
+    s, line = "", " "
+    for i, v in enumerate(row):
+        word = fmt(v)
+        if len(line) + len(word) > 74 and len(line) > 1:
+            s += line.rstrip() + "\n"
+            line = " "
+        line += word
+        if i + 1 < len(row):
+            line += " "
+    s += line
+    return "[" + s[1:] + "]"

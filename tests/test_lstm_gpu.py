@@ -68,3 +68,31 @@ def test_lstm_rejects_other_stacks(cuda_device):
     m.add(k.layers.LSTM(8, activation="tanh", input_shape=(1, 18)))
     with pytest.raises(NotImplementedError):
         m.predict(np.zeros((2, 1, 18), np.float32))
+
+
+@pytest.mark.parametrize("path", ["tcgen05", "fp32"])
+@pytest.mark.parametrize("n_rows,look_back,shift", [(1200, 1, 1), (777, 4, 1), (1000, 16, 3), (5, 8, 1)])
+def test_lstm_sliding_windows_read_in_place(cuda_device, monkeypatch, n_rows, look_back, shift, path):
+    """dataset.window(look_back, shift, drop_remainder=True) fused into the forward pass (LSTM-…/cardata-v1.py:184-185): the
+    kernel reads window i at rows [i*shift, i*shift+look_back) of the stream; result == predict on the materialised windows."""
+    monkeypatch.setenv("B2_LSTM_TC", "1" if path == "tcgen05" else "0")
+    m = _lstm_model(look_back)
+    g = np.random.default_rng(n_rows)
+    rows = g.uniform(-1, 1, size=(n_rows, 18)).astype(np.float32)
+    win = bs.keras.Windows(rows, look_back, shift)
+    n_win = 0 if n_rows < look_back else (n_rows - look_back) // shift + 1
+    assert len(win) == n_win
+    y = m.predict(win)
+    assert y.shape == (n_win, look_back, 18)
+    if n_win == 0:
+        return
+    xw = win.numpy()
+    assert xw.shape == (n_win, look_back, 18)
+    np.testing.assert_array_equal(xw[-1], rows[(n_win - 1) * shift:(n_win - 1) * shift + look_back])
+    np.testing.assert_array_equal(y, m.predict(xw))  # same kernel, same arithmetic: bit-identical
+    np.testing.assert_allclose(y, orc.lstm_forward(xw, m.get_flat_weights(), dtype=np.float64), rtol=1e-4, atol=1e-4)
+    # the script's (x, y) pairing: y_i = row i + look_back, zip truncates to the shorter side (:189-191)
+    t = win.targets()
+    assert t.shape[0] == min(n_rows - look_back, n_win) and t.shape[1:] == (1, 18)
+    if shift == 1 and t.shape[0]:
+        np.testing.assert_array_equal(t[0, 0], rows[look_back])
