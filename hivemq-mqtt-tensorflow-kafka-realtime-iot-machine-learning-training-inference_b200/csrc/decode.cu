@@ -459,7 +459,7 @@ __device__ __forceinline__ int avro_decode_record(const uint8_t* __restrict__ ba
 
 // ---- the kernel --------------------------------------------------------------------------------------------------
 // MODE 0: decode only (runtime n_out);  MODE 1: fused decode + score for the D-14-7-7-D autoencoder
-template <int D, int MODE, bool FT>
+template <int D, int MODE, bool FT, int FMT>
 __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ DecodeArgs<D> a) {
   extern __shared__ __align__(128) uint8_t smem[];
   // carve: [stage bytes | offsets (TILE+1) x2 | status (TILE) | label (TILE) | mbarrier | xt]
@@ -482,7 +482,9 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
   unsigned flagged = 0, n_ok = 0, n_err = 0;
   unsigned long long n_bytes = 0;
   const long long n_tiles = (a.n + DEC_TILE - 1) / DEC_TILE;
-  int32_t* const offs_buf[2] = {s_offs, s_offs2};
+  // the two offset buffers are adjacent: select by arithmetic (an indexed pointer array would live in local memory and turn
+  // every access into a generic load)
+  auto offs_buf = [s_offs](int which) -> int32_t* { return s_offs + which * (DEC_TILE + 4); };
 
   // Work items are sub-tiles: (tile row0, rows, first record `sub`, record count `cnt`).  The byte stage is single: as soon as
   // phase A/B have consumed it, the NEXT item is planned (how many records fit) and its bulk copy issued, so the copy runs
@@ -531,7 +533,7 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
     int buf = 0;
     long long row0 = tile * DEC_TILE;
     int rows = (int)min((long long)DEC_TILE, a.n - row0);
-    for (int i = tid; i <= rows; i += DEC_NT) offs_buf[0][i] = a.offs[row0 + i];
+    for (int i = tid; i <= rows; i += DEC_NT) offs_buf(0)[i] = a.offs[row0 + i];
     __syncthreads();
     // offsets of the following tile → registers
     long long ntile = tile + gridDim.x;
@@ -546,22 +548,22 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
     };
     prefetch(ntile);
     int sub = 0, rel = 0;
-    int cnt = plan(offs_buf[0], row0, rows, sub, rel);
+    int cnt = plan(offs_buf(0), row0, rows, sub, rel);
     while (true) {
       // next tile's offsets: registers → the other offsets buffer (visible after the barrier below)
       if (ntile < n_tiles) {
-        offs_buf[buf ^ 1][tid] = pre0;
-        if (tid == 0) offs_buf[buf ^ 1][DEC_TILE] = pre1;
+        offs_buf(buf ^ 1)[tid] = pre0;
+        if (tid == 0) offs_buf(buf ^ 1)[DEC_TILE] = pre1;
       }
       if (cnt > 0) {
         mbar_wait(&full[0], phase);
         phase ^= 1u;
         // ---- phase A: one record per thread → field-begin table ----
       if (tid < cnt) {
-        const int b = offs_buf[buf][sub + tid] + rel, e = offs_buf[buf][sub + tid + 1] + rel;
+        const int b = offs_buf(buf)[sub + tid] + rel, e = offs_buf(buf)[sub + tid + 1] + rel;
         int st;
         uint8_t lab = 2;
-        if (a.fmt == FMT_CSV) {
+        if (FMT == FMT_CSV) {
           float* xrow = s_xt + (size_t)tid * xt_stride;
           int32_t* sp = (MODE == 0 && a.span) ? a.span + (row0 + sub + tid) * a.csv.n_str * 2 : nullptr;
           st = csv_walk(stage, b, e, a.csv, xrow, sp, rel);
@@ -585,7 +587,7 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
       int n_rel = 0, n_cnt = 0;
       for (;;) {
         if (sub < rows) {
-          n_cnt = plan(offs_buf[buf], row0, rows, sub, n_rel);
+          n_cnt = plan(offs_buf(buf), row0, rows, sub, n_rel);
           if (n_cnt > 0) break;
         }
         if (ntile >= n_tiles) {
@@ -593,8 +595,8 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
           break;
         }
         if (!staged) {  // rare: a whole tile had no record that fits; its successor's offsets are still in registers
-          offs_buf[buf ^ 1][tid] = pre0;
-          if (tid == 0) offs_buf[buf ^ 1][DEC_TILE] = pre1;
+          offs_buf(buf ^ 1)[tid] = pre0;
+          if (tid == 0) offs_buf(buf ^ 1)[DEC_TILE] = pre1;
           __syncthreads();
         }
         buf ^= 1;  // move on to the next tile (its offsets were staged at the top of the loop)
@@ -626,7 +628,7 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
           if (a.mse) a.mse[gr] = m;
           if (a.flag) a.flag[gr] = f ? 1 : 0;
           if (a.status) a.status[gr] = st;
-          if (a.label) a.label[gr] = a.fmt == FMT_AVRO && st == B2_REC_OK ? s_lab[tid] : 2;
+          if (a.label) a.label[gr] = FMT == FMT_AVRO && st == B2_REC_OK ? s_lab[tid] : 2;
           flagged += f;
           n_ok += st == B2_REC_OK;
           n_err += st != B2_REC_OK;
@@ -640,7 +642,7 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
           const long long gr = row0_c + sub_c + tid;
           const int st = s_stat[tid];
           if (a.status) a.status[gr] = st;
-          if (a.label) a.label[gr] = a.fmt == FMT_AVRO && st == B2_REC_OK ? s_lab[tid] : 2;
+          if (a.label) a.label[gr] = FMT == FMT_AVRO && st == B2_REC_OK ? s_lab[tid] : 2;
           n_ok += st == B2_REC_OK;
           n_err += st != B2_REC_OK;
         }
@@ -750,8 +752,8 @@ static size_t decode_smem_bytes(int stage_cap, int xt_stride) {
   return s + 64;
 }
 
-template <int D, int MODE, bool FT>
-static int launch_decode(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stream) {
+template <int D, int MODE, bool FT, int FMT>
+static int launch_decode_fmt(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stream) {
   const int xt_stride = MODE == 1 ? D : args.n_out;
   // byte stage: 48 KB unless the schema bounds the record size (Avro without strings) — a smaller stage means more CTAs/SM
   args.stage_cap = STAGE_CAP_MAX;
@@ -762,7 +764,7 @@ static int launch_decode(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stream) 
   }
   const size_t smem = decode_smem_bytes(args.stage_cap, xt_stride);
   B2_REQUIRE(smem <= (size_t)ctx->smem_optin, "decode: tile needs %zu bytes of shared memory (max %d)", smem, ctx->smem_optin);
-  auto kern = decode_kernel<D, MODE, FT>;
+  auto kern = decode_kernel<D, MODE, FT, FMT>;
   B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int occ = 0;
   B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, DEC_NT, smem));
@@ -773,6 +775,13 @@ static int launch_decode(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stream) 
   kern<<<(unsigned)grid, DEC_NT, smem, stream>>>(args);
   B2_CUDA(cudaGetLastError());
   return B2_OK;
+}
+
+// the record format is a template parameter: each instantiation carries only its own decoder (fewer registers, smaller code)
+template <int D, int MODE, bool FT>
+static int launch_decode(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stream) {
+  if (args.fmt == FMT_CSV) return launch_decode_fmt<D, MODE, FT, FMT_CSV>(ctx, args, stream);
+  return launch_decode_fmt<D, MODE, FT, FMT_AVRO>(ctx, args, stream);
 }
 
 extern "C" int b2_decode_csv(b2_ctx* ctx, const uint8_t* bytes_dev, const int32_t* offs_dev, int64_t n, const b2_csv_spec* spec,
