@@ -69,6 +69,7 @@ _P = C.c_void_p
 _PROTOTYPES = {
     "b2_ctx_create": (C.c_int, [C.c_int, C.POINTER(_P)]),
     "b2_ctx_destroy": (None, [_P]),
+    "b2_ctx_set_record_bytes_hint": (C.c_int, [_P, C.c_int]),
     "b2_ctx_sm_count": (C.c_int, [_P]),
     "b2_strerror": (C.c_char_p, [C.c_int]),
     "b2_last_error": (C.c_char_p, []),

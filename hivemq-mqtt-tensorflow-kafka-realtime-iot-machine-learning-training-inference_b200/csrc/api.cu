@@ -50,6 +50,13 @@ extern "C" int b2_ctx_create(int device, b2_ctx** out) {
 extern "C" void b2_ctx_destroy(b2_ctx* ctx) { delete ctx; }
 extern "C" int b2_ctx_sm_count(const b2_ctx* ctx) { return ctx ? ctx->sm_count : 0; }
 
+extern "C" int b2_ctx_set_record_bytes_hint(b2_ctx* ctx, int avg_record_bytes) {
+  B2_REQUIRE(ctx, "b2_ctx_set_record_bytes_hint: NULL context");
+  B2_REQUIRE(avg_record_bytes >= 0, "b2_ctx_set_record_bytes_hint: negative size");
+  ctx->record_bytes_hint = avg_record_bytes;
+  return B2_OK;
+}
+
 // ---- autoencoder handle ------------------------------------------------------------------------------------
 static int count_params(const b2_ae_desc& d) {
   int n = 0;

@@ -36,6 +36,7 @@ struct b2_ctx {
   int device;
   int sm_count;
   int smem_optin;  // max dynamic shared memory per block (bytes)
+  int record_bytes_hint = 0;  // b2_ctx_set_record_bytes_hint: average record size of the batches to come, 0 = unknown
 };
 
 // RAII "make this device current for the call" guard (callers may sit on another device)

@@ -18,8 +18,8 @@
 #include "float_parse.cuh"
 
 constexpr int DEC_NT = 256;
-constexpr int DEC_TILE = 256;
-constexpr int STAGE_CAP_MAX = 48 * 1024;  // most bytes of payload staged per sub-tile (the launch may choose less)
+constexpr int DEC_WARPS = DEC_NT / 32;
+constexpr int STAGE_CAP_MAX = 24 * 1024;  // most bytes of payload one warp stages per item (the launch normally chooses far less)
 
 enum { FMT_CSV = 0, FMT_AVRO = 1 };
 enum { AV_INT = 1, AV_LONG, AV_FLOAT, AV_DOUBLE, AV_STRING, AV_BOOLEAN, AV_BYTES, AV_NULL };
@@ -49,7 +49,8 @@ struct DecodeArgs {
   long long n;
   int fmt;
   int n_out;            // floats per record produced by the decode (== D when scoring)
-  int stage_cap;        // bytes of the shared-memory byte stage chosen for this launch
+  int stage_cap;        // bytes of each warp's shared-memory byte stage chosen for this launch (multiple of 16)
+  int warp_bytes;       // shared memory per warp: apron + stage + float tile + mbarrier
   CsvP csv;
   AvroP avro;
   // decode-only outputs
@@ -458,38 +459,36 @@ __device__ __forceinline__ int avro_decode_record(const uint8_t* __restrict__ ba
 }
 
 // ---- the kernel --------------------------------------------------------------------------------------------------
-// MODE 0: decode only (runtime n_out);  MODE 1: fused decode + score for the D-14-7-7-D autoencoder
+// MODE 0: decode only (runtime n_out);  MODE 1: fused decode + score for the D-14-7-7-D autoencoder.
+// Every WARP is an independent worker: it owns a byte stage, a 32-row float tile and an mbarrier in shared memory and walks
+// chunks of 32 consecutive records (chunk = global warp index, + total warps, …).  Lane i owns record i of the chunk from its
+// offsets to its results; there is no block-wide barrier anywhere, so a warp that hits slow records, a wrap of the line or
+// the end of its range never holds up the other warps of the SM.  Per item (the records of the chunk whose bytes fit the stage —
+// normally all 32): wait for the bulk copy, decode, then — the stage being free again — plan the next item and issue its
+// copy so that it flies under this item's score phase, then score and store.
 template <int D, int MODE, bool FT, int FMT>
 __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ DecodeArgs<D> a) {
   extern __shared__ __align__(128) uint8_t smem[];
-  // carve: [stage bytes | offsets (TILE+1) x2 | status (TILE) | label (TILE) | mbarrier | xt]
-  uint8_t* stage = smem + 16;  // 16-byte apron in front: the token-tail load may start up to 3 bytes before the first token
-  int32_t* s_offs = reinterpret_cast<int32_t*>(smem + a.stage_cap + 64);
-  int32_t* s_offs2 = s_offs + DEC_TILE + 4;
-  int32_t* s_stat = s_offs2 + DEC_TILE + 4;
-  uint8_t* s_lab = reinterpret_cast<uint8_t*>(s_stat + DEC_TILE);
-  uint64_t* full = reinterpret_cast<uint64_t*>(s_lab + DEC_TILE);
+  constexpr unsigned FULL = 0xffffffffu;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int xt_stride = MODE == 1 ? D : a.n_out;
-  float* s_xt = reinterpret_cast<float*>(full + 2);
-
-  const int tid = threadIdx.x;
-  if (tid == 0) {
-    mbar_init(&full[0], 1);
+  // per warp: [16-byte apron | stage (stage_cap) | 16 spare | xt 32 rows | mbarrier]
+  uint8_t* wbase = smem + (size_t)warp * a.warp_bytes;
+  uint8_t* stage = wbase + 16;  // apron in front: the token-tail load may start up to 3 bytes before the first token
+  float* xt = reinterpret_cast<float*>(wbase + 32 + a.stage_cap);
+  uint64_t* full = reinterpret_cast<uint64_t*>(wbase + a.warp_bytes - 16);
+  if (lane == 0) {
+    mbar_init(full, 1);
     mbar_fence_init();
   }
-  __syncthreads();
+  __syncwarp();
   uint32_t phase = 0;
   unsigned flagged = 0, n_ok = 0, n_err = 0;
   unsigned long long n_bytes = 0;
-  const long long n_tiles = (a.n + DEC_TILE - 1) / DEC_TILE;
-  // the two offset buffers are adjacent: select by arithmetic (an indexed pointer array would live in local memory and turn
-  // every access into a generic load)
-  auto offs_buf = [s_offs](int which) -> int32_t* { return s_offs + which * (DEC_TILE + 4); };
+  const long long n_chunks = (a.n + 31) / 32;
+  const long long n_workers = (long long)gridDim.x * DEC_WARPS;
 
-  // Work items are sub-tiles: (tile row0, rows, first record `sub`, record count `cnt`).  The byte stage is single: as soon as
-  // phase A/B have consumed it, the NEXT item is planned (how many records fit) and its bulk copy issued, so the copy runs
-  // under the current item's score phase; the next tile's offsets were fetched into registers one item earlier.
-  auto oversize = [&](long long row) {  // a single record larger than the stage: refuse it, keep going (thread 0)
+  auto oversize = [&](long long row) {  // a single record larger than the stage: refuse it, keep going (lane 0)
     if (a.status) a.status[row] = B2_REC_TOO_LONG;
     if (MODE == 1) {
       if (a.mse) a.mse[row] = __int_as_float(0x7FC00000);
@@ -500,173 +499,129 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
     if (a.label) a.label[row] = 2;
     ++n_err;
   };
-  // plan the item starting at record `sub` of the tile whose offsets sit in `so`: returns cnt (0 = tile exhausted) and
-  // issues its bulk copy; every thread must call it (block-wide count)
-  auto plan = [&](const int32_t* so, long long row0, int rows, int& sub, int& rel) -> int {
-    while (sub < rows) {
-      const long long b_abs = so[sub];
-      const uintptr_t a0 = (reinterpret_cast<uintptr_t>(a.bytes) + (uintptr_t)b_abs) & ~(uintptr_t)15;
-      const int lead = (int)((reinterpret_cast<uintptr_t>(a.bytes) + (uintptr_t)b_abs) - a0);
-      const int rr = sub + tid;
-      const int fit = rr < rows && (long long)so[rr + 1] - b_abs + lead <= (long long)a.stage_cap;
-      const int cnt = __syncthreads_count(fit);  // record ends are monotone: this is the number of records that fit
+
+  // cursor over this warp's chunks: lane i holds the byte range [ob, oe) of record i of the current chunk
+  long long chunk = (long long)blockIdx.x * DEC_WARPS + warp - n_workers, row0 = 0;
+  int rows = 0, sub = 0, ob = 0, oe = 0;
+  // plans the next item (records [sub, sub+cnt) of the cursor's chunk), issues its bulk copy and advances the cursor
+  auto next_item = [&](long long& it_row0, int& it_sub, int& it_cnt, int& it_b, int& it_e) -> bool {
+    for (;;) {
+      if (sub >= rows) {
+        chunk += n_workers;
+        if (chunk >= n_chunks) return false;
+        row0 = chunk * 32;
+        rows = (int)min(32ll, a.n - row0);
+        sub = 0;
+        const int o = a.offs[row0 + min(lane, rows)];
+        ob = o;
+        oe = __shfl_down_sync(FULL, o, 1);
+        if (lane == 31 && rows == 32) oe = a.offs[row0 + 32];
+      }
+      const int b_abs = __shfl_sync(FULL, ob, sub);
+      const uintptr_t p0 = reinterpret_cast<uintptr_t>(a.bytes) + (uintptr_t)(long long)b_abs;
+      const uintptr_t a0 = p0 & ~(uintptr_t)15;
+      const int lead = (int)(p0 - a0);
+      const bool fit = lane >= sub && lane < rows && (long long)oe - b_abs + lead <= (long long)a.stage_cap;
+      const int cnt = __popc(__ballot_sync(FULL, fit));  // record ends are monotone: the records that fit are sub .. sub+cnt-1
       if (cnt == 0) {
-        if (tid == 0) oversize(row0 + sub);
+        if (lane == 0) oversize(row0 + sub);
         sub += 1;
         continue;
       }
-      const long long e_abs = so[sub + cnt];
-      const uint32_t nbytes = (uint32_t)(((e_abs - b_abs + lead) + 15) & ~15ll);
-      if (tid == 0) {
-        mbar_expect_tx(&full[0], nbytes);
-        bulk_g2s(stage, reinterpret_cast<const void*>(a0), nbytes, &full[0]);
+      const int e_abs = __shfl_sync(FULL, oe, sub + cnt - 1);
+      if (lane == 0) {
+        const uint32_t nbytes = (uint32_t)(((e_abs - b_abs + lead) + 15) & ~15);
+        mbar_expect_tx(full, nbytes);
+        bulk_g2s(stage, reinterpret_cast<const void*>(a0), nbytes, full);
         n_bytes += (unsigned long long)(e_abs - b_abs);
       }
-      rel = lead - (int)b_abs;  // stage offset of absolute byte x is x + rel
-      return cnt;
+      const int rel = lead - b_abs;  // stage offset of absolute byte x is x + rel
+      it_row0 = row0;
+      it_sub = sub;
+      it_cnt = cnt;
+      it_b = ob + rel;
+      it_e = oe + rel;
+      sub += cnt;
+      return true;
     }
-    return 0;
   };
 
-  long long tile = blockIdx.x;
-  if (tile < n_tiles) {
-    int buf = 0;
-    long long row0 = tile * DEC_TILE;
-    int rows = (int)min((long long)DEC_TILE, a.n - row0);
-    for (int i = tid; i <= rows; i += DEC_NT) offs_buf(0)[i] = a.offs[row0 + i];
-    __syncthreads();
-    // offsets of the following tile → registers
-    long long ntile = tile + gridDim.x;
-    int pre0 = 0, pre1 = 0;
-    auto prefetch = [&](long long t) {
-      if (t < n_tiles) {
-        const long long r0 = t * DEC_TILE;
-        const long long last = min((long long)DEC_TILE, a.n - r0);
-        if (tid <= last) pre0 = a.offs[r0 + tid];
-        if (tid == 0 && last == DEC_TILE) pre1 = a.offs[r0 + DEC_TILE];
-      }
-    };
-    prefetch(ntile);
-    int sub = 0, rel = 0;
-    int cnt = plan(offs_buf(0), row0, rows, sub, rel);
-    while (true) {
-      // next tile's offsets: registers → the other offsets buffer (visible after the barrier below)
-      if (ntile < n_tiles) {
-        offs_buf(buf ^ 1)[tid] = pre0;
-        if (tid == 0) offs_buf(buf ^ 1)[DEC_TILE] = pre1;
-      }
-      if (cnt > 0) {
-        mbar_wait(&full[0], phase);
-        phase ^= 1u;
-        // ---- phase A: one record per thread → field-begin table ----
-      if (tid < cnt) {
-        const int b = offs_buf(buf)[sub + tid] + rel, e = offs_buf(buf)[sub + tid + 1] + rel;
-        int st;
-        uint8_t lab = 2;
-        if (FMT == FMT_CSV) {
-          float* xrow = s_xt + (size_t)tid * xt_stride;
-          int32_t* sp = (MODE == 0 && a.span) ? a.span + (row0 + sub + tid) * a.csv.n_str * 2 : nullptr;
-          st = csv_walk(stage, b, e, a.csv, xrow, sp, rel);
-          if (st < 0) st = csv_record_careful(stage, b, e, a.csv, xrow, sp, rel);
-        } else {
-          float* xrow = s_xt + (size_t)tid * xt_stride;
-          if (!a.avro.all_routed)
-            for (int j = 0; j < xt_stride; ++j) xrow[j] = 0.0f;  // columns no field routes to
-          st = avro_decode_record(stage, b, e, a.avro, xrow, &lab);
-        }
-        s_stat[tid] = st;
-        s_lab[tid] = lab;
-      }
-      }
-      __syncthreads();  // stage consumed (and the next tile's offsets are in place)
-      // ---- plan the next item and start its copy ----
-      const long long c_row0 = row0;
-      const int c_sub = sub, c_cnt = cnt;
-      bool more = true, staged = true;
-      sub += cnt;
-      int n_rel = 0, n_cnt = 0;
-      for (;;) {
-        if (sub < rows) {
-          n_cnt = plan(offs_buf(buf), row0, rows, sub, n_rel);
-          if (n_cnt > 0) break;
-        }
-        if (ntile >= n_tiles) {
-          more = false;
-          break;
-        }
-        if (!staged) {  // rare: a whole tile had no record that fits; its successor's offsets are still in registers
-          offs_buf(buf ^ 1)[tid] = pre0;
-          if (tid == 0) offs_buf(buf ^ 1)[DEC_TILE] = pre1;
-          __syncthreads();
-        }
-        buf ^= 1;  // move on to the next tile (its offsets were staged at the top of the loop)
-        tile = ntile;
-        row0 = tile * DEC_TILE;
-        rows = (int)min((long long)DEC_TILE, a.n - row0);
-        sub = 0;
-        ntile = tile + gridDim.x;
-        prefetch(ntile);
-        staged = false;
-      }
-      // ---- phase C on the CURRENT item ----
-      if (c_cnt > 0) {
-        const long long row0_c = c_row0;
-        const int sub_c = c_sub, cnt_c = c_cnt;
-      // ---- phase C ----
-      if (MODE == 1) {
-        const bool va = tid < cnt_c;
-        float* const rowp[1] = {s_xt + (size_t)tid * D};
-        float mm[1] = {0.f};
-        if (va) {
-          if (a.has_norm) ae_forward_rows<D, 1, true, false, FT>(a.w, a.nm, rowp, mm);
-          else ae_forward_rows<D, 1, false, false, FT>(a.w, a.nm, rowp, mm);
-          const long long gr = row0_c + sub_c + tid;
-          const int st = s_stat[tid];
-          float m = mm[0];
-          if (st != B2_REC_OK) m = __int_as_float(0x7FC00000);
-          const bool f = m > a.threshold;
-          if (a.mse) a.mse[gr] = m;
-          if (a.flag) a.flag[gr] = f ? 1 : 0;
-          if (a.status) a.status[gr] = st;
-          if (a.label) a.label[gr] = FMT == FMT_AVRO && st == B2_REC_OK ? s_lab[tid] : 2;
-          flagged += f;
-          n_ok += st == B2_REC_OK;
-          n_err += st != B2_REC_OK;
-        }
+  long long c_row0 = 0, n_row0 = 0;
+  int c_sub = 0, c_cnt = 0, c_b = 0, c_e = 0, n_sub = 0, n_cnt = 0, n_b = 0, n_e = 0;
+  bool have = next_item(c_row0, c_sub, c_cnt, c_b, c_e);
+  while (have) {
+    mbar_wait(full, phase);
+    phase ^= 1u;
+    const bool active = lane >= c_sub && lane < c_sub + c_cnt;
+    const long long gr = c_row0 + lane;
+    float* xrow = xt + (size_t)lane * xt_stride;
+    int st = B2_REC_OK;
+    uint8_t lab = 2;
+    if (active) {
+      if (FMT == FMT_CSV) {
+        int32_t* sp = (MODE == 0 && a.span) ? a.span + gr * a.csv.n_str * 2 : nullptr;
+        const int rel = c_b - ob;  // stage offset minus absolute offset (the cursor still sits on this item's chunk)
+        st = csv_walk(stage, c_b, c_e, a.csv, xrow, sp, rel);
+        if (st < 0) st = csv_record_careful(stage, c_b, c_e, a.csv, xrow, sp, rel);
       } else {
-        for (int i = tid; i < cnt_c * xt_stride; i += DEC_NT) {
-          const int r = i / xt_stride;
-          a.out[(row0_c + sub_c) * xt_stride + i] = s_stat[r] == B2_REC_OK ? s_xt[i] : __int_as_float(0x7FC00000);
-        }
-        if (tid < cnt_c) {
-          const long long gr = row0_c + sub_c + tid;
-          const int st = s_stat[tid];
-          if (a.status) a.status[gr] = st;
-          if (a.label) a.label[gr] = FMT == FMT_AVRO && st == B2_REC_OK ? s_lab[tid] : 2;
-          n_ok += st == B2_REC_OK;
-          n_err += st != B2_REC_OK;
-        }
+        if (!a.avro.all_routed)
+          for (int j = 0; j < xt_stride; ++j) xrow[j] = 0.0f;  // columns no field routes to
+        st = avro_decode_record(stage, c_b, c_e, a.avro, xrow, &lab);
       }
-      }
-      __syncthreads();  // tile tables free again
-      if (!more) break;
-      cnt = n_cnt;
-      rel = n_rel;
     }
+    __syncwarp();  // every lane is done with the stage
+    have = next_item(n_row0, n_sub, n_cnt, n_b, n_e);
+    if (MODE == 1) {
+      if (active) {
+        float* const rowp[1] = {xrow};
+        float mm[1] = {0.f};
+        if (a.has_norm) ae_forward_rows<D, 1, true, false, FT>(a.w, a.nm, rowp, mm);
+        else ae_forward_rows<D, 1, false, false, FT>(a.w, a.nm, rowp, mm);
+        float m = mm[0];
+        if (st != B2_REC_OK) m = __int_as_float(0x7FC00000);
+        const bool f = m > a.threshold;
+        if (a.mse) a.mse[gr] = m;
+        if (a.flag) a.flag[gr] = f ? 1 : 0;
+        if (a.status) a.status[gr] = st;
+        if (a.label) a.label[gr] = FMT == FMT_AVRO && st == B2_REC_OK ? lab : 2;
+        flagged += f;
+        n_ok += st == B2_REC_OK;
+        n_err += st != B2_REC_OK;
+      }
+    } else {
+      // coalesced write-out of the item's rows (they are contiguous in xt); a bad record's row becomes NaN
+      const int total = c_cnt * xt_stride;
+      const float* src = xt + (size_t)c_sub * xt_stride;
+      float* dst = a.out + (c_row0 + c_sub) * xt_stride;
+      for (int i0 = 0; i0 < total; i0 += 32) {
+        const int i = i0 + lane;
+        const int r = min(i, total - 1) / xt_stride;
+        const int st_r = __shfl_sync(FULL, st, c_sub + r);
+        if (i < total) dst[i] = st_r == B2_REC_OK ? src[i] : __int_as_float(0x7FC00000);
+      }
+      if (active) {
+        if (a.status) a.status[gr] = st;
+        if (a.label) a.label[gr] = FMT == FMT_AVRO && st == B2_REC_OK ? lab : 2;
+        n_ok += st == B2_REC_OK;
+        n_err += st != B2_REC_OK;
+      }
+      __syncwarp();  // xt is rewritten by the next item's decode
+    }
+    c_row0 = n_row0, c_sub = n_sub, c_cnt = n_cnt, c_b = n_b, c_e = n_e;
   }
   if (a.counters) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
-      flagged += __shfl_xor_sync(0xffffffffu, flagged, o);
-      n_ok += __shfl_xor_sync(0xffffffffu, n_ok, o);
-      n_err += __shfl_xor_sync(0xffffffffu, n_err, o);
+      flagged += __shfl_xor_sync(FULL, flagged, o);
+      n_ok += __shfl_xor_sync(FULL, n_ok, o);
+      n_err += __shfl_xor_sync(FULL, n_err, o);
     }
-    if ((tid & 31) == 0) {
+    if (lane == 0) {
       if (n_ok) atomicAdd(&a.counters[0], (unsigned long long)n_ok);
       if (flagged) atomicAdd(&a.counters[1], (unsigned long long)flagged);
       if (n_err) atomicAdd(&a.counters[2], (unsigned long long)n_err);
+      if (n_bytes) atomicAdd(&a.counters[3], n_bytes);
     }
-    if (tid == 0 && n_bytes) atomicAdd(&a.counters[3], n_bytes);
   }
 }
 
@@ -742,36 +697,53 @@ static int avro_max_record_bytes(const AvroP& a) {
   return n;
 }
 
-static size_t decode_smem_bytes(int stage_cap, int xt_stride) {
-  size_t s = (size_t)stage_cap + 64;
-  s += 2 * sizeof(int32_t) * (DEC_TILE + 4);       // offsets (double-buffered)
-  s += sizeof(int32_t) * DEC_TILE;                 // status
-  s += DEC_TILE;                                   // label
-  s += 2 * sizeof(uint64_t);                       // mbarrier
-  s += (size_t)DEC_TILE * xt_stride * 4;
-  return s + 64;
+static int align16i(int v) { return (v + 15) & ~15; }
+
+// Bytes one warp stages per item.  Avro without strings: 32 records of the schema's maximum size.  Otherwise an estimate of 32
+// typical records (a chunk whose bytes do not fit is simply split into several items, at the price of idle lanes):
+// `hint` = the caller's average record size if known, else ~10 bytes per CSV field / the fixed part + 16 bytes per Avro string.
+static int choose_stage_cap(int fmt, const CsvP& csv, const AvroP& avro, int hint) {
+  int per_rec;
+  if (fmt == FMT_AVRO) {
+    const int mx = avro_max_record_bytes(avro);
+    if (mx > 0) return min(STAGE_CAP_MAX, align16i(mx * 32 + 32));
+    per_rec = avro.skip_prefix;
+    for (int i = 0; i < avro.n_fields; ++i) {
+      per_rec += avro.f[i].nullable ? 1 : 0;
+      switch (avro.f[i].type) {
+        case AV_FLOAT: per_rec += 4; break;
+        case AV_DOUBLE: per_rec += 8; break;
+        case AV_BOOLEAN: per_rec += 1; break;
+        case AV_INT: per_rec += 3; break;
+        case AV_LONG: per_rec += 5; break;
+        case AV_STRING: case AV_BYTES: per_rec += 17; break;
+        default: break;
+      }
+    }
+  } else {
+    per_rec = csv.n_fields * 10;
+  }
+  if (hint > 0) per_rec = hint;
+  // a known average gets 6 % head-room (32 records rarely sum to more), an estimate none: the stage also sets how many CTAs fit
+  return max(2048, min(STAGE_CAP_MAX, align16i(per_rec * 32 + (hint > 0 ? per_rec * 2 : 0) + 48)));
 }
 
 template <int D, int MODE, bool FT, int FMT>
 static int launch_decode_fmt(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stream) {
   const int xt_stride = MODE == 1 ? D : args.n_out;
-  // byte stage: 48 KB unless the schema bounds the record size (Avro without strings) — a smaller stage means more CTAs/SM
-  args.stage_cap = STAGE_CAP_MAX;
-  if (args.fmt == FMT_AVRO) {
-    const int mx = avro_max_record_bytes(args.avro);
-    if (mx > 0) args.stage_cap = min(STAGE_CAP_MAX, ((mx * DEC_TILE + 31) & ~15));
-    else args.stage_cap = 40 * 1024;
-  }
-  const size_t smem = decode_smem_bytes(args.stage_cap, xt_stride);
+  args.stage_cap = choose_stage_cap(args.fmt, args.csv, args.avro, ctx->record_bytes_hint);
+  args.warp_bytes = 16 + args.stage_cap + 16 + align16i(32 * xt_stride * 4) + 16;
+  const size_t smem = (size_t)args.warp_bytes * DEC_WARPS;
   B2_REQUIRE(smem <= (size_t)ctx->smem_optin, "decode: tile needs %zu bytes of shared memory (max %d)", smem, ctx->smem_optin);
   auto kern = decode_kernel<D, MODE, FT, FMT>;
   B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int occ = 0;
   B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, DEC_NT, smem));
   B2_REQUIRE(occ >= 1, "decode: kernel does not fit on an SM");
-  const long long n_tiles = (args.n + DEC_TILE - 1) / DEC_TILE;
+  const long long n_chunks = (args.n + 31) / 32;
   long long grid = (long long)ctx->sm_count * occ;
-  if (grid > n_tiles) grid = n_tiles;
+  const long long need = (n_chunks + DEC_WARPS - 1) / DEC_WARPS;
+  if (grid > need) grid = need;
   kern<<<(unsigned)grid, DEC_NT, smem, stream>>>(args);
   B2_CUDA(cudaGetLastError());
   return B2_OK;

@@ -68,6 +68,14 @@ def _as_batch(records) -> RecordBatch:
     return records if isinstance(records, RecordBatch) else RecordBatch.from_messages(records)
 
 
+def _size_hint(rb: "RecordBatch") -> None:
+    """Tell the library the batch's average record size (its decode kernels size each warp's byte stage from it)."""
+    avg = getattr(rb, "avg_record_bytes", None)  # set by callers that pass a window of a larger buffer
+    if avg is None:
+        avg = (rb.nbytes + max(rb.n, 1) - 1) // max(rb.n, 1)
+    _ffi.check(_ffi.lib().b2_ctx_set_record_bytes_hint(get_ctx(rb.data.device.index), int(avg)), "b2_ctx_set_record_bytes_hint")
+
+
 def _raise_on_status(status: torch.Tensor, what: str):
     bad = torch.nonzero(status).flatten()
     if bad.numel():
@@ -104,6 +112,7 @@ def decode_csv_matrix(records, kinds, defaults=None, field_delim=",", use_quote_
     out = torch.empty((rb.n, nf), dtype=torch.float32, device=rb.data.device)
     span = torch.zeros((rb.n, max(ns, 1), 2), dtype=torch.int32, device=rb.data.device) if ns else None
     status = torch.empty(rb.n, dtype=torch.int32, device=rb.data.device)
+    _size_hint(rb)
     _ffi.check(_ffi.lib().b2_decode_csv(get_ctx(rb.data.device.index), _ffi.ptr(rb.data), _ffi.ptr(rb.offsets), rb.n, C.byref(spec),
                                         _ffi.ptr(out), _ffi.ptr(span), _ffi.ptr(status), _stream_ptr()), "b2_decode_csv")
     if raise_on_error:
@@ -149,6 +158,7 @@ def decode_avro_matrix(records, schema, skip_prefix: Optional[int] = None, raise
     label = torch.empty(rb.n, dtype=torch.uint8, device=rb.data.device)
     status = torch.empty(rb.n, dtype=torch.int32, device=rb.data.device)
     skip = rb.skip_prefix if skip_prefix is None else skip_prefix
+    _size_hint(rb)
     _ffi.check(_ffi.lib().b2_decode_avro(get_ctx(rb.data.device.index), _ffi.ptr(rb.data), _ffi.ptr(rb.offsets), rb.n, skip, C.byref(p),
                                          _ffi.ptr(out), _ffi.ptr(label), _ffi.ptr(status), _stream_ptr()), "b2_decode_avro")
     if raise_on_error:
@@ -202,6 +212,7 @@ def decode_score(model, records, csv_kinds=None, csv_defaults=None, avro_schema=
         if label is None:
             label = torch.empty(rb.n, dtype=torch.uint8, device=dev)
     nm = model._norm_struct()
+    _size_hint(rb)
     _ffi.check(_ffi.lib().b2_decode_score(model._handle(), _ffi.ptr(rb.data), _ffi.ptr(rb.offsets), rb.n,
                                           C.byref(spec) if spec is not None else None, C.byref(p) if p is not None else None,
                                           rb.skip_prefix, C.byref(nm), float(threshold), _ffi.ptr(mse), _ffi.ptr(flag), _ffi.ptr(label),
@@ -260,6 +271,7 @@ def decode_score_host(model, data, offsets, csv_kinds=None, csv_defaults=None, a
         main.wait_event(ev)
         rb = RecordBatch.__new__(RecordBatch)
         rb.data, rb.offsets, rb.n, rb.skip_prefix = d_dev, o_dev[c0:c1 + 1], c1 - c0, skip_prefix
+        rb.avg_record_bytes = (int(oh[n]) - int(oh[0]) + n - 1) // max(n, 1)
         decode_score(model, rb, csv_kinds=csv_kinds, csv_defaults=csv_defaults, avro_schema=avro_schema, threshold=threshold,
                      mse=mse[c0:c1], flag=flag[c0:c1], status=status[c0:c1], label=None if label is None else label[c0:c1])
         hm[c0:c1].copy_(mse[c0:c1], non_blocking=True)

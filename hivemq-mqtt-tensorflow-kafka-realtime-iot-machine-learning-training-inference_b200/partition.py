@@ -102,6 +102,11 @@ class PartitionDriver:
             arr[i].mse_dev, arr[i].flag_dev = b.mse.data_ptr(), b.flag.data_ptr()
         nm = self.model._norm_struct()
         st = _ffi.RunStats()
+        tot_n = sum(b.n for b in batches)
+        tot_bytes = sum(int(b.data.numel()) for b in batches)
+        from .keras_compat import get_ctx
+        _ffi.check(l.b2_ctx_set_record_bytes_hint(get_ctx(dev.index), (tot_bytes + max(tot_n, 1) - 1) // max(tot_n, 1)),
+                   "b2_ctx_set_record_bytes_hint")
         torch.cuda.current_stream().synchronize()  # inputs were produced on torch's stream; the driver uses its own
         _ffi.check(l.b2_partition_run(self.model._handle(), arr, len(batches), C.byref(self._csv) if self._csv is not None else None,
                                       C.byref(self._avro) if self._avro is not None else None, skip, C.byref(nm), self.threshold,

@@ -55,6 +55,10 @@ typedef struct b2_lstm b2_lstm; /* LSTM stack of LSTM-TensorFlow-IO-Kafka/cardat
 int  b2_ctx_create(int device, b2_ctx** out);
 void b2_ctx_destroy(b2_ctx* ctx);
 int  b2_ctx_sm_count(const b2_ctx* ctx);
+/* Optional sizing hint for the decode calls that follow on this context: the average record size (bytes) of the batches to
+ * come, e.g. total payload bytes / N (0 = unknown, the default: estimated from the schema).  Each warp stages 32 records at a
+ * time; a good hint makes a 32-record chunk fit its stage in one piece and lets more CTAs share an SM. */
+int  b2_ctx_set_record_bytes_hint(b2_ctx* ctx, int avg_record_bytes);
 const char* b2_strerror(int code);
 const char* b2_last_error(void);      /* thread-local detail of the last failure */
 const char* b2_version(void);
