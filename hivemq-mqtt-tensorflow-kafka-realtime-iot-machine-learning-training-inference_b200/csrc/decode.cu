@@ -6,13 +6,14 @@
 //           kafka_io.decode_avro(e, schema, dtype) cardata-v1.py:16-37  (+ int→float casts :61-66)
 //
 // HBM layout: a Kafka partition batch is `uint8 data[]` (message payloads back to back, no separators) plus
-// `int32 offsets[n+1]`.  A persistent CTA walks tiles of TILE = 2*NT consecutive records.  The bytes of (a prefix of) the
-// tile are one contiguous range, fetched by ONE 1-D bulk async copy (TMA engine) into shared memory — sub-tiled when
-// the records are long (credit-card CSV ≈ 550 B/record) so that a sub-tile never exceeds STAGE_CAP bytes.
-//   phase A  thread-per-record   CSV: SWAR delimiter scan → field-begin table (u16) in smem;  Avro: the whole walk (uniform
-//                                field type across the warp, unaligned 32-bit loads) → f32 tile
-//   phase B  thread-per-field    CSV only: registers-only digit scan + Eisel-Lemire → f32 tile
-//   phase C  thread-per-record   fused normalise → Dense stack → MSE → flag (ae_math.cuh), or coalesced tile write-out
+// `int32 offsets[n+1]`.  Every warp of a persistent grid is an independent worker over chunks of 32 consecutive records
+// (lane i ↔ record i).  The bytes of a chunk are one contiguous range, fetched by ONE 1-D bulk async copy (TMA engine) into
+// the warp's own shared-memory stage and signalled on the warp's own mbarrier; a chunk whose bytes exceed the stage is taken
+// in several items.  Per item:
+//   decode   lane-per-record   CSV: lock-step field walk, numbers parsed straight from the byte stream;  Avro: the schema
+//                              walk (uniform field type across the warp, unaligned 32-bit loads) → the lane's f32 row
+//   (then the next item is planned and its copy issued, so that it flies under the score phase)
+//   score    lane-per-record   fused normalise → Dense stack → MSE → flag (ae_math.cuh), or a coalesced write-out of the rows
 // Algorithmic bytes/record: payload + 4 (offset) read, 5 written (fused) or 4*F + 4 written (decode only).
 #include "ae_math.cuh"
 #include "float_parse.cuh"
