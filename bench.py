@@ -227,7 +227,8 @@ class DecodeScoreWorkload:
     def describe(self):
         return {"workload": self.name, "format": {"csv": "CSV line per message (car-sensor-data.csv layout, 20 fields)",
                                                   "avro_a": "Confluent-framed Avro, testdata/cardata-v1.avsc (63 B/record)",
-                                                  "avro_b": "Confluent-framed Avro, KSQL cardata-v1.avsc (nullable unions, ~139 B/record)"}[self.fmt],
+                                                  "avro_b": "Confluent-framed Avro, KSQL cardata-v1.avsc (nullable unions, ~139 B/record)",
+                                                  "json": "flat JSON object per message, the simulator's sensor-data topic (LSTM-…/cardata-v1.json member names, ~520 B/record)"}[self.fmt],
                 "features": 18, "model": "Dense AE 18-14-7-7-18", "weights": "Glorot-uniform seed 314 (no 18-wide weights are shipped)",
                 "normalise": True, "records_per_batch": self.batch, "batches_per_step_per_gpu": self.nb, "threshold": THRESHOLD,
                 "partitioning": "rank r owns partition batches p with seed 314 + (r * batches_per_step + p); no data-path collective",
@@ -249,6 +250,8 @@ class DecodeScoreWorkload:
             return bs.synth.csv_batch(rows, seed=seed)
         if self.fmt == "avro_a":
             return bs.synth.avro_a_batch(rows)
+        if self.fmt == "json":
+            return bs.synth.json_batch(rows, labels=(np.arange(rows.shape[0]) % 64 == 0))
         d, o, _ = bs.synth.avro_b_batch(rows, seed=seed)
         return d, o
 
@@ -257,6 +260,8 @@ class DecodeScoreWorkload:
 
         if self.fmt == "csv":
             return dict(csv_kinds=[0, 0] + [1] * 18)
+        if self.fmt == "json":
+            return dict(json_keys=list(bs.schemas.FEATURE_NAMES), json_label="failure_occurred")
         return dict(avro_schema=bs.schemas.schema_a_json() if self.fmt == "avro_a" else bs.schemas.schema_b_json())
 
     def setup(self, dev, rank):
@@ -271,7 +276,7 @@ class DecodeScoreWorkload:
         for p in range(self.nb):
             d, o = self._host_batch(314 + rank * self.nb + p)
             tot_bytes += int(o[-1])
-            rb = bs.decode.RecordBatch(d, o, dev, skip_prefix=0 if self.fmt == "csv" else 5)
+            rb = bs.decode.RecordBatch(d, o, dev, skip_prefix=0 if self.fmt in ("csv", "json") else 5)
             rb.mse = torch.empty(rb.n, dtype=torch.float32, device=dev)
             rb.flag = torch.empty(rb.n, dtype=torch.uint8, device=dev)
             rb.status = torch.empty(rb.n, dtype=torch.int32, device=dev)
@@ -299,7 +304,7 @@ class DecodeScoreWorkload:
     def step_e2e(self, i):
         import b200_sensor as bs
 
-        bs.decode.decode_score_host(self.m, self.hd, self.ho, threshold=THRESHOLD, skip_prefix=0 if self.fmt == "csv" else 5,
+        bs.decode.decode_score_host(self.m, self.hd, self.ho, threshold=THRESHOLD, skip_prefix=0 if self.fmt in ("csv", "json") else 5,
                                     reuse_output=True, **self.kw)
         return self.e2e_rows
 
@@ -307,6 +312,17 @@ class DecodeScoreWorkload:
         import b200_sensor as bs
         from oracle import c_oracle as co
 
+        if self.fmt == "json":  # no C restatement of the JSON walk: Python's json + the NumPy scoring restatement, one core
+            from oracle import cpu_oracle as orc
+
+            d, o = self._host_batch(7, n=min(n, 1 << 16))
+            w, nm = self.weights(), bs.schemas.norm_arrays()
+            done, t0 = 0, time.perf_counter()
+            while done < min(n, 1 << 18):
+                x, _, _ = orc.decode_json(d, o, list(bs.schemas.FEATURE_NAMES), "failure_occurred")
+                orc.score(x, w, W18, ACTS, norm=nm, threshold=THRESHOLD)
+                done += len(o) - 1
+            return done, time.perf_counter() - t0, 1
         co.set_threads(threads or os.cpu_count())
         d, o = self._host_batch(7, n=min(n, 1 << 20))
         nrec = len(o) - 1
@@ -428,6 +444,7 @@ WORKLOADS = {
     "csv": lambda: DecodeScoreWorkload("csv"),
     "avro_a": lambda: DecodeScoreWorkload("avro_a", batches_per_step=8),
     "avro_b": lambda: DecodeScoreWorkload("avro_b"),
+    "json": lambda: DecodeScoreWorkload("json", batch_log2=19),
 }
 DEFAULT_WORKLOAD = "avro_a"   # decode+score on the schema BASELINE.json names (testdata/cardata-v1.avsc)
 

@@ -46,6 +46,14 @@ class AvroProg(C.Structure):
     _fields_ = [("n_fields", C.c_int32), ("n_out", C.c_int32), ("f", AvroField * MAX_FIELDS)]
 
 
+JSON_NAME_MAX = 32
+
+
+class JsonSpec(C.Structure):
+    _fields_ = [("n_keys", C.c_int32), ("n_out", C.c_int32), ("name", (C.c_char * JSON_NAME_MAX) * MAX_FIELDS),
+                ("name_len", C.c_uint8 * MAX_FIELDS), ("out", C.c_int8 * MAX_FIELDS)]
+
+
 class Adam(C.Structure):
     _fields_ = [("lr", C.c_float), ("beta1", C.c_float), ("beta2", C.c_float), ("eps", C.c_float), ("iter", C.c_int64)]
 
@@ -82,6 +90,8 @@ _PROTOTYPES = {
     "b2_ae_score": (C.c_int, [_P, _P, C.c_int64, C.POINTER(Norm), C.c_float, _P, _P, _P, _P, _P]),
     "b2_decode_csv": (C.c_int, [_P, _P, _P, C.c_int64, C.POINTER(CsvSpec), _P, _P, _P, _P]),
     "b2_decode_avro": (C.c_int, [_P, _P, _P, C.c_int64, C.c_int, C.POINTER(AvroProg), _P, _P, _P, _P]),
+    "b2_decode_json": (C.c_int, [_P, _P, _P, C.c_int64, C.POINTER(JsonSpec), _P, _P, _P, _P]),
+    "b2_decode_score_json": (C.c_int, [_P, _P, _P, C.c_int64, C.POINTER(JsonSpec), C.POINTER(Norm), C.c_float, _P, _P, _P, _P, _P, _P]),
     "b2_decode_score": (C.c_int, [_P, _P, _P, C.c_int64, C.POINTER(CsvSpec), C.POINTER(AvroProg), C.c_int,
                                   C.POINTER(Norm), C.c_float, _P, _P, _P, _P, _P, _P]),
     "b2_ae_fit_steps": (C.c_int, [_P, _P, _P, C.c_int64, C.c_int, C.POINTER(Norm), C.POINTER(Adam), _P, _P, _P]),
@@ -157,6 +167,22 @@ def make_avro_prog(prog) -> AvroProg:
     for i, f in enumerate(prog.fields):
         p.f[i].type, p.f[i].nullable, p.f[i].out, p.f[i].pad = f.type, f.nullable, f.out, 0
     return p
+
+
+def make_json_spec(keys, label_key=None) -> JsonSpec:
+    """keys: member names routed to output columns 0..len(keys)-1 (in that order); label_key: member holding "true"/"false"."""
+    names = [(k, j) for j, k in enumerate(keys)] + ([(label_key, -2)] if label_key else [])
+    if not 1 <= len(names) <= MAX_FIELDS:
+        raise ValueError(f"1..{MAX_FIELDS} member names, got {len(names)}")
+    s = JsonSpec()
+    s.n_keys, s.n_out = len(names), len(keys)
+    for i, (k, out) in enumerate(names):
+        kb = k.encode("latin-1") if isinstance(k, str) else bytes(k)
+        if not 1 <= len(kb) <= JSON_NAME_MAX:
+            raise ValueError(f"member name {k!r}: 1..{JSON_NAME_MAX} bytes")
+        C.memmove(C.addressof(s.name[i]), kb, len(kb))
+        s.name_len[i], s.out[i] = len(kb), out
+    return s
 
 
 def make_csv_spec(kinds, defaults=None, delim=",", use_quote_delim=True) -> CsvSpec:

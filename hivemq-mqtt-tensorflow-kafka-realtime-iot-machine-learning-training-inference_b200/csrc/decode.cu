@@ -17,12 +17,13 @@
 // Algorithmic bytes/record: payload + 4 (offset) read, 5 written (fused) or 4*F + 4 written (decode only).
 #include "ae_math.cuh"
 #include "float_parse.cuh"
+#include "json_walk.cuh"
 
 constexpr int DEC_NT = 256;
 constexpr int DEC_WARPS = DEC_NT / 32;
 constexpr int STAGE_CAP_MAX = 24 * 1024;  // most bytes of payload one warp stages per item (the launch normally chooses far less)
 
-enum { FMT_CSV = 0, FMT_AVRO = 1 };
+enum { FMT_CSV = 0, FMT_AVRO = 1, FMT_JSON = 2 };
 enum { AV_INT = 1, AV_LONG, AV_FLOAT, AV_DOUBLE, AV_STRING, AV_BOOLEAN, AV_BYTES, AV_NULL };
 
 struct CsvP {
@@ -54,6 +55,7 @@ struct DecodeArgs {
   int warp_bytes;       // shared memory per warp: apron + stage + float tile + mbarrier
   CsvP csv;
   AvroP avro;
+  JsonP json;
   // decode-only outputs
   float* out;
   int32_t* span;
@@ -487,7 +489,8 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
   unsigned flagged = 0, n_ok = 0, n_err = 0;
   unsigned long long n_bytes = 0;
   const long long n_chunks = (a.n + 31) / 32;
-  const long long n_workers = (long long)gridDim.x * DEC_WARPS;
+  const int warps_per_cta = blockDim.x >> 5;  // the launch picks 8, 4 or 2 warps per CTA: whatever packs most warps into an SM
+  const long long n_workers = (long long)gridDim.x * warps_per_cta;
 
   auto oversize = [&](long long row) {  // a single record larger than the stage: refuse it, keep going (lane 0)
     if (a.status) a.status[row] = B2_REC_TOO_LONG;
@@ -502,7 +505,7 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
   };
 
   // cursor over this warp's chunks: lane i holds the byte range [ob, oe) of record i of the current chunk
-  long long chunk = (long long)blockIdx.x * DEC_WARPS + warp - n_workers, row0 = 0;
+  long long chunk = (long long)blockIdx.x * warps_per_cta + warp - n_workers, row0 = 0;
   int rows = 0, sub = 0, ob = 0, oe = 0;
   // plans the next item (records [sub, sub+cnt) of the cursor's chunk), issues its bulk copy and advances the cursor
   auto next_item = [&](long long& it_row0, int& it_sub, int& it_cnt, int& it_b, int& it_e) -> bool {
@@ -564,6 +567,9 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
         const int rel = c_b - ob;  // stage offset minus absolute offset (the cursor still sits on this item's chunk)
         st = csv_walk(stage, c_b, c_e, a.csv, xrow, sp, rel);
         if (st < 0) st = csv_record_careful(stage, c_b, c_e, a.csv, xrow, sp, rel);
+      } else if (FMT == FMT_JSON) {
+        for (int j = 0; j < xt_stride; ++j) xrow[j] = 0.0f;  // members that are absent or null
+        st = b2_json_record_auto(stage, c_b, c_e, a.json, xrow, &lab);
       } else {
         if (!a.avro.all_routed)
           for (int j = 0; j < xt_stride; ++j) xrow[j] = 0.0f;  // columns no field routes to
@@ -584,7 +590,7 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
         if (a.mse) a.mse[gr] = m;
         if (a.flag) a.flag[gr] = f ? 1 : 0;
         if (a.status) a.status[gr] = st;
-        if (a.label) a.label[gr] = FMT == FMT_AVRO && st == B2_REC_OK ? lab : 2;
+        if (a.label) a.label[gr] = FMT != FMT_CSV && st == B2_REC_OK ? lab : 2;
         flagged += f;
         n_ok += st == B2_REC_OK;
         n_err += st != B2_REC_OK;
@@ -602,7 +608,7 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
       }
       if (active) {
         if (a.status) a.status[gr] = st;
-        if (a.label) a.label[gr] = FMT == FMT_AVRO && st == B2_REC_OK ? lab : 2;
+        if (a.label) a.label[gr] = FMT != FMT_CSV && st == B2_REC_OK ? lab : 2;
         n_ok += st == B2_REC_OK;
         n_err += st != B2_REC_OK;
       }
@@ -703,9 +709,12 @@ static int align16i(int v) { return (v + 15) & ~15; }
 // Bytes one warp stages per item.  Avro without strings: 32 records of the schema's maximum size.  Otherwise an estimate of 32
 // typical records (a chunk whose bytes do not fit is simply split into several items, at the price of idle lanes):
 // `hint` = the caller's average record size if known, else ~10 bytes per CSV field / the fixed part + 16 bytes per Avro string.
-static int choose_stage_cap(int fmt, const CsvP& csv, const AvroP& avro, int hint) {
+static int choose_stage_cap(int fmt, const CsvP& csv, const AvroP& avro, const JsonP& json, int hint) {
   int per_rec;
-  if (fmt == FMT_AVRO) {
+  if (fmt == FMT_JSON) {
+    per_rec = 2;
+    for (int k = 0; k < json.n_keys; ++k) per_rec += json.len[k] + 14;  // "name":value,
+  } else if (fmt == FMT_AVRO) {
     const int mx = avro_max_record_bytes(avro);
     if (mx > 0) return min(STAGE_CAP_MAX, align16i(mx * 32 + 32));
     per_rec = avro.skip_prefix;
@@ -732,20 +741,29 @@ static int choose_stage_cap(int fmt, const CsvP& csv, const AvroP& avro, int hin
 template <int D, int MODE, bool FT, int FMT>
 static int launch_decode_fmt(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stream) {
   const int xt_stride = MODE == 1 ? D : args.n_out;
-  args.stage_cap = choose_stage_cap(args.fmt, args.csv, args.avro, ctx->record_bytes_hint);
+  args.stage_cap = choose_stage_cap(args.fmt, args.csv, args.avro, args.json, ctx->record_bytes_hint);
   args.warp_bytes = 16 + args.stage_cap + 16 + align16i(32 * xt_stride * 4) + 16;
-  const size_t smem = (size_t)args.warp_bytes * DEC_WARPS;
-  B2_REQUIRE(smem <= (size_t)ctx->smem_optin, "decode: tile needs %zu bytes of shared memory (max %d)", smem, ctx->smem_optin);
   auto kern = decode_kernel<D, MODE, FT, FMT>;
-  B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  int occ = 0;
-  B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, DEC_NT, smem));
+  // no block-wide synchronisation in the kernel, so the CTA size is free: take the one that packs most warps into an SM
+  int best_warps = 0, threads = DEC_NT, occ = 0;
+  size_t smem = 0;
+  B2_REQUIRE((size_t)args.warp_bytes * 2 <= (size_t)ctx->smem_optin, "decode: a warp's stage needs %d bytes of shared memory (max %d per CTA)",
+             args.warp_bytes, ctx->smem_optin / 2);
+  B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->smem_optin));
+  for (int w = DEC_WARPS; w >= 2; w >>= 1) {
+    const size_t sm = (size_t)args.warp_bytes * w;
+    if (sm > (size_t)ctx->smem_optin) continue;
+    int o = 0;
+    B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, kern, w * 32, sm));
+    if (o * w > best_warps) best_warps = o * w, threads = w * 32, occ = o, smem = sm;
+  }
   B2_REQUIRE(occ >= 1, "decode: kernel does not fit on an SM");
+  const int wpc = threads / 32;
   const long long n_chunks = (args.n + 31) / 32;
   long long grid = (long long)ctx->sm_count * occ;
-  const long long need = (n_chunks + DEC_WARPS - 1) / DEC_WARPS;
+  const long long need = (n_chunks + wpc - 1) / wpc;
   if (grid > need) grid = need;
-  kern<<<(unsigned)grid, DEC_NT, smem, stream>>>(args);
+  kern<<<(unsigned)grid, threads, smem, stream>>>(args);
   B2_CUDA(cudaGetLastError());
   return B2_OK;
 }
@@ -754,6 +772,7 @@ static int launch_decode_fmt(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stre
 template <int D, int MODE, bool FT>
 static int launch_decode(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stream) {
   if (args.fmt == FMT_CSV) return launch_decode_fmt<D, MODE, FT, FMT_CSV>(ctx, args, stream);
+  if (args.fmt == FMT_JSON) return launch_decode_fmt<D, MODE, FT, FMT_JSON>(ctx, args, stream);
   return launch_decode_fmt<D, MODE, FT, FMT_AVRO>(ctx, args, stream);
 }
 
@@ -801,9 +820,50 @@ extern "C" int b2_decode_avro(b2_ctx* ctx, const uint8_t* bytes_dev, const int32
   return launch_decode<18, 0, false>(ctx, args, (cudaStream_t)stream);
 }
 
+static int fill_json(const b2_json_spec* sp, JsonP& j) {
+  B2_REQUIRE(sp->n_keys >= 1 && sp->n_keys <= B2_JSON_MAX_KEYS, "json: n_keys=%d out of range", sp->n_keys);
+  B2_REQUIRE(sp->n_out >= 1 && sp->n_out <= B2_MAX_WIDTH, "json: n_out=%d out of range", sp->n_out);
+  memset(&j, 0, sizeof(j));
+  j.n_keys = sp->n_keys;
+  j.n_out = sp->n_out;
+  for (int k = 0; k < sp->n_keys; ++k) {
+    const int len = sp->name_len[k];
+    B2_REQUIRE(len >= 1 && len <= B2_JSON_NAME_BYTES, "json: name %d has length %d (1..%d)", k, len, B2_JSON_NAME_BYTES);
+    B2_REQUIRE(sp->out[k] >= -2 && sp->out[k] < sp->n_out, "json: name %d routed to column %d", k, sp->out[k]);
+    const uint8_t* nm = reinterpret_cast<const uint8_t*>(sp->name[k]);
+    memcpy(j.name[k], nm, len);
+    j.len[k] = (uint8_t)len;
+    j.out[k] = sp->out[k];
+  }
+  b2_json_finish_spec(j);
+  return B2_OK;
+}
+
+extern "C" int b2_decode_json(b2_ctx* ctx, const uint8_t* bytes_dev, const int32_t* offs_dev, int64_t n, const b2_json_spec* spec,
+                              float* out_dev, uint8_t* label_dev, int32_t* status_dev, void* stream) {
+  B2_REQUIRE(ctx && spec, "b2_decode_json: NULL argument");
+  B2_REQUIRE(n >= 0, "b2_decode_json: n < 0");
+  if (n == 0) return B2_OK;
+  B2_REQUIRE(bytes_dev && offs_dev && out_dev, "b2_decode_json: NULL device pointer");
+  DeviceGuard g(ctx->device);
+  DecodeArgs<18> args;
+  memset(&args, 0, sizeof(args));
+  int rc = fill_json(spec, args.json);
+  if (rc) return rc;
+  args.bytes = bytes_dev;
+  args.offs = offs_dev;
+  args.n = n;
+  args.fmt = FMT_JSON;
+  args.n_out = spec->n_out;
+  args.out = out_dev;
+  args.status = status_dev;
+  args.label = label_dev;
+  return launch_decode<18, 0, false>(ctx, args, (cudaStream_t)stream);
+}
+
 template <int D>
 static int decode_score_spec(b2_ae* ae, const uint8_t* bytes, const int32_t* offs, int64_t n, const b2_csv_spec* csv,
-                             const b2_avro_prog* avro, int skip_prefix, const b2_norm* norm, float threshold, float* mse, uint8_t* flag,
+                             const b2_avro_prog* avro, const b2_json_spec* json, int skip_prefix, const b2_norm* norm, float threshold, float* mse, uint8_t* flag,
                              uint8_t* label, int32_t* status, unsigned long long* counters, cudaStream_t stream) {
   DecodeArgs<D> args;
   memset(&args, 0, sizeof(args));
@@ -813,6 +873,11 @@ static int decode_score_spec(b2_ae* ae, const uint8_t* bytes, const int32_t* off
     if (rc) return rc;
     B2_REQUIRE(args.csv.n_float == D, "b2_decode_score: CSV spec yields %d float columns, model input is %d", args.csv.n_float, D);
     args.fmt = FMT_CSV;
+  } else if (json) {
+    rc = fill_json(json, args.json);
+    if (rc) return rc;
+    B2_REQUIRE(json->n_out == D, "b2_decode_score_json: spec yields %d columns, model input is %d", json->n_out, D);
+    args.fmt = FMT_JSON;
   } else {
     rc = fill_avro(avro, skip_prefix, args.avro);
     if (rc) return rc;
@@ -843,27 +908,43 @@ static int decode_score_spec(b2_ae* ae, const uint8_t* bytes, const int32_t* off
   return launch_decode<D, 1, false>(ae->ctx, args, stream);
 }
 
-extern "C" int b2_decode_score(b2_ae* ae, const uint8_t* bytes_dev, const int32_t* offs_dev, int64_t n, const b2_csv_spec* csv,
-                               const b2_avro_prog* avro, int skip_prefix, const b2_norm* norm, float threshold, float* mse_dev,
-                               uint8_t* flag_dev, uint8_t* label_dev, int32_t* status_dev, unsigned long long* counters_dev,
-                               void* stream) {
-  B2_REQUIRE(ae != nullptr, "b2_decode_score: ae is NULL");
-  B2_REQUIRE((csv != nullptr) != (avro != nullptr), "b2_decode_score: exactly one of csv / avro must be given");
-  B2_REQUIRE(n >= 0, "b2_decode_score: n < 0");
+static int decode_score_any(const char* who, b2_ae* ae, const uint8_t* bytes_dev, const int32_t* offs_dev, int64_t n, const b2_csv_spec* csv,
+                            const b2_avro_prog* avro, const b2_json_spec* json, int skip_prefix, const b2_norm* norm, float threshold,
+                            float* mse_dev, uint8_t* flag_dev, uint8_t* label_dev, int32_t* status_dev, unsigned long long* counters_dev,
+                            void* stream) {
+  B2_REQUIRE(ae != nullptr, "%s: ae is NULL", who);
+  B2_REQUIRE(n >= 0, "%s: n < 0", who);
   if (n == 0) return B2_OK;
-  B2_REQUIRE(bytes_dev && offs_dev, "b2_decode_score: NULL device pointer");
-  B2_REQUIRE(!norm || norm->n == 0 || norm->n == ae->desc.widths[0], "b2_decode_score: norm table has %d features, model has %d",
+  B2_REQUIRE(bytes_dev && offs_dev, "%s: NULL device pointer", who);
+  B2_REQUIRE(!norm || norm->n == 0 || norm->n == ae->desc.widths[0], "%s: norm table has %d features, model has %d", who,
              norm ? norm->n : 0, ae->desc.widths[0]);
   DeviceGuard g(ae->ctx->device);
   int rc = b2_ae_sync_host(ae);
   if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   if (ae->spec_d == 18)
-    return decode_score_spec<18>(ae, bytes_dev, offs_dev, n, csv, avro, skip_prefix, norm, threshold, mse_dev, flag_dev, label_dev,
+    return decode_score_spec<18>(ae, bytes_dev, offs_dev, n, csv, avro, json, skip_prefix, norm, threshold, mse_dev, flag_dev, label_dev,
                                  status_dev, counters_dev, st);
   if (ae->spec_d == 30)
-    return decode_score_spec<30>(ae, bytes_dev, offs_dev, n, csv, avro, skip_prefix, norm, threshold, mse_dev, flag_dev, label_dev,
+    return decode_score_spec<30>(ae, bytes_dev, offs_dev, n, csv, avro, json, skip_prefix, norm, threshold, mse_dev, flag_dev, label_dev,
                                  status_dev, counters_dev, st);
-  b2_set_error("b2_decode_score: fused path needs the D-14-7-7-D autoencoder with D in {18, 30}; decode and score separately");
+  b2_set_error("%s: fused path needs the D-14-7-7-D autoencoder with D in {18, 30}; decode and score separately", who);
   return B2_EUNSUPPORTED;
+}
+
+extern "C" int b2_decode_score(b2_ae* ae, const uint8_t* bytes_dev, const int32_t* offs_dev, int64_t n, const b2_csv_spec* csv,
+                               const b2_avro_prog* avro, int skip_prefix, const b2_norm* norm, float threshold, float* mse_dev,
+                               uint8_t* flag_dev, uint8_t* label_dev, int32_t* status_dev, unsigned long long* counters_dev,
+                               void* stream) {
+  B2_REQUIRE((csv != nullptr) != (avro != nullptr), "b2_decode_score: exactly one of csv / avro must be given");
+  return decode_score_any("b2_decode_score", ae, bytes_dev, offs_dev, n, csv, avro, nullptr, skip_prefix, norm, threshold, mse_dev, flag_dev,
+                          label_dev, status_dev, counters_dev, stream);
+}
+
+extern "C" int b2_decode_score_json(b2_ae* ae, const uint8_t* bytes_dev, const int32_t* offs_dev, int64_t n, const b2_json_spec* json,
+                                    const b2_norm* norm, float threshold, float* mse_dev, uint8_t* flag_dev, uint8_t* label_dev,
+                                    int32_t* status_dev, unsigned long long* counters_dev, void* stream) {
+  B2_REQUIRE(json != nullptr, "b2_decode_score_json: spec is NULL");
+  return decode_score_any("b2_decode_score_json", ae, bytes_dev, offs_dev, n, nullptr, nullptr, json, 0, norm, threshold, mse_dev, flag_dev,
+                          label_dev, status_dev, counters_dev, stream);
 }

@@ -88,7 +88,7 @@ B2_HD uint64_t b2_pow5(int q, int half) {
 // w × 10^q → IEEE binary32 bits (sign excluded), round-to-nearest-even.  w != 0 is exact.
 B2_HD uint32_t b2_eisel_lemire32(uint64_t w, int q) {
   if (w == 0 || q < -64) return 0u;            // below half the smallest subnormal for any 64-bit w
-  if (q > B2_POW5_MAX_Q) return 0x7F800000u;   // overflow → inf
+  if (q > 38) return 0x7F800000u;              // overflow → inf
   const int lz = b2_clz64(w);
   w <<= lz;
   uint64_t hi, lo;
@@ -154,14 +154,90 @@ B2_HD uint32_t b2_dec32(uint64_t w, int q) {
   return b2_eisel_lemire32(w, q);
 }
 
+// ---- decimal → binary64 (the JSON wire format: KSQL's DOUBLE columns, then one more rounding to the model's float32) -------
+// Same Eisel-Lemire step with binary64 parameters; exact for any 64-bit w (Mushtak & Lemire, "Fast number parsing without
+// fallback", 2023).  Clinger's short cut in front: w < 2^53 and |q| ≤ 22 are exactly representable operands of ONE correctly
+// rounded multiplication or division.
+B2_HD uint64_t b2_eisel_lemire64(uint64_t w, int q) {
+  if (w == 0 || q < -342) return 0ull;
+  if (q > 308) return 0x7FF0000000000000ull;
+  const int lz = b2_clz64(w);
+  w <<= lz;
+  uint64_t hi, lo;
+  b2_mul64(w, b2_pow5(q, 0), hi, lo);
+  const uint64_t precision_mask = 0xFFFFFFFFFFFFFFFFull >> 55;  // mantissa bits (52) + 3
+  if ((hi & precision_mask) == precision_mask) {
+    uint64_t hi2, lo2;
+    b2_mul64(w, b2_pow5(q, 1), hi2, lo2);
+    lo += hi2;
+    if (hi2 > lo) ++hi;
+  }
+  const int upperbit = (int)(hi >> 63);
+  const int shift = upperbit + 64 - 52 - 3;
+  uint64_t m = hi >> shift;
+  int p2 = (((152170 + 65536) * q) >> 16) + 63 + upperbit - lz + 1023;
+  if (p2 <= 0) {  // subnormal
+    if (-p2 + 1 >= 64) return 0ull;
+    m >>= -p2 + 1;
+    m += (m & 1);
+    m >>= 1;
+    p2 = (m < (1ull << 52)) ? 0 : 1;
+    return ((uint64_t)p2 << 52) | (m & 0xFFFFFFFFFFFFFull);
+  }
+  if (lo <= 1 && q >= -4 && q <= 23 && (m & 3) == 1) {  // exactly halfway and even: do not round up
+    if ((m << shift) == hi) m &= ~1ull;
+  }
+  m += (m & 1);
+  m >>= 1;
+  if (m >= (2ull << 52)) {
+    m = 1ull << 52;
+    ++p2;
+  }
+  m &= ~(1ull << 52);
+  if (p2 >= 0x7FF) return 0x7FF0000000000000ull;
+  return ((uint64_t)p2 << 52) | m;
+}
+
+B2_HD uint64_t b2_dec64(uint64_t w, int q) {
+  if (w < (1ull << 53) && q >= -22 && q <= 22) {
+    uint64_t bits;
+#if defined(__CUDA_ARCH__)
+    const double p = b2dev::b2_p10d[(q < 0 ? -q : q) + 22];
+    const double d = q < 0 ? __ddiv_rn((double)w, p) : __dmul_rn((double)w, p);
+    bits = (uint64_t)__double_as_longlong(d);
+#else
+    const double p = b2host::b2_p10d[(q < 0 ? -q : q) + 22];
+    volatile double dv = q < 0 ? (double)w / p : (double)w * p;
+    const double d = dv;
+    __builtin_memcpy(&bits, &d, 8);
+#endif
+    return bits;
+  }
+  return b2_eisel_lemire64(w, q);
+}
+
+B2_HD uint32_t b2_f64bits_to_f32bits(uint64_t bits) {  // round-to-nearest-even narrowing, like tf.cast / np.float32(double)
+#if defined(__CUDA_ARCH__)
+  return __float_as_uint(__double2float_rn(__longlong_as_double((long long)bits)));
+#else
+  double d;
+  __builtin_memcpy(&d, &bits, 8);
+  const float f = (float)d;
+  uint32_t fb;
+  __builtin_memcpy(&fb, &f, 4);
+  return fb;
+#endif
+}
+
 B2_HD bool b2_is_digit(uint8_t c) { return (uint8_t)(c - '0') < 10; }
 B2_HD uint8_t b2_lower(uint8_t c) { return (c >= 'A' && c <= 'Z') ? (uint8_t)(c + 32) : c; }
 
 // Parse s[0..n) as one float field.  Grammar (what both safe_strtof and strtof accept for decimal input):
 //   ws* [+-]? ( digits [. digits*] | . digits+ ) ( [eE] [+-]? digits+ )? ws*   |   ws* [+-]? (inf|infinity|nan) ws*
 // Hex floats and nan(payload) are rejected.  Returns B2_NUM_*; *out receives the IEEE bits.
-template <typename BytePtr>
-B2_HD int b2_parse_float(BytePtr s, int n, uint32_t* out) {
+// WIDE = false: *out32 = binary32 bits (one rounding);  WIDE = true: *out64 = binary64 bits
+template <bool WIDE, typename BytePtr>
+B2_HD int b2_parse_number(BytePtr s, int n, uint32_t* out32, uint64_t* out64) {
   int i = 0;
   while (i < n && (s[i] == ' ' || s[i] == '\t')) ++i;
   while (n > i && (s[n - 1] == ' ' || s[n - 1] == '\t')) --n;
@@ -178,7 +254,8 @@ B2_HD int b2_parse_float(BytePtr s, int n, uint32_t* out) {
     const int len = n - i;
     uint8_t c0 = b2_lower(s[i]);
     if (len == 3 && c0 == 'n' && b2_lower(s[i + 1]) == 'a' && b2_lower(s[i + 2]) == 'n') {
-      *out = sign | 0x7FC00000u;
+      if (WIDE) *out64 = ((uint64_t)sign << 32) | 0x7FF8000000000000ull;
+      else *out32 = sign | 0x7FC00000u;
       return B2_NUM_OK;
     }
     if ((len == 3 || len == 8) && c0 == 'i' && b2_lower(s[i + 1]) == 'n' && b2_lower(s[i + 2]) == 'f') {
@@ -187,7 +264,8 @@ B2_HD int b2_parse_float(BytePtr s, int n, uint32_t* out) {
         for (int k = 0; k < 5; ++k)
           if (b2_lower(s[i + 3 + k]) != (uint8_t)rest[k]) return B2_NUM_BAD;
       }
-      *out = sign | 0x7F800000u;
+      if (WIDE) *out64 = ((uint64_t)sign << 32) | 0x7FF0000000000000ull;
+      else *out32 = sign | 0x7F800000u;
       return B2_NUM_OK;
     }
     return B2_NUM_BAD;
@@ -248,18 +326,34 @@ B2_HD int b2_parse_float(BytePtr s, int n, uint32_t* out) {
   }
   if (i != n) return B2_NUM_BAD;
   if (w == 0) {
-    *out = sign;
+    if (WIDE) *out64 = (uint64_t)sign << 32;
+    else *out32 = sign;
     return B2_NUM_OK;
   }
   if (q < -400) q = -400;
   if (q > 400) q = 400;
+  if (WIDE) {
+    const uint64_t a = truncated ? b2_eisel_lemire64(w, q) : b2_dec64(w, q);
+    if (truncated && a != b2_eisel_lemire64(w + 1, q)) return B2_NUM_TOO_LONG;
+    *out64 = ((uint64_t)sign << 32) | a;
+    return B2_NUM_OK;
+  }
   const uint32_t a = truncated ? b2_eisel_lemire32(w, q) : b2_dec32(w, q);
   if (truncated) {
     const uint32_t b = b2_eisel_lemire32(w + 1, q);
     if (a != b) return B2_NUM_TOO_LONG;
   }
-  *out = sign | a;
+  *out32 = sign | a;
   return B2_NUM_OK;
+}
+
+template <typename BytePtr>
+B2_HD int b2_parse_float(BytePtr s, int n, uint32_t* out) {
+  return b2_parse_number<false>(s, n, out, (uint64_t*)nullptr);
+}
+template <typename BytePtr>
+B2_HD int b2_parse_double(BytePtr s, int n, uint64_t* out) {
+  return b2_parse_number<true>(s, n, (uint32_t*)nullptr, out);
 }
 
 
@@ -393,7 +487,10 @@ B2_HD uint32_t b2_four_digits_fast(uint32_t x) {  // like b2_four_digits; two by
 #endif
 }
 
-B2_HD int b2_csv_num16(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, uint32_t w4, int sh, int rem, uint32_t delim, uint32_t* out) {
+// Shared core: MODE 0 = CSV field (terminator `delim` or the record's end; result binary32, one rounding);
+// MODE 1 = JSON number (terminator ',' or '}'; RFC 8259 shape checks; result binary32 by way of binary64, two roundings).
+template <int MODE>
+B2_HD int b2_num16(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, uint32_t w4, int sh, int rem, uint32_t delim, uint32_t* out) {
   const int neg = (((w0 >> sh) & 0xFFu) == '-' && rem > 0) ? 1 : 0;
   const int s = sh + 8 * neg;  // ≤ 32: the clamped funnel shift returns the upper word for 32
   const uint32_t t0 = b2_fsr(w0, w1, s), t1 = b2_fsr(w1, w2, s), t2 = b2_fsr(w2, w3, s), t3 = b2_fsr(w3, w4, s);
@@ -406,7 +503,7 @@ B2_HD int b2_csv_num16(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, uint3
   if (p1 >= 16) return -1;
   const uint32_t c1 = b2_byte16(t0, t1, t2, t3, p1);
   int Lm, pd, has_dot, ex = 0, L;
-  if (p1 >= rem || c1 == delim) {
+  if (MODE == 0 ? (p1 >= rem || c1 == delim) : (c1 == ',' || c1 == '}')) {
     if (p1 == 0) return neg ? -1 : 0;  // empty field ("-" alone is not a number)
     Lm = pd = L = p1;
     has_dot = 0;
@@ -420,7 +517,7 @@ B2_HD int b2_csv_num16(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, uint3
       pd = p1;
       has_dot = 1;
       Lm = L = p2;
-      if (!(p2 >= rem || c2 == delim)) {
+      if (!(MODE == 0 ? (p2 >= rem || c2 == delim) : (c2 == ',' || c2 == '}'))) {
         if ((c2 | 0x20u) != 'e') return -1;
         pe = p2;
       }
@@ -442,7 +539,10 @@ B2_HD int b2_csv_num16(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, uint3
       const int p3 = b2_ffs32(Be) - 1;
       const int ne = p3 - es;
       if (p3 >= 16 || ne < 1 || ne > 2) return -1;
-      if (!(p3 >= rem || b2_byte16(t0, t1, t2, t3, p3) == delim)) return -1;
+      {
+        const uint32_t c3 = b2_byte16(t0, t1, t2, t3, p3 & 15);
+        if (!(MODE == 0 ? (p3 >= rem || c3 == delim) : (p3 < rem && (c3 == ',' || c3 == '}')))) return -1;
+      }
       ex = (int)b2_byte16(t0, t1, t2, t3, es) - '0';
       if (ne == 2) ex = ex * 10 + (int)b2_byte16(t0, t1, t2, t3, es + 1) - '0';
       if (eneg) ex = -ex;
@@ -451,6 +551,9 @@ B2_HD int b2_csv_num16(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, uint3
   }
   const int nd = Lm - has_dot;  // digit characters
   if (nd < 1 || Lm > 12) return -1;
+  if (MODE == 1) {  // JSON: at least one digit on each side of a point, no leading zeros (the careful walk gives the verdict)
+    if (L > rem || pd < 1 || (has_dot && Lm - pd - 1 < 1) || (pd > 1 && (t0 & 0xFFu) == '0')) return -1;
+  }
   // squeeze the dot out (bytes after it move down by one) and zero everything from digit nd on: 12 digits, zero-padded on the right
   const uint32_t u0 = b2_fsr(x0, x1, 8), u1 = b2_fsr(x1, x2, 8), u2 = x2 >> 8;
   const uint32_t a0 = b2_bytemask(pd), a1 = b2_bytemask(pd - 4), a2 = b2_bytemask(pd - 8);
@@ -459,6 +562,15 @@ B2_HD int b2_csv_num16(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, uint3
   const uint32_t hi8 = b2_four_digits_fast(r0) * 10000u + b2_four_digits_fast(r1);
   const uint64_t w = (uint64_t)hi8 * 10000u + b2_four_digits_fast(r2);
   const int q = ex - (nd - pd) - (12 - nd);  // fraction digits and the padding zeros
-  *out = (neg ? 0x80000000u : 0u) | b2_dec32(w, q);
+  if (MODE == 1) *out = b2_f64bits_to_f32bits((neg ? 0x8000000000000000ull : 0ull) | b2_dec64(w, q));
+  else *out = (neg ? 0x80000000u : 0u) | b2_dec32(w, q);
   return L + neg;
+}
+
+B2_HD int b2_csv_num16(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, uint32_t w4, int sh, int rem, uint32_t delim, uint32_t* out) {
+  return b2_num16<0>(w0, w1, w2, w3, w4, sh, rem, delim, out);
+}
+// a JSON number followed by ',' or '}': returns its length (≥ 1) or -1 (not the plain short form: let the careful walk decide)
+B2_HD int b2_json_num16(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, uint32_t w4, int sh, int rem, uint32_t* out) {
+  return b2_num16<1>(w0, w1, w2, w3, w4, sh, rem, 0u, out);
 }

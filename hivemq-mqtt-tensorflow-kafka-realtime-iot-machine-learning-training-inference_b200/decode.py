@@ -188,7 +188,28 @@ def decode_avro(records, schema, dtype=None) -> List[np.ndarray]:
     return cols
 
 
-def decode_score(model, records, csv_kinds=None, csv_defaults=None, avro_schema=None, threshold: float = 5.0,
+def decode_json_matrix(records, keys, label_key: Optional[str] = None, raise_on_error=True):
+    """One flat JSON object per record (the raw ``sensor-data`` topic: LSTM-…/cardata-v1.json; KSQL value_format='JSON',
+    01_installConfluentPlatform.sh:235) → (f32[N, len(keys)], label u8[N], status int32[N]) on the device.  Numbers take the
+    JSON reader's route: text → binary64 → float32; absent / null members give 0; the last of equal names wins."""
+    rb = _as_batch(records)
+    dev = rb.data.device
+    spec = _ffi.make_json_spec(keys, label_key)
+    out = torch.empty((rb.n, len(keys)), dtype=torch.float32, device=dev)
+    label = torch.empty(rb.n, dtype=torch.uint8, device=dev)
+    status = torch.empty(rb.n, dtype=torch.int32, device=dev)
+    if rb.skip_prefix:
+        raise ValueError("JSON records carry no framing prefix")
+    _size_hint(rb)
+    _ffi.check(_ffi.lib().b2_decode_json(get_ctx(dev.index), _ffi.ptr(rb.data), _ffi.ptr(rb.offsets), rb.n, C.byref(spec), _ffi.ptr(out),
+                                         _ffi.ptr(label), _ffi.ptr(status), _stream_ptr()), "b2_decode_json")
+    if raise_on_error:
+        _raise_on_status(status, "decode_json")
+    return out, label, status
+
+
+def decode_score(model, records, csv_kinds=None, csv_defaults=None, avro_schema=None, json_keys=None, json_label=None,
+                 threshold: float = 5.0,
                  mse: Optional[torch.Tensor] = None, flag: Optional[torch.Tensor] = None, label: Optional[torch.Tensor] = None,
                  status: Optional[torch.Tensor] = None, counters: Optional[torch.Tensor] = None, field_delim=",", use_quote_delim=True):
     """The streaming scoring loop of cardata-v1.py:176-231 in ONE kernel: decode → normalize_fn → Dense AE → MSE → flag.
@@ -201,9 +222,19 @@ def decode_score(model, records, csv_kinds=None, csv_defaults=None, avro_schema=
         flag = torch.empty(rb.n, dtype=torch.uint8, device=dev)
     if status is None:
         status = torch.empty(rb.n, dtype=torch.int32, device=dev)
-    if (csv_kinds is None) == (avro_schema is None):
-        raise ValueError("give exactly one of csv_kinds / avro_schema")
+    if (csv_kinds is not None) + (avro_schema is not None) + (json_keys is not None) != 1:
+        raise ValueError("give exactly one of csv_kinds / avro_schema / json_keys")
     spec = p = None
+    if json_keys is not None:
+        js = _ffi.make_json_spec(json_keys, json_label)
+        if label is None:
+            label = torch.empty(rb.n, dtype=torch.uint8, device=dev)
+        nm = model._norm_struct()
+        _size_hint(rb)
+        _ffi.check(_ffi.lib().b2_decode_score_json(model._handle(), _ffi.ptr(rb.data), _ffi.ptr(rb.offsets), rb.n, C.byref(js), C.byref(nm),
+                                                   float(threshold), _ffi.ptr(mse), _ffi.ptr(flag), _ffi.ptr(label), _ffi.ptr(status),
+                                                   _ffi.ptr(counters), _stream_ptr()), "b2_decode_score_json")
+        return mse, flag, label, status
     if csv_kinds is not None:
         spec = _ffi.make_csv_spec(csv_kinds, csv_defaults, field_delim, use_quote_delim)
     else:
@@ -225,7 +256,7 @@ _side_stream = {}  # device index → copy stream
 
 
 def decode_score_host(model, data, offsets, csv_kinds=None, csv_defaults=None, avro_schema=None, threshold: float = 5.0,
-                      skip_prefix: int = 0, chunks: int = 4, reuse_output: bool = False):
+                      skip_prefix: int = 0, chunks: int = 4, reuse_output: bool = False, json_keys=None, json_label=None):
     """End-to-end form for HOST buffers (what a Kafka consumer hands over): ``data`` uint8 / ``offsets`` int32 as NumPy arrays
     or (ideally pinned) CPU tensors → H2D copy → fused kernel → D2H of (mse f32[n], flag u8[n]) as NumPy arrays.
 
@@ -272,7 +303,8 @@ def decode_score_host(model, data, offsets, csv_kinds=None, csv_defaults=None, a
         rb = RecordBatch.__new__(RecordBatch)
         rb.data, rb.offsets, rb.n, rb.skip_prefix = d_dev, o_dev[c0:c1 + 1], c1 - c0, skip_prefix
         rb.avg_record_bytes = (int(oh[n]) - int(oh[0]) + n - 1) // max(n, 1)
-        decode_score(model, rb, csv_kinds=csv_kinds, csv_defaults=csv_defaults, avro_schema=avro_schema, threshold=threshold,
+        decode_score(model, rb, csv_kinds=csv_kinds, csv_defaults=csv_defaults, avro_schema=avro_schema, json_keys=json_keys,
+                     json_label=json_label, threshold=threshold,
                      mse=mse[c0:c1], flag=flag[c0:c1], status=status[c0:c1], label=None if label is None else label[c0:c1])
         hm[c0:c1].copy_(mse[c0:c1], non_blocking=True)
         hf[c0:c1].copy_(flag[c0:c1], non_blocking=True)

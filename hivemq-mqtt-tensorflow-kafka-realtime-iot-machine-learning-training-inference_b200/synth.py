@@ -168,6 +168,39 @@ def credit_csv_batch(rows: np.ndarray, labels: Optional[np.ndarray] = None) -> T
     return _arrow_strings_to_batch(joined)
 
 
+def json_batch(rows: np.ndarray, labels: Optional[np.ndarray] = None, camel_duplicates: bool = False
+               ) -> Tuple[np.ndarray, np.ndarray]:
+    """The simulator's JSON messages on the raw ``sensor-data`` topic (LSTM-…/cardata-v1.json): one flat object per record,
+    members in schema order, floats as Java prints them, tyre pressures / firmware as integers; ``failure_occurred`` as a
+    string when ``labels`` (0/1) is given; ``camel_duplicates`` repeats every member under its camelCase name like the fixture."""
+    import pyarrow as pa
+    import pyarrow.compute as pc
+
+    def camel(name):
+        parts = name.split("_")
+        return parts[0] + "".join(p.capitalize() if not p.isdigit() else p for p in parts[1:])
+
+    n = rows.shape[0]
+    vals = []
+    for j, (_, is_int) in enumerate(schemas.FEATURES):
+        vals.append(pc.cast(pa.array(np.rint(rows[:, j]).astype(np.int64)), pa.string()) if is_int else _float_col_to_text(rows[:, j]))
+    pieces = []
+    first = True
+    for names in ([schemas.FEATURE_NAMES] + ([[camel(k) for k in schemas.FEATURE_NAMES]] if camel_duplicates else [])):
+        for k, v in zip(names, vals):
+            pieces.append(pa.scalar(("{" if first else ",") + '"' + k + '":'))
+            pieces.append(v)
+            first = False
+    if labels is not None:
+        lab = pa.array(np.where(np.asarray(labels) != 0, "true", "false"))
+        pieces += [pa.scalar(',"failure_occurred":"'), lab, pa.scalar('"')]
+    pieces.append(pa.scalar("}"))
+    joined = pc.binary_join_element_wise(*pieces, "")
+    if isinstance(joined, pa.ChunkedArray):
+        joined = joined.combine_chunks()
+    return _arrow_strings_to_batch(joined)
+
+
 # ----------------------------------------------------------------------------------------------
 # Avro
 # ----------------------------------------------------------------------------------------------

@@ -46,6 +46,7 @@ extern "C" {
 #define B2_REC_TRUNCATED   5  /* Avro: record ends inside a field */
 #define B2_REC_BAD_BRANCH  6  /* Avro: union branch index out of range */
 #define B2_REC_TOO_LONG    7  /* CSV: number with > 19 significant digits that cannot be rounded unambiguously */
+#define B2_REC_BAD_JSON    8  /* JSON: not one well-formed RFC 8259 object */
 
 typedef struct b2_ctx b2_ctx;   /* one per device / rank */
 typedef struct b2_ae b2_ae;     /* Dense autoencoder: weights (+ Adam state once fit is called) */
@@ -123,6 +124,27 @@ typedef struct {
  * (cardata-v1.py:13-37,61-66).  label_dev u8[N]: 0 "false", 1 "true", 2 null/empty, 3 other (NULL to skip). */
 int  b2_decode_avro(b2_ctx* ctx, const uint8_t* bytes_dev, const int32_t* offs_dev, int64_t n, int skip_prefix,
                     const b2_avro_prog* prog, float* out_dev, uint8_t* label_dev, int32_t* status_dev, void* stream);
+
+/* ---- JSON records (the raw `sensor-data` topic) ----------------------------------------------
+ * One flat JSON object per message, as the car simulator publishes it and KSQL reads it with value_format='JSON'
+ * (01_installConfluentPlatform.sh:235; fixture python-scripts/LSTM-TensorFlow-IO-Kafka/cardata-v1.json).  The members named
+ * in the spec are routed to output columns; numbers go text → binary64 (correctly rounded) → binary32 (the scripts' cast);
+ * absent or null members give 0, the last of several equal names wins, other members are skipped (validated as RFC 8259).
+ * out[k] = column, -2 = the label member ("true"/"false" as string or literal → label_dev 1/0, null/"" 2, else 3), -1 ignore. */
+#define B2_JSON_NAME_MAX 32
+typedef struct {
+  int32_t n_keys;
+  int32_t n_out;
+  char    name[B2_MAX_FIELDS][B2_JSON_NAME_MAX];   /* member names, raw bytes (no escapes), not NUL-terminated */
+  uint8_t name_len[B2_MAX_FIELDS];
+  int8_t  out[B2_MAX_FIELDS];
+} b2_json_spec;
+int  b2_decode_json(b2_ctx* ctx, const uint8_t* bytes_dev, const int32_t* offs_dev, int64_t n, const b2_json_spec* spec,
+                    float* out_dev, uint8_t* label_dev, int32_t* status_dev, void* stream);
+/* b2_decode_score for JSON records (same outputs and counters). */
+int  b2_decode_score_json(b2_ae* ae, const uint8_t* bytes_dev, const int32_t* offs_dev, int64_t n, const b2_json_spec* json,
+                          const b2_norm* norm, float threshold, float* mse_dev, uint8_t* flag_dev, uint8_t* label_dev,
+                          int32_t* status_dev, unsigned long long* counters_dev, void* stream);
 
 /* Fused decode → normalise → score: the streaming scoring loop of cardata-v1.py:176-231 in one kernel.
  * Exactly one of csv / avro is non-NULL.  Records whose status != 0 get mse = NaN, flag = 0 and are counted

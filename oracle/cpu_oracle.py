@@ -561,3 +561,60 @@ def _array2string_np114(row: np.ndarray) -> str:
             line += " "
     s += line
     return "[" + s[1:] + "]"
+
+
+# ---- JSON wire format of the raw sensor-data topic --------------------------------------------------------------
+REC_BAD_JSON = 8
+
+
+def decode_json(data: np.ndarray, offsets: np.ndarray, keys: Sequence[str], label_key: Optional[str] = None):
+    """One flat JSON object per record (LSTM-…/cardata-v1.json; KSQL value_format='JSON',
+    01_installConfluentPlatform.sh:235) → float32[N, len(keys)], label u8[N], status int32[N].
+    The parser is Python's ``json`` (RFC 8259, numbers through binary64 like any JSON reader), then the float32 cast of
+    cardata-v1.py:16-37; a member that is absent or null gives 0 (KSQL NULL → Avro null → 0), duplicate names: last wins.
+    Bytes are taken as Latin-1 so that the grammar, not UTF-8 validity, decides."""
+    import json
+
+    def _reject(name):
+        raise ValueError(name)  # NaN / Infinity / -Infinity are not JSON
+
+    n = len(offsets) - 1
+    out = np.zeros((n, len(keys)), dtype=np.float32)
+    label = np.full(n, 2, dtype=np.uint8)
+    status = np.zeros(n, dtype=np.int32)
+    buf = bytes(np.asarray(data, dtype=np.uint8))
+    for i in range(n):
+        txt = buf[offsets[i]:offsets[i + 1]].decode("latin-1")
+        if any(ch in txt for ch in "\x0b\x0c\x1c\x1d\x1e\x1f\x85\xa0"):
+            # Python's str.strip-free scanner treats only ' \t\n\r' as white space, like RFC 8259 — nothing to adjust; kept explicit
+            pass
+        try:
+            obj = json.loads(txt, parse_constant=_reject)
+        except (ValueError, RecursionError):
+            status[i] = REC_BAD_JSON
+            continue
+        if not isinstance(obj, dict):
+            status[i] = REC_BAD_JSON
+            continue
+        st = 0
+        for j, k in enumerate(keys):
+            v = obj.get(k)
+            if v is None:
+                continue
+            if isinstance(v, bool) or not isinstance(v, (int, float)):
+                st = st or REC_BAD_NUMBER
+                continue
+            with np.errstate(over="ignore"):
+                out[i, j] = np.float32(float(v))
+        if label_key is not None and label_key in obj:
+            v = obj[label_key]
+            if v is None or v == "":
+                label[i] = 2
+            elif v is True or v == "true":
+                label[i] = 1
+            elif v is False or v == "false":
+                label[i] = 0
+            else:
+                label[i] = 3
+        status[i] = st
+    return out, label, status

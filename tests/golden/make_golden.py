@@ -9,6 +9,7 @@ Outputs:
   car_sensor_sample.csv                    header + first 512 data lines of testdata/car-sensor-data.csv
   csv_tokens.npz                           all unique numeric tokens of that CSV with their glibc-strtof float32 bit patterns
   appg_vectors.json                        SURVEY.md App. G known-answer vectors recomputed with oracle/cpu_oracle.py (float32)
+  cardata_v1_sample.json                   the 10 simulator messages of python-scripts/LSTM-TensorFlow-IO-Kafka/cardata-v1.json
 """
 import json
 import os
@@ -55,6 +56,8 @@ def extract(h5path):
 
 
 def main():
+    with open(os.path.join(REF, 'python-scripts', 'LSTM-TensorFlow-IO-Kafka', 'cardata-v1.json')) as f:
+        open(os.path.join(HERE, 'cardata_v1_sample.json'), 'w').write(''.join(f.readlines()[:10]))
     widths, acts = [30, 14, 7, 7, 30], [orc.ACT_TANH, orc.ACT_RELU, orc.ACT_TANH, orc.ACT_RELU]
     appg = {}
     for key, fn in MODELS.items():

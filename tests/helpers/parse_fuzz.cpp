@@ -12,7 +12,7 @@
 
 #include "../../hivemq-mqtt-tensorflow-kafka-realtime-iot-machine-learning-training-inference_b200/csrc/float_parse.cuh"
 
-static long long bad = 0, checked = 0, fast_hits = 0;
+static long long bad = 0, checked = 0, fast_hits = 0, checked64 = 0;
 
 // the SWAR fast path sees the token the way the kernel hands it over: 16 bytes + the last 4 bytes, garbage around it
 static void check_fast(const std::string& tok, uint32_t ref_bits, bool ref_ok) {
@@ -76,6 +76,22 @@ static void check(const std::string& tok) {
   if (st == B2_NUM_TOO_LONG) return;  // allowed refusal (counted separately by the caller if needed)
   const bool hex = t.find('x') != std::string::npos || t.find('X') != std::string::npos;
   const bool ref_ok = !t.empty() && !hex && end == t.c_str() + t.size() && t.find_first_not_of(" \t") != std::string::npos;
+  {  // binary64 parse (the JSON path) against strtod
+    uint64_t got64 = 0;
+    const int st64 = b2_parse_double((const uint8_t*)tok.data(), (int)tok.size(), &got64);
+    char* end64 = nullptr;
+    const double dref = strtod(t.c_str(), &end64);
+    uint64_t ref64;
+    memcpy(&ref64, &dref, 8);
+    if (st64 != B2_NUM_TOO_LONG) {
+      ++checked64;
+      const bool nan64 = isnan(dref) && (got64 & 0x7FFFFFFFFFFFFFFFull) > 0x7FF0000000000000ull;
+      if ((st64 == B2_NUM_OK) != ref_ok || (ref_ok && got64 != ref64 && !nan64)) {
+        if (bad < 20) fprintf(stderr, "F64 MISMATCH '%s' got st=%d 0x%016llx ref ok=%d 0x%016llx\n", tok.c_str(), st64, (unsigned long long)got64, (int)ref_ok, (unsigned long long)ref64);
+        ++bad;
+      }
+    }
+  }
   check_fast(tok, ref, ref_ok && !isnan(f));
   check_num16(tok, ref, ref_ok && !isnan(f));
   if ((st == B2_NUM_OK) != ref_ok || (ref_ok && got != ref && !(isnan(f) && (got & 0x7FFFFFFF) > 0x7F800000))) {
@@ -109,6 +125,19 @@ int main(int argc, char** argv) {
       snprintf(buf, sizeof buf, "%.17g", nextafter(mid, -1e300));
       check(buf);
     }
+  }
+  // 1b. random doubles at 17 and 16 digits, and Float.toString-like 9-digit values across the exponent range
+  for (long long i = 0; i < n; ++i) {
+    uint64_t b64 = g();
+    if ((b64 & 0x7FF0000000000000ull) == 0x7FF0000000000000ull) b64 &= ~0x0010000000000000ull;
+    double dv;
+    memcpy(&dv, &b64, 8);
+    snprintf(buf, sizeof buf, "%.17g", dv);
+    check(buf);
+    snprintf(buf, sizeof buf, "%.16g", dv);
+    check(buf);
+    snprintf(buf, sizeof buf, "%.15g", dv);
+    check(buf);
   }
   // 2. random decimal strings: d digits, random point position, optional exponent
   for (long long i = 0; i < n; ++i) {
@@ -195,6 +224,6 @@ int main(int argc, char** argv) {
     else if (mode == 4) s += "e-" + std::to_string(10 + (int)(g() % 36));
     check(s);
   }
-  printf("mismatches=%lld checked=%lld fast_path_hits=%lld num16_hits=%lld\n", bad, checked, fast_hits, num16_hits);
+  printf("mismatches=%lld checked=%lld checked64=%lld fast_path_hits=%lld num16_hits=%lld\n", bad, checked, checked64, fast_hits, num16_hits);
   return bad ? 1 : 0;
 }
