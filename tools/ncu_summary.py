@@ -1,7 +1,8 @@
-"""Summarise an .ncu-rep (raw page) into the handful of numbers DESIGN.md / profiles/ quote.  Usage: ncu_summary.py rep [out.json]"""
+"""Summarise an .ncu-rep (raw page), or the CSV of its raw page (`ncu -i rep --page raw --csv`, for reports too large to bring
+back from the GPU box), into the handful of numbers DESIGN.md / profiles/ quote.  Usage: ncu_summary.py rep|raw.csv [out.json]"""
 import csv, json, subprocess, sys
 rep = sys.argv[1]
-raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+raw = open(rep).read() if rep.endswith(".csv") else subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(raw.splitlines()))
 hdr, units = rows[0], rows[1]
 KEYS = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "dram__throughput.avg.pct_of_peak_sustained_elapsed",
