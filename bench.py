@@ -469,10 +469,22 @@ def run_reference(args, wl, rank, world):
                              "sample": f"{per_step} records/step x {args.steps} steps, oracle/oracle.c (OpenMP, gcc -O3 -march=native); "
                                        "TensorFlow/Keras is not installable offline, so the reference's predict path is timed as its C restatement"},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_JSON_OUT, flush=True)
+
+
+_JSON_OUT = sys.stdout
+
+
+def _quiet_stdout():
+    """Keep stdout for the ONE JSON line: libraries that print to file descriptor 1 (NCCL's version banner) go to stderr."""
+    global _JSON_OUT
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
 
 
 def main():
+    _quiet_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=8)
@@ -630,7 +642,7 @@ def main():
                 "data": "synthetic", "config": config, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
                 "gpu_launches": launches, "clocks": clocks, "also": also,
                 "counters": {"records": counters[0], "flagged": counters[1], "decode_errors": counters[2], "bytes": counters[3]}}
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=_JSON_OUT, flush=True)
     if world > 1:
         dist.destroy_process_group()
 
