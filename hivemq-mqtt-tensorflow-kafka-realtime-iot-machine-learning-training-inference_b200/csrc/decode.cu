@@ -39,7 +39,7 @@ struct AvroRun {
 };
 struct AvroP {
   int32_t n_fields, n_out, skip_prefix, all_routed;  // all_routed: every output column is written by some field
-  int32_t n_runs, pad[3];
+  int32_t n_runs, known, pad[2];  // known: 1 / 2 = the program is the reference's schema A / B (straight-line walk below)
   b2_avro_field f[B2_MAX_FIELDS];
   AvroRun run[B2_MAX_FIELDS];
 };
@@ -461,6 +461,134 @@ __device__ __forceinline__ int avro_decode_record(const uint8_t* __restrict__ ba
   return B2_REC_OK;
 }
 
+// ---- Avro, the reference's own two schemas: straight-line walks ---------------------------------------------------------------
+// The generic walk above interprets runs with run-time counts; for the two schemas the reference commits — the simulator's
+// (testdata/cardata-v1.avsc: 9 float, 4 int, 4 float, 1 int) and KSQL's (python-scripts/*/cardata-v1.avsc: the same 18 as
+// ["null", double|int] unions + a ["null", string] label) — the run list is known at compile time, so the same steps are
+// emitted with constant counts and columns: no loops, no descriptor reads.  A record that is not in the common shape (an int
+// of more than two bytes, a union tag other than 0/2, a long label) returns -1 and takes the generic walk; results are
+// identical by construction and checked against each other in tests/test_decode_gpu.py.
+template <int COUNT, int OUT0>
+__device__ __forceinline__ int avs_floats(const uint8_t* __restrict__ base, int p, float* __restrict__ xrow) {
+  const uint32_t* wp = reinterpret_cast<const uint32_t*>(base + (p & ~3));
+  const int sh = (p & 3) * 8;
+  uint32_t w_prev = wp[0];
+#pragma unroll
+  for (int j = 0; j < COUNT; ++j) {
+    const uint32_t w_next = wp[j + 1];
+    xrow[OUT0 + j] = __uint_as_float(__funnelshift_r(w_prev, w_next, sh));
+    w_prev = w_next;
+  }
+  return p + 4 * COUNT;
+}
+__device__ __forceinline__ float av_zigzag_f32(uint32_t u) { return __int2float_rn((int)(u >> 1) ^ -(int)(u & 1u)); }
+// one zig-zag varint of one or two bytes → float; returns bytes used, 0 = longer (caller bails out)
+__device__ __forceinline__ int avs_small_int(uint32_t w, float* v) {
+  const uint32_t b0 = w & 0xFFu, b1 = (w >> 8) & 0xFFu;
+  const bool one = b0 < 0x80u;
+  *v = av_zigzag_f32(one ? b0 : ((b0 & 0x7Fu) | (b1 << 7)));
+  return one ? 1 : (b1 < 0x80u ? 2 : 0);
+}
+template <int COUNT, int OUT0>
+__device__ __forceinline__ int avs_ints(const uint8_t* __restrict__ base, int p, float* __restrict__ xrow) {
+  if (COUNT == 4) {
+    const uint32_t w4 = lds_u32_unaligned(base, p);
+    if ((w4 & 0x80808080u) == 0) {  // four one-byte values (tyre pressures)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) xrow[OUT0 + q] = av_zigzag_f32((w4 >> (8 * q)) & 0xFFu);
+      return p + 4;
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < COUNT; ++j) {
+    float v;
+    const int used = avs_small_int(lds_u32_unaligned(base, p), &v);
+    if (used == 0) return -1;
+    xrow[OUT0 + j] = v;
+    p += used;
+  }
+  return p;
+}
+__device__ __forceinline__ int avro_walk_schema_a(const uint8_t* __restrict__ base, int p, int e, int skip, float* __restrict__ xrow) {
+  p += skip;
+  p = avs_floats<9, 0>(base, p, xrow);
+  p = avs_ints<4, 9>(base, p, xrow);
+  if (p < 0) return -1;
+  p = avs_floats<4, 13>(base, p, xrow);
+  p = avs_ints<1, 17>(base, p, xrow);
+  if (p < 0) return -1;
+  return p > e ? B2_REC_TRUNCATED : B2_REC_OK;
+}
+
+// ["null", double]: tag 0x00 = null (→ 0), 0x02 = value; anything else bails out
+template <int COUNT, int OUT0>
+__device__ __forceinline__ int avs_nullable_doubles(const uint8_t* __restrict__ base, int p, float* __restrict__ xrow) {
+  bool ok = true;
+#pragma unroll
+  for (int j = 0; j < COUNT; ++j) {
+    // tag + 8 value bytes always sit inside three aligned words
+    const uint32_t* wp = reinterpret_cast<const uint32_t*>(base + (p & ~3));
+    const uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2];
+    const int sh = (p & 3) * 8;
+    const uint32_t tag = (w0 >> sh) & 0xFFu;
+    const unsigned long long bits =
+        (unsigned long long)__funnelshift_rc(w0, w1, sh + 8) | ((unsigned long long)__funnelshift_rc(w1, w2, sh + 8) << 32);
+    const float v = __double2float_rn(__longlong_as_double((long long)bits));
+    ok = ok && (tag == 0u || tag == 2u);
+    xrow[OUT0 + j] = tag == 2u ? v : 0.0f;
+    p += tag == 2u ? 9 : 1;
+  }
+  return ok ? p : -1;
+}
+template <int COUNT, int OUT0>
+__device__ __forceinline__ int avs_nullable_ints(const uint8_t* __restrict__ base, int p, float* __restrict__ xrow) {
+  bool ok = true;
+#pragma unroll
+  for (int j = 0; j < COUNT; ++j) {
+    const uint32_t w = lds_u32_unaligned(base, p);
+    const uint32_t tag = w & 0xFFu;
+    float v;
+    const int used = avs_small_int(w >> 8, &v);  // bytes 1..3 of the window: a one- or two-byte varint fits
+    ok = ok && (tag == 0u || (tag == 2u && used != 0));
+    xrow[OUT0 + j] = tag == 2u ? v : 0.0f;
+    p += tag == 2u ? 1 + used : 1;
+  }
+  return ok ? p : -1;
+}
+__device__ __forceinline__ int avro_walk_schema_b(const uint8_t* __restrict__ base, int p, int e, int skip, float* __restrict__ xrow,
+                                                  uint8_t* label) {
+  p += skip;
+  p = avs_nullable_doubles<9, 0>(base, p, xrow);
+  if (p < 0) return -1;
+  p = avs_nullable_ints<4, 9>(base, p, xrow);
+  if (p < 0) return -1;
+  p = avs_nullable_doubles<4, 13>(base, p, xrow);
+  if (p < 0) return -1;
+  p = avs_nullable_ints<1, 17>(base, p, xrow);
+  if (p < 0) return -1;
+  // ["null", string] label: tag, one-byte length, bytes
+  const uint32_t w = lds_u32_unaligned(base, p);
+  const uint32_t tag = w & 0xFFu, lz = (w >> 8) & 0xFFu;
+  uint8_t lab = 2;
+  if (tag == 2u) {
+    if (lz >= 0x80u || (lz & 1u)) return -1;  // long or negative length: generic walk
+    const int L = (int)(lz >> 1);
+    if (p + 2 + L > e) return B2_REC_TRUNCATED;
+    const uint32_t c4 = lds_u32_unaligned(base, p + 2);
+    if (L == 5 && c4 == 0x736C6166u && base[p + 6] == 'e') lab = 0;  // "fals" + "e"
+    else if (L == 4 && c4 == 0x65757274u) lab = 1;                   // "true"
+    else lab = L == 0 ? 2 : 3;
+    p += 2 + L;
+  } else if (tag == 0u) {
+    p += 1;
+  } else {
+    return -1;
+  }
+  if (p > e) return B2_REC_TRUNCATED;
+  *label = lab;
+  return B2_REC_OK;
+}
+
 // ---- the kernel --------------------------------------------------------------------------------------------------
 // MODE 0: decode only (runtime n_out);  MODE 1: fused decode + score for the D-14-7-7-D autoencoder.
 // Every WARP is an independent worker: it owns a byte stage, a 32-row float tile and an mbarrier in shared memory and walks
@@ -573,7 +701,13 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
       } else {
         if (!a.avro.all_routed)
           for (int j = 0; j < xt_stride; ++j) xrow[j] = 0.0f;  // columns no field routes to
-        st = avro_decode_record(stage, c_b, c_e, a.avro, xrow, &lab);
+        st = -1;
+        if (a.avro.known == 1) st = avro_walk_schema_a(stage, c_b, c_e, a.avro.skip_prefix, xrow);
+        else if (a.avro.known == 2) st = avro_walk_schema_b(stage, c_b, c_e, a.avro.skip_prefix, xrow, &lab);
+        if (st < 0) {
+          lab = 2;
+          st = avro_decode_record(stage, c_b, c_e, a.avro, xrow, &lab);
+        }
       }
     }
     __syncwarp();  // every lane is done with the stage
@@ -683,6 +817,19 @@ static int fill_avro(const b2_avro_prog* p, int skip_prefix, AvroP& a) {
   for (int i = 0; i < p->n_fields; ++i)
     if (p->f[i].out >= 0) routed |= 1ull << p->f[i].out;
   a.all_routed = routed == (p->n_out >= 64 ? ~0ull : ((1ull << p->n_out) - 1));
+  // the reference's own schemas (see avro_walk_schema_a / _b); B2_AVRO_GENERIC=1 keeps the generic walk (tests compare the two)
+  {
+    static const int8_t is_int[18] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 0, 0, 0, 0, 1};
+    bool is_a = p->n_fields == 18 && p->n_out == 18, is_b = p->n_fields == 19 && p->n_out == 18;
+    for (int i = 0; i < 18 && (is_a || is_b); ++i) {
+      const b2_avro_field& f = p->f[i];
+      is_a = is_a && f.out == i && f.nullable == 0 && f.type == (is_int[i] ? AV_INT : AV_FLOAT);
+      is_b = is_b && f.out == i && f.nullable == 1 && f.type == (is_int[i] ? AV_INT : AV_DOUBLE);
+    }
+    is_b = is_b && p->f[18].type == AV_STRING && p->f[18].nullable == 1 && p->f[18].out == -2;
+    const char* g = getenv("B2_AVRO_GENERIC");
+    a.known = (g && g[0] == '1') ? 0 : (is_a ? 1 : (is_b ? 2 : 0));
+  }
   return B2_OK;
 }
 
@@ -744,19 +891,31 @@ static int launch_decode_fmt(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stre
   args.stage_cap = choose_stage_cap(args.fmt, args.csv, args.avro, args.json, ctx->record_bytes_hint);
   args.warp_bytes = 16 + args.stage_cap + 16 + align16i(32 * xt_stride * 4) + 16;
   auto kern = decode_kernel<D, MODE, FT, FMT>;
-  // no block-wide synchronisation in the kernel, so the CTA size is free: take the one that packs most warps into an SM
-  int best_warps = 0, threads = DEC_NT, occ = 0;
-  size_t smem = 0;
-  B2_REQUIRE((size_t)args.warp_bytes * 2 <= (size_t)ctx->smem_optin, "decode: a warp's stage needs %d bytes of shared memory (max %d per CTA)",
-             args.warp_bytes, ctx->smem_optin / 2);
-  B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->smem_optin));
-  for (int w = DEC_WARPS; w >= 2; w >>= 1) {
-    const size_t sm = (size_t)args.warp_bytes * w;
-    if (sm > (size_t)ctx->smem_optin) continue;
-    int o = 0;
-    B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, kern, w * 32, sm));
-    if (o * w > best_warps) best_warps = o * w, threads = w * 32, occ = o, smem = sm;
+  // no block-wide synchronisation in the kernel, so the CTA size is free: take the one that packs most warps into an SM.
+  // The choice depends only on (instantiation, device, bytes per warp): remembered, a launch is then one driver call.
+  struct Cfg {
+    int device, warp_bytes, threads, occ;
+  };
+  static thread_local Cfg cached = {-1, 0, 0, 0};
+  int threads = DEC_NT, occ = 0;
+  if (cached.device == ctx->device && cached.warp_bytes == args.warp_bytes) {
+    threads = cached.threads;
+    occ = cached.occ;
+  } else {
+    int best_warps = 0;
+    B2_REQUIRE((size_t)args.warp_bytes * 2 <= (size_t)ctx->smem_optin, "decode: a warp's stage needs %d bytes of shared memory (max %d per CTA)",
+               args.warp_bytes, ctx->smem_optin / 2);
+    B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->smem_optin));
+    for (int w = DEC_WARPS; w >= 2; w >>= 1) {
+      const size_t sm = (size_t)args.warp_bytes * w;
+      if (sm > (size_t)ctx->smem_optin) continue;
+      int o = 0;
+      B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, kern, w * 32, sm));
+      if (o * w > best_warps) best_warps = o * w, threads = w * 32, occ = o;
+    }
+    if (occ >= 1) cached = Cfg{ctx->device, args.warp_bytes, threads, occ};
   }
+  const size_t smem = (size_t)args.warp_bytes * (threads / 32);
   B2_REQUIRE(occ >= 1, "decode: kernel does not fit on an SM");
   const int wpc = threads / 32;
   const long long n_chunks = (args.n + 31) / 32;

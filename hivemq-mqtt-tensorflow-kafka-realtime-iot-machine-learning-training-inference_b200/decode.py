@@ -68,12 +68,55 @@ def _as_batch(records) -> RecordBatch:
     return records if isinstance(records, RecordBatch) else RecordBatch.from_messages(records)
 
 
+# Host-side structs are built once per distinct schema / spec and reused: at 10^10 records/s a launch lasts tens of
+# microseconds, so re-parsing a schema string per call would make the host the bottleneck.
+_avro_cache: dict = {}
+_csv_cache: dict = {}
+_json_cache: dict = {}
+_hint_cache: dict = {}
+
+
+def _avro_prog_struct(schema):
+    key = schema if isinstance(schema, str) else id(schema)
+    hit = _avro_cache.get(key)
+    if hit is None:
+        prog = schema if isinstance(schema, av.AvroProgram) else av.compile_schema(schema)
+        hit = (prog, _ffi.make_avro_prog(prog), schema)  # keep `schema` alive so that an id() key stays unique
+        if len(_avro_cache) > 64:
+            _avro_cache.clear()
+        _avro_cache[key] = hit
+    return hit[0], hit[1]
+
+
+def _csv_spec_struct(kinds, defaults, field_delim, use_quote_delim):
+    key = (tuple(kinds), None if defaults is None else tuple(defaults), field_delim, bool(use_quote_delim))
+    hit = _csv_cache.get(key)
+    if hit is None:
+        if len(_csv_cache) > 64:
+            _csv_cache.clear()
+        hit = _csv_cache[key] = _ffi.make_csv_spec(kinds, defaults, field_delim, use_quote_delim)
+    return hit
+
+
+def _json_spec_struct(keys, label_key):
+    key = (tuple(keys), label_key)
+    hit = _json_cache.get(key)
+    if hit is None:
+        if len(_json_cache) > 64:
+            _json_cache.clear()
+        hit = _json_cache[key] = _ffi.make_json_spec(keys, label_key)
+    return hit
+
+
 def _size_hint(rb: "RecordBatch") -> None:
     """Tell the library the batch's average record size (its decode kernels size each warp's byte stage from it)."""
     avg = getattr(rb, "avg_record_bytes", None)  # set by callers that pass a window of a larger buffer
     if avg is None:
         avg = (rb.nbytes + max(rb.n, 1) - 1) // max(rb.n, 1)
-    _ffi.check(_ffi.lib().b2_ctx_set_record_bytes_hint(get_ctx(rb.data.device.index), int(avg)), "b2_ctx_set_record_bytes_hint")
+    dev = rb.data.device.index
+    if _hint_cache.get(dev) != int(avg):
+        _ffi.check(_ffi.lib().b2_ctx_set_record_bytes_hint(get_ctx(dev), int(avg)), "b2_ctx_set_record_bytes_hint")
+        _hint_cache[dev] = int(avg)
 
 
 def _raise_on_status(status: torch.Tensor, what: str):
@@ -106,7 +149,7 @@ def csv_spec_from_defaults(record_defaults, select_cols=None, field_delim=",", u
 def decode_csv_matrix(records, kinds, defaults=None, field_delim=",", use_quote_delim=True, raise_on_error=True):
     """Fused ``decode_csv`` + ``tf.stack(cols, 1)``: device matrix f32[n, n_float] (row-major) + status i32[n]."""
     rb = _as_batch(records)
-    spec = _ffi.make_csv_spec(kinds, defaults, field_delim, use_quote_delim)
+    spec = _csv_spec_struct(kinds, defaults, field_delim, use_quote_delim)
     nf = sum(1 for k in kinds if k == 1)
     ns = sum(1 for k in kinds if k == 2)
     out = torch.empty((rb.n, nf), dtype=torch.float32, device=rb.data.device)
@@ -152,8 +195,7 @@ _NP_DTYPES = {"float32": np.float32, "float64": np.float64, "int32": np.int32, "
 def decode_avro_matrix(records, schema, skip_prefix: Optional[int] = None, raise_on_error=True):
     """Avro records → device matrix f32[n, n_numeric] + label u8[n] (0 "false", 1 "true", 2 null/empty, 3 other) + status."""
     rb = _as_batch(records)
-    prog = schema if isinstance(schema, av.AvroProgram) else av.compile_schema(schema)
-    p = _ffi.make_avro_prog(prog)
+    prog, p = _avro_prog_struct(schema)
     out = torch.empty((rb.n, prog.n_out), dtype=torch.float32, device=rb.data.device)
     label = torch.empty(rb.n, dtype=torch.uint8, device=rb.data.device)
     status = torch.empty(rb.n, dtype=torch.int32, device=rb.data.device)
@@ -194,7 +236,7 @@ def decode_json_matrix(records, keys, label_key: Optional[str] = None, raise_on_
     JSON reader's route: text → binary64 → float32; absent / null members give 0; the last of equal names wins."""
     rb = _as_batch(records)
     dev = rb.data.device
-    spec = _ffi.make_json_spec(keys, label_key)
+    spec = _json_spec_struct(keys, label_key)
     out = torch.empty((rb.n, len(keys)), dtype=torch.float32, device=dev)
     label = torch.empty(rb.n, dtype=torch.uint8, device=dev)
     status = torch.empty(rb.n, dtype=torch.int32, device=dev)
@@ -226,7 +268,7 @@ def decode_score(model, records, csv_kinds=None, csv_defaults=None, avro_schema=
         raise ValueError("give exactly one of csv_kinds / avro_schema / json_keys")
     spec = p = None
     if json_keys is not None:
-        js = _ffi.make_json_spec(json_keys, json_label)
+        js = _json_spec_struct(json_keys, json_label)
         if label is None:
             label = torch.empty(rb.n, dtype=torch.uint8, device=dev)
         nm = model._norm_struct()
@@ -236,10 +278,9 @@ def decode_score(model, records, csv_kinds=None, csv_defaults=None, avro_schema=
                                                    _ffi.ptr(counters), _stream_ptr()), "b2_decode_score_json")
         return mse, flag, label, status
     if csv_kinds is not None:
-        spec = _ffi.make_csv_spec(csv_kinds, csv_defaults, field_delim, use_quote_delim)
+        spec = _csv_spec_struct(csv_kinds, csv_defaults, field_delim, use_quote_delim)
     else:
-        prog = avro_schema if isinstance(avro_schema, av.AvroProgram) else av.compile_schema(avro_schema)
-        p = _ffi.make_avro_prog(prog)
+        prog, p = _avro_prog_struct(avro_schema)
         if label is None:
             label = torch.empty(rb.n, dtype=torch.uint8, device=dev)
     nm = model._norm_struct()

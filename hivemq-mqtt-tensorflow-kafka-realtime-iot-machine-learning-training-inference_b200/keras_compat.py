@@ -365,6 +365,7 @@ class Model:
     def set_normalization(self, kind, lo, rng):
         """Fuse ``normalize_fn`` (cardata-v1.py:40-131) into score/predict/fit: raw rows in, normalised inside the kernel."""
         self._norm = None if kind is None else (list(kind), list(lo), list(rng))
+        self._norm_struct_key = None  # the cached C struct belongs to the previous table
         return self
 
     # -- native handles ------------------------------------------------------------------------------
@@ -409,7 +410,10 @@ class Model:
             pass
 
     def _norm_struct(self):
-        return _ffi.make_norm(*self._norm) if self._norm is not None else _ffi.make_norm()
+        if getattr(self, "_norm_struct_key", None) is None:  # rebuilt only after set_normalization installed a new table
+            self._norm_struct_cached = _ffi.make_norm(*self._norm) if self._norm is not None else _ffi.make_norm()
+            self._norm_struct_key = True
+        return self._norm_struct_cached
 
     # -- inference -------------------------------------------------------------------------------------
     def score_device(self, x: torch.Tensor, threshold: float = 5.0, mse: Optional[torch.Tensor] = None,

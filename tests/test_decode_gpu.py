@@ -254,3 +254,36 @@ def test_host_end_to_end_path_matches_device_path(cuda_device, fmt):
         np.testing.assert_array_equal(flag_h, flag_d.cpu().numpy())
     mse_h, flag_h = dec.decode_score_host(m, data[: offs[7]], offs[:8], skip_prefix=skip, chunks=16, **kw)  # more chunks than records/4
     np.testing.assert_array_equal(mse_h, mse_d.cpu().numpy()[:7])
+
+
+@pytest.mark.parametrize("fmt", ["avro_a", "avro_b"])
+def test_reference_schema_walks_equal_the_generic_walk(cuda_device, monkeypatch, fmt):
+    """The straight-line walks for the reference's two schemas (avro_walk_schema_a / _b) against the run-interpreting generic
+    walk (B2_AVRO_GENERIC=1): bit-identical values, labels and statuses, including nulls, wide varints and damaged records."""
+    x = synth.sensor_rows(50_003, seed=21)
+    x[::97, 9] = 20000.0      # three-byte varint → the record leaves the straight-line walk
+    x[::89, 17] = -3.0        # negative firmware
+    if fmt == "avro_a":
+        data, offs = synth.avro_a_batch(x)
+        sch = schemas.schema_a_json()
+    else:
+        data, offs, _ = synth.avro_b_batch(x, null_frac=0.02, seed=5, label_probs=(0.9, 0.05, 0.05))
+        sch = schemas.schema_b_json()
+    data = data.copy()
+    g = np.random.default_rng(3)
+    for i in g.integers(0, len(offs) - 1, 200):       # damage some records: flip a byte / cut the record short
+        b, e = int(offs[i]), int(offs[i + 1])
+        data[b + 5 + int(g.integers(0, e - b - 5))] ^= 0xFF
+    offs2 = offs.copy()
+    offs2[-1] -= 7
+    rb = dec.RecordBatch(data[:offs2[-1]], offs2, skip_prefix=5)
+    res = {}
+    for mode in ("0", "1"):
+        monkeypatch.setenv("B2_AVRO_GENERIC", mode)
+        out, label, status, _ = dec.decode_avro_matrix(rb, sch, raise_on_error=False)
+        res[mode] = (out.cpu().numpy().copy(), label.cpu().numpy().copy(), status.cpu().numpy().copy())
+    np.testing.assert_array_equal(res["0"][2], res["1"][2])
+    ok = res["1"][2] == 0
+    assert ok.sum() > 40_000 and (~ok).sum() > 5
+    np.testing.assert_array_equal(_bits(res["0"][0])[ok], _bits(res["1"][0])[ok])
+    np.testing.assert_array_equal(res["0"][1][ok], res["1"][1][ok])
