@@ -287,3 +287,52 @@ def test_reference_schema_walks_equal_the_generic_walk(cuda_device, monkeypatch,
     assert ok.sum() > 40_000 and (~ok).sum() > 5
     np.testing.assert_array_equal(_bits(res["0"][0])[ok], _bits(res["1"][0])[ok])
     np.testing.assert_array_equal(res["0"][1][ok], res["1"][1][ok])
+
+
+@pytest.mark.parametrize("fmt", ["csv", "avro_a", "json"])
+def test_full_size_decode_score_properties(cuda_device, fmt):
+    """At the benchmark's batch size (2^20 records + a ragged tail) parity is checked through size-independent properties: the
+    batch scored in one launch, as two unequal pieces (different chunking, different stage alignment) and with a different
+    record-size hint (different stage size, items split differently) gives bit-identical per-record results; counters add up;
+    a sample is compared with the CPU oracle."""
+    import ctypes as C
+
+    m = _model18()
+    n = (1 << 20) + 37
+    x = synth.sensor_rows(n, seed=31)
+    if fmt == "csv":
+        data, offs = synth.csv_batch(x, seed=2)
+        kw, skip = dict(csv_kinds=SENSOR_KINDS), 0
+    elif fmt == "json":
+        data, offs = synth.json_batch(x, labels=(np.arange(n) % 9 == 0))
+        kw, skip = dict(json_keys=list(schemas.FEATURE_NAMES), json_label="failure_occurred"), 0
+    else:
+        data, offs = synth.avro_a_batch(x)
+        kw, skip = dict(avro_schema=schemas.schema_a_json()), 5
+    rb = dec.RecordBatch(data, offs, skip_prefix=skip)
+    cnt = torch.zeros(4, dtype=torch.int64, device="cuda")
+    mse, flag, _, st = dec.decode_score(m, rb, counters=cnt, **kw)
+    assert not st.any()
+    c = cnt.cpu().numpy()
+    assert c[0] == n and c[1] == int(flag.sum()) and c[2] == 0 and c[3] == int(offs[-1])
+    # two unequal pieces
+    h = n // 3 + 5
+    d_dev, o_dev = rb.data, rb.offsets
+    parts = []
+    for lo, hi in ((0, h), (h, n)):
+        b0 = int(offs[lo])
+        sub = dec.RecordBatch(d_dev[b0:int(offs[hi])], (o_dev[lo:hi + 1] - b0).contiguous(), skip_prefix=skip)
+        parts.append(dec.decode_score(m, sub, **kw)[:2])
+    assert torch.equal(mse, torch.cat([p[0] for p in parts])) and torch.equal(flag, torch.cat([p[1] for p in parts]))
+    # a much smaller stage (hint = a third of the real record size): every chunk is taken in several items
+    rb2 = dec.RecordBatch(d_dev, o_dev, skip_prefix=skip)
+    rb2.avg_record_bytes = max(8, int(offs[-1]) // n // 3)
+    mse2, flag2, _, st2 = dec.decode_score(m, rb2, **kw)
+    assert torch.equal(mse, mse2) and torch.equal(flag, flag2) and not st2.any()
+    # sample against the oracle's scoring of the source rows
+    idx = np.arange(0, n, 3001)
+    xs = x[idx].copy()
+    xs[:, [9, 10, 11, 12, 17]] = np.rint(xs[:, [9, 10, 11, 12, 17]])
+    ref = orc.score(xs, m.get_flat_weights(), [18, 14, 7, 7, 18], ACTS, norm=schemas.norm_arrays(), dtype=np.float64)[0]
+    got = mse.cpu().numpy()[idx].astype(np.float64)
+    assert (np.abs(got - ref) <= np.maximum(1e-5 * ref, 1e-7)).all()
