@@ -230,6 +230,21 @@ def decode_avro(records, schema, dtype=None) -> List[np.ndarray]:
     return cols
 
 
+def to_number(strings, out_type=np.float32) -> np.ndarray:
+    """``tf.strings.to_number(entry[30], tf.int32)`` (Sensor-Kafka-Consumer-and-TensorFlow-Model-Training.py:39): the label
+    column that ``decode_csv`` returned as strings → numbers.  Host side (one short string per record); like TF it raises on
+    text that is not a number of the requested type."""
+    dt = np.dtype(out_type)
+    out = np.empty(len(strings), dtype=dt)
+    for i, s in enumerate(strings):
+        t = s.decode("utf-8") if isinstance(s, (bytes, bytearray)) else str(s)
+        try:
+            out[i] = int(t.strip()) if dt.kind in "iu" else float(t.strip())
+        except ValueError:
+            raise DecodeError(f"to_number: record {i}: StringToNumberOp could not correctly convert string: {t!r}") from None
+    return out
+
+
 def decode_json_matrix(records, keys, label_key: Optional[str] = None, raise_on_error=True):
     """One flat JSON object per record (the raw ``sensor-data`` topic: LSTM-…/cardata-v1.json; KSQL value_format='JSON',
     01_installConfluentPlatform.sh:235) → (f32[N, len(keys)], label u8[N], status int32[N]) on the device.  Numbers take the

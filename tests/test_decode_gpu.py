@@ -120,7 +120,9 @@ def test_csv_credit_card_form_subtiles_and_strings(cuda_device):
     np.testing.assert_array_equal(_bits(np.stack(cols[:30], 1)), _bits(ref))
     assert [int(c) for c in cols[30]] == labels.tolist()
     # tf.stack(entry[0:30], 1) + to_number(entry[30]) — process_x_y of the reference script
-    np.testing.assert_array_equal(np.array([int(c) for c in cols[30]], dtype=np.int32), labels.astype(np.int32))
+    np.testing.assert_array_equal(dec.to_number(cols[30], np.int32), labels.astype(np.int32))
+    with pytest.raises(dec.DecodeError):
+        dec.to_number([b"1", b"x"], np.int32)
 
 
 def test_csv_malformed_injection(cuda_device):
