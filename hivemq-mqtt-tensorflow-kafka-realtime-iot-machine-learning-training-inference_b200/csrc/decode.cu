@@ -31,7 +31,6 @@ struct CsvP {
   uint8_t kind[B2_MAX_FIELDS];       // 0 skip, 1 float, 2 string
   uint8_t has_default[B2_MAX_FIELDS];
   uint8_t col[B2_MAX_FIELDS];        // output column (float) or span slot (string) of field i
-  uint8_t fidx[B2_MAX_FIELDS];       // k-th non-skipped field → field index
   float dflt[B2_MAX_FIELDS];
 };
 struct AvroRun {
@@ -72,7 +71,7 @@ struct DecodeArgs {
   unsigned long long* counters;
 };
 
-// ---- CSV phase A: field boundaries of one record -------------------------------------------------------------
+// ---- CSV, careful path step 1: field boundaries of one record (RFC-4180 quotes) ---------------------------------------------
 // fb[f] = offset (relative to the stage base) of the first payload byte of field f, fb[n_fields] = end + 1, so that
 // field f spans [fb[f], fb[f+1] - 1 - quoted(f)).  qmask bit f = field f was quoted.
 __device__ __forceinline__ int csv_scan_slow(const uint8_t* base, int b, int e, const CsvP& c, uint16_t* fb, unsigned long long* qmask) {
@@ -161,19 +160,13 @@ __device__ __forceinline__ int csv_scan(const uint8_t* base, int b, int e, const
   return B2_REC_OK;
 }
 
-// ---- CSV phase B: one float token, registers only ----------------------------------------------------------------------
+// ---- CSV, careful path step 2: one float token, registers only -----------------------------------------------------------
 // The token's first 16 bytes are pulled into registers with 5 aligned 32-bit loads + funnel shifts, its last 4 bytes with 2
 // more, and handed to the branch-free SWAR parser b2_fast_token16() (float_parse.cuh; fuzzed on the CPU against strtof).
 // Anything that parser declines (long mantissas, '+', blanks, inf/nan, junk) takes the general b2_parse_float().
 __device__ __forceinline__ uint32_t lds_u32_unaligned(const uint8_t* __restrict__ st, int off) {
   const uint32_t* wp = reinterpret_cast<const uint32_t*>(st + (off & ~3));
   return __funnelshift_r(wp[0], wp[1], (off & 3) * 8);
-}
-__device__ __forceinline__ unsigned long long lds_u64_unaligned(const uint8_t* __restrict__ st, int off) {
-  const uint32_t* wp = reinterpret_cast<const uint32_t*>(st + (off & ~3));
-  const uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2];
-  const int sh = (off & 3) * 8;
-  return (unsigned long long)__funnelshift_r(w0, w1, sh) | ((unsigned long long)__funnelshift_r(w1, w2, sh) << 32);
 }
 __device__ __forceinline__ bool csv_fast_token(const uint8_t* __restrict__ st, int b, int L, uint32_t* bits) {
   const uint32_t* wp = reinterpret_cast<const uint32_t*>(st + (b & ~3));
@@ -783,7 +776,6 @@ static int fill_csv(const b2_csv_spec* s, CsvP& c) {
     c.kind[i] = (uint8_t)s->kind[i];
     c.has_default[i] = s->has_default[i] ? 1 : 0;
     c.dflt[i] = s->dflt[i];
-    if (s->kind[i] != 0) c.fidx[c.n_float + c.n_str] = (uint8_t)i;
     if (s->kind[i] == 1) c.col[i] = (uint8_t)c.n_float++;
     else if (s->kind[i] == 2) c.col[i] = (uint8_t)c.n_str++;
   }
