@@ -404,6 +404,38 @@ def aux_format_rows(dev):
             "kernel": "format_rows_kernel", "numpy_array2string_rows_per_s_1core": len(ref) / t_np, "numpy": np.__version__}
 
 
+def aux_metrics(dev):
+    """the threshold sweep behind roc_curve / precision_recall_curve (nb2.0 cells 23-24) on 2^22 device-resident
+    scores; scikit-learn's roc_curve on the same data on one host core beside it."""
+    import torch
+
+    import b200_sensor as bs
+
+    n = 1 << 22
+    g = torch.Generator(device=dev).manual_seed(314)
+    y = (torch.rand(n, device=dev, generator=g) < 0.002).to(torch.uint8)
+    s = torch.randn(n, device=dev, generator=g) ** 2 + y * 6.0
+    for _ in range(2):
+        bs.metrics.threshold_sweep(y, s)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(5):
+        fps, tps, thr = bs.metrics.threshold_sweep(y, s)   # includes the small D2H of the counters
+    torch.cuda.synchronize()
+    dt = (time.perf_counter() - t0) / 5
+    out = {"value": n / dt, "unit": "scores/s", "n": n, "thresholds": int(thr.numel()), "kernel": "mt_bitonic_* + mt_sweep"}
+    try:
+        from sklearn.metrics import roc_curve
+
+        yh, sh = y.cpu().numpy(), s.cpu().numpy()
+        t0 = time.perf_counter()
+        roc_curve(yh, sh)
+        out["sklearn_roc_curve_scores_per_s_1core"] = n / (time.perf_counter() - t0)
+    except Exception as e:  # scikit-learn is optional for the bench
+        out["sklearn"] = "unavailable: %s" % type(e).__name__
+    return out
+
+
 def aux_lstm(dev, T):
     """BASELINE.json configs[4]: LSTM stack forward on synthetic sequences (B = 2^20 / T)."""
     import torch
@@ -637,6 +669,7 @@ def main():
             also["lstm_forward_T1"] = aux_lstm(dev, 1)
             also["lstm_forward_T16"] = aux_lstm(dev, 16)
             also["format_rows_d18"] = aux_format_rows(dev)
+            also["metrics_threshold_sweep"] = aux_metrics(dev)
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
                 "data": "synthetic", "config": config, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,

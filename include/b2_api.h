@@ -231,6 +231,19 @@ int64_t b2_format_rows_bound(int n_cols);
 int  b2_format_rows(b2_ctx* ctx, const float* x_dev, int64_t n, int n_cols, int numpy_compat, uint8_t* text_dev, int64_t text_cap,
                     int64_t* offs_dev, int32_t* len_dev, unsigned long long* cursor_dev, void* stream);
 
+/* ---- evaluation metrics ----------------------------------------------------------------------
+ * The threshold sweep behind sklearn.metrics.roc_curve / precision_recall_curve as the notebooks call them on the
+ * reconstruction error (nb2.0 cells 23-24): scores sorted in decreasing order, one threshold per distinct score,
+ * tps[r] / fps[r] = positives / negatives with score >= thresholds[r] (scikit-learn's confusion_matrix_at_thresholds).
+ * score_dev f32[n], y_dev u8[n] (non-zero = positive class); outputs sized n; n_thresholds_dev int64[2]: [0] number of
+ * thresholds written, [1] number of NaN scores (the result is meaningless then; scikit-learn refuses NaN input).
+ * scratch_dev: b2_threshold_sweep_scratch_bytes(n) bytes, caller-owned.  Exact integer work (bitonic sort + scan). */
+int64_t b2_threshold_sweep_scratch_bytes(int64_t n);
+int  b2_threshold_sweep(b2_ctx* ctx, const float* score_dev, const uint8_t* y_dev, int64_t n, float* thresholds_dev, int64_t* tps_dev,
+                        int64_t* fps_dev, int64_t* n_thresholds_dev, void* scratch_dev, int64_t scratch_bytes, void* stream);
+/* sklearn.metrics.confusion_matrix(y_true, pred_y) of nb2.0 cell 27 for two classes: counts_dev int64[4] = {tn, fp, fn, tp}. */
+int  b2_confusion_matrix(b2_ctx* ctx, const uint8_t* y_true_dev, const uint8_t* y_pred_dev, int64_t n, int64_t* counts_dev, void* stream);
+
 /* ---- per-GPU partition driver --------------------------------------------------------------------------- */
 typedef struct {
   const uint8_t* bytes_dev;         /* device-resident message payloads of one Kafka partition batch */

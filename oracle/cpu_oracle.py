@@ -618,3 +618,25 @@ def decode_json(data: np.ndarray, offsets: np.ndarray, keys: Sequence[str], labe
                 label[i] = 3
         status[i] = st
     return out, label, status
+
+
+# ---- evaluation metrics of the notebooks (nb2.0 cells 23, 24, 27) ------------------------------------------------------------------
+# PINNED: the arithmetic owner is scikit-learn, which is installed — the oracle is the library call.
+def sk_roc_curve(y_true, y_score, **kw):
+    from sklearn.metrics import roc_curve
+    return roc_curve(y_true, y_score, **kw)
+
+
+def sk_precision_recall_curve(y_true, y_score, **kw):
+    from sklearn.metrics import precision_recall_curve
+    return precision_recall_curve(y_true, y_score, **kw)
+
+
+def sk_auc(x, y):
+    from sklearn.metrics import auc
+    return auc(x, y)
+
+
+def sk_confusion_matrix(y_true, y_pred):
+    from sklearn.metrics import confusion_matrix
+    return confusion_matrix(y_true, y_pred, labels=[0, 1])
