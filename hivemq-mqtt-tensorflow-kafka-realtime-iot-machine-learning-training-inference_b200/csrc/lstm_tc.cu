@@ -4,7 +4,8 @@
 // SURVEY.md App. F) — this is the one genuinely GEMM-shaped piece of the hot path (36 480 FLOP per record-step), and its parity
 // budget (1e-4) leaves room for split-precision TF32, which the 1e-5 budget of the Dense autoencoder does not.
 //
-// One CTA = 128 sequences = 128 threads = the 128 TMEM lanes.  Thread t owns sequence t for the whole time loop:
+// One CTA = 128 sequences = the 128 TMEM lanes, two threads per sequence (t and t + 128: warps w and w + 4 address the same 32
+// lanes) that split every layer's units between them — twice the warps to hide the epilogue's MUFU latency.  For the whole time loop:
 //   * the A operand of every layer-step GEMM, [bias-1 | x_t | h_prev ...], lives in TMEM and is written by the owning thread
 //     with tcgen05.st as a (hi, lo) TF32 pair — no shared-memory staging, no transposes; consecutive layers overlap their
 //     column ranges so that h1 written once is both layer 1's recurrent input and layer 2's input (ditto h3, h4);
@@ -17,7 +18,8 @@
 // Algorithmic bytes per record-step: 4F read + 4F written; weights are read once per CTA.
 #include "lstm_tc.h"
 
-constexpr int TC_NT = 128;
+constexpr int TC_NT = 128;      // sequences per CTA = TMEM lanes
+constexpr int TC_THREADS = 256; // two threads per sequence: thread t and t + 128 share TMEM lane t and split the units between them
 constexpr int TC_ALO = 80;    // TMEM column of the "lo" copy of the A panel (hi copy at 0); the panel is 80 columns wide
 constexpr int TC_D = 256;     // TMEM column of the accumulator (≤ 128 columns)
 constexpr int TC_TMEM_COLS = 512;
@@ -130,13 +132,14 @@ __device__ __forceinline__ void issue_layer(const TcLayer& L, uint32_t tbase, co
   tc_commit(bar);
 }
 
-// LSTM epilogue for U units: pull the gate pre-activations of 8 units at a time, update c (registers), write h into the A panel
-template <int U>
-__device__ __forceinline__ void lstm_epilogue(uint32_t lane_base, int h_col, float (&c)[U], float* h_out /* U or nullptr */) {
+// LSTM epilogue for this thread's UH units (half of the layer's; the other half belongs to the thread 128 above / below on the
+// same TMEM lane): pull the gate pre-activations of 8 units at a time, update c (registers), write h into the A panel
+template <int UH>
+__device__ __forceinline__ void lstm_epilogue(uint32_t lane_base, int half, int h_col, float (&c)[UH], float* h_out /* UH or nullptr */) {
 #pragma unroll
-  for (int ch = 0; ch < U / 8; ++ch) {
+  for (int ch = 0; ch < UH / 8; ++ch) {
     uint32_t z[32];
-    tmem_ld32(lane_base + TC_D + ch * 32, z);
+    tmem_ld32(lane_base + TC_D + (half * (UH / 8) + ch) * 32, z);
     tc_wait_ld();
     float h[8];
 #pragma unroll
@@ -150,11 +153,11 @@ __device__ __forceinline__ void lstm_epilogue(uint32_t lane_base, int h_col, flo
       h[q] = og * fmaxf(c[u], 0.f);
       if (h_out) h_out[u] = h[q];
     }
-    a_store<8>(lane_base, h_col + ch * 8, h);
+    a_store<8>(lane_base, h_col + half * UH + ch * 8, h);
   }
 }
 
-__global__ void __launch_bounds__(TC_NT, 1) lstm_forward_tc_kernel(const __grid_constant__ LstmTcArgs a) {
+__global__ void __launch_bounds__(TC_THREADS, 1) lstm_forward_tc_kernel(const __grid_constant__ LstmTcArgs a) {
   extern __shared__ __align__(128) float wsm[];
   __shared__ uint32_t s_tmem;
   __shared__ __align__(8) uint64_t bar;
@@ -168,13 +171,14 @@ __global__ void __launch_bounds__(TC_NT, 1) lstm_forward_tc_kernel(const __grid_
     mbar_init(&bar, 1);
     mbar_fence_init();
   }
-  for (int i = tid; i < a.packed_floats; i += TC_NT) wsm[i] = a.packed[i];
+  for (int i = tid; i < a.packed_floats; i += TC_THREADS) wsm[i] = a.packed[i];
   fence_proxy_async();  // generic-proxy writes of the weights → visible to the tensor core's async-proxy reads
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tbase = s_tmem;
-  const uint32_t lane_base = tbase + ((uint32_t)(warp * 32) << 16);
+  const int half = tid >> 7, row = tid & (TC_NT - 1);  // warps w and w + 4 address the same 32 TMEM lanes
+  const uint32_t lane_base = tbase + ((uint32_t)((warp & 3) * 32) << 16);
   uint32_t parity = 0;
 
   auto run_layer = [&](int l) {  // all threads: previous A-panel writes are complete → issue → wait for the accumulator
@@ -189,15 +193,15 @@ __global__ void __launch_bounds__(TC_NT, 1) lstm_forward_tc_kernel(const __grid_
 
   const long long n_tiles = (a.batch + TC_NT - 1) / TC_NT;
   for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    const long long seq = tile * TC_NT + tid;
+    const long long seq = tile * TC_NT + row;
     const bool live = seq < a.batch;
-    float c1[32], c2[16], c3[16], c4[32], h2[16];
+    float c1[16], c2[8], c3[8], c4[16], h2[8];  // this thread's half of every layer's units
 #pragma unroll
-    for (int i = 0; i < 32; ++i) c1[i] = c4[i] = 0.f;
+    for (int i = 0; i < 16; ++i) c1[i] = c4[i] = 0.f;
 #pragma unroll
-    for (int i = 0; i < 16; ++i) c2[i] = c3[i] = h2[i] = 0.f;
+    for (int i = 0; i < 8; ++i) c2[i] = c3[i] = h2[i] = 0.f;
     // ---- phase 1 panel: [1, 0×5, x(18), h1(32), h2(16), 1, 0×7] ----
-    {
+    if (half == 0) {
       float z16[16];
 #pragma unroll
       for (int i = 0; i < 16; ++i) z16[i] = 0.f;
@@ -216,49 +220,65 @@ __global__ void __launch_bounds__(TC_NT, 1) lstm_forward_tc_kernel(const __grid_
       a_store<16>(lane_base, 64, last);   // 64..79
     }
     for (int t = 0; t < a.T; ++t) {
-      float xv[24];  // cols 0..23 of the panel: [1, 0, 0, 0, 0, 0, x0..x17]
+      // cols 0..23 of the panel: [1, 0, 0, 0, 0, 0, x0..x17]; half 0 writes cols 0..15, half 1 cols 16..23
+      if (half == 0) {
+        float xv[16];
 #pragma unroll
-      for (int i = 0; i < 24; ++i) xv[i] = 0.f;
-      xv[0] = 1.0f;
-      if (live) {
-        const float* xp = a.x + (seq * a.seq_stride + t) * F;
-        for (int f = 0; f < F; ++f) xv[6 + f] = __ldg(xp + f);
+        for (int i = 0; i < 16; ++i) xv[i] = 0.f;
+        xv[0] = 1.0f;
+        if (live) {
+          const float* xp = a.x + (seq * a.seq_stride + t) * F;
+          for (int f = 0; f < min(F, 10); ++f) xv[6 + f] = __ldg(xp + f);
+        }
+        a_store<16>(lane_base, 0, xv);
+      } else {
+        float xv[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) xv[i] = 0.f;
+        if (live) {
+          const float* xp = a.x + (seq * a.seq_stride + t) * F;
+          for (int f = 10; f < F; ++f) xv[f - 10] = __ldg(xp + f);
+        }
+        a_store<8>(lane_base, 16, xv);
       }
-      a_store<16>(lane_base, 0, xv);
-      a_store<8>(lane_base, 16, xv + 16);
       run_layer(0);                                        // L1: cols [0,56) → 128 gate columns
-      lstm_epilogue<32>(lane_base, 24, c1, nullptr);       // h1 → cols 24..55
+      lstm_epilogue<16>(lane_base, half, 24, c1, nullptr);  // h1 → cols 24..55
       run_layer(1);                                        // L2: cols [24,80) → 64 gate columns
-      lstm_epilogue<16>(lane_base, 56, c2, h2);            // h2 → cols 56..71 (kept in registers for phase 2)
+      lstm_epilogue<8>(lane_base, half, 56, c2, h2);        // h2 → cols 56..71 (kept in registers for phase 2)
     }
     // ---- phase 2 panel: [1, 0×7, h2_final(16), h3(16), h4(32), 1, 0×7] ----
     {
-      float head[8];
-#pragma unroll
-      for (int i = 0; i < 8; ++i) head[i] = 0.f;
-      head[0] = 1.0f;
-      a_store<8>(lane_base, 0, head);
-      a_store<16>(lane_base, 8, h2);      // RepeatVector: the same h2_T feeds every decoder step
+      a_store<8>(lane_base, 8 + half * 8, h2);  // RepeatVector: the same h2_T feeds every decoder step (each half its 8 units)
       float z16[16];
 #pragma unroll
       for (int i = 0; i < 16; ++i) z16[i] = 0.f;
-      a_store<16>(lane_base, 24, z16);    // h3 = 0
-      a_store<16>(lane_base, 40, z16);    // h4 = 0
-      a_store<16>(lane_base, 56, z16);
+      if (half == 0) {
+        float head[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) head[i] = 0.f;
+        head[0] = 1.0f;
+        a_store<8>(lane_base, 0, head);
+        a_store<16>(lane_base, 24, z16);    // h3 = 0
+      } else {
+        a_store<16>(lane_base, 40, z16);    // h4 = 0
+        a_store<16>(lane_base, 56, z16);
+      }
       // cols 72..79 still hold [1, 0×7] from phase 1
     }
     for (int t = 0; t < a.T; ++t) {
       run_layer(2);                                        // L3: cols [0,40)
-      lstm_epilogue<16>(lane_base, 24, c3, nullptr);       // h3 → cols 24..39
+      lstm_epilogue<8>(lane_base, half, 24, c3, nullptr);   // h3 → cols 24..39
       run_layer(3);                                        // L4: cols [24,80)
-      lstm_epilogue<32>(lane_base, 40, c4, nullptr);       // h4 → cols 40..71
+      lstm_epilogue<16>(lane_base, half, 40, c4, nullptr);  // h4 → cols 40..71
       run_layer(4);                                        // TimeDistributed(Dense): cols [40,80) → 32 columns
-      uint32_t z[32];
-      tmem_ld32(lane_base + TC_D, z);
-      tc_wait_ld();
-      if (live) {
-        float* yp = a.y + (seq * a.T + t) * F;
-        for (int f = 0; f < F; ++f) yp[f] = __uint_as_float(z[f]);
+      if (half == 0) {  // the 18 output columns are one 32-column read: one thread per sequence writes the row
+        uint32_t z[32];
+        tmem_ld32(lane_base + TC_D, z);
+        tc_wait_ld();
+        if (live) {
+          float* yp = a.y + (seq * a.T + t) * F;
+          for (int f = 0; f < F; ++f) yp[f] = __uint_as_float(z[f]);
+        }
       }
     }
     tc_fence_before();
@@ -353,7 +373,7 @@ int b2_lstm_tc_launch(b2_ctx* ctx, const float* d_packed, int packed_floats, con
   long long tiles = (batch + TC_NT - 1) / TC_NT;
   long long grid = ctx->sm_count;
   if (grid > tiles) grid = tiles;
-  lstm_forward_tc_kernel<<<(unsigned)grid, TC_NT, smem, stream>>>(a);
+  lstm_forward_tc_kernel<<<(unsigned)grid, TC_THREADS, smem, stream>>>(a);
   B2_CUDA(cudaGetLastError());
   return B2_OK;
 }
