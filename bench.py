@@ -625,7 +625,10 @@ def main():
                     "peak_source": peak_src, "algorithmic_bytes_per_record": wl.bytes_per_record,
                     "flop_per_record": wl.flop_per_record,
                     "fp32_tflops_achieved": wl.flop_per_record * (recs / args.steps / wl.launches_per_step) / (per_launch_ms * 1e-3) / 1e12,
-                    "kernel_ms_per_launch": per_launch_ms}
+                    "kernel_ms_per_launch": per_launch_ms,
+                    "binding_limit": "FP32 pipe (fma pipe 79 % busy in ncu), HBM second" if isinstance(wl, ScoreWorkload) else
+                                     "instruction issue (70-75 % of issue slots busy in ncu); DRAM traffic equals the algorithmic bytes",
+                    "evidence": "profiles/r1_ncu_full_summary.json, profiles/round1_notes.md"}
         cpu = None
         if not args.no_cpu_baseline and world == 1:  # reported at N=1 only
             n_target = 1 << 22 if isinstance(wl, ScoreWorkload) else 1 << 20
