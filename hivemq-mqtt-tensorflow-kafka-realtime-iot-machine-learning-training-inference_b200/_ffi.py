@@ -90,6 +90,8 @@ _PROTOTYPES = {
     "b2_ae_score": (C.c_int, [_P, _P, C.c_int64, C.POINTER(Norm), C.c_float, _P, _P, _P, _P, _P]),
     "b2_decode_csv": (C.c_int, [_P, _P, _P, C.c_int64, C.POINTER(CsvSpec), _P, _P, _P, _P]),
     "b2_decode_avro": (C.c_int, [_P, _P, _P, C.c_int64, C.c_int, C.POINTER(AvroProg), _P, _P, _P, _P]),
+    "b2_avro_encode_sizes": (C.c_int, [_P, _P, _P, C.c_int64, C.POINTER(AvroProg), C.c_int, _P, _P]),
+    "b2_avro_encode": (C.c_int, [_P, _P, _P, C.c_int64, C.POINTER(AvroProg), C.c_int, C.c_int, _P, _P, _P]),
     "b2_decode_json": (C.c_int, [_P, _P, _P, C.c_int64, C.POINTER(JsonSpec), _P, _P, _P, _P]),
     "b2_decode_score_json": (C.c_int, [_P, _P, _P, C.c_int64, C.POINTER(JsonSpec), C.POINTER(Norm), C.c_float, _P, _P, _P, _P, _P, _P]),
     "b2_decode_score": (C.c_int, [_P, _P, _P, C.c_int64, C.POINTER(CsvSpec), C.POINTER(AvroProg), C.c_int,

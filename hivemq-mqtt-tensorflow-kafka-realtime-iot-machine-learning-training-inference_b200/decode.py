@@ -230,6 +230,44 @@ def decode_avro(records, schema, dtype=None) -> List[np.ndarray]:
     return cols
 
 
+def encode_avro(x, schema, label=None, schema_id: int = 1, confluent_prefix: bool = True) -> RecordBatch:
+    """Rows ``x[N, n_out]`` (+ ``label`` u8[N]: 0 "false", 1 "true", else null) → Avro binary records under ``schema`` as a
+    device-resident :class:`RecordBatch` (the inverse of ``decode_avro_matrix``; NaN in a nullable column becomes null)."""
+    prog, p = _avro_prog_struct(schema)
+    dev = x.device if isinstance(x, torch.Tensor) and x.is_cuda else torch.device("cuda", torch.cuda.current_device())
+    xd = x if isinstance(x, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(np.asarray(x, dtype=np.float32)))
+    xd = xd.to(dev, torch.float32).contiguous()
+    if xd.dim() != 2 or xd.shape[1] != prog.n_out:
+        raise ValueError(f"expected rows of shape (N, {prog.n_out}), got {tuple(xd.shape)}")
+    n = int(xd.shape[0])
+    lab = None
+    if label is not None:
+        lab = label if isinstance(label, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(np.asarray(label, dtype=np.uint8)))
+        lab = lab.to(dev, torch.uint8).contiguous()
+    lib, ctx, pre = _ffi.lib(), get_ctx(dev.index), 1 if confluent_prefix else 0
+    sizes = torch.empty(n, dtype=torch.int32, device=dev)
+    _ffi.check(lib.b2_avro_encode_sizes(ctx, _ffi.ptr(xd), _ffi.ptr(lab), n, C.byref(p), pre, _ffi.ptr(sizes), _stream_ptr()),
+               "b2_avro_encode_sizes")
+    offs = torch.zeros(n + 1, dtype=torch.int64, device=dev)
+    torch.cumsum(sizes, 0, out=offs[1:])
+    total = int(offs[-1]) if n else 0
+    if total >= 2 ** 31:
+        raise ValueError("batch exceeds int32 offsets")
+    offs32 = offs.to(torch.int32)
+    data = torch.empty(max(total, 1), dtype=torch.uint8, device=dev)
+    _ffi.check(lib.b2_avro_encode(ctx, _ffi.ptr(xd), _ffi.ptr(lab), n, C.byref(p), pre, int(schema_id), _ffi.ptr(offs32), _ffi.ptr(data),
+                                  _stream_ptr()), "b2_avro_encode")
+    return RecordBatch(data[:total], offs32, dev, skip_prefix=5 if confluent_prefix else 0)
+
+
+def json_to_avro(records, keys, schema, label_key: Optional[str] = None, schema_id: int = 1) -> RecordBatch:
+    """The reference's KSQL projection ``CREATE STREAM SENSOR_DATA_S_AVRO WITH (VALUE_FORMAT='AVRO') AS SELECT * FROM
+    SENSOR_DATA_S`` (01_installConfluentPlatform.sh:235-242) for one batch: JSON messages in, Confluent-framed Avro records
+    out, both on the device.  ``keys[i]`` feeds output column i of ``schema``; records that are not valid JSON raise."""
+    x, lab, _ = decode_json_matrix(records, keys, label_key)
+    return encode_avro(x, schema, lab if label_key else None, schema_id)
+
+
 def to_number(strings, out_type=np.float32) -> np.ndarray:
     """``tf.strings.to_number(entry[30], tf.int32)`` (Sensor-Kafka-Consumer-and-TensorFlow-Model-Training.py:39): the label
     column that ``decode_csv`` returned as strings → numbers.  Host side (one short string per record); like TF it raises on

@@ -146,6 +146,19 @@ int  b2_decode_score_json(b2_ae* ae, const uint8_t* bytes_dev, const int32_t* of
                           const b2_norm* norm, float threshold, float* mse_dev, uint8_t* flag_dev, uint8_t* label_dev,
                           int32_t* status_dev, unsigned long long* counters_dev, void* stream);
 
+/* ---- Avro encoder (inverse of b2_decode_avro) -------------------------------------------------------------------
+ * Rows x_dev f32[n, prog->n_out] (+ label_dev u8[n]: 0 "false", 1 "true", else null; NULL = all null) → Avro binary records
+ * under the same field program: the KSQL projection of the reference (CREATE STREAM … WITH (VALUE_FORMAT='AVRO') AS SELECT *,
+ * 01_installConfluentPlatform.sh:242) is b2_decode_json followed by this; also the result sink as Avro, the TODO of
+ * python-scripts/README.md:108.  int/long = the value rounded to nearest, double = the float widened, a NaN in a nullable
+ * column = null, prefix != 0 puts the Confluent framing (0x00 + big-endian schema_id) in front of every record.
+ * Two passes: b2_avro_encode_sizes fills size_dev int32[n]; the caller scans them into offs_dev int32[n+1] (offs[0] = 0) and
+ * provides bytes_dev of offs[n] bytes; b2_avro_encode writes the records back to back in row order. */
+int  b2_avro_encode_sizes(b2_ctx* ctx, const float* x_dev, const uint8_t* label_dev, int64_t n, const b2_avro_prog* prog, int prefix,
+                          int32_t* size_dev, void* stream);
+int  b2_avro_encode(b2_ctx* ctx, const float* x_dev, const uint8_t* label_dev, int64_t n, const b2_avro_prog* prog, int prefix,
+                    int schema_id, const int32_t* offs_dev, uint8_t* bytes_dev, void* stream);
+
 /* Fused decode → normalise → score: the streaming scoring loop of cardata-v1.py:176-231 in one kernel.
  * Exactly one of csv / avro is non-NULL.  Records whose status != 0 get mse = NaN, flag = 0 and are counted
  * in counters[2]; counters_dev u64[4] += {records ok, flagged, decode errors, payload bytes}. */
