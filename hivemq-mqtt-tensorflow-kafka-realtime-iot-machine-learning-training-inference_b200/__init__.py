@@ -11,7 +11,7 @@ Compute lives in ``libb2sensor.so`` (csrc/*.cu, sm_100a); see include/b2_api.h f
 """
 from . import _ffi, avro_schema, h5lite, schemas  # noqa: F401  (pure-Python, importable without a GPU)
 
-__all__ = ["_ffi", "avro_schema", "h5lite", "schemas", "keras", "decode", "synth", "partition", "sink", "metrics", "build_native"]
+__all__ = ["_ffi", "avro_schema", "h5lite", "schemas", "keras", "decode", "synth", "partition", "sink", "metrics", "kafka", "build_native"]
 
 
 def build_native(force: bool = False, verbose: bool = False) -> str:
@@ -26,7 +26,7 @@ def __getattr__(name):
 
     if name == "keras":
         mod = importlib.import_module(".keras_compat", __name__)
-    elif name in ("decode", "synth", "partition", "sink", "metrics", "keras_compat"):
+    elif name in ("decode", "synth", "partition", "sink", "metrics", "kafka", "keras_compat"):
         mod = importlib.import_module("." + name, __name__)
     else:
         raise AttributeError(name)

@@ -1,0 +1,144 @@
+"""Kafka record-batch (message format v2) framing: broker bytes → the ``RecordBatch`` of message values the decoders take.
+
+In the reference this is tensorflow-io's ``KafkaDataset`` / librdkafka (cardata-v1.py:10).  ``scan_batches`` walks the batch
+chain on the host (12 bytes per batch), ``values_from_segment`` lets the GPU check every batch's CRC-32C, walk its records
+(``b2_kafka_index_records``) and pack the values back to back (``b2_kafka_gather_values``).  ``write_segment`` is the inverse,
+host side, for tests and synthetic input (Kafka itself is replaced offline by in-memory bytes, BASELINE.json).
+"""
+from __future__ import annotations
+
+import struct
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from . import _ffi
+from .decode import RecordBatch
+from .keras_compat import _stream_ptr, get_ctx
+
+FRAME_STATUS = {0: "ok", 1: "not message format v2", 2: "CRC-32C mismatch", 3: "truncated", 4: "compressed batch"}
+_HEADER = 61
+
+
+class FrameError(ValueError):
+    pass
+
+
+def _crc32c_table() -> np.ndarray:
+    t = np.arange(256, dtype=np.uint32)
+    for _ in range(8):
+        t = np.where(t & 1, (t >> 1) ^ np.uint32(0x82F63B78), t >> 1).astype(np.uint32)
+    return t
+
+
+_TAB = _crc32c_table()
+
+
+def crc32c(data: bytes) -> int:
+    """CRC-32C (Castagnoli), the checksum of Kafka record batches.  crc32c(b"123456789") == 0xE3069283 (RFC 3720 B.4)."""
+    c = 0xFFFFFFFF
+    tab = _TAB.tolist()
+    for b in data:
+        c = tab[(c ^ b) & 0xFF] ^ (c >> 8)
+    return c ^ 0xFFFFFFFF
+
+
+def _varint(v: int) -> bytes:
+    u = (v << 1) ^ (v >> 63)
+    out = bytearray()
+    while u >= 0x80:
+        out.append((u & 0x7F) | 0x80)
+        u >>= 7
+    out.append(u)
+    return bytes(out)
+
+
+def write_segment(values: Sequence[bytes], records_per_batch: int = 500, keys: Optional[Sequence[Optional[bytes]]] = None,
+                  base_offset: int = 0, headers: bool = False) -> bytes:
+    """Message values → log-segment bytes: uncompressed v2 record batches of ``records_per_batch`` records each."""
+    out = bytearray()
+    n = len(values)
+    for b0 in range(0, n, records_per_batch):
+        recs = bytearray()
+        cnt = min(records_per_batch, n - b0)
+        for i in range(cnt):
+            v = values[b0 + i]
+            k = keys[b0 + i] if keys is not None else None
+            body = bytearray(b"\x00") + _varint(i * 3) + _varint(i)          # attributes, timestampDelta, offsetDelta
+            body += _varint(-1) if k is None else _varint(len(k)) + k
+            body += _varint(-1) if v is None else _varint(len(v)) + v
+            if headers and i % 7 == 0:
+                body += _varint(1) + _varint(2) + b"hk" + _varint(3) + b"hv!"
+            else:
+                body += _varint(0)
+            recs += _varint(len(body)) + body
+        after_crc = struct.pack(">hiqqqhii", 0, cnt - 1, 1567606196000, 1567606196000 + 3 * cnt, -1, -1, -1, cnt) + bytes(recs)
+        batch_len = 4 + 1 + 4 + len(after_crc)                               # leader epoch, magic, crc, rest
+        out += struct.pack(">qiib", base_offset + b0, batch_len, 0, 2) + struct.pack(">I", crc32c(after_crc)) + after_crc
+    return bytes(out)
+
+
+def scan_batches(segment) -> Tuple[np.ndarray, np.ndarray]:
+    """Host walk of the batch chain → (batch_pos int64[nb], record_count int64[nb]).  A trailing partial batch (a fetch response
+    may end in one) is ignored, like consumers do."""
+    buf = memoryview(segment.numpy() if isinstance(segment, torch.Tensor) else segment).cast("B")
+    n, pos = len(buf), 0
+    bp: List[int] = []
+    rc: List[int] = []
+    while pos + _HEADER <= n:
+        (blen,) = struct.unpack_from(">i", buf, pos + 8)
+        if blen < _HEADER - 12 or pos + 12 + blen > n:
+            break
+        (cnt,) = struct.unpack_from(">i", buf, pos + 57)
+        bp.append(pos)
+        rc.append(max(cnt, 0))
+        pos += 12 + blen
+    return np.asarray(bp, dtype=np.int64), np.asarray(rc, dtype=np.int64)
+
+
+def values_from_segment(segment, verify_crc: bool = True, device: Optional[torch.device] = None, skip_prefix: int = 0,
+                        raise_on_error: bool = True):
+    """Log-segment / fetch-response bytes (``bytes``, NumPy uint8, or a CPU / CUDA uint8 tensor; the batch chain is walked on
+    the host copy) → ``(RecordBatch of the message values, batch status int32[nb] on the device)``.  Records of a refused batch
+    come out empty; with ``raise_on_error`` a refused batch raises :class:`FrameError` instead."""
+    if isinstance(segment, torch.Tensor):
+        host = segment.cpu() if segment.is_cuda else segment
+        seg_t = segment
+    else:
+        host = torch.from_numpy(np.frombuffer(segment, dtype=np.uint8).copy() if isinstance(segment, (bytes, bytearray, memoryview))
+                                else np.ascontiguousarray(segment, dtype=np.uint8))
+        seg_t = host
+    dev = device or (seg_t.device if seg_t.is_cuda else torch.device("cuda", torch.cuda.current_device()))
+    pos, cnt = scan_batches(host)
+    nb, n = len(pos), int(cnt.sum())
+    base = np.zeros(nb, dtype=np.int64)
+    if nb:
+        np.cumsum(cnt[:-1], out=base[1:])
+    d = seg_t.to(dev).contiguous()
+    begin = torch.zeros(max(n, 1), dtype=torch.int32, device=dev)
+    end = torch.zeros(max(n, 1), dtype=torch.int32, device=dev)
+    status = torch.zeros(max(nb, 1), dtype=torch.int32, device=dev)
+    lib, ctx = _ffi.lib(), get_ctx(dev.index)
+    with torch.cuda.device(dev):
+        pos_d, base_d = torch.from_numpy(pos).to(dev), torch.from_numpy(base).to(dev)
+        _ffi.check(lib.b2_kafka_index_records(ctx, _ffi.ptr(d), int(d.numel()), _ffi.ptr(pos_d), _ffi.ptr(base_d), nb, 1 if verify_crc else 0,
+                                              _ffi.ptr(begin), _ffi.ptr(end), _ffi.ptr(status), _stream_ptr()), "b2_kafka_index_records")
+        status = status[:nb]
+        if raise_on_error and nb:
+            bad = torch.nonzero(status).flatten()
+            if bad.numel():
+                b = int(bad[0])
+                raise FrameError(f"record batch {b} at byte {int(pos[b])}: {FRAME_STATUS.get(int(status[b]), '?')} "
+                                 f"({bad.numel()} of {nb} batches refused)")
+        offs = torch.zeros(n + 1, dtype=torch.int64, device=dev)
+        if n:
+            torch.cumsum((end[:n] - begin[:n]).to(torch.int64), 0, out=offs[1:])
+        total = int(offs[-1])
+        if total >= 2 ** 31:
+            raise ValueError("values exceed int32 offsets")
+        offs32 = offs.to(torch.int32)
+        out = torch.empty(max(total, 1), dtype=torch.uint8, device=dev)
+        _ffi.check(lib.b2_kafka_gather_values(ctx, _ffi.ptr(d), _ffi.ptr(begin), _ffi.ptr(end), n, _ffi.ptr(offs32), _ffi.ptr(out),
+                                              _stream_ptr()), "b2_kafka_gather_values")
+    return RecordBatch(out[:total], offs32, dev, skip_prefix=skip_prefix), status

@@ -244,6 +244,25 @@ int64_t b2_format_rows_bound(int n_cols);
 int  b2_format_rows(b2_ctx* ctx, const float* x_dev, int64_t n, int n_cols, int numpy_compat, uint8_t* text_dev, int64_t text_cap,
                     int64_t* offs_dev, int32_t* len_dev, unsigned long long* cursor_dev, void* stream);
 
+/* ---- Kafka record-batch framing (message format v2) ------------------------------------------
+ * What tensorflow-io's KafkaDataset / librdkafka does in front of the reference's scripts (cardata-v1.py:10): fetch-response or
+ * log-segment bytes → message values.  The caller walks the batch chain on the host (baseOffset i64, batchLength i32: the next
+ * batch starts 12 + batchLength bytes on; recordCount i32 at byte 57) and passes batch_pos_dev int64[n_batches] and rec_base_dev
+ * int64[n_batches] (records in the batches before each one).  One thread per batch checks magic == 2, the CRC-32C (verify_crc)
+ * and walks the records: begin_dev / end_dev int32[n_records] receive each value's byte range inside bytes_dev, status_dev
+ * int32[n_batches] a B2_FRAME_* code (records of a refused batch get the empty range [0, 0)).
+ * b2_kafka_gather_values then packs the values back to back at out_offs_dev int32[n] (the caller's scan of end - begin), giving
+ * the (bytes, offsets) batch every decode entry point takes. */
+#define B2_FRAME_OK         0
+#define B2_FRAME_BAD_MAGIC  1  /* not message format v2 */
+#define B2_FRAME_BAD_CRC    2
+#define B2_FRAME_TRUNCATED  3  /* batch or record runs past its container */
+#define B2_FRAME_COMPRESSED 4  /* gzip / snappy / lz4 / zstd batch: not inflated here */
+int  b2_kafka_index_records(b2_ctx* ctx, const uint8_t* bytes_dev, int64_t n_bytes, const int64_t* batch_pos_dev, const int64_t* rec_base_dev,
+                            int64_t n_batches, int verify_crc, int32_t* begin_dev, int32_t* end_dev, int32_t* status_dev, void* stream);
+int  b2_kafka_gather_values(b2_ctx* ctx, const uint8_t* bytes_dev, const int32_t* begin_dev, const int32_t* end_dev, int64_t n,
+                            const int32_t* out_offs_dev, uint8_t* out_bytes_dev, void* stream);
+
 /* ---- evaluation metrics ----------------------------------------------------------------------
  * The threshold sweep behind sklearn.metrics.roc_curve / precision_recall_curve as the notebooks call them on the
  * reconstruction error (nb2.0 cells 23-24): scores sorted in decreasing order, one threshold per distinct score,

@@ -1,0 +1,63 @@
+"""K9: Kafka record-batch (v2) framing on the GPU — values out of log-segment bytes, CRC-32C check, refused batches — and the
+decode kernels running on the result (segment bytes → scores)."""
+import numpy as np
+import pytest
+import torch
+
+import b200_sensor as bs
+from b200_sensor import decode as dec, schemas, synth
+
+pytestmark = pytest.mark.gpu
+
+
+def test_crc32c_known_answers():
+    assert bs.kafka.crc32c(b"123456789") == 0xE3069283 and bs.kafka.crc32c(bytes(32)) == 0x8A9136AA  # RFC 3720 B.4
+
+
+def test_values_keys_headers_nulls(cuda_device):
+    g = np.random.default_rng(1)
+    vals = [bytes(g.integers(0, 256, int(g.integers(0, 300)), dtype=np.uint8)) for _ in range(2000)]
+    vals[5], vals[77] = None, b""
+    keys = [None if i % 3 else b"car%d" % i for i in range(2000)]
+    seg = bs.kafka.write_segment(vals, records_per_batch=97, keys=keys, headers=True)
+    rb, st = bs.kafka.values_from_segment(seg)
+    assert rb.n == 2000 and not st.any() and st.numel() == 21
+    d, o = rb.data.cpu().numpy().tobytes(), rb.offsets.cpu().numpy()
+    assert [d[o[i]:o[i + 1]] for i in range(2000)] == [v or b"" for v in vals]
+
+
+def test_bad_batches_are_refused_not_fatal(cuda_device):
+    vals = [b"v%04d" % i for i in range(300)]
+    seg = bytearray(bs.kafka.write_segment(vals, records_per_batch=100))
+    pos, _ = bs.kafka.scan_batches(bytes(seg))
+    seg[pos[1] + 80] ^= 0x01      # payload bit flip → CRC mismatch
+    seg[pos[2] + 22] |= 0x02      # attributes: snappy
+    with pytest.raises(bs.kafka.FrameError):
+        bs.kafka.values_from_segment(bytes(seg))
+    rb, st = bs.kafka.values_from_segment(bytes(seg), raise_on_error=False)
+    assert st.cpu().tolist() == [0, 2, 4]
+    d, o = rb.data.cpu().numpy().tobytes(), rb.offsets.cpu().numpy()
+    got = [d[o[i]:o[i + 1]] for i in range(300)]
+    assert got[:100] == vals[:100] and all(g == b"" for g in got[100:])
+    rb2, st2 = bs.kafka.values_from_segment(bytes(seg[:pos[2] + 40]), raise_on_error=False, verify_crc=False)  # partial trailing batch
+    assert rb2.n == 200 and st2.cpu().tolist() == [0, 0]
+
+
+def test_segment_to_scores(cuda_device):
+    """Broker bytes → framing → fused Avro decode + score == decode + score of the bare record batch."""
+    rows = synth.sensor_rows(20_000, seed=3)
+    data, offs = synth.avro_a_batch(rows)
+    vals = [data[offs[i]:offs[i + 1]].tobytes() for i in range(len(offs) - 1)]
+    seg = bs.kafka.write_segment(vals, records_per_batch=512)
+    rb, _ = bs.kafka.values_from_segment(seg, skip_prefix=5)
+    np.testing.assert_array_equal(rb.offsets.cpu().numpy(), offs)
+    k = bs.keras
+    inp = k.layers.Input(shape=(18,))
+    h = k.layers.Dense(14, activation="tanh")(inp)
+    h = k.layers.Dense(7, activation="relu")(h)
+    h = k.layers.Dense(7, activation="tanh")(h)
+    m = k.models.Model(inputs=inp, outputs=k.layers.Dense(18, activation="relu")(h))
+    m.set_normalization(*schemas.norm_arrays())
+    a = dec.decode_score(m, rb, avro_schema=schemas.schema_a_json())
+    b = dec.decode_score(m, dec.RecordBatch(data, offs, skip_prefix=5), avro_schema=schemas.schema_a_json())
+    assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
