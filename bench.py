@@ -109,21 +109,26 @@ def golden_weights():
 class ScoreWorkload:
     """BASELINE.json configs[1]: synthetic pre-decoded float sensor rows, fused AE forward + MSE + flag."""
 
-    def __init__(self, d, rows_log2, e2e_rows_log2):
+    def __init__(self, d, rows_log2, e2e_rows_log2, repeat=1):
         self.d = d
-        self.rows = 1 << rows_log2
+        self.launch_rows = 1 << rows_log2
+        self.repeat = repeat
+        self.rows = self.launch_rows * repeat
         self.e2e_rows = 1 << e2e_rows_log2
         self.name = f"score_predecoded_d{d}"
         self.bytes_per_record = 4 * d + 5
         self.flop_per_record = 2 * (14 * d + 98 + 49 + 7 * d)
-        self.launches_per_step = 1
+        self.launches_per_step = repeat
+        self.decode_launches_per_step = repeat
         self.kernel_key = f"ae_score_d{d}"
+        self.kernel_ms = 0.0
 
     def describe(self):
         return {"workload": self.name, "features": self.d, "model": "Dense AE %d-14-7-7-%d" % (self.d, self.d),
                 "weights": "autoencoder_sensor_anomaly_detection.h5 (shipped)" if self.d == 30 else "Glorot-uniform seed 314 (no 18-wide weights are shipped)",
-                "normalise": self.d == 18, "rows_per_step_per_gpu": self.rows, "threshold": THRESHOLD,
-                "l2_policy": "input per step (%.1f GB) is far larger than the 126 MB L2; offsets rotate" % (self.rows * 4 * self.d / 1e9),
+                "normalise": self.d == 18, "rows_per_launch": self.launch_rows, "launches_per_step": self.repeat,
+                "records_per_step_per_gpu": self.rows, "threshold": THRESHOLD,
+                "l2_policy": "input per launch (%.1f GB) is far larger than the 126 MB L2; offsets rotate" % (self.launch_rows * 4 * self.d / 1e9),
                 "e2e_rows_per_step_per_gpu": self.e2e_rows}
 
     def weights(self):
@@ -165,7 +170,7 @@ class ScoreWorkload:
         self.m = self.model()
         base = torch.from_numpy(self.host_rows(1 << 20, 314 + rank)).to(dev)
         # tile the seeded 2^20-row block with per-copy jitter so that all rows differ, entirely on the device
-        reps = self.rows // base.shape[0] + 1  # one extra block so that steps can start at rotating offsets
+        reps = self.launch_rows // base.shape[0] + 1  # one extra block so that launches can start at rotating offsets
         self.x = torch.empty((reps * base.shape[0], self.d), dtype=torch.float32, device=dev)
         g = torch.Generator(device=dev).manual_seed(314 + rank)
         for r in range(reps):
@@ -173,15 +178,34 @@ class ScoreWorkload:
             blk.copy_(base)
             if self.d == 30:
                 blk.mul_(1.0 + 0.01 * torch.rand((), device=dev, generator=g))
-        self.mse = torch.empty(self.rows, dtype=torch.float32, device=dev)
-        self.flag = torch.empty(self.rows, dtype=torch.uint8, device=dev)
+        self.mse = torch.empty(self.launch_rows, dtype=torch.float32, device=dev)
+        self.flag = torch.empty(self.launch_rows, dtype=torch.uint8, device=dev)
         self.counters = torch.zeros(4, dtype=torch.int64, device=dev)
-        self.max_off = self.x.shape[0] - self.rows
+        self.max_off = self.x.shape[0] - self.launch_rows
+        self.e0, self.e1, self.pending = self._ev(), self._ev(), []
 
     def step(self, i):
-        off = ((i * 104729 * 2) % max(self.max_off, 1)) & ~1  # even row offset keeps the 16-byte alignment of the bulk path
-        self.m.score_device(self.x[off:off + self.rows], THRESHOLD, mse=self.mse, flag=self.flag, counters=self.counters)
+        self.e0.record()
+        for r in range(self.repeat):
+            off = (((i * self.repeat + r) * 104729 * 2) % max(self.max_off, 1)) & ~1  # even row offset: 16-byte aligned bulk path
+            self.m.score_device(self.x[off:off + self.launch_rows], THRESHOLD, mse=self.mse, flag=self.flag, counters=self.counters)
+        self.e1.record()
+        self.pending.append((self.e0, self.e1))
+        self.e0, self.e1 = self._ev(), self._ev()
         return self.rows
+
+    def _ev(self):
+        import torch
+
+        return torch.cuda.Event(enable_timing=True)
+
+    def finish(self):
+        """Sum of the per-launch CUDA-event times (events on torch's current stream = the stream the kernel is launched on)."""
+        import torch
+
+        torch.cuda.synchronize()
+        self.kernel_ms += sum(a.elapsed_time(b) for a, b in self.pending)
+        self.pending = []
 
     def setup_e2e(self, dev, rank):
         import torch
@@ -194,35 +218,61 @@ class ScoreWorkload:
         mse, flag = self.m.score(self.hx, THRESHOLD)  # host in → host out through the public API
         return self.e2e_rows
 
-    def cpu_sample(self, n, threads=None):
+    def host_stats(self):
+        return self.bytes_per_record
+
+    def copy_only(self, dev, steps):
+        import torch
+
+        dx = torch.empty_like(self.hx, device=dev)
+        res = torch.empty(self.e2e_rows * 5, dtype=torch.uint8, device=dev)
+        hres = torch.empty(self.e2e_rows * 5, dtype=torch.uint8).pin_memory()
+        for _ in range(2):
+            dx.copy_(self.hx, non_blocking=True), hres.copy_(res, non_blocking=True)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            dx.copy_(self.hx, non_blocking=True), hres.copy_(res, non_blocking=True)
+            torch.cuda.synchronize()
+        return (time.perf_counter() - t0) * 1e3 / steps
+
+    def cpu_prepare(self, threads=None):
         from oracle import c_oracle as co
 
         co.set_threads(threads or os.cpu_count())  # torchrun exports OMP_NUM_THREADS=1: ask for every host thread explicitly
-        x = self.host_rows(min(n, 1 << 22), 7)
+        x = self.host_rows(1 << 22, 7)
         w, wd, nm = self.weights(), self.widths(), self.norm()
-        co.score(x[:1024], w, wd, ACTS, norm=nm)
-        done, t0 = 0, time.perf_counter()
-        while done < n:
+
+        def run():
             co.score(x, w, wd, ACTS, norm=nm, threshold=THRESHOLD)
-            done += x.shape[0]
-        return done, time.perf_counter() - t0, co.max_threads() if not threads else threads
+
+        return run, x.shape[0], (co.max_threads() if not threads else threads)
 
 
 class DecodeScoreWorkload:
-    """BASELINE.json configs[2]: synthetic Kafka-shaped record batches (CSV lines / Confluent-framed Avro), fused
-    decode → normalize_fn → Dense AE 18-14-7-7-18 → MSE → flag, one kernel launch per partition batch."""
+    """BASELINE.json configs[2] / SURVEY §8d C3: synthetic Kafka-shaped record batches (CSV lines / Confluent-framed Avro / JSON),
+    1e-4 of the records malformed, fused decode → normalize_fn → Dense AE 18-14-7-7-18 → MSE → flag.  One step = the rank's
+    partition batches pushed `repeat` times through b2_partition_run_repeat (the per-GPU partition driver, K5): one kernel launch
+    per partition batch, no Python between launches."""
 
-    def __init__(self, fmt, batch_log2=20, batches_per_step=4):
+    MALFORMED = 1e-4
+
+    def __init__(self, fmt, batch_log2=20, n_batches=4, repeat=32):
         self.fmt = fmt
         self.batch = 1 << batch_log2
-        self.nb = batches_per_step
+        self.nb = n_batches
+        self.repeat = repeat
         self.name = f"decode_score_{fmt}"
-        self.launches_per_step = batches_per_step
+        # CSV / JSON launches are followed by their (normally empty) oversize-retry launch
+        self.launches_per_step = n_batches * repeat * (2 if fmt in ("csv", "json", "avro_b") else 1)
+        self.decode_launches_per_step = n_batches * repeat
         self.kernel_key = f"decode_score_{fmt}"
         self.flop_per_record = 2 * (14 * 18 + 98 + 49 + 7 * 18)
-        self.bytes_per_record = None  # measured from the generated batches in setup()
-        self.rows = self.batch * self.nb
+        self.bytes_per_record = None  # measured from the generated batches (host_stats / setup)
+        self.rows = self.batch * self.nb * self.repeat
         self.e2e_rows = self.batch
+        self.kernel_ms = 0.0
+        self.n_streams = 2
 
     def describe(self):
         return {"workload": self.name, "format": {"csv": "CSV line per message (car-sensor-data.csv layout, 20 fields)",
@@ -230,10 +280,13 @@ class DecodeScoreWorkload:
                                                   "avro_b": "Confluent-framed Avro, KSQL cardata-v1.avsc (nullable unions, ~139 B/record)",
                                                   "json": "flat JSON object per message, the simulator's sensor-data topic (LSTM-…/cardata-v1.json member names, ~520 B/record)"}[self.fmt],
                 "features": 18, "model": "Dense AE 18-14-7-7-18", "weights": "Glorot-uniform seed 314 (no 18-wide weights are shipped)",
-                "normalise": True, "records_per_batch": self.batch, "batches_per_step_per_gpu": self.nb, "threshold": THRESHOLD,
-                "partitioning": "rank r owns partition batches p with seed 314 + (r * batches_per_step + p); no data-path collective",
-                "l2_policy": "each step streams %d distinct batches (> 126 MB L2 in total for CSV/Avro-B; Avro-A batches rotate so "
-                             "that consecutive launches never touch the same bytes)" % self.nb,
+                "normalise": True, "records_per_batch": self.batch, "partition_batches_per_gpu": self.nb,
+                "passes_per_step": self.repeat, "records_per_step_per_gpu": self.rows, "malformed_fraction": self.MALFORMED,
+                "threshold": THRESHOLD,
+                "partitioning": "rank r owns partition batches p with seed 314 + (r * partition_batches_per_gpu + p); no data-path "
+                                "collective; driver = b2_partition_run_repeat on 2 CUDA streams",
+                "l2_policy": "every pass streams %d distinct batches back to back (%s in total, the L2 holds 126 MB), so no launch "
+                             "finds its input in L2" % (self.nb, "> 250 MB"),
                 "bytes_per_record_payload_plus_offset_plus_out": self.bytes_per_record,
                 "e2e_rows_per_step_per_gpu": self.e2e_rows}
 
@@ -247,13 +300,22 @@ class DecodeScoreWorkload:
 
         rows = bs.synth.sensor_rows(n or self.batch, seed=seed)
         if self.fmt == "csv":
-            return bs.synth.csv_batch(rows, seed=seed)
-        if self.fmt == "avro_a":
-            return bs.synth.avro_a_batch(rows)
-        if self.fmt == "json":
-            return bs.synth.json_batch(rows, labels=(np.arange(rows.shape[0]) % 64 == 0))
-        d, o, _ = bs.synth.avro_b_batch(rows, seed=seed)
+            d, o = bs.synth.csv_batch(rows, seed=seed)
+        elif self.fmt == "avro_a":
+            d, o = bs.synth.avro_a_batch(rows)
+        elif self.fmt == "json":
+            d, o = bs.synth.json_batch(rows, labels=(np.arange(rows.shape[0]) % 64 == 0))
+        else:
+            d, o, _ = bs.synth.avro_b_batch(rows, seed=seed)
+        d, o, _ = bs.synth.corrupt_batch(d, o, self.fmt, self.MALFORMED, seed=seed)
         return d, o
+
+    def host_stats(self):
+        """bytes/record of this workload from one generated batch (same generator and seed in both arms)."""
+        if self.bytes_per_record is None:
+            d, o = self._host_batch(314, n=1 << 16)
+            self.bytes_per_record = round(float(o[-1]) / (len(o) - 1) + 4 + 5, 1)
+        return self.bytes_per_record
 
     def _kw(self):
         import b200_sensor as bs
@@ -269,27 +331,38 @@ class DecodeScoreWorkload:
 
         import b200_sensor as bs
 
+        self.host_stats()
         self.m = ScoreWorkload(18, 20, 20).model()
         self.kw = self._kw()
         self.batches = []
-        tot_bytes = 0
         for p in range(self.nb):
             d, o = self._host_batch(314 + rank * self.nb + p)
-            tot_bytes += int(o[-1])
             rb = bs.decode.RecordBatch(d, o, dev, skip_prefix=0 if self.fmt in ("csv", "json") else 5)
             rb.mse = torch.empty(rb.n, dtype=torch.float32, device=dev)
             rb.flag = torch.empty(rb.n, dtype=torch.uint8, device=dev)
             rb.status = torch.empty(rb.n, dtype=torch.int32, device=dev)
             self.batches.append(rb)
-        self.bytes_per_record = tot_bytes / (self.nb * self.batch) + 4 + 5
         self.counters = torch.zeros(4, dtype=torch.int64, device=dev)
+        self.driver = None
+        if self.fmt != "json":  # the partition driver takes CSV / Avro specs; JSON batches go through the Python loop
+            self.driver = bs.partition.PartitionDriver(self.m, threshold=THRESHOLD, n_streams=self.n_streams, **self.kw)
+        self.e0, self.e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 
     def step(self, i):
         import b200_sensor as bs
 
-        for rb in self.batches:
-            bs.decode.decode_score(self.m, rb, threshold=THRESHOLD, mse=rb.mse, flag=rb.flag, status=rb.status,
-                                   counters=self.counters, **self.kw)
+        if self.driver is not None:
+            st = self.driver.run(self.batches, counters=self.counters, repeat=self.repeat)
+            self.kernel_ms += st.elapsed_ms   # CUDA events recorded on the driver's own streams around the launches
+            return self.rows
+        self.e0.record()
+        for _ in range(self.repeat):
+            for rb in self.batches:
+                bs.decode.decode_score(self.m, rb, threshold=THRESHOLD, mse=rb.mse, flag=rb.flag, status=rb.status,
+                                       counters=self.counters, **self.kw)
+        self.e1.record()
+        self.e1.synchronize()
+        self.kernel_ms += self.e0.elapsed_time(self.e1)
         return self.rows
 
     def setup_e2e(self, dev, rank):
@@ -308,36 +381,52 @@ class DecodeScoreWorkload:
                                     reuse_output=True, **self.kw)
         return self.e2e_rows
 
-    def cpu_sample(self, n, threads=None):
+    def copy_only(self, dev, steps):
+        """The e2e step's transfers alone (same pinned buffers: payload + offsets H2D, 5 B/record D2H, no kernel)."""
+        import torch
+
+        dd = torch.empty(self.hd.numel(), dtype=torch.uint8, device=dev)
+        do = torch.empty(self.ho.numel(), dtype=torch.int32, device=dev)
+        res = torch.empty(self.e2e_rows * 5, dtype=torch.uint8, device=dev)
+        hres = torch.empty(self.e2e_rows * 5, dtype=torch.uint8).pin_memory()
+        for _ in range(2):
+            dd.copy_(self.hd, non_blocking=True), do.copy_(self.ho, non_blocking=True), hres.copy_(res, non_blocking=True)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            dd.copy_(self.hd, non_blocking=True), do.copy_(self.ho, non_blocking=True), hres.copy_(res, non_blocking=True)
+            torch.cuda.synchronize()
+        return (time.perf_counter() - t0) * 1e3 / steps
+
+    def cpu_prepare(self, threads=None):
+        """→ (run, n_records, cores): `run()` pushes one generated batch through the CPU restatement (oracle/oracle.c, OpenMP)."""
         import b200_sensor as bs
         from oracle import c_oracle as co
 
         if self.fmt == "json":  # no C restatement of the JSON walk: Python's json + the NumPy scoring restatement, one core
             from oracle import cpu_oracle as orc
 
-            d, o = self._host_batch(7, n=min(n, 1 << 16))
+            d, o = self._host_batch(7, n=1 << 14)
             w, nm = self.weights(), bs.schemas.norm_arrays()
-            done, t0 = 0, time.perf_counter()
-            while done < min(n, 1 << 18):
+
+            def run_json():
                 x, _, _ = orc.decode_json(d, o, list(bs.schemas.FEATURE_NAMES), "failure_occurred")
-                orc.score(x, w, W18, ACTS, norm=nm, threshold=THRESHOLD)
-                done += len(o) - 1
-            return done, time.perf_counter() - t0, 1
-        co.set_threads(threads or os.cpu_count())
-        d, o = self._host_batch(7, n=min(n, 1 << 20))
-        nrec = len(o) - 1
+                orc.score(np.nan_to_num(x), w, W18, ACTS, norm=nm, threshold=THRESHOLD)
+
+            return run_json, len(o) - 1, 1
+        co.set_threads(threads or os.cpu_count())  # torchrun exports OMP_NUM_THREADS=1: ask for every host thread explicitly
+        d, o = self._host_batch(7, n=1 << 20)
         w, nm = self.weights(), bs.schemas.norm_arrays()
         if self.fmt == "csv":
             kw = dict(csv=([0, 0] + [1] * 18, None, ",", True))
         else:
             prog = bs.avro_schema.compile_schema(self._kw()["avro_schema"])
             kw = dict(avro=[(f.type, f.nullable, f.out) for f in prog.fields], skip_prefix=5)
-        co.decode_score(d[: o[1024]], o[:1025], w, W18, ACTS, norm=nm, **kw)
-        done, t0 = 0, time.perf_counter()
-        while done < n:
+
+        def run():
             co.decode_score(d, o, w, W18, ACTS, norm=nm, threshold=THRESHOLD, **kw)
-            done += nrec
-        return done, time.perf_counter() - t0, co.max_threads() if not threads else threads
+
+        return run, len(o) - 1, (co.max_threads() if not threads else threads)
 
 
 def aux_fit(dev):
@@ -470,36 +559,65 @@ def aux_lstm(dev, T):
             "fp32_frac_of_74.4": 36480 * B * T / dt / 74.4e12}
 
 
+# records per step are sized so that a step lasts ~0.1 s and the default 20 timed steps ~2 s (clocks and power reach their
+# sustained state inside the timed region); the batches of one pass always exceed the L2
 WORKLOADS = {
-    "score30": lambda: ScoreWorkload(30, 27, 22),
-    "score18": lambda: ScoreWorkload(18, 27, 22),
-    "csv": lambda: DecodeScoreWorkload("csv"),
-    "avro_a": lambda: DecodeScoreWorkload("avro_a", batches_per_step=8),
-    "avro_b": lambda: DecodeScoreWorkload("avro_b"),
-    "json": lambda: DecodeScoreWorkload("json", batch_log2=19),
+    "score30": lambda: ScoreWorkload(30, 27, 22, repeat=24),
+    "score18": lambda: ScoreWorkload(18, 27, 22, repeat=24),
+    "csv": lambda: DecodeScoreWorkload("csv", n_batches=4, repeat=128),
+    "avro_a": lambda: DecodeScoreWorkload("avro_a", n_batches=8, repeat=320),
+    "avro_b": lambda: DecodeScoreWorkload("avro_b", n_batches=4, repeat=384),
+    "json": lambda: DecodeScoreWorkload("json", batch_log2=19, n_batches=4, repeat=96),
 }
 DEFAULT_WORKLOAD = "avro_a"   # decode+score on the schema BASELINE.json names (testdata/cardata-v1.avsc)
 
 
 # ------------------------------------------------------------------------------------------------------------
+def cpu_steady(wl, seconds, threads=None):
+    """Steady-state rate of the CPU restatement: one batch generated up front, one untimed pass to wake the OpenMP threads and
+    warm the caches, then whole passes over it until `seconds` have gone by.  → (records, seconds, cores)"""
+    run, nrec, cores = wl.cpu_prepare(threads)
+    run()
+    done, t0 = 0, time.perf_counter()
+    while True:
+        run()
+        done += nrec
+        dt = time.perf_counter() - t0
+        if dt >= seconds:
+            return done, dt, cores
+
+
+CPU_SAMPLE_TEXT = ("oracle/oracle.c (OpenMP, gcc -O3 -march=native) on every host thread; TensorFlow/Keras is not installable offline, "
+                   "so the reference's predict path is timed as its C restatement")
+
+
 def run_reference(args, wl, rank, world):
+    """`--impl reference`: the reference's CPU path for the same workload, timed on rank 0's host cores.  One step = a bounded
+    sample: whole passes over one generated batch for ~cpu_seconds / steps of wall time, in steady state (same loop as the
+    cpu_baseline leg of the b200 arm)."""
     if rank != 0:
         return
-    per_step = 1 << 22 if isinstance(wl, ScoreWorkload) else 1 << 20
-    for _ in range(args.warmup):
-        wl.cpu_sample(per_step // 4)
-    t_tot, n_tot, cores = 0.0, 0, 1
+    wl.host_stats()
+    run, nrec, cores = wl.cpu_prepare()
+    per_step_s = max(args.cpu_seconds * 2.0 / max(args.steps, 1), 0.25)
+    for _ in range(max(args.warmup, 1)):
+        run()
+    t_tot, n_tot = 0.0, 0
     for _ in range(args.steps):
-        n, dt, cores = wl.cpu_sample(per_step)
-        t_tot += dt
-        n_tot += n
+        t0 = time.perf_counter()
+        while True:
+            run()
+            n_tot += nrec
+            if time.perf_counter() - t0 >= per_step_s:
+                break
+        t_tot += time.perf_counter() - t0
     v = n_tot / t_tot
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * t_tot / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": wl.describe(),
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
-                             "sample": f"{per_step} records/step x {args.steps} steps, oracle/oracle.c (OpenMP, gcc -O3 -march=native); "
-                                       "TensorFlow/Keras is not installable offline, so the reference's predict path is timed as its C restatement"},
+                             "sample": f"{n_tot} records of the same workload in {t_tot:.1f} s ({nrec} per pass, whole passes for "
+                                       f">= {per_step_s:.2f} s per step); " + CPU_SAMPLE_TEXT},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
     print(json.dumps(line), file=_JSON_OUT, flush=True)
 
@@ -515,11 +633,38 @@ def _quiet_stdout():
     os.dup2(2, 1)
 
 
+def load_instr(kernel_key):
+    """Executed warp-instructions per record of the dominant kernel from the committed ncu --set full capture
+    (smsp__inst_executed.sum / records of that launch; profiles/instr_per_record.json)."""
+    p = os.path.join(ROOT, "profiles", "instr_per_record.json")
+    if os.path.exists(p):
+        return json.load(open(p)).get(kernel_key)
+    return None
+
+
+def timed_steps(wl, steps, first_step, torch):
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    wl.kernel_ms = 0.0
+    t0 = time.perf_counter()
+    e0.record()
+    recs = 0
+    for i in range(steps):
+        recs += wl.step(first_step + i)
+    e1.record()
+    torch.cuda.synchronize()
+    wall = (time.perf_counter() - t0) * 1e3
+    if hasattr(wl, "finish"):
+        wl.finish()
+    # the partition driver synchronises its own streams inside each step, so the host clock brackets all device work; the
+    # event pair on torch's stream covers launches made there.  Whichever is longer is the step time.
+    return recs, max(e0.elapsed_time(e1), wall)
+
+
 def main():
     _quiet_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=8)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--workload", default=os.environ.get("B2_BENCH_WORKLOAD", DEFAULT_WORKLOAD), choices=sorted(WORKLOADS))
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
@@ -569,6 +714,8 @@ def main():
     wl.setup(dev, rank)
     for i in range(args.warmup):
         wl.step(i)
+    if hasattr(wl, "finish"):
+        wl.finish()
     barrier()
     sampler = ClockSampler(local)
     if rank == 0:
@@ -576,16 +723,15 @@ def main():
         time.sleep(0.25)
     wl.counters.zero_()
     barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    recs = 0
-    for i in range(args.steps):
-        recs += wl.step(args.warmup + i)
+    recs, ms_local = timed_steps(wl, args.steps, args.warmup, torch)
+    kernel_ms = wl.kernel_ms
     if world > 1:  # the path's only exchange: the final count reduction over NVLink (cardata-style per-partition counters)
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        c0.record()
         dist.all_reduce(wl.counters, op=dist.ReduceOp.SUM)
-    e1.record()
-    torch.cuda.synchronize()
-    ms_local = e0.elapsed_time(e1)
+        c1.record()
+        torch.cuda.synchronize()
+        ms_local += c0.elapsed_time(c1)
     barrier()
     clocks = sampler.stop() if rank == 0 else None
     ms = max_over_ranks(ms_local)
@@ -593,51 +739,80 @@ def main():
     value = total_records / (ms * 1e-3)
     counters = wl.counters.cpu().numpy().tolist()
 
-    # end-to-end: pinned host → device → kernel → host, through the public API
+    # end-to-end: pinned host → device → kernel → host, through the public API; and the same transfers with no kernel
     e2e = None
     if not args.no_e2e:
         wl.setup_e2e(dev, rank)
         for i in range(2):
             wl.step_e2e(i)
         barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e2e_steps = max(args.steps, 8) * 8   # an e2e step is one 2^20-record batch (~1.5 ms): many of them for a stable figure
         t0 = time.perf_counter()
         e0.record()
         n_e2e = 0
-        for i in range(args.steps):
+        for i in range(e2e_steps):
             n_e2e += wl.step_e2e(i)
         e1.record()
         torch.cuda.synchronize()
         wall = (time.perf_counter() - t0) * 1e3
         ms_e2e = max_over_ranks(max(e0.elapsed_time(e1), wall))
+        barrier()
+        ms_copy = max_over_ranks(wl.copy_only(dev, 32))
         e2e = {"value": n_e2e * world / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": wl.h2d, "d2h_bytes_per_step": wl.d2h,
-               "ms_per_step": ms_e2e / args.steps,
+               "ms_per_step": ms_e2e / e2e_steps, "steps": e2e_steps,
+               "copy_only": {"ms_per_step": ms_copy, "gb_per_s_per_gpu": (wl.h2d + wl.d2h) / (ms_copy * 1e-3) / 1e9,
+                             "records_per_s_ceiling": wl.e2e_rows * world / (ms_copy * 1e-3),
+                             "note": "the same pinned buffers copied H2D + D2H with no kernel, max over ranks: what the host / PCIe "
+                                     "side alone allows at this N"},
                "api": "Model.score(pinned host tensor) -> (mse, flag) numpy" if isinstance(wl, ScoreWorkload) else
                       "decode.decode_score_host(model, pinned bytes, pinned offsets) -> (mse, flag) numpy; 4 chunks, H2D overlapped"}
 
     if rank == 0:
         peak, peak_src = load_peaks()
         config = wl.describe()
-        per_launch_ms = ms_local / (args.steps * wl.launches_per_step)
-        achieved = wl.bytes_per_record * (recs / args.steps / wl.launches_per_step) / (per_launch_ms * 1e-3) / 1e9
+        n_launch = args.steps * wl.decode_launches_per_step
+        per_launch_ms = kernel_ms / n_launch
+        rec_per_launch = recs / n_launch
+        achieved = wl.bytes_per_record * rec_per_launch / (per_launch_ms * 1e-3) / 1e9
         traffic = load_traffic(wl.kernel_key)
-        roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                    "traffic": None if traffic is None else traffic * (recs / args.steps / wl.launches_per_step),
+        sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
+        ipr = load_instr(wl.kernel_key)
+        issue_peak = 148 * 4 * sm_mhz * 1e6     # warp-instructions/s: 4 schedulers per SM, one issue per clock each
+        issue = None
+        hbm_ceiling = peak * 1e9 / wl.bytes_per_record
+        fp32_ceiling = 148 * 128 * 2 * sm_mhz * 1e6 / wl.flop_per_record
+        bound = "hbm"
+        if ipr:
+            ach = ipr * rec_per_launch / (per_launch_ms * 1e-3)
+            issue = {"achieved": ach, "peak": issue_peak, "unit": "warp-instr/s", "frac": ach / issue_peak,
+                     "warp_instr_per_record": ipr, "records_per_s_ceiling": issue_peak / ipr,
+                     "source": "smsp__inst_executed.sum of the committed ncu capture / records of that launch "
+                               "(profiles/instr_per_record.json); peak = 148 SMs x 4 schedulers x SM clock under load"}
+            if issue_peak / ipr < min(hbm_ceiling, fp32_ceiling):
+                bound = "issue"
+        if bound == "hbm" and fp32_ceiling < hbm_ceiling:
+            bound = "fp32"
+        roofline = {"bound": bound, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                    "traffic": None if traffic is None else traffic * rec_per_launch,
                     "peak_source": peak_src, "algorithmic_bytes_per_record": wl.bytes_per_record,
                     "flop_per_record": wl.flop_per_record,
-                    "fp32_tflops_achieved": wl.flop_per_record * (recs / args.steps / wl.launches_per_step) / (per_launch_ms * 1e-3) / 1e12,
-                    "kernel_ms_per_launch": per_launch_ms,
-                    "binding_limit": "FP32 pipe (fma pipe 79 % busy in ncu), HBM second" if isinstance(wl, ScoreWorkload) else
-                                     "instruction issue (70-75 % of issue slots busy in ncu); DRAM traffic equals the algorithmic bytes",
-                    "evidence": "profiles/r1_ncu_full_summary.json, profiles/round1_notes.md"}
+                    "fp32_tflops_achieved": wl.flop_per_record * rec_per_launch / (per_launch_ms * 1e-3) / 1e12,
+                    "kernel_ms_per_launch": per_launch_ms, "records_per_launch": rec_per_launch,
+                    "kernel_time_share_of_step": kernel_ms / ms_local,
+                    "timing": "CUDA events on the launching streams around the launches of each step (partition driver: "
+                              "b2_run_stats.elapsed_ms), divided by the launches; with 2 streams consecutive launches overlap at "
+                              "their tails, so this is the effective duration per launch",
+                    "ceilings_records_per_s": {"hbm": hbm_ceiling, "fp32": fp32_ceiling,
+                                               "issue": None if not ipr else issue_peak / ipr},
+                    "issue": issue,
+                    "note": "`bound` names the lowest of the three ceilings for this kernel; `frac` is always against the HBM peak",
+                    "evidence": "profiles/r2_ncu_full_summary.json, profiles/round2_notes.md"}
         cpu = None
         if not args.no_cpu_baseline and world == 1:  # reported at N=1 only
-            n_target = 1 << 22 if isinstance(wl, ScoreWorkload) else 1 << 20
-            n, dt, cores = wl.cpu_sample(n_target)
-            rate = n / dt
-            n2 = int(min(max(rate * args.cpu_seconds, n_target), 1 << 28))
-            n, dt, cores = wl.cpu_sample(n2)
+            n, dt, cores = cpu_steady(wl, args.cpu_seconds)
             cpu = {"value": n / dt, "unit": UNIT, "cores": cores, "kind": "port",
-                   "sample": f"{n} records of the same workload through oracle/oracle.c (OpenMP, all host threads), {dt:.1f} s"}
+                   "sample": f"{n} records of the same workload in {dt:.1f} s, steady state; " + CPU_SAMPLE_TEXT}
         launches = args.steps * wl.launches_per_step
         also = {}
         names = [w for w in WORKLOADS if w != args.workload] if (args.also is None and world == 1) else \
@@ -652,18 +827,16 @@ def main():
             w2.setup(dev, rank)
             for i in range(3):
                 w2.step(i)
+            if hasattr(w2, "finish"):
+                w2.finish()
             torch.cuda.synchronize()
-            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a0.record()
-            r2 = 0
-            for i in range(args.steps):
-                r2 += w2.step(3 + i)
-            a1.record()
-            torch.cuda.synchronize()
-            t2 = a0.elapsed_time(a1) * 1e-3
+            r2, t2 = timed_steps(w2, max(args.steps // 4, 3), 3, torch)
+            t2 *= 1e-3
+            ipr2 = load_instr(w2.kernel_key)
             also[w2.name] = {"value": r2 / t2, "unit": UNIT, "hbm_frac": w2.bytes_per_record * r2 / t2 / 1e9 / peak,
                              "algorithmic_bytes_per_record": w2.bytes_per_record,
-                             "fp32_tflops": w2.flop_per_record * r2 / t2 / 1e12}
+                             "fp32_tflops": w2.flop_per_record * r2 / t2 / 1e12,
+                             "issue_frac": None if not ipr2 else ipr2 * r2 / t2 / issue_peak}
             w2 = None
         if names:
             gc.collect()

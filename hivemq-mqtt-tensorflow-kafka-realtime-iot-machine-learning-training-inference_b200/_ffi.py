@@ -79,6 +79,10 @@ _PROTOTYPES = {
     "b2_ctx_destroy": (None, [_P]),
     "b2_ctx_set_record_bytes_hint": (C.c_int, [_P, C.c_int]),
     "b2_ctx_sm_count": (C.c_int, [_P]),
+    "b2_ctx_set_option": (C.c_int, [_P, C.c_char_p, C.c_int]),
+    "b2_ctx_get_option": (C.c_int, [_P, C.c_char_p, C.POINTER(C.c_int)]),
+    "b2_normalize": (C.c_int, [_P, _P, C.c_int64, C.c_int, C.POINTER(Norm), _P, _P]),
+    "b2_selftest_normalize": (C.c_int, [_P, C.POINTER(Norm), C.c_int, C.c_uint64, C.c_uint64, _P, _P]),
     "b2_strerror": (C.c_char_p, [C.c_int]),
     "b2_last_error": (C.c_char_p, []),
     "b2_version": (C.c_char_p, []),
@@ -118,6 +122,8 @@ _PROTOTYPES = {
     "b2_lstm_forward_windows": (C.c_int, [_P, _P, C.c_int64, C.c_int, C.c_int, _P, _P]),
     "b2_partition_run": (C.c_int, [_P, C.POINTER(Partition), C.c_int, C.POINTER(CsvSpec), C.POINTER(AvroProg), C.c_int,
                                    C.POINTER(Norm), C.c_float, C.c_int, _P, C.POINTER(RunStats)]),
+    "b2_partition_run_repeat": (C.c_int, [_P, C.POINTER(Partition), C.c_int, C.POINTER(CsvSpec), C.POINTER(AvroProg), C.c_int,
+                                          C.POINTER(Norm), C.c_float, C.c_int, C.c_int, _P, C.POINTER(RunStats)]),
 }
 
 _lib: Optional[C.CDLL] = None

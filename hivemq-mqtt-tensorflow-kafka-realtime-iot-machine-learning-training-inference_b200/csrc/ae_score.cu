@@ -185,10 +185,8 @@ __global__ void __launch_bounds__(128) ae_score_generic_kernel(const __grid_cons
 }
 
 // ---- host side ----------------------------------------------------------------------------------------------
-static int env_int(const char* name, int dflt) {
-  const char* v = getenv(name);
-  return v ? atoi(v) : dflt;
-}
+int b2_ae_score_tc(b2_ae* ae, const float* x_dev, int64_t n, const b2_norm* norm, float threshold, float* mse_dev, uint8_t* flag_dev,
+                   unsigned long long* counters_dev, cudaStream_t stream);
 
 template <int D, int NT, int STAGES, bool NORM, bool RECON, bool FT>
 static int launch_score(b2_ae* ae, const ScoreArgs<D>& args, cudaStream_t stream) {
@@ -235,12 +233,12 @@ static int score_spec(b2_ae* ae, const float* x, int64_t n, const b2_norm* norm,
   args.counters = counters;
   args.n = n;
   args.threshold = threshold;
-  args.use_bulk = (((uintptr_t)x & 15) == 0) && (!recon || ((uintptr_t)recon & 15) == 0) && !env_int("B2_NO_BULK", 0);
+  args.use_bulk = (((uintptr_t)x & 15) == 0) && (!recon || ((uintptr_t)recon & 15) == 0) && !ae->ctx->knobs.no_bulk;
   // defaults chosen by measurement (profiles/round1_notes.md): the exp-only tanh costs 7 instead of ~23 instructions per
   // pair and leaves the max relative mse error at 1.1e-6 (accurate variant 0.9e-6, float32 NumPy itself 0.8e-6);
   // one stage per CTA with 7 CTAs/SM edges out deeper per-CTA pipelining.  B2_FAST_TANH=0 selects the ≤4-ulp tanh.
-  const bool ft = env_int("B2_FAST_TANH", 1) != 0;
-  const int cfg = env_int("B2_SCORE_CFG", 1);  // tuning knob: 0 = 128 thr x 2 stages, 1 = 128 x 1, 2 = 256 x 1
+  const bool ft = ae->ctx->knobs.fast_tanh != 0;
+  const int cfg = ae->ctx->knobs.score_cfg;  // tuning knob: 0 = 128 thr x 2 stages, 1 = 128 x 1, 2 = 256 x 1
   if (recon) {
     if (has_norm) return launch_score<D, 128, 2, true, true, false>(ae, args, stream);
     return launch_score<D, 128, 2, false, true, false>(ae, args, stream);
@@ -273,9 +271,11 @@ extern "C" int b2_ae_score(b2_ae* ae, const float* x_dev, int64_t n, const b2_no
   int rc = b2_ae_sync_host(ae);
   if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
-  if (ae->spec_d == 30 && !env_int("B2_FORCE_GENERIC", 0))
+  if (ae->spec_d != 0 && ae->ctx->knobs.score_tc && !recon_dev && !ae->ctx->knobs.force_generic)
+    return b2_ae_score_tc(ae, x_dev, n, norm, threshold, mse_dev, flag_dev, counters_dev, st);  // K1t: tcgen05 variant (ae_score_tc.cu)
+  if (ae->spec_d == 30 && !ae->ctx->knobs.force_generic)
     return score_spec<30>(ae, x_dev, n, norm, threshold, mse_dev, flag_dev, recon_dev, counters_dev, st);
-  if (ae->spec_d == 18 && !env_int("B2_FORCE_GENERIC", 0))
+  if (ae->spec_d == 18 && !ae->ctx->knobs.force_generic)
     return score_spec<18>(ae, x_dev, n, norm, threshold, mse_dev, flag_dev, recon_dev, counters_dev, st);
   GenericArgs ga;
   memset(&ga, 0, sizeof(ga));

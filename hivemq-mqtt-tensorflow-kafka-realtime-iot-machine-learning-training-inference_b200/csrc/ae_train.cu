@@ -512,6 +512,7 @@ static int fit_spec(b2_ae* ae, const float* x, const int32_t* order, int64_t row
   B2_CUDA(cudaGetLastError());
   adam->iter += (rows_total + batch - 1) / batch;
   ae->host_stale = true;
+  ae->tc_valid = false;
   return B2_OK;
 }
 
@@ -601,6 +602,7 @@ extern "C" int b2_ae_apply(b2_ae* ae, const float* grads_dev, b2_adam* adam, flo
   B2_CUDA(cudaGetLastError());
   adam->iter += 1;
   ae->host_stale = true;
+  ae->tc_valid = false;
   return B2_OK;
 }
 

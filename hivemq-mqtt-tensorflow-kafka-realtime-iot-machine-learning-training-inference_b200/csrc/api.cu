@@ -1,5 +1,6 @@
 // Context, error reporting and the autoencoder handle (weights upload / read-back).
 #include <stdarg.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -27,6 +28,20 @@ extern "C" const char* b2_strerror(int code) {
 
 extern "C" const char* b2_version(void) { return "b2sensor 0.1 (sm_100a)"; }
 
+namespace {
+struct KnobName {
+  const char* name;
+  const char* env;
+  int b2_knobs::*field;
+};
+const KnobName kKnobs[] = {
+    {"fast_tanh", "B2_FAST_TANH", &b2_knobs::fast_tanh},       {"score_cfg", "B2_SCORE_CFG", &b2_knobs::score_cfg},
+    {"no_bulk", "B2_NO_BULK", &b2_knobs::no_bulk},             {"force_generic", "B2_FORCE_GENERIC", &b2_knobs::force_generic},
+    {"avro_generic", "B2_AVRO_GENERIC", &b2_knobs::avro_generic}, {"lstm_tc", "B2_LSTM_TC", &b2_knobs::lstm_tc},
+    {"score_tc", "B2_SCORE_TC", &b2_knobs::score_tc},
+};
+}  // namespace
+
 extern "C" int b2_ctx_create(int device, b2_ctx** out) {
   B2_REQUIRE(out != nullptr, "b2_ctx_create: out is NULL");
   int count = 0;
@@ -43,11 +58,71 @@ extern "C" int b2_ctx_create(int device, b2_ctx** out) {
   c->device = device;
   c->sm_count = prop.multiProcessorCount;
   c->smem_optin = (int)prop.sharedMemPerBlockOptin;
+  for (const KnobName& k : kKnobs) {
+    const char* v = getenv(k.env);
+    if (v && *v) c->knobs.*(k.field) = atoi(v);
+  }
+  {
+    DeviceGuard g(device);
+    const size_t bytes = sizeof(int32_t) * (size_t)B2_MAX_STREAM_SLOTS * (1 + B2_OVERSIZE_CAP);
+    cudaError_t e = cudaMalloc(&c->oversize_pool, bytes);
+    if (e == cudaSuccess) e = cudaMemset(c->oversize_pool, 0, bytes);
+    if (e != cudaSuccess) {
+      b2_set_error("b2_ctx_create: %s", cudaGetErrorString(e));
+      if (c->oversize_pool) cudaFree(c->oversize_pool);
+      delete c;
+      return B2_ECUDA;
+    }
+  }
   *out = c;
   return B2_OK;
 }
 
-extern "C" void b2_ctx_destroy(b2_ctx* ctx) { delete ctx; }
+extern "C" void b2_ctx_destroy(b2_ctx* ctx) {
+  if (!ctx) return;
+  DeviceGuard g(ctx->device);
+  for (int i = 0; i < ctx->n_run_streams; ++i) {
+    cudaStreamDestroy(ctx->run_streams[i]);
+    cudaEventDestroy(ctx->run_done[i]);
+  }
+  if (ctx->run_start) cudaEventDestroy(ctx->run_start);
+  if (ctx->run_stop) cudaEventDestroy(ctx->run_stop);
+  if (ctx->oversize_pool) cudaFree(ctx->oversize_pool);
+  delete ctx;
+}
+
+int32_t* b2_ctx_oversize_slot(b2_ctx* ctx, cudaStream_t stream) {
+  int i = 0;
+  for (; i < ctx->n_stream_slots; ++i)
+    if (ctx->slot_stream[i] == stream) break;
+  if (i == ctx->n_stream_slots) {
+    if (ctx->n_stream_slots < B2_MAX_STREAM_SLOTS) ctx->slot_stream[ctx->n_stream_slots++] = stream;
+    else i = B2_MAX_STREAM_SLOTS - 1;  // more distinct streams than slots: the surplus share the last one (see b2_api.h)
+  }
+  return ctx->oversize_pool + (size_t)i * (1 + B2_OVERSIZE_CAP);
+}
+
+extern "C" int b2_ctx_set_option(b2_ctx* ctx, const char* name, int value) {
+  B2_REQUIRE(ctx && name, "b2_ctx_set_option: NULL argument");
+  for (const KnobName& k : kKnobs)
+    if (!strcmp(name, k.name)) {
+      ctx->knobs.*(k.field) = value;
+      return B2_OK;
+    }
+  b2_set_error("b2_ctx_set_option: unknown option '%s'", name);
+  return B2_EINVAL;
+}
+
+extern "C" int b2_ctx_get_option(const b2_ctx* ctx, const char* name, int* value) {
+  B2_REQUIRE(ctx && name && value, "b2_ctx_get_option: NULL argument");
+  for (const KnobName& k : kKnobs)
+    if (!strcmp(name, k.name)) {
+      *value = ctx->knobs.*(k.field);
+      return B2_OK;
+    }
+  b2_set_error("b2_ctx_get_option: unknown option '%s'", name);
+  return B2_EINVAL;
+}
 extern "C" int b2_ctx_sm_count(const b2_ctx* ctx) { return ctx ? ctx->sm_count : 0; }
 
 extern "C" int b2_ctx_set_record_bytes_hint(b2_ctx* ctx, int avg_record_bytes) {
@@ -105,6 +180,7 @@ extern "C" void b2_ae_destroy(b2_ae* ae) {
   if (ae->d_w) cudaFree(ae->d_w);
   if (ae->d_m) cudaFree(ae->d_m);
   if (ae->d_v) cudaFree(ae->d_v);
+  if (ae->d_tc) cudaFree(ae->d_tc);
   delete ae;
 }
 
@@ -133,6 +209,7 @@ extern "C" int b2_ae_set_weights(b2_ae* ae, const float* host_weights) {
   ae->h_w.assign(host_weights, host_weights + ae->n_params);
   B2_CUDA(cudaMemcpy(ae->d_w, host_weights, sizeof(float) * ae->n_params, cudaMemcpyHostToDevice));
   ae->host_stale = false;
+  ae->tc_valid = false;
   return B2_OK;
 }
 

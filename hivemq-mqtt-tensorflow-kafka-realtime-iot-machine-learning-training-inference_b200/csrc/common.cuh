@@ -32,12 +32,40 @@ void b2_set_error(const char* fmt, ...);
     }                                \
   } while (0)
 
+// Tuning / debugging knobs.  Read ONCE from the environment (B2_FAST_TANH, B2_SCORE_CFG, …) when the context is created — a
+// launch never calls getenv — and changed afterwards with b2_ctx_set_option().
+struct b2_knobs {
+  int fast_tanh = 1;      // B2_FAST_TANH     1: exp2-based tanh (7 instr / pair), 0: the ≤ 4-ulp variant
+  int score_cfg = 1;      // B2_SCORE_CFG     ae_score launch shape: 0 = 128 thr x 2 stages, 1 = 128 x 1, 2 = 256 x 1
+  int no_bulk = 0;        // B2_NO_BULK       1: plain loads instead of bulk async copies in ae_score
+  int force_generic = 0;  // B2_FORCE_GENERIC 1: generic Dense-stack kernel even for D-14-7-7-D
+  int avro_generic = 0;   // B2_AVRO_GENERIC  1: interpreted Avro walk even for the two known schemas
+  int lstm_tc = 1;        // B2_LSTM_TC       0: FP32 FMA LSTM kernel instead of the tcgen05 one
+  int score_tc = 0;       // B2_SCORE_TC      1: tcgen05 score kernel (K1t) for the pre-decoded path
+};
+
+constexpr int B2_MAX_STREAM_SLOTS = 32;
+constexpr int B2_OVERSIZE_CAP = 1024;  // oversize records one decode launch can hand to its retry pass
+
 struct b2_ctx {
   int device;
   int sm_count;
   int smem_optin;  // max dynamic shared memory per block (bytes)
   int record_bytes_hint = 0;  // b2_ctx_set_record_bytes_hint: average record size of the batches to come, 0 = unknown
+  b2_knobs knobs;
+  // b2_partition_run: streams and events created on first use and kept for the life of the context
+  int n_run_streams = 0;
+  cudaStream_t run_streams[16] = {};
+  cudaEvent_t run_done[16] = {};
+  cudaEvent_t run_start = nullptr, run_stop = nullptr;
+  // decode retry lists: one slot per stream that has launched a decode on this context (same-stream launches are ordered, so
+  // a slot is never shared by two launches in flight).  Slot = int32[1 + B2_OVERSIZE_CAP] in one device allocation made at
+  // context creation.
+  int32_t* oversize_pool = nullptr;
+  int n_stream_slots = 0;
+  cudaStream_t slot_stream[B2_MAX_STREAM_SLOTS] = {};
 };
+int32_t* b2_ctx_oversize_slot(b2_ctx* ctx, cudaStream_t stream);  // never NULL once the pool exists; shares the last slot when full
 
 // RAII "make this device current for the call" guard (callers may sit on another device)
 struct DeviceGuard {
@@ -63,7 +91,10 @@ struct b2_ae {
   float* d_m;                  // Adam slots (allocated on first fit)
   float* d_v;
   bool host_stale;             // device weights changed by fit; h_w must be refreshed before param-passing
+  float* d_tc = nullptr;       // tensor-core path: packed (hi, lo) weight panels (ae_tc.cuh), built on first use
+  bool tc_valid = false;       // … and rebuilt after every change of the weights
 };
+int b2_ae_tc_panels(b2_ae* ae, const float** out);  // device pointer to the current panels (packs + uploads when stale)
 int b2_ae_sync_host(b2_ae* ae);    // refresh h_w from d_w if stale
 int b2_ae_ensure_adam(b2_ae* ae);  // allocate + zero the Adam slots on first use
 

@@ -69,6 +69,10 @@ struct DecodeArgs {
   float* mse;
   uint8_t* flag;
   unsigned long long* counters;
+  // records that do not fit a warp's stage: the main launch appends their row numbers to over_list ([0] = count, then rows);
+  // the retry launch (list_mode = 1: one CTA, one record per chunk, STAGE_CAP_MAX bytes of stage) reads them back
+  int32_t* over_list;
+  int list_mode;
 };
 
 // ---- CSV, careful path step 1: field boundaries of one record (RFC-4180 quotes) ---------------------------------------------
@@ -609,11 +613,15 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
   uint32_t phase = 0;
   unsigned flagged = 0, n_ok = 0, n_err = 0;
   unsigned long long n_bytes = 0;
-  const long long n_chunks = (a.n + 31) / 32;
+  const bool list_mode = a.list_mode != 0;
+  const long long n_chunks = list_mode ? (long long)min(a.over_list[0], B2_OVERSIZE_CAP) : (a.n + 31) / 32;
   const int warps_per_cta = blockDim.x >> 5;  // the launch picks 8, 4 or 2 warps per CTA: whatever packs most warps into an SM
   const long long n_workers = (long long)gridDim.x * warps_per_cta;
 
-  auto oversize = [&](long long row) {  // a single record larger than the stage: refuse it, keep going (lane 0)
+  // a single record larger than the stage (lane 0): mark it refused and hand it to the retry launch, whose stage holds
+  // STAGE_CAP_MAX bytes; what does not fit even there stays refused
+  auto oversize = [&](long long row) {
+    if (list_mode) return;  // already marked and counted by the main launch
     if (a.status) a.status[row] = B2_REC_TOO_LONG;
     if (MODE == 1) {
       if (a.mse) a.mse[row] = __int_as_float(0x7FC00000);
@@ -623,6 +631,10 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
     }
     if (a.label) a.label[row] = 2;
     ++n_err;
+    if (a.over_list) {
+      const int slot = atomicAdd(a.over_list, 1);
+      if (slot < B2_OVERSIZE_CAP) a.over_list[1 + slot] = (int32_t)row;
+    }
   };
 
   // cursor over this warp's chunks: lane i holds the byte range [ob, oe) of record i of the current chunk
@@ -634,8 +646,8 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
       if (sub >= rows) {
         chunk += n_workers;
         if (chunk >= n_chunks) return false;
-        row0 = chunk * 32;
-        rows = (int)min(32ll, a.n - row0);
+        row0 = list_mode ? (long long)a.over_list[1 + chunk] : chunk * 32;
+        rows = list_mode ? 1 : (int)min(32ll, a.n - row0);
         sub = 0;
         const int o = a.offs[row0 + min(lane, rows)];
         ob = o;
@@ -753,15 +765,17 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
     if (lane == 0) {
       if (n_ok) atomicAdd(&a.counters[0], (unsigned long long)n_ok);
       if (flagged) atomicAdd(&a.counters[1], (unsigned long long)flagged);
-      if (n_err) atomicAdd(&a.counters[2], (unsigned long long)n_err);
+      // retry launch: every record it was handed had been counted as an error; the ones that decoded now are taken back
+      // (a record that fails again, with whatever status, stays counted once)
+      if (list_mode) atomicAdd(&a.counters[2], 0ull - (unsigned long long)n_ok);
+      else if (n_err) atomicAdd(&a.counters[2], (unsigned long long)n_err);
       if (n_bytes) atomicAdd(&a.counters[3], n_bytes);
     }
   }
-}
-
-static int env_int(const char* name, int dflt) {
-  const char* v = getenv(name);
-  return v ? atoi(v) : dflt;
+  if (list_mode) {  // one CTA: everybody has read the count long ago; leave the list empty for the stream's next launch
+    __syncthreads();
+    if (tid == 0) a.over_list[0] = 0;
+  }
 }
 
 // ---- host side ----------------------------------------------------------------------------------------------------
@@ -783,7 +797,7 @@ static int fill_csv(const b2_csv_spec* s, CsvP& c) {
   return B2_OK;
 }
 
-static int fill_avro(const b2_avro_prog* p, int skip_prefix, AvroP& a) {
+static int fill_avro(const b2_ctx* ctx, const b2_avro_prog* p, int skip_prefix, AvroP& a) {
   B2_REQUIRE(p->n_fields >= 1 && p->n_fields <= B2_MAX_FIELDS, "avro: n_fields=%d out of range", p->n_fields);
   B2_REQUIRE(p->n_out >= 1 && p->n_out <= B2_MAX_WIDTH, "avro: n_out=%d out of range", p->n_out);
   B2_REQUIRE(skip_prefix >= 0 && skip_prefix <= 64, "avro: skip_prefix=%d out of range", skip_prefix);
@@ -819,8 +833,7 @@ static int fill_avro(const b2_avro_prog* p, int skip_prefix, AvroP& a) {
       is_b = is_b && f.out == i && f.nullable == 1 && f.type == (is_int[i] ? AV_INT : AV_DOUBLE);
     }
     is_b = is_b && p->f[18].type == AV_STRING && p->f[18].nullable == 1 && p->f[18].out == -2;
-    const char* g = getenv("B2_AVRO_GENERIC");
-    a.known = (g && g[0] == '1') ? 0 : (is_a ? 1 : (is_b ? 2 : 0));
+    a.known = ctx->knobs.avro_generic ? 0 : (is_a ? 1 : (is_b ? 2 : 0));
   }
   return B2_OK;
 }
@@ -914,8 +927,26 @@ static int launch_decode_fmt(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stre
   long long grid = (long long)ctx->sm_count * occ;
   const long long need = (n_chunks + wpc - 1) / wpc;
   if (grid > need) grid = need;
+  // records longer than the stage can only occur when the stage was sized from an average (CSV, JSON, Avro with strings) and
+  // is below the maximum: those launches get a retry pass (below) for the few records they had to refuse
+  const bool may_overflow = args.stage_cap < STAGE_CAP_MAX && !(args.fmt == FMT_AVRO && avro_max_record_bytes(args.avro) > 0);
+  args.list_mode = 0;
+  args.over_list = may_overflow ? b2_ctx_oversize_slot(ctx, stream) : nullptr;
   kern<<<(unsigned)grid, threads, smem, stream>>>(args);
   B2_CUDA(cudaGetLastError());
+  if (may_overflow) {
+    // same kernel, list mode: ONE CTA whose warps each take one listed record at a time into a STAGE_CAP_MAX-byte stage.  The
+    // list is normally empty and the launch returns at once (a few microseconds on the stream); the hard limit of a record
+    // is therefore STAGE_CAP_MAX bytes whatever the average was, and B2_OVERSIZE_CAP such records per launch.
+    DecodeArgs<D> r = args;
+    r.list_mode = 1;
+    r.stage_cap = STAGE_CAP_MAX;
+    r.warp_bytes = 16 + r.stage_cap + 16 + align16i(32 * xt_stride * 4) + 16;
+    int rw = 4;
+    while (rw > 1 && (size_t)r.warp_bytes * rw > (size_t)ctx->smem_optin) rw >>= 1;
+    kern<<<1, rw * 32, (size_t)r.warp_bytes * rw, stream>>>(r);
+    B2_CUDA(cudaGetLastError());
+  }
   return B2_OK;
 }
 
@@ -958,7 +989,7 @@ extern "C" int b2_decode_avro(b2_ctx* ctx, const uint8_t* bytes_dev, const int32
   DeviceGuard g(ctx->device);
   DecodeArgs<18> args;
   memset(&args, 0, sizeof(args));
-  int rc = fill_avro(prog, skip_prefix, args.avro);
+  int rc = fill_avro(ctx, prog, skip_prefix, args.avro);
   if (rc) return rc;
   args.bytes = bytes_dev;
   args.offs = offs_dev;
@@ -1030,7 +1061,7 @@ static int decode_score_spec(b2_ae* ae, const uint8_t* bytes, const int32_t* off
     B2_REQUIRE(json->n_out == D, "b2_decode_score_json: spec yields %d columns, model input is %d", json->n_out, D);
     args.fmt = FMT_JSON;
   } else {
-    rc = fill_avro(avro, skip_prefix, args.avro);
+    rc = fill_avro(ae->ctx, avro, skip_prefix, args.avro);
     if (rc) return rc;
     B2_REQUIRE(avro->n_out == D, "b2_decode_score: Avro program yields %d columns, model input is %d", avro->n_out, D);
     args.fmt = FMT_AVRO;
@@ -1055,7 +1086,7 @@ static int decode_score_spec(b2_ae* ae, const uint8_t* bytes, const int32_t* off
   args.mse = mse;
   args.flag = flag;
   args.counters = counters;
-  if (env_int("B2_FAST_TANH", 1)) return launch_decode<D, 1, true>(ae->ctx, args, stream);
+  if (ae->ctx->knobs.fast_tanh) return launch_decode<D, 1, true>(ae->ctx, args, stream);
   return launch_decode<D, 1, false>(ae->ctx, args, stream);
 }
 

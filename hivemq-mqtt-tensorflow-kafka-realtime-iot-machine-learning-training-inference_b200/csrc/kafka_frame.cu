@@ -91,22 +91,26 @@ __global__ void __launch_bounds__(KF_NT) kafka_index_kernel(const FrameArgs a) {
     if ((c ^ 0xFFFFFFFFu) != be32(s + pos + 17)) st = B2_FRAME_BAD_CRC;
   }
   const long long r0 = a.rec_base[b];
+  if (st == B2_FRAME_OK && (s[pos + 22] & 0x20u)) st = B2_FRAME_CONTROL;  // attributes bit 5: transaction markers, never delivered
   if (st == B2_FRAME_OK) {
     long long p = pos + KF_HEADER;
     for (long long r = 0; r < n_rec; ++r) {
+      // every length is untrusted: compare it with the bytes that are left instead of adding it to the cursor (a crafted
+      // varint near 2^63 would wrap the sum negative and slip past a `>` test)
       long long len, v, klen, vlen;
-      if (!read_varint(s, p, endb, &len) || len < 0 || p + len > endb) {
+      if (!read_varint(s, p, endb, &len) || len < 0 || len > endb - p) {
         st = B2_FRAME_TRUNCATED;
         break;
       }
       const long long rec_end = p + len;
       p += 1;                                                     // attributes
-      if (!read_varint(s, p, rec_end, &v) || !read_varint(s, p, rec_end, &v) || !read_varint(s, p, rec_end, &klen)) {
+      if (p > rec_end || !read_varint(s, p, rec_end, &v) || !read_varint(s, p, rec_end, &v) || !read_varint(s, p, rec_end, &klen) ||
+          klen < -1 || klen > rec_end - p) {
         st = B2_FRAME_TRUNCATED;
         break;
       }
       if (klen > 0) p += klen;
-      if (p > rec_end || !read_varint(s, p, rec_end, &vlen) || (vlen > 0 && p + vlen > rec_end)) {
+      if (!read_varint(s, p, rec_end, &vlen) || vlen < -1 || vlen > rec_end - p) {
         st = B2_FRAME_TRUNCATED;
         break;
       }
@@ -115,8 +119,10 @@ __global__ void __launch_bounds__(KF_NT) kafka_index_kernel(const FrameArgs a) {
       p = rec_end;                                                // headers are skipped with the record length
     }
   }
+  // a refused batch yields the empty range [0, 0) for each of the records its header announces (the caller sized begin / end
+  // from those same counts) — also when the record walk itself ran into a truncation: ranges written before the break are withdrawn
   if (st != B2_FRAME_OK)
-    for (long long r = 0; r < n_rec && st != B2_FRAME_TRUNCATED; ++r) a.begin[r0 + r] = a.end[r0 + r] = 0;
+    for (long long r = 0; r < n_rec; ++r) a.begin[r0 + r] = a.end[r0 + r] = 0;
   a.status[b] = st;
 }
 

@@ -287,8 +287,7 @@ static int lstm_launch(b2_lstm* m, const float* x_dev, int64_t batch, int timest
   DeviceGuard g(m->ctx->device);
   {
     // default: tensor-core kernel (tcgen05, split-precision TF32, within the 1e-4 parity budget); B2_LSTM_TC=0 → FP32 FMA kernel
-    const char* env = getenv("B2_LSTM_TC");
-    const bool want_tc = !(env && env[0] == '0');
+    const bool want_tc = m->ctx->knobs.lstm_tc != 0;
     if (want_tc && m->tc_floats > 0)
       return b2_lstm_tc_launch(m->ctx, m->d_packed_tc, m->tc_floats, m->tc_layers, m->desc.features, x_dev, batch, timesteps, seq_stride,
                                y_dev, (cudaStream_t)stream);

@@ -17,7 +17,7 @@ import numpy as np
 import torch
 
 from . import _ffi, avro_schema as av
-from .keras_compat import _stream_ptr, get_ctx
+from .keras_compat import _stream_ptr, get_ctx, set_record_bytes_hint
 
 STATUS_TEXT = {1: "wrong number of fields", 2: "field is not a valid float", 3: "empty field without a default (required)",
                4: "quote inside an unquoted field or unterminated quoted field", 5: "record ends inside a field (truncated Avro)",
@@ -73,7 +73,6 @@ def _as_batch(records) -> RecordBatch:
 _avro_cache: dict = {}
 _csv_cache: dict = {}
 _json_cache: dict = {}
-_hint_cache: dict = {}
 
 
 def _avro_prog_struct(schema):
@@ -113,10 +112,7 @@ def _size_hint(rb: "RecordBatch") -> None:
     avg = getattr(rb, "avg_record_bytes", None)  # set by callers that pass a window of a larger buffer
     if avg is None:
         avg = (rb.nbytes + max(rb.n, 1) - 1) // max(rb.n, 1)
-    dev = rb.data.device.index
-    if _hint_cache.get(dev) != int(avg):
-        _ffi.check(_ffi.lib().b2_ctx_set_record_bytes_hint(get_ctx(dev), int(avg)), "b2_ctx_set_record_bytes_hint")
-        _hint_cache[dev] = int(avg)
+    set_record_bytes_hint(rb.data.device.index, int(avg))
 
 
 def _raise_on_status(status: torch.Tensor, what: str):
@@ -346,7 +342,31 @@ def decode_score(model, records, csv_kinds=None, csv_defaults=None, avro_schema=
 
 
 _pinned_out = {}   # n → pinned uint8[5n] result buffer (reuse_output=True)
-_side_stream = {}  # device index → copy stream
+_host_ws = {}      # device index → _HostWorkspace
+
+
+class _HostWorkspace:
+    """Per-device buffers of decode_score_host, kept between calls (grow-only): payload + offsets staging on the device, ONE
+    result buffer laid out like the host result ([mse f32[n] | flag u8[n]]) so that a single D2H copy brings a call's results
+    back, the copy stream and a ring of events.  A call therefore allocates nothing once the sizes have been seen."""
+
+    def __init__(self, dev):
+        self.dev = dev
+        self.side = torch.cuda.Stream(device=dev)
+        self.cap_bytes = self.cap_n = 0
+        self.d = self.o = self.res = self.status = self.label = None
+        self.events = [torch.cuda.Event() for _ in range(64)]
+
+    def fit(self, nbytes, n):
+        if nbytes > self.cap_bytes:
+            self.cap_bytes = max(nbytes, int(self.cap_bytes * 1.25))
+            self.d = torch.empty(self.cap_bytes, dtype=torch.uint8, device=self.dev)
+        if n > self.cap_n:
+            self.cap_n = max(n, int(self.cap_n * 1.25))
+            self.o = torch.empty(self.cap_n + 1, dtype=torch.int32, device=self.dev)
+            self.res = torch.empty(self.cap_n * 5 + 16, dtype=torch.uint8, device=self.dev)
+            self.status = torch.empty(self.cap_n, dtype=torch.int32, device=self.dev)
+            self.label = torch.empty(self.cap_n, dtype=torch.uint8, device=self.dev)
 
 
 def decode_score_host(model, data, offsets, csv_kinds=None, csv_defaults=None, avro_schema=None, threshold: float = 5.0,
@@ -355,8 +375,9 @@ def decode_score_host(model, data, offsets, csv_kinds=None, csv_defaults=None, a
     or (ideally pinned) CPU tensors → H2D copy → fused kernel → D2H of (mse f32[n], flag u8[n]) as NumPy arrays.
 
     The batch is cut into ``chunks`` record ranges: the payload bytes of range c+1 cross PCIe on a copy stream while range c is
-    decoded + scored and its 5 B/record results travel back (PCIe is full duplex).  With ``reuse_output`` the returned arrays
-    are views of a per-size pinned buffer that the next call of the same size overwrites (no pinned allocation per call)."""
+    decoded + scored; the 5 B/record results come back in ONE copy at the end.  Device staging buffers, the copy stream and the
+    events are kept per device between calls.  With ``reuse_output`` the returned arrays are views of a per-size pinned buffer
+    that the next call of the same size overwrites (no pinned allocation per call)."""
     dev = torch.device("cuda", torch.cuda.current_device())
     d = data if isinstance(data, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(data, dtype=np.uint8))
     o = offsets if isinstance(offsets, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(offsets, dtype=np.int32))
@@ -369,39 +390,37 @@ def decode_score_host(model, data, offsets, csv_kinds=None, csv_defaults=None, a
         out = torch.empty(n * 5, dtype=torch.uint8).pin_memory()
         if reuse_output:
             _pinned_out[n] = out
-    hm = out[: n * 4].view(torch.float32)
-    hf = out[n * 4:]
-    main = torch.cuda.current_stream()
-    side = _side_stream.setdefault(dev.index, torch.cuda.Stream(device=dev))
-    d_dev = torch.empty(d.numel(), dtype=torch.uint8, device=dev)
-    o_dev = o.to(dev, non_blocking=True)
-    mse = torch.empty(n, dtype=torch.float32, device=dev)
-    flag = torch.empty(n, dtype=torch.uint8, device=dev)
-    status = torch.empty(n, dtype=torch.int32, device=dev)
-    label = torch.empty(n, dtype=torch.uint8, device=dev) if avro_schema is not None else None
-    side.wait_stream(main)  # the fresh device buffers are ordered after whatever the caller queued
-    bounds = [n * c // chunks for c in range(chunks + 1)]
-    bounds = sorted(set(bounds))
+    ws = _host_ws.get(dev.index)
+    if ws is None:
+        ws = _host_ws[dev.index] = _HostWorkspace(dev)
     oh = o.numpy() if not o.is_cuda else o.cpu().numpy()
-    events = []
+    b_first, b_last = int(oh[0]), int(oh[n])
+    ws.fit(b_last, n)
+    main, side = torch.cuda.current_stream(), ws.side
+    d_dev, o_dev = ws.d, ws.o[: n + 1]
+    mse = ws.res[: n * 4].view(torch.float32)
+    flag = ws.res[n * 4: n * 5]
+    status = ws.status[:n]
+    label = ws.label[:n] if avro_schema is not None else None
+    o_dev.copy_(o, non_blocking=True)
+    side.wait_stream(main)  # the staging buffers are reused: ordered after whatever the previous call still had in flight
+    chunks = max(1, min(int(chunks), len(ws.events)))
+    bounds = sorted(set(n * c // chunks for c in range(chunks + 1)))
     with torch.cuda.stream(side):
-        for c0, c1 in zip(bounds[:-1], bounds[1:]):
+        for k, (c0, c1) in enumerate(zip(bounds[:-1], bounds[1:])):
             b0, b1 = int(oh[c0]), int(oh[c1])
             if b1 > b0:
                 d_dev[b0:b1].copy_(d[b0:b1], non_blocking=True)
-            ev = torch.cuda.Event()
-            ev.record(side)
-            events.append(ev)
-    for (c0, c1), ev in zip(zip(bounds[:-1], bounds[1:]), events):
-        main.wait_event(ev)
+            ws.events[k].record(side)
+    avg = (b_last - b_first + n - 1) // max(n, 1)
+    for k, (c0, c1) in enumerate(zip(bounds[:-1], bounds[1:])):
+        main.wait_event(ws.events[k])
         rb = RecordBatch.__new__(RecordBatch)
         rb.data, rb.offsets, rb.n, rb.skip_prefix = d_dev, o_dev[c0:c1 + 1], c1 - c0, skip_prefix
-        rb.avg_record_bytes = (int(oh[n]) - int(oh[0]) + n - 1) // max(n, 1)
+        rb.avg_record_bytes = avg
         decode_score(model, rb, csv_kinds=csv_kinds, csv_defaults=csv_defaults, avro_schema=avro_schema, json_keys=json_keys,
                      json_label=json_label, threshold=threshold,
                      mse=mse[c0:c1], flag=flag[c0:c1], status=status[c0:c1], label=None if label is None else label[c0:c1])
-        hm[c0:c1].copy_(mse[c0:c1], non_blocking=True)
-        hf[c0:c1].copy_(flag[c0:c1], non_blocking=True)
+    out.copy_(ws.res[: n * 5], non_blocking=True)
     main.synchronize()
-    d_dev.record_stream(side)
-    return hm.numpy(), hf.numpy()
+    return out[: n * 4].view(torch.float32).numpy(), out[n * 4:].numpy()

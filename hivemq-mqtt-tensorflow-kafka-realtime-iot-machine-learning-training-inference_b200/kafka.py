@@ -17,7 +17,7 @@ from . import _ffi
 from .decode import RecordBatch
 from .keras_compat import _stream_ptr, get_ctx
 
-FRAME_STATUS = {0: "ok", 1: "not message format v2", 2: "CRC-32C mismatch", 3: "truncated", 4: "compressed batch"}
+FRAME_STATUS = {0: "ok", 1: "not message format v2", 2: "CRC-32C mismatch", 3: "truncated", 4: "compressed batch", 5: "control batch"}
 _HEADER = 61
 
 

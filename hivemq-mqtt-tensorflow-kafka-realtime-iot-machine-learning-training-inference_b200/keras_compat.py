@@ -44,6 +44,49 @@ def _stream_ptr() -> int:
     return torch.cuda.current_stream().cuda_stream
 
 
+def set_option(name: str, value: int, device: Optional[int] = None) -> None:
+    """Tuning / debugging switch of the device's context (``b2_ctx_set_option``): "fast_tanh", "score_cfg", "no_bulk",
+    "force_generic", "avro_generic", "lstm_tc", "score_tc".  The environment (B2_FAST_TANH, ...) only sets the defaults,
+    once, when the context is created."""
+    _ffi.check(_ffi.lib().b2_ctx_set_option(get_ctx(device), name.encode(), int(value)), "b2_ctx_set_option")
+
+
+def get_option(name: str, device: Optional[int] = None) -> int:
+    v = C.c_int()
+    _ffi.check(_ffi.lib().b2_ctx_get_option(get_ctx(device), name.encode(), C.byref(v)), "b2_ctx_get_option")
+    return int(v.value)
+
+
+_hint_cache: Dict[int, int] = {}
+
+
+def set_record_bytes_hint(device: int, avg_record_bytes: int) -> None:
+    """The ONE place that forwards the average record size of the batches to come to ``b2_ctx_set_record_bytes_hint`` (decode
+    calls and the partition driver both come through here, so the cached value can never go stale)."""
+    avg = int(avg_record_bytes)
+    if _hint_cache.get(device) != avg:
+        _ffi.check(_ffi.lib().b2_ctx_set_record_bytes_hint(get_ctx(device), avg), "b2_ctx_set_record_bytes_hint")
+        _hint_cache[device] = avg
+
+
+def normalize_fn(x, kind, lo, rng, device: Optional[int] = None):
+    """``normalize_fn`` (cardata-v1.py:40-131) as a stand-alone operator on a row-major ``[N, D]`` float32 matrix:
+    ``(v - lo) / (hi - lo) * 2.0 - 1.0`` per scaled feature, 0.0 for the four forced-zero ones, in binary32 with the
+    reference's operation order.  Returns a device tensor (torch in) or a NumPy array (NumPy in)."""
+    is_np = not isinstance(x, torch.Tensor)
+    xd = torch.from_numpy(np.ascontiguousarray(np.asarray(x, dtype=np.float32))) if is_np else x
+    dev = xd.device if xd.is_cuda else torch.device("cuda", torch.cuda.current_device() if device is None else device)
+    xd = xd.to(dev, torch.float32).contiguous()
+    if xd.dim() != 2 or xd.shape[1] != len(kind):
+        raise ValueError(f"expected rows of shape (N, {len(kind)}), got {tuple(xd.shape)}")
+    out = torch.empty_like(xd)
+    nm = _ffi.make_norm(kind, lo, rng)
+    with torch.cuda.device(dev):
+        _ffi.check(_ffi.lib().b2_normalize(get_ctx(dev.index), _ffi.ptr(xd), int(xd.shape[0]), int(xd.shape[1]), C.byref(nm),
+                                           _ffi.ptr(out), _stream_ptr()), "b2_normalize")
+    return out.cpu().numpy() if is_np else out
+
+
 # ----------------------------------------------------------------------------------------------
 # layers / regularisers / callbacks (declarative only)
 # ----------------------------------------------------------------------------------------------
@@ -687,14 +730,20 @@ class Model:
             _ffi.check(_ffi.lib().b2_ae_get_adam(self._ae, m.ctypes.data, v.ctypes.data), "b2_ae_get_adam")
             adam: Dict[str, object] = {"iter:0": np.array(self._adam["iter"], dtype=np.int64)}
             p = 0
+            # Keras' load_model_from_hdf5 reads optimizer_weights.attrs['weight_names'] unconditionally; its order is the
+            # optimizer's variable order: iter, every slot m (kernel, bias per layer), then every slot v
+            # (models/autoencoder_sensor_anomaly_detection.h5 carries these 17 names for its 4 Dense layers).
             wn = ["training/Adam/iter:0"]
+            for slot in ("m", "v"):
+                for l in dense:
+                    wn += [f"training/Adam/{l.name}/kernel/{slot}:0", f"training/Adam/{l.name}/bias/{slot}:0"]
             for i, l in enumerate(dense):
                 kshape, bshape = ws[2 * i].shape, ws[2 * i + 1].shape
                 kn, bn = int(np.prod(kshape)), int(np.prod(bshape))
                 adam[l.name] = {"kernel": {"m:0": m[p:p + kn].reshape(kshape), "v:0": v[p:p + kn].reshape(kshape)},
                                 "bias": {"m:0": m[p + kn:p + kn + bn], "v:0": v[p + kn:p + kn + bn]}}
                 p += kn + bn
-            tree["optimizer_weights"] = {"training": {"Adam": adam}}
+            tree["optimizer_weights"] = {"training": {"Adam": adam}, "@attrs": {"weight_names": np.array(wn)}}
         training_config = {"optimizer_config": {"class_name": "Adam", "config": {
             "name": "Adam", "learning_rate": self._adam["lr"], "decay": 0.0, "beta_1": self._adam["beta1"],
             "beta_2": self._adam["beta2"], "epsilon": self._adam["eps"], "amsgrad": False}},
@@ -792,3 +841,5 @@ models = _NS()
 models.Model, models.Sequential, models.load_model = Model, Sequential, load_model
 callbacks = _NS()
 callbacks.Callback, callbacks.ModelCheckpoint = Callback, ModelCheckpoint
+
+# module-level helpers reachable as bs.keras.<name> (bs.keras is this module): set_option / get_option / normalize_fn

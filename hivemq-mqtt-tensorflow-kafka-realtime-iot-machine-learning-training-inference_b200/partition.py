@@ -80,8 +80,9 @@ class PartitionDriver:
             prog = avro_schema if isinstance(avro_schema, av.AvroProgram) else av.compile_schema(avro_schema)
             self._avro = _ffi.make_avro_prog(prog)
 
-    def run(self, batches, counters=None) -> RunStats:
-        """batches: RecordBatch list (device resident).  Per-record outputs land in ``batch.mse`` / ``batch.flag``."""
+    def run(self, batches, counters=None, repeat: int = 1) -> RunStats:
+        """batches: RecordBatch list (device resident).  Per-record outputs land in ``batch.mse`` / ``batch.flag``.
+        ``repeat`` > 1 walks the list that many times inside the one C call (a consumer polling the same partitions)."""
         import torch
 
         from . import _ffi
@@ -104,11 +105,10 @@ class PartitionDriver:
         st = _ffi.RunStats()
         tot_n = sum(b.n for b in batches)
         tot_bytes = sum(int(b.data.numel()) for b in batches)
-        from .keras_compat import get_ctx
-        _ffi.check(l.b2_ctx_set_record_bytes_hint(get_ctx(dev.index), (tot_bytes + max(tot_n, 1) - 1) // max(tot_n, 1)),
-                   "b2_ctx_set_record_bytes_hint")
+        from .keras_compat import set_record_bytes_hint
+        set_record_bytes_hint(dev.index, (tot_bytes + max(tot_n, 1) - 1) // max(tot_n, 1))
         torch.cuda.current_stream().synchronize()  # inputs were produced on torch's stream; the driver uses its own
-        _ffi.check(l.b2_partition_run(self.model._handle(), arr, len(batches), C.byref(self._csv) if self._csv is not None else None,
-                                      C.byref(self._avro) if self._avro is not None else None, skip, C.byref(nm), self.threshold,
-                                      self.n_streams, counters.data_ptr(), C.byref(st)), "b2_partition_run")
+        _ffi.check(l.b2_partition_run_repeat(self.model._handle(), arr, len(batches), C.byref(self._csv) if self._csv is not None else None,
+                                             C.byref(self._avro) if self._avro is not None else None, skip, C.byref(nm), self.threshold,
+                                             self.n_streams, int(repeat), counters.data_ptr(), C.byref(st)), "b2_partition_run_repeat")
         return RunStats(int(st.records), int(st.flagged), int(st.decode_errors), int(st.bytes), float(st.elapsed_ms))

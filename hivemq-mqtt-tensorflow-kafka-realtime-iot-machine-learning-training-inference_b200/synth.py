@@ -260,3 +260,58 @@ def corrupt_csv(data: np.ndarray, offsets: np.ndarray, frac: float = 1e-4, seed:
         lines[i] = b",".join(parts)
     d, o = lines_to_batch(lines)
     return d, o, bad
+
+
+def corrupt_batch(data: np.ndarray, offsets: np.ndarray, fmt: str, frac: float = 1e-4, seed: int = BASE_SEED
+                  ) -> Tuple[np.ndarray, np.ndarray, np.ndarray]:
+    """``frac`` of the records of a batch malformed (truncated, empty field, bad digit / bad varint), for any of
+    the wire formats ("csv", "avro_a", "avro_b", "json").  Only the damaged records are touched (the batch is re-packed around
+    them), so this is cheap at 2^20 records.  Returns (data, offsets, indices of the damaged records)."""
+    g = rng_for(seed + 32452843)
+    n = len(offsets) - 1
+    k = max(1, int(round(n * frac))) if frac > 0 else 0
+    if k == 0:
+        return data, offsets, np.zeros(0, dtype=np.int64)
+    bad = np.sort(g.choice(n, size=k, replace=False))
+    lens = np.diff(offsets.astype(np.int64))
+    pieces, prev = [], 0
+    for i in bad:
+        b, e = int(offsets[i]), int(offsets[i + 1])
+        rec = data[b:e].tobytes()
+        mode = int(g.integers(0, 3))
+        if fmt == "csv":
+            parts = rec.split(b",")
+            if mode == 0:
+                parts = parts[: int(g.integers(3, len(parts)))]          # truncated: too few fields
+            elif mode == 1:
+                parts[int(g.integers(2, len(parts)))] = b""              # empty numeric field, no default
+            else:
+                j = int(g.integers(2, len(parts)))
+                parts[j] = parts[j][:1] + b"x" + parts[j][1:]            # junk inside a number
+            rec2 = b",".join(parts)
+        elif fmt == "json":
+            if mode == 0:
+                rec2 = rec[: int(g.integers(2, len(rec) - 1))]           # cut inside the object
+            else:
+                import re
+
+                digits = [m.start(1) for m in re.finditer(rb":-?(\d)", rec)]   # first digit of a number VALUE (not of a name)
+                p = digits[int(g.integers(0, len(digits)))]
+                rec2 = rec[:p] + b"x" + rec[p + 1:]                      # junk inside a number
+        else:
+            if mode == 0 or len(rec) < 48:
+                rec2 = rec[: max(5, len(rec) - int(g.integers(1, 9)))]   # truncated inside the last fields
+            elif fmt == "avro_b" and mode == 1:
+                rec2 = rec[:5] + b"\x04" + rec[6:]                       # union branch index 2 of a two-branch union
+            else:
+                p = 5 + 36 if fmt == "avro_a" else len(rec) - 12
+                rec2 = rec[:p] + b"\xff" * 6 + rec[p + 1:]               # an int varint that never ends
+        pieces.append(data[prev:b])
+        pieces.append(np.frombuffer(rec2, dtype=np.uint8))
+        lens[i] = len(rec2)
+        prev = e
+    pieces.append(data[prev:])
+    offs2 = np.zeros(n + 1, dtype=np.int64)
+    np.cumsum(lens, out=offs2[1:])
+    return np.concatenate(pieces), offs2.astype(np.int32), bad
+

@@ -45,7 +45,7 @@ extern "C" {
 #define B2_REC_BAD_QUOTE   4  /* CSV: quote inside unquoted field / unterminated quoted field */
 #define B2_REC_TRUNCATED   5  /* Avro: record ends inside a field */
 #define B2_REC_BAD_BRANCH  6  /* Avro: union branch index out of range */
-#define B2_REC_TOO_LONG    7  /* CSV: number with > 19 significant digits that cannot be rounded unambiguously */
+#define B2_REC_TOO_LONG    7  /* CSV: number with > 19 significant digits that cannot be rounded unambiguously; any format: record > 24 KB */
 #define B2_REC_BAD_JSON    8  /* JSON: not one well-formed RFC 8259 object */
 
 typedef struct b2_ctx b2_ctx;   /* one per device / rank */
@@ -60,6 +60,11 @@ int  b2_ctx_sm_count(const b2_ctx* ctx);
  * come, e.g. total payload bytes / N (0 = unknown, the default: estimated from the schema).  Each warp stages 32 records at a
  * time; a good hint makes a 32-record chunk fit its stage in one piece and lets more CTAs share an SM. */
 int  b2_ctx_set_record_bytes_hint(b2_ctx* ctx, int avg_record_bytes);
+/* Tuning / debugging switches: "fast_tanh", "score_cfg", "no_bulk", "force_generic", "avro_generic", "lstm_tc", "score_tc".
+ * Their defaults come from the environment (B2_FAST_TANH, …) ONCE, when the context is created; no launch reads the
+ * environment afterwards. */
+int  b2_ctx_set_option(b2_ctx* ctx, const char* name, int value);
+int  b2_ctx_get_option(const b2_ctx* ctx, const char* name, int* value);
 const char* b2_strerror(int code);
 const char* b2_last_error(void);      /* thread-local detail of the last failure */
 const char* b2_version(void);
@@ -96,7 +101,27 @@ int  b2_ae_score(b2_ae* ae, const float* x_dev, int64_t n, const b2_norm* norm, 
                  float* mse_dev, uint8_t* flag_dev, float* recon_dev, unsigned long long* counters_dev,
                  void* stream);
 
-/* ---- record decode -------------------------------------------------------------------------------------- */
+/* normalize_fn as a stand-alone operator (cardata-v1.py:40-131; LSTM-TensorFlow-IO-Kafka/cardata-v1.py:53-143):
+ * out[r][j] = (x[r][j] - lo[j]) / range[j] * 2.0 - 1.0 (B2_NORM_SCALE), 0.0 (B2_NORM_ZERO) or x[r][j], x_dev / out_dev f32[n, d]
+ * row-major, in binary32 with the reference's operation order — the device function the fused kernels apply, bit-identical
+ * to an IEEE division for every input as long as range[j] and 1 / range[j] are both normal float32 numbers
+ * (1.2e-38 < |range| < 8.5e37; the reference's table uses 1 … 7500).  b2_selftest_normalize proves that on the device: for every float32 bit pattern in
+ * [first_bits, first_bits + count) and every feature of the table it compares that function with sub → IEEE div → fma and
+ * adds the number of differences to out_dev[0] (u64[2], zeroed by the caller; [1] = feature << 32 | bits of one of them). */
+int  b2_normalize(b2_ctx* ctx, const float* x_dev, int64_t n, int d, const b2_norm* norm, float* out_dev, void* stream);
+int  b2_selftest_normalize(b2_ctx* ctx, const b2_norm* norm, int d, uint64_t first_bits, uint64_t count,
+                           unsigned long long* out_dev, void* stream);
+
+/* ---- record decode --------------------------------------------------------------------------------------
+ * Input contract shared by every decode entry point: record i is bytes_dev[offs_dev[i] .. offs_dev[i+1]).  The kernels fetch
+ * a chunk of records with 16-byte-granular bulk copies, so they READ (never write) the whole 16-byte lines that hold the
+ * first and the last payload byte: up to 15 bytes before bytes_dev + offs_dev[0] and up to 15 bytes past
+ * bytes_dev + offs_dev[n] must be readable.  Any cudaMalloc'ed (256-byte aligned, 256-byte granular) or torch buffer is;
+ * a caller that sub-allocates with byte granularity must pad its arena by 16 bytes at both ends.
+ * Record length: each warp stages 32 records in shared memory, sized from the schema or from b2_ctx_set_record_bytes_hint (a pure
+ * performance hint).  A record that does not fit is decoded by a second, small launch on the same stream with a 24 KB stage,
+ * so the only hard limit is 24 KB per record (beyond: B2_REC_TOO_LONG), and at most 1024 such records per call; launches on
+ * more than 32 distinct streams per context share that retry list and must not overlap. */
 typedef struct {
   int32_t n_fields;                 /* fields per record (20 sensor CSV, 31 credit-card CSV) */
   int32_t kind[B2_MAX_FIELDS];      /* 0 skip, 1 float32 → next output column, 2 string (span reported) */
@@ -250,7 +275,8 @@ int  b2_format_rows(b2_ctx* ctx, const float* x_dev, int64_t n, int n_cols, int 
  * batch starts 12 + batchLength bytes on; recordCount i32 at byte 57) and passes batch_pos_dev int64[n_batches] and rec_base_dev
  * int64[n_batches] (records in the batches before each one).  One thread per batch checks magic == 2, the CRC-32C (verify_crc)
  * and walks the records: begin_dev / end_dev int32[n_records] receive each value's byte range inside bytes_dev, status_dev
- * int32[n_batches] a B2_FRAME_* code (records of a refused batch get the empty range [0, 0)).
+ * int32[n_batches] a B2_FRAME_* code (every record a refused batch's header announces gets the empty range [0, 0); record, key and
+ * value lengths are untrusted input and are checked against the bytes that remain).
  * b2_kafka_gather_values then packs the values back to back at out_offs_dev int32[n] (the caller's scan of end - begin), giving
  * the (bytes, offsets) batch every decode entry point takes. */
 #define B2_FRAME_OK         0
@@ -258,6 +284,7 @@ int  b2_format_rows(b2_ctx* ctx, const float* x_dev, int64_t n, int n_cols, int 
 #define B2_FRAME_BAD_CRC    2
 #define B2_FRAME_TRUNCATED  3  /* batch or record runs past its container */
 #define B2_FRAME_COMPRESSED 4  /* gzip / snappy / lz4 / zstd batch: not inflated here */
+#define B2_FRAME_CONTROL    5  /* control batch (attributes bit 5: transaction markers); consumers never see its records */
 int  b2_kafka_index_records(b2_ctx* ctx, const uint8_t* bytes_dev, int64_t n_bytes, const int64_t* batch_pos_dev, const int64_t* rec_base_dev,
                             int64_t n_batches, int verify_crc, int32_t* begin_dev, int32_t* end_dev, int32_t* status_dev, void* stream);
 int  b2_kafka_gather_values(b2_ctx* ctx, const uint8_t* bytes_dev, const int32_t* begin_dev, const int32_t* end_dev, int64_t n,
@@ -297,6 +324,12 @@ typedef struct {
 int  b2_partition_run(b2_ae* ae, const b2_partition* parts, int n_parts, const b2_csv_spec* csv,
                       const b2_avro_prog* avro, int skip_prefix, const b2_norm* norm, float threshold,
                       int n_streams, unsigned long long* counters_dev, b2_run_stats* host_out);
+/* The same run `repeat` times over the partition list inside one call (a consumer that keeps polling the same partitions;
+ * what bench.py times: no host work between launches but the launches themselves).  Streams and events belong to the
+ * context: created on first use, reused by every run. */
+int  b2_partition_run_repeat(b2_ae* ae, const b2_partition* parts, int n_parts, const b2_csv_spec* csv,
+                             const b2_avro_prog* avro, int skip_prefix, const b2_norm* norm, float threshold,
+                             int n_streams, int repeat, unsigned long long* counters_dev, b2_run_stats* host_out);
 
 #ifdef __cplusplus
 }

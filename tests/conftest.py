@@ -52,3 +52,16 @@ def cuda_device():
 
     bs._ffi.lib()  # raises if libb2sensor.so is missing: no fallback
     return torch.device("cuda", 0)
+
+
+@pytest.fixture
+def lstm_path(cuda_device):
+    """Select the LSTM kernel for one test ("tcgen05" = the default tensor-core kernel, "fp32" = the FMA one) through the
+    context option; the default is restored afterwards."""
+    import b200_sensor as bs
+
+    def pick(path):
+        bs.keras.set_option("lstm_tc", 1 if path == "tcgen05" else 0)
+
+    yield pick
+    bs.keras.set_option("lstm_tc", 1)

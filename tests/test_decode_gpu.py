@@ -259,9 +259,9 @@ def test_host_end_to_end_path_matches_device_path(cuda_device, fmt):
 
 
 @pytest.mark.parametrize("fmt", ["avro_a", "avro_b"])
-def test_reference_schema_walks_equal_the_generic_walk(cuda_device, monkeypatch, fmt):
+def test_reference_schema_walks_equal_the_generic_walk(cuda_device, fmt):
     """The straight-line walks for the reference's two schemas (avro_walk_schema_a / _b) against the run-interpreting generic
-    walk (B2_AVRO_GENERIC=1): bit-identical values, labels and statuses, including nulls, wide varints and damaged records."""
+    walk (context option avro_generic = 1): bit-identical values, labels and statuses, including nulls, wide varints and damaged records."""
     x = synth.sensor_rows(50_003, seed=21)
     x[::97, 9] = 20000.0      # three-byte varint → the record leaves the straight-line walk
     x[::89, 17] = -3.0        # negative firmware
@@ -280,10 +280,13 @@ def test_reference_schema_walks_equal_the_generic_walk(cuda_device, monkeypatch,
     offs2[-1] -= 7
     rb = dec.RecordBatch(data[:offs2[-1]], offs2, skip_prefix=5)
     res = {}
-    for mode in ("0", "1"):
-        monkeypatch.setenv("B2_AVRO_GENERIC", mode)
-        out, label, status, _ = dec.decode_avro_matrix(rb, sch, raise_on_error=False)
-        res[mode] = (out.cpu().numpy().copy(), label.cpu().numpy().copy(), status.cpu().numpy().copy())
+    try:
+        for mode in ("0", "1"):
+            bs.keras.set_option("avro_generic", int(mode))
+            out, label, status, _ = dec.decode_avro_matrix(rb, sch, raise_on_error=False)
+            res[mode] = (out.cpu().numpy().copy(), label.cpu().numpy().copy(), status.cpu().numpy().copy())
+    finally:
+        bs.keras.set_option("avro_generic", 0)
     np.testing.assert_array_equal(res["0"][2], res["1"][2])
     ok = res["1"][2] == 0
     assert ok.sum() > 40_000 and (~ok).sum() > 5

@@ -61,3 +61,39 @@ def test_segment_to_scores(cuda_device):
     a = dec.decode_score(m, rb, avro_schema=schemas.schema_a_json())
     b = dec.decode_score(m, dec.RecordBatch(data, offs, skip_prefix=5), avro_schema=schemas.schema_a_json())
     assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
+
+
+def _golden():
+    import json
+    import os
+
+    return json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "kafka_v2_batches.json")))
+
+
+def test_hand_assembled_protocol_batches(cuda_device):
+    """Batches packed field by field from the protocol guide (tests/golden/make_kafka_golden.py, bitwise CRC-32C): keyed records,
+    headers (incl. a null header value), null and empty values, a 130-byte key (two-byte length varint), a control batch."""
+    fx = _golden()
+    seg = bytes.fromhex(fx["segment_hex"])
+    rb, st = bs.kafka.values_from_segment(seg, raise_on_error=False)
+    assert st.cpu().tolist() == fx["batch_status"]  # [ok, control batch, ok]
+    d, o = rb.data.cpu().numpy().tobytes(), rb.offsets.cpu().numpy()
+    got = [d[o[i]:o[i + 1]] for i in range(rb.n)]
+    assert got == [b"" if h is None else bytes.fromhex(h) for h in fx["values_hex"]]
+    with pytest.raises(bs.kafka.FrameError, match="control batch"):
+        bs.kafka.values_from_segment(seg)
+
+
+def test_hostile_lengths_are_truncation_not_a_fault(cuda_device):
+    """Key / value lengths near 2^62 and negative key lengths, each inside a batch whose CRC is valid: refused as truncated,
+    no range of the batch survives, and the context is still usable afterwards."""
+    fx = _golden()
+    for name, hx in fx["hostile_hex"].items():
+        for crc in (True, False):
+            rb, st = bs.kafka.values_from_segment(bytes.fromhex(hx), raise_on_error=False, verify_crc=crc)
+            assert st.cpu().tolist() == [3], name
+            o = rb.offsets.cpu().numpy()
+            assert (o == 0).all(), name
+    torch.cuda.synchronize()
+    rb, st = bs.kafka.values_from_segment(bs.kafka.write_segment([b"still", b"alive"]))
+    assert rb.n == 2 and not st.any()

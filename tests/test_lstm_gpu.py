@@ -22,9 +22,9 @@ def _lstm_model(look_back, features=18, seed=314):
 
 @pytest.mark.parametrize("path", ["tcgen05", "fp32"])
 @pytest.mark.parametrize("batch,T", [(1, 1), (200, 1), (127, 4), (129, 16), (5000, 3)])
-def test_lstm_forward_matches_oracle(cuda_device, monkeypatch, batch, T, path):
+def test_lstm_forward_matches_oracle(cuda_device, lstm_path, batch, T, path):
     """Both kernels: the default tensor-core one (tcgen05.mma kind::tf32, split precision) and the FP32 FMA one."""
-    monkeypatch.setenv("B2_LSTM_TC", "1" if path == "tcgen05" else "0")
+    lstm_path(path)
     m = _lstm_model(T)
     assert m.count_params() == 18642
     w = m.get_flat_weights()
@@ -72,10 +72,10 @@ def test_lstm_rejects_other_stacks(cuda_device):
 
 @pytest.mark.parametrize("path", ["tcgen05", "fp32"])
 @pytest.mark.parametrize("n_rows,look_back,shift", [(1200, 1, 1), (777, 4, 1), (1000, 16, 3), (5, 8, 1)])
-def test_lstm_sliding_windows_read_in_place(cuda_device, monkeypatch, n_rows, look_back, shift, path):
+def test_lstm_sliding_windows_read_in_place(cuda_device, lstm_path, n_rows, look_back, shift, path):
     """dataset.window(look_back, shift, drop_remainder=True) fused into the forward pass (LSTM-…/cardata-v1.py:184-185): the
     kernel reads window i at rows [i*shift, i*shift+look_back) of the stream; result == predict on the materialised windows."""
-    monkeypatch.setenv("B2_LSTM_TC", "1" if path == "tcgen05" else "0")
+    lstm_path(path)
     m = _lstm_model(look_back)
     g = np.random.default_rng(n_rows)
     rows = g.uniform(-1, 1, size=(n_rows, 18)).astype(np.float32)

@@ -12,6 +12,8 @@ import b200_sensor as bs
 from b200_sensor import _ffi, schemas, synth
 from oracle import cpu_oracle as orc
 
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
 pytestmark = pytest.mark.gpu
 ACTS = [orc.ACT_TANH, orc.ACT_RELU, orc.ACT_TANH, orc.ACT_RELU]
 L1 = float(np.float32(1e-7))
@@ -121,6 +123,20 @@ def test_save_load_roundtrip_with_adam_slots_and_checkpoint(cuda_device, tmp_pat
     assert os.path.exists(tmp_path / "best.h5")
     f = bs.h5lite.H5File(p)
     assert "optimizer_weights" in f and f.attrs["keras_version"] == "2.2.4-tf"
+    # tf.keras' loader walks optimizer_weights.attrs['weight_names']: same list as the reference's own file (iter, all m, all v),
+    # layer names aside, and every name resolves to a dataset
+    wn = [str(s) for s in np.atleast_1d(f["optimizer_weights"].attrs["weight_names"])]
+    ref = bs.h5lite.H5File(os.path.join(GOLDEN, "ae30_5epochs.h5"))
+    ref_wn = [str(s) for s in np.atleast_1d(ref["optimizer_weights"].attrs["weight_names"])]
+    ours = [l.name for l in m.layers if isinstance(l, bs.keras_compat.Dense)]
+    theirs = ["dense", "dense_1", "dense_2", "dense_3"]
+    assert len(wn) == len(ref_wn) == 17
+    for a, b in zip(wn, ref_wn):
+        parts = b.split("/")
+        if len(parts) == 5:
+            parts[2] = ours[theirs.index(parts[2])]
+        assert a == "/".join(parts)
+        assert f["optimizer_weights/" + a].read() is not None
 
 
 def test_fit_rejects_what_the_reference_never_does(cuda_device):

@@ -46,16 +46,20 @@ def test_noalloc_matches_b2_ae_grad_on_two_calls_in_a_row(cuda_device):
         free_after, _ = torch.cuda.mem_get_info()
         if seed == 2:  # set-up is behind us on the second call: the device's free memory must not have moved
             assert free_after >= free_before
-        # same tolerance as tests/test_train_gpu.py uses for gradient sums
-        np.testing.assert_allclose(got.cpu().numpy(), ref, rtol=2e-4, atol=2e-7)
+        # both entry points run the same kernels with the same launch shape and fold the partial sums in the same fixed
+        # order, so the numbers have to agree bit for bit, not just within the gradient tolerance of tests/test_train_gpu.py
+        np.testing.assert_array_equal(got.cpu().numpy(), ref)
         assert got.cpu().numpy()[P + 2] == n
 
 
-def test_noalloc_refuses_what_does_not_fit(cuda_device):
+def test_noalloc_rejects_bad_arguments_and_its_buffer_covers_a_b200_launch(cuda_device):
+    """The size refusal itself cannot be provoked on a B200: a launch uses at most one CTA per SM (148) and the built-in
+    buffer is sized for 160, so here only the arithmetic behind that claim and the argument checks are exercised."""
     l = _ffi.lib()
     m = bs.keras.models.load_model(os.path.join(GOLDEN, "ae30_5epochs.h5"))
     h, P = m._handle(), m.n_params
-    assert 148 * (P + 3) <= _ffi.NOALLOC_SCRATCH_FLOATS  # a B200 launch always fits; the check guards bigger parts
+    sms = torch.cuda.get_device_properties(0).multi_processor_count
+    assert sms * (P + 3) <= _ffi.NOALLOC_SCRATCH_FLOATS
     nm = _ffi.make_norm()
     g = torch.empty(P + 3, dtype=torch.float32, device="cuda")
     x = torch.zeros((4, 30), dtype=torch.float32, device="cuda")

@@ -11,7 +11,7 @@ for d in (30, 18):
     wl.setup(dev, 0)
     wl.step(0)
 for fmt in ("csv", "avro_a", "avro_b", "json"):
-    wl = bench.DecodeScoreWorkload(fmt, batch_log2=18, batches_per_step=1)
+    wl = bench.DecodeScoreWorkload(fmt, batch_log2=18, n_batches=1, repeat=1)
     wl.setup(dev, 0)
     wl.step(0)
 m = bench.ScoreWorkload(30, 20, 20).model()

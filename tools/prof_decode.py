@@ -5,7 +5,7 @@ import torch
 import bench
 
 fmt = sys.argv[1] if len(sys.argv) > 1 else "csv"
-wl = bench.DecodeScoreWorkload(fmt, batch_log2=int(sys.argv[2]) if len(sys.argv) > 2 else 18, batches_per_step=1)
+wl = bench.DecodeScoreWorkload(fmt, batch_log2=int(sys.argv[2]) if len(sys.argv) > 2 else 18, n_batches=1, repeat=1)
 wl.setup(torch.device("cuda", 0), 0)
 for i in range(3):
     wl.step(i)
