@@ -11,7 +11,7 @@ import os
 from typing import Optional
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libb2sensor.so")
+LIB_PATH = os.environ.get("B2_LIB") or os.path.join(HERE, "libb2sensor.so")  # B2_LIB: A/B runs against another build
 
 MAX_WIDTH = 64
 MAX_FIELDS = 64

@@ -124,7 +124,9 @@ __device__ __forceinline__ float norm_feature(float v, int kind, float lo, float
 // correctly rounded quotient t/range (Markstein's theorem) for every finite t whose quotient neither overflows nor
 // lands in the subnormal range.  A subnormal-range slip is absorbed by the final `*2 - 1` (|q| < 2^-25 gives -1 either
 // way); an infinite t or an overflowing quotient shows up as q0 = ±inf, which is then the IEEE result and is selected
-// explicitly (the correction step would turn it into NaN).  NaN propagates.  Hence bit-identical to norm_feature().
+// explicitly (the correction step would turn it into NaN).  NaN propagates.  Hence bit-identical to norm_feature() for
+// 2^-64 <= |range| <= 2^64 (beyond that the residual r itself can go subnormal); checked exhaustively on the device over all
+// 2^32 inputs by b2_selftest_normalize (tests/test_normalize_gpu.py).
 template <int D>
 __device__ __forceinline__ float2 norm_pair_fast(float2 v, const NormP<D>& nm, int i) {
   const float2 lo = make_float2(nm.lo[i], nm.lo[i + 1]);
@@ -239,5 +241,88 @@ __device__ __forceinline__ void ae_forward_rows(const AeW<D>& w, const NormP<D>&
   }
 #pragma unroll
   for (int r = 0; r < R; ++r) mse[r] = __fdiv_rn(se[r].x + se[r].y, (float)D);
+}
+// ---- two rows per thread, packed along the ROW dimension -------------------------------------------------------------------
+// row[i] = (x_i of record A, x_i of record B): the lane's two records interleaved element by element, so one LDS.64 delivers an
+// operand pair as it is.  Every FFMA2 multiplies that pair by ONE weight (broadcast .F32 operand straight from the constant
+// bank), i.e. a weight is fetched once per two records and an LDCU.128 feeds four FFMA2 — a quarter of the weight fetches per
+// record of the output-packed form above, which is what the fused decode kernel (issue-bound, one record per lane before) needs.
+// Per record the products are accumulated in the same order as in ae_forward_rows, and the squared error keeps its even / odd
+// partial sums, so both forms give the same bits.
+template <int D>
+__device__ __forceinline__ float2 norm_rows_fast(float2 v, const NormP<D>& nm, int i) {  // feature i of two records
+  const int kind = nm.kind[i];
+  if (kind == B2_NORM_ZERO) return make_float2(0.0f, 0.0f);
+  if (kind != B2_NORM_SCALE) return v;
+  const float2 t = fma2(splat(nm.lo[i]), splat(-1.0f), v);  // v - lo, one rounding
+  const float2 q0 = mul2(t, splat(nm.rinv[i]));
+  const float2 r = fma2(make_float2(-q0.x, -q0.y), splat(nm.range[i]), t);
+  float2 q = fma2(r, splat(nm.rinv[i]), q0);
+  if (fabsf(q0.x) == __int_as_float(0x7F800000)) q.x = q0.x;
+  if (fabsf(q0.y) == __int_as_float(0x7F800000)) q.y = q0.y;
+  return fma2(q, splat(2.0f), splat(-1.0f));
+}
+
+template <int D, bool NORM, bool FAST_TANH>
+__device__ __forceinline__ void ae_forward_pair(const AeW<D>& w, const NormP<D>& nm, float2* __restrict__ row, float (&mse)[2]) {
+  // Layer 1 is taken in two halves of 7 units, each folded into layer 2's accumulators as soon as it has gone through tanh: the
+  // live state is 14 + 14 + 2 registers instead of 28 + 14 + 2 (x is read from shared memory once per half).  That is what lets
+  // the fused kernel keep two records per lane within 80 registers, i.e. 24 warps per SM.
+  constexpr int HALF = AE_H1 / 2;
+  float2 h2[AE_H2];
+#pragma unroll
+  for (int j = 0; j < AE_H2; ++j) h2[j] = splat(w.b2[j]);
+#pragma unroll
+  for (int half = 0; half < 2; ++half) {
+    float2 h1[HALF];
+#pragma unroll
+    for (int j = 0; j < HALF; ++j) h1[j] = splat(w.b1[half * HALF + j]);
+#pragma unroll
+    for (int i = 0; i < D; ++i) {
+      float2 xv = row[i];
+      if (NORM && half == 0) {
+        xv = norm_rows_fast<D>(xv, nm, i);
+        row[i] = xv;
+      }
+#pragma unroll
+      for (int j = 0; j < HALF; ++j) h1[j] = fma2(xv, splat(w.k1[i][half * HALF + j]), h1[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < HALF; ++j) h1[j] = tanh2_sel<FAST_TANH>(h1[j]);
+    // layer 2 accumulates over its inputs in index order: half 0 contributes inputs 0..6 first, half 1 inputs 7..13 — the same
+    // order of additions as the one-pass form
+#pragma unroll
+    for (int i = 0; i < HALF; ++i)
+#pragma unroll
+      for (int j = 0; j < AE_H2; ++j) h2[j] = fma2(h1[i], splat(w.k2[half * HALF + i][j]), h2[j]);
+    if (half == 0) asm volatile("" ::: "memory");  // read x again for the second half instead of keeping it in registers
+  }
+#pragma unroll
+  for (int j = 0; j < AE_H2; ++j) h2[j] = relu2(h2[j]);
+
+  float2 h3[AE_H3];
+#pragma unroll
+  for (int j = 0; j < AE_H3; ++j) h3[j] = splat(w.b3[j]);
+#pragma unroll
+  for (int i = 0; i < AE_H2; ++i)
+#pragma unroll
+    for (int j = 0; j < AE_H3; ++j) h3[j] = fma2(h2[i], splat(w.k3[i][j]), h3[j]);
+#pragma unroll
+  for (int j = 0; j < AE_H3; ++j) h3[j] = tanh2_sel<FAST_TANH>(h3[j]);
+
+  asm volatile("" ::: "memory");  // re-read x from shared memory below instead of keeping D pairs live
+  float2 se_even = make_float2(0.f, 0.f), se_odd = make_float2(0.f, 0.f);
+#pragma unroll
+  for (int j = 0; j < D; ++j) {
+    float2 y = splat(w.b4[j]);
+#pragma unroll
+    for (int k = 0; k < AE_H3; ++k) y = fma2(h3[k], splat(w.k4[k][j]), y);
+    y = relu2(y);
+    const float2 d = fma2(y, splat(-1.0f), row[j]);
+    if (j & 1) se_odd = fma2(d, d, se_odd);
+    else se_even = fma2(d, d, se_even);
+  }
+  mse[0] = __fdiv_rn(se_even.x + se_odd.x, (float)D);
+  mse[1] = __fdiv_rn(se_even.y + se_odd.y, (float)D);
 }
 #endif

@@ -21,7 +21,7 @@ struct ScoreTcArgs {
 };
 
 template <int D, bool NORM, bool FT>
-__global__ void __launch_bounds__(TCS_ROWS, 4) ae_score_tc_kernel(const __grid_constant__ ScoreTcArgs<D> a) {
+__global__ void __launch_bounds__(TCS_ROWS, 512 / TcShape<D>::TMEM_COLS > 6 ? 6 : 512 / TcShape<D>::TMEM_COLS) ae_score_tc_kernel(const __grid_constant__ ScoreTcArgs<D> a) {
   constexpr int STAGES = 2;
   constexpr uint32_t TILE_BYTES = TCS_ROWS * D * 4;
   extern __shared__ __align__(128) uint8_t smem[];
@@ -87,7 +87,7 @@ __global__ void __launch_bounds__(TCS_ROWS, 4) ae_score_tc_kernel(const __grid_c
     }
     s = (s + 1 == STAGES) ? 0 : s + 1;
   }
-  tcs_teardown(c, tid);
+  tcs_teardown<D>(c, tid);
 
   if (a.counters) {
 #pragma unroll
@@ -124,17 +124,21 @@ template <int D, bool NORM, bool FT>
 static int launch_score_tc(b2_ae* ae, const ScoreTcArgs<D>& args, cudaStream_t stream) {
   constexpr size_t smem = (size_t)2 * TCS_ROWS * D * 4 + sizeof(float) * TcShape<D>::TOTAL;
   auto kern = ae_score_tc_kernel<D, NORM, FT>;
-  static int occ_cache[16] = {0};
+  static bool attr_set[16] = {false};
   const int dev = ae->ctx->device;
-  if (occ_cache[dev & 15] == 0) {
+  if (!attr_set[dev & 15]) {
     B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int occ = 0;
-    B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, TCS_ROWS, smem));
-    B2_REQUIRE(occ >= 1, "ae_score_tc: kernel does not fit on an SM (smem %zu)", smem);
-    occ_cache[dev & 15] = occ > 4 ? 4 : occ;  // 4 x 128 TMEM columns per SM
+    B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    attr_set[dev & 15] = true;
   }
+  // CTAs per SM by construction: 512 TMEM columns / this kernel's allocation (4 for D = 30, up to 8 for D = 18; registers
+  // allow 6 there), ~40 / ~28 KB of shared memory each; the context option "tc_ctas" overrides it for experiments.
+  // (cudaOccupancyMaxActiveBlocksPerMultiprocessor answers 1 for this kernel; tile striding is static, so a CTA that had to
+  // wait for a slot would only cost balance, never correctness.)
+  const int want = ae->ctx->knobs.tc_ctas > 0 ? ae->ctx->knobs.tc_ctas : 512 / TcShape<D>::TMEM_COLS;
+  const int CTAS_PER_SM = want < 1 ? 1 : (want > 512 / TcShape<D>::TMEM_COLS ? 512 / TcShape<D>::TMEM_COLS : want);
   const long long n_tiles = (args.n + TCS_ROWS - 1) / TCS_ROWS;
-  long long grid = (long long)ae->ctx->sm_count * occ_cache[dev & 15];
+  long long grid = (long long)ae->ctx->sm_count * CTAS_PER_SM;
   if (grid > n_tiles) grid = n_tiles;
   if (grid < 1) grid = 1;
   kern<<<(unsigned)grid, TCS_ROWS, smem, stream>>>(args);

@@ -10,14 +10,13 @@
 //     K-major no-swizzle layout, again as (hi, lo);
 //   * D = A_hi·B_hi + A_lo·B_hi + A_hi·B_lo (3 × K/8 MMAs, M = 128, N = 16 or 32) → an FP32 accumulator in TMEM, read back by the
 //     row-owning threads with tcgen05.ld for the activation / the squared error.
-// TMEM per CTA: 128 columns = A panel hi [0,32) + lo [32,64) + accumulator [64,96): four CTAs share an SM's 512 columns.
+// TMEM per CTA: D = 30 → 128 columns (A panel hi [0,32) + lo [32,64) + accumulator [64,96)): four CTAs share an SM's 512 columns;
+// D = 18 → 64 columns (hi [0,24) + lo [24,48) + a 16-column accumulator at 48; the last layer's 32-column accumulator sits at
+// [32,64), free by then because its A panel is only [0,8) + [24,32)): up to eight CTAs per SM.
 #pragma once
 #include "ae_math.cuh"
 
 constexpr int TCS_ROWS = 128;      // rows per tile = TMEM lanes = threads per CTA
-constexpr int TCS_ALO = 32;        // column of the lo copy of the A panel
-constexpr int TCS_ACC = 64;        // first accumulator column
-constexpr int TCS_TMEM_COLS = 128;
 
 // GEMM shapes: K includes the bias row and zero padding to a multiple of 8; N is padded to 16 / 32 (M = 128 needs N % 16 == 0)
 template <int D>
@@ -31,7 +30,13 @@ struct TcShape {
   static constexpr int OFF3 = OFF2 + 2 * N2 * K2;
   static constexpr int OFF4 = OFF3 + 2 * N3 * K3;
   static constexpr int TOTAL = OFF4 + 2 * N4 * K4;
+  // TMEM columns
+  static constexpr int ALO = K1;                           // lo copy of the A panel right behind the hi copy
+  static constexpr int ACC = 2 * K1;                       // accumulator of layers 1-3 (16 columns)
+  static constexpr int ACC4 = (2 * K1 + 16 <= 64) ? 32 : 2 * K1;  // accumulator of layer 4 (32 columns)
+  static constexpr int TMEM_COLS = (2 * K1 + 16 <= 64) ? 64 : 128;
   static_assert(K1 <= 32 && N4 <= 32, "panel wider than the TMEM budget");
+  static_assert(ACC + 16 <= TMEM_COLS && ACC4 + N4 <= TMEM_COLS && ACC4 >= ALO + 8, "TMEM layout overlaps");
 };
 
 template <int D>
@@ -115,30 +120,38 @@ __device__ __forceinline__ void tcs_mma(uint32_t d_tmem, uint32_t a_tmem, uint64
 __device__ __forceinline__ void tcs_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
+// TF32 head (round to nearest on the 13 dropped mantissa bits) + exact remainder.  cvt.rna.tf32.f32 expands to five SASS
+// instructions on sm_100a (ncu: LOP3 + FSETP + VIADD + SEL + FADD per value, 40 % of the first version of this kernel); the
+// integer form below is three.  It differs only where the rounding carries into the exponent field of the largest binade
+// (|v| > 3.4e38 · (1 - 2^-12)): hi becomes inf there and the record's error NaN — such a value squared overflows binary32 anyway.
 __device__ __forceinline__ void tcs_split(float v, uint32_t& hi, uint32_t& lo) {
-  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi) : "f"(v));
+  hi = (__float_as_uint(v) + 0x1000u) & 0xFFFFE000u;
   lo = __float_as_uint(v - __uint_as_float(hi));
 }
 
-// store KP (8, 16, 24 or 32) A-panel values of this thread's row as (hi, lo)
-template <int KP>
+// store KP (8, 16, 24 or 32) A-panel values of this thread's row as (hi, lo); every store is aligned to its own width
+template <int KP, int ALO>
 __device__ __forceinline__ void tcs_a_store(uint32_t lane_base, const float* v) {
   uint32_t hi[KP], lo[KP];
 #pragma unroll
   for (int i = 0; i < KP; ++i) tcs_split(v[i], hi[i], lo[i]);
 #pragma unroll
-  for (int c = 0; c + 16 <= KP; c += 16) {
-    tcs_st16(lane_base + c, hi + c);
-    tcs_st16(lane_base + TCS_ALO + c, lo + c);
-  }
-  if (KP % 16 == 8) {
-    tcs_st8(lane_base + (KP - 8), hi + (KP - 8));
-    tcs_st8(lane_base + TCS_ALO + (KP - 8), lo + (KP - 8));
+  for (int c = 0; c + 16 <= KP; c += 16) tcs_st16(lane_base + c, hi + c);
+  if (KP % 16 == 8) tcs_st8(lane_base + (KP - 8), hi + (KP - 8));
+  if (ALO % 16 == 0) {
+#pragma unroll
+    for (int c = 0; c + 16 <= KP; c += 16) tcs_st16(lane_base + ALO + c, lo + c);
+    if (KP % 16 == 8) tcs_st8(lane_base + ALO + (KP - 8), lo + (KP - 8));
+  } else {  // ALO % 16 == 8: one 8-wide store brings the cursor to a 16-column boundary
+    tcs_st8(lane_base + ALO, lo);
+#pragma unroll
+    for (int c = 8; c + 16 <= KP; c += 16) tcs_st16(lane_base + ALO + c, lo + c);
+    if (KP % 16 == 0) tcs_st8(lane_base + ALO + (KP - 8), lo + (KP - 8));
   }
 }
 
 // one thread: D[128 x N] = A_hi·B_hi + A_lo·B_hi + A_hi·B_lo with A = TMEM columns [0, K) / [TCS_ALO, TCS_ALO + K), then commit
-template <int N, int K>
+template <int N, int K, int ALO, int ACC>
 __device__ __forceinline__ void tcs_issue(uint32_t tbase, uint32_t b_hi_saddr, uint64_t* bar) {
   tcs_fence_after();
   constexpr uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((128u >> 4) << 24);
@@ -147,11 +160,11 @@ __device__ __forceinline__ void tcs_issue(uint32_t tbase, uint32_t b_hi_saddr, u
   uint32_t acc = 0;
 #pragma unroll
   for (int pass = 0; pass < 3; ++pass) {
-    const uint32_t a0 = tbase + (pass == 1 ? TCS_ALO : 0);
+    const uint32_t a0 = tbase + (pass == 1 ? ALO : 0);
     const uint32_t b0 = pass == 2 ? b_lo_saddr : b_hi_saddr;
 #pragma unroll
     for (int j = 0; j < K / 8; ++j) {
-      tcs_mma(tbase + TCS_ACC, a0 + 8 * j, tcs_bdesc(b0 + j * 2 * chunk, chunk, 128), idesc, acc);
+      tcs_mma(tbase + ACC, a0 + 8 * j, tcs_bdesc(b0 + j * 2 * chunk, chunk, 128), idesc, acc);
       acc = 1;
     }
   }
@@ -168,12 +181,12 @@ struct TcCtx {
 };
 
 // All 128 threads: A-panel stores are complete → one thread issues layer (N, K) → everybody waits for its accumulator.
-template <int N, int K>
+template <int N, int K, int ALO, int ACC>
 __device__ __forceinline__ void tcs_run_layer(TcCtx& c, int w_off_floats, int tid) {
   tcs_wait_st();
   tcs_fence_before();
   __syncthreads();
-  if (tid == 0) tcs_issue<N, K>(c.tbase, c.w_saddr + (uint32_t)w_off_floats * 4u, c.bar);
+  if (tid == 0) tcs_issue<N, K, ALO, ACC>(c.tbase, c.w_saddr + (uint32_t)w_off_floats * 4u, c.bar);
   mbar_wait(c.bar, c.parity);
   c.parity ^= 1u;
   tcs_fence_after();
@@ -188,12 +201,12 @@ __device__ __forceinline__ float tcs_score_row(TcCtx& c, const float (&x)[D], in
     float a[S::K1];
 #pragma unroll
     for (int i = 0; i < S::K1; ++i) a[i] = i < D ? x[i] : (i == D ? 1.0f : 0.0f);
-    tcs_a_store<S::K1>(c.lane_base, a);
+    tcs_a_store<S::K1, S::ALO>(c.lane_base, a);
   }
-  tcs_run_layer<S::N1, S::K1>(c, S::OFF1, tid);
+  tcs_run_layer<S::N1, S::K1, S::ALO, S::ACC>(c, S::OFF1, tid);
   {  // h1 = tanh(z1) → layer 2 panel [h1(14) | 1 | 0]
     uint32_t z[16];
-    tcs_ld16(c.lane_base + TCS_ACC, z);
+    tcs_ld16(c.lane_base + S::ACC, z);
     tcs_wait_ld();
     float a[16];
 #pragma unroll
@@ -204,23 +217,23 @@ __device__ __forceinline__ float tcs_score_row(TcCtx& c, const float (&x)[D], in
     }
     a[14] = 1.0f;
     a[15] = 0.0f;
-    tcs_a_store<16>(c.lane_base, a);
+    tcs_a_store<16, S::ALO>(c.lane_base, a);
   }
-  tcs_run_layer<S::N2, S::K2>(c, S::OFF2, tid);
+  tcs_run_layer<S::N2, S::K2, S::ALO, S::ACC>(c, S::OFF2, tid);
   {  // h2 = relu(z2) → layer 3 panel [h2(7) | 1]
     uint32_t z[8];
-    tcs_ld8(c.lane_base + TCS_ACC, z);
+    tcs_ld8(c.lane_base + S::ACC, z);
     tcs_wait_ld();
     float a[8];
 #pragma unroll
     for (int i = 0; i < 7; ++i) a[i] = fmaxf(__uint_as_float(z[i]), 0.0f);
     a[7] = 1.0f;
-    tcs_a_store<8>(c.lane_base, a);
+    tcs_a_store<8, S::ALO>(c.lane_base, a);
   }
-  tcs_run_layer<S::N3, S::K3>(c, S::OFF3, tid);
+  tcs_run_layer<S::N3, S::K3, S::ALO, S::ACC>(c, S::OFF3, tid);
   {  // h3 = tanh(z3) → layer 4 panel [h3(7) | 1]
     uint32_t z[8];
-    tcs_ld8(c.lane_base + TCS_ACC, z);
+    tcs_ld8(c.lane_base + S::ACC, z);
     tcs_wait_ld();
     float a[8];
 #pragma unroll
@@ -230,16 +243,16 @@ __device__ __forceinline__ float tcs_score_row(TcCtx& c, const float (&x)[D], in
       a[2 * q + 1] = t.y;
     }
     a[7] = 1.0f;
-    tcs_a_store<8>(c.lane_base, a);
+    tcs_a_store<8, S::ALO>(c.lane_base, a);
   }
-  tcs_run_layer<S::N4, S::K4>(c, S::OFF4, tid);
+  tcs_run_layer<S::N4, S::K4, S::ALO, S::ACC4>(c, S::OFF4, tid);
   float2 se = make_float2(0.f, 0.f);
   {  // ŷ = relu(z4); squared error against x, 16 columns at a time
 #pragma unroll
     for (int c0 = 0; c0 < D; c0 += 16) {
       uint32_t z[16];
-      if (D - c0 > 8) tcs_ld16(c.lane_base + TCS_ACC + c0, z);  // the accumulator is N4 = 32 columns wide
-      else tcs_ld8(c.lane_base + TCS_ACC + c0, z);               // D = 18: columns 16..23
+      if (D - c0 > 8) tcs_ld16(c.lane_base + S::ACC4 + c0, z);  // the accumulator is N4 = 32 columns wide
+      else tcs_ld8(c.lane_base + S::ACC4 + c0, z);               // D = 18: columns 16..23
       tcs_wait_ld();
 #pragma unroll
       for (int j = 0; j < 16; j += 2) {
@@ -260,7 +273,7 @@ template <int D>
 __device__ __forceinline__ void tcs_setup(TcCtx& c, const float* __restrict__ panels, float* wsm, uint32_t* s_tmem, uint64_t* bar, int tid) {
   const int warp = tid >> 5;
   if (warp == 0) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(s_tmem)), "r"(TCS_TMEM_COLS));
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(s_tmem)), "r"(TcShape<D>::TMEM_COLS));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
   }
   if (tid == 0) {
@@ -278,9 +291,10 @@ __device__ __forceinline__ void tcs_setup(TcCtx& c, const float* __restrict__ pa
   c.bar = bar;
   c.parity = 0;
 }
+template <int D>
 __device__ __forceinline__ void tcs_teardown(TcCtx& c, int tid) {
   tcs_fence_before();
   __syncthreads();
-  if ((tid >> 5) == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(c.tbase), "r"(TCS_TMEM_COLS));
+  if ((tid >> 5) == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(c.tbase), "r"(TcShape<D>::TMEM_COLS));
 }
 #endif

@@ -42,6 +42,8 @@ struct b2_knobs {
   int avro_generic = 0;   // B2_AVRO_GENERIC  1: interpreted Avro walk even for the two known schemas
   int lstm_tc = 1;        // B2_LSTM_TC       0: FP32 FMA LSTM kernel instead of the tcgen05 one
   int score_tc = 0;       // B2_SCORE_TC      1: tcgen05 score kernel (K1t) for the pre-decoded path
+  int decode_r2 = 0;      // B2_DECODE_R2     fused Avro decode: 0 one record per lane (default), 2 / 3 two (85 / 102 registers)
+  int tc_ctas = 0;        // B2_TC_CTAS       CTAs per SM of the tcgen05 score kernels (0 = as many as TMEM allows)
 };
 
 constexpr int B2_MAX_STREAM_SLOTS = 32;

@@ -21,6 +21,9 @@
 
 constexpr int DEC_NT = 256;
 constexpr int DEC_WARPS = DEC_NT / 32;
+// two-records-per-lane kernels run as CTAs of at most 4 warps; the MINB template parameter (CTAs per SM the registers must
+// allow: 5 → at most 102 registers, 4 → 128) is a launch-time choice
+constexpr int DEC_NT_R2 = 128;
 constexpr int STAGE_CAP_MAX = 24 * 1024;  // most bytes of payload one warp stages per item (the launch normally chooses far less)
 
 enum { FMT_CSV = 0, FMT_AVRO = 1, FMT_JSON = 2 };
@@ -187,6 +190,7 @@ __device__ __forceinline__ bool csv_fast_token(const uint8_t* __restrict__ st, i
 // classification finds the field's end, so there is no separate delimiter scan); a skipped / string field is stepped over by
 // a delimiter search.  Returns B2_REC_OK, or -1 as soon as anything is not the plain grammar (quotes, blanks, '+', long tokens,
 // missing or surplus fields, an empty field without default): the caller then runs csv_record_careful on the record.
+template <int XS>
 __device__ __forceinline__ int csv_walk(const uint8_t* __restrict__ stage, int b, int e, const CsvP& c, float* __restrict__ xrow,
                                         int32_t* __restrict__ span, int rel) {
   if (c.delim < 0x2C) return -1;  // the "byte below ','" test for quotes / CR / LF below needs the delimiter above them
@@ -206,7 +210,7 @@ __device__ __forceinline__ int csv_walk(const uint8_t* __restrict__ stage, int b
         if (!c.has_default[f]) return -1;
         v = c.dflt[f];
       }
-      xrow[c.col[f]] = v;
+      xrow[c.col[f] * XS] = v;
       pos += r + 1;
     } else {
       const int beg = pos;
@@ -240,7 +244,7 @@ __device__ __forceinline__ int csv_walk(const uint8_t* __restrict__ stage, int b
 // ---- CSV, everything else: full decode_csv grammar for one record ------------------------------------------------------------
 // Delimiter scan with RFC-4180 quotes (csv_scan), then field by field through the SWAR token parser or the general one.
 __device__ __noinline__ int csv_record_careful(const uint8_t* __restrict__ stage, int b, int e, const CsvP& c, float* __restrict__ xrow,
-                                               int32_t* __restrict__ span, int rel) {
+                                               int xs, int32_t* __restrict__ span, int rel) {
   uint16_t fb[B2_MAX_FIELDS + 1];
   unsigned long long qm = 0;
   int st = csv_scan(stage, b, e, c, fb, &qm);
@@ -265,7 +269,7 @@ __device__ __noinline__ int csv_record_careful(const uint8_t* __restrict__ stage
         }
         v = __uint_as_float(bits);
       }
-      xrow[c.col[f]] = v;
+      xrow[c.col[f] * xs] = v;
     } else if (span) {
       span[2 * c.col[f]] = fbeg - rel;
       span[2 * c.col[f] + 1] = fend - rel;
@@ -365,7 +369,7 @@ __device__ __forceinline__ int avro_field(const uint8_t* __restrict__ base, int 
 // the general step above.  Fixed-size fields are not bounds-checked one by one: the walk can overshoot `e` by at most a
 // few hundred bytes, which stays inside this CTA's shared memory, and the final check rejects the record.
 __device__ __forceinline__ int avro_decode_record(const uint8_t* __restrict__ base, int p, int e, const AvroP& a, float* __restrict__ xrow,
-                                                  uint8_t* label) {
+                                                  int xs, uint8_t* label) {
   uint8_t lab_out = 2;
   p += a.skip_prefix;
   if (p > e) return B2_REC_TRUNCATED;
@@ -379,7 +383,7 @@ __device__ __forceinline__ int avro_decode_record(const uint8_t* __restrict__ ba
 #pragma unroll 4
       for (int j = 0; j < count; ++j) {
         const uint32_t w_next = wp[j + 1];
-        xrow[out0 + j] = __uint_as_float(__funnelshift_r(w_prev, w_next, sh));
+        xrow[(out0 + j) * xs] = __uint_as_float(__funnelshift_r(w_prev, w_next, sh));
         w_prev = w_next;
       }
       p += 4 * count;
@@ -391,7 +395,7 @@ __device__ __forceinline__ int avro_decode_record(const uint8_t* __restrict__ ba
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           const uint32_t u = (w4 >> (8 * q)) & 0xFFu;
-          xrow[out0 + j + q] = __int2float_rn((int)(u >> 1) ^ -(int)(u & 1u));  // tf.cast(int32 → float32), cardata-v1.py:61-66
+          xrow[(out0 + j + q) * xs] = __int2float_rn((int)(u >> 1) ^ -(int)(u & 1u));  // tf.cast(int32 → float32), cardata-v1.py:61-66
         }
         p += 4;
       }
@@ -399,11 +403,11 @@ __device__ __forceinline__ int avro_decode_record(const uint8_t* __restrict__ ba
         const uint32_t w = lds_u32_unaligned(base, p);
         const uint32_t b0 = w & 0xFFu, b1 = (w >> 8) & 0xFFu;
         if (b0 < 0x80u) {
-          xrow[out0 + j] = __int2float_rn((int)(b0 >> 1) ^ -(int)(b0 & 1u));
+          xrow[(out0 + j) * xs] = __int2float_rn((int)(b0 >> 1) ^ -(int)(b0 & 1u));
           p += 1;
         } else if (b1 < 0x80u) {
           const uint32_t u = (b0 & 0x7Fu) | (b1 << 7);
-          xrow[out0 + j] = __int2float_rn((int)(u >> 1) ^ -(int)(u & 1u));
+          xrow[(out0 + j) * xs] = __int2float_rn((int)(u >> 1) ^ -(int)(u & 1u));
           p += 2;
         } else {
           float val;
@@ -411,7 +415,7 @@ __device__ __forceinline__ int avro_decode_record(const uint8_t* __restrict__ ba
           int st = B2_REC_OK;
           p = avro_field(base, p, e, type, 0, &val, &lab, &st);
           if (p < 0) return st;
-          xrow[out0 + j] = val;
+          xrow[(out0 + j) * xs] = val;
         }
       }
     } else if (!nullable && type == AV_DOUBLE && out0 >= 0) {
@@ -419,7 +423,7 @@ __device__ __forceinline__ int avro_decode_record(const uint8_t* __restrict__ ba
       for (int j = 0; j < count; ++j) {
         const unsigned long long bits =
             (unsigned long long)lds_u32_unaligned(base, p + 8 * j) | ((unsigned long long)lds_u32_unaligned(base, p + 8 * j + 4) << 32);
-        xrow[out0 + j] = __double2float_rn(__longlong_as_double((long long)bits));
+        xrow[(out0 + j) * xs] = __double2float_rn(__longlong_as_double((long long)bits));
       }
       p += 8 * count;
     } else if (nullable == 1 && type == AV_DOUBLE && out0 >= 0) {  // ["null", "double"]: tag 0x00 = null, 0x02 = value
@@ -439,7 +443,7 @@ __device__ __forceinline__ int avro_decode_record(const uint8_t* __restrict__ ba
           p = avro_field(base, p, e, type, nullable, &val, &lab, &st);
           if (p < 0) return st;
         }
-        xrow[out0 + j] = val;
+        xrow[(out0 + j) * xs] = val;
       }
     } else {
       for (int j = 0; j < count; ++j) {
@@ -448,7 +452,7 @@ __device__ __forceinline__ int avro_decode_record(const uint8_t* __restrict__ ba
         int st = B2_REC_OK;
         p = avro_field(base, p, e, type, nullable, &val, &lab, &st);
         if (p < 0) return st;
-        if (out0 >= 0) xrow[out0 + j] = val;
+        if (out0 >= 0) xrow[(out0 + j) * xs] = val;
         else if (out0 == -2) lab_out = lab;
       }
     }
@@ -465,7 +469,7 @@ __device__ __forceinline__ int avro_decode_record(const uint8_t* __restrict__ ba
 // emitted with constant counts and columns: no loops, no descriptor reads.  A record that is not in the common shape (an int
 // of more than two bytes, a union tag other than 0/2, a long label) returns -1 and takes the generic walk; results are
 // identical by construction and checked against each other in tests/test_decode_gpu.py.
-template <int COUNT, int OUT0>
+template <int COUNT, int OUT0, int XS>
 __device__ __forceinline__ int avs_floats(const uint8_t* __restrict__ base, int p, float* __restrict__ xrow) {
   const uint32_t* wp = reinterpret_cast<const uint32_t*>(base + (p & ~3));
   const int sh = (p & 3) * 8;
@@ -473,7 +477,7 @@ __device__ __forceinline__ int avs_floats(const uint8_t* __restrict__ base, int 
 #pragma unroll
   for (int j = 0; j < COUNT; ++j) {
     const uint32_t w_next = wp[j + 1];
-    xrow[OUT0 + j] = __uint_as_float(__funnelshift_r(w_prev, w_next, sh));
+    xrow[(OUT0 + j) * XS] = __uint_as_float(__funnelshift_r(w_prev, w_next, sh));
     w_prev = w_next;
   }
   return p + 4 * COUNT;
@@ -486,13 +490,13 @@ __device__ __forceinline__ int avs_small_int(uint32_t w, float* v) {
   *v = av_zigzag_f32(one ? b0 : ((b0 & 0x7Fu) | (b1 << 7)));
   return one ? 1 : (b1 < 0x80u ? 2 : 0);
 }
-template <int COUNT, int OUT0>
+template <int COUNT, int OUT0, int XS>
 __device__ __forceinline__ int avs_ints(const uint8_t* __restrict__ base, int p, float* __restrict__ xrow) {
   if (COUNT == 4) {
     const uint32_t w4 = lds_u32_unaligned(base, p);
     if ((w4 & 0x80808080u) == 0) {  // four one-byte values (tyre pressures)
 #pragma unroll
-      for (int q = 0; q < 4; ++q) xrow[OUT0 + q] = av_zigzag_f32((w4 >> (8 * q)) & 0xFFu);
+      for (int q = 0; q < 4; ++q) xrow[(OUT0 + q) * XS] = av_zigzag_f32((w4 >> (8 * q)) & 0xFFu);
       return p + 4;
     }
   }
@@ -501,24 +505,25 @@ __device__ __forceinline__ int avs_ints(const uint8_t* __restrict__ base, int p,
     float v;
     const int used = avs_small_int(lds_u32_unaligned(base, p), &v);
     if (used == 0) return -1;
-    xrow[OUT0 + j] = v;
+    xrow[(OUT0 + j) * XS] = v;
     p += used;
   }
   return p;
 }
+template <int XS>
 __device__ __forceinline__ int avro_walk_schema_a(const uint8_t* __restrict__ base, int p, int e, int skip, float* __restrict__ xrow) {
   p += skip;
-  p = avs_floats<9, 0>(base, p, xrow);
-  p = avs_ints<4, 9>(base, p, xrow);
+  p = avs_floats<9, 0, XS>(base, p, xrow);
+  p = avs_ints<4, 9, XS>(base, p, xrow);
   if (p < 0) return -1;
-  p = avs_floats<4, 13>(base, p, xrow);
-  p = avs_ints<1, 17>(base, p, xrow);
+  p = avs_floats<4, 13, XS>(base, p, xrow);
+  p = avs_ints<1, 17, XS>(base, p, xrow);
   if (p < 0) return -1;
   return p > e ? B2_REC_TRUNCATED : B2_REC_OK;
 }
 
 // ["null", double]: tag 0x00 = null (→ 0), 0x02 = value; anything else bails out
-template <int COUNT, int OUT0>
+template <int COUNT, int OUT0, int XS>
 __device__ __forceinline__ int avs_nullable_doubles(const uint8_t* __restrict__ base, int p, float* __restrict__ xrow) {
   bool ok = true;
 #pragma unroll
@@ -532,12 +537,12 @@ __device__ __forceinline__ int avs_nullable_doubles(const uint8_t* __restrict__ 
         (unsigned long long)__funnelshift_rc(w0, w1, sh + 8) | ((unsigned long long)__funnelshift_rc(w1, w2, sh + 8) << 32);
     const float v = __double2float_rn(__longlong_as_double((long long)bits));
     ok = ok && (tag == 0u || tag == 2u);
-    xrow[OUT0 + j] = tag == 2u ? v : 0.0f;
+    xrow[(OUT0 + j) * XS] = tag == 2u ? v : 0.0f;
     p += tag == 2u ? 9 : 1;
   }
   return ok ? p : -1;
 }
-template <int COUNT, int OUT0>
+template <int COUNT, int OUT0, int XS>
 __device__ __forceinline__ int avs_nullable_ints(const uint8_t* __restrict__ base, int p, float* __restrict__ xrow) {
   bool ok = true;
 #pragma unroll
@@ -547,21 +552,22 @@ __device__ __forceinline__ int avs_nullable_ints(const uint8_t* __restrict__ bas
     float v;
     const int used = avs_small_int(w >> 8, &v);  // bytes 1..3 of the window: a one- or two-byte varint fits
     ok = ok && (tag == 0u || (tag == 2u && used != 0));
-    xrow[OUT0 + j] = tag == 2u ? v : 0.0f;
+    xrow[(OUT0 + j) * XS] = tag == 2u ? v : 0.0f;
     p += tag == 2u ? 1 + used : 1;
   }
   return ok ? p : -1;
 }
+template <int XS>
 __device__ __forceinline__ int avro_walk_schema_b(const uint8_t* __restrict__ base, int p, int e, int skip, float* __restrict__ xrow,
                                                   uint8_t* label) {
   p += skip;
-  p = avs_nullable_doubles<9, 0>(base, p, xrow);
+  p = avs_nullable_doubles<9, 0, XS>(base, p, xrow);
   if (p < 0) return -1;
-  p = avs_nullable_ints<4, 9>(base, p, xrow);
+  p = avs_nullable_ints<4, 9, XS>(base, p, xrow);
   if (p < 0) return -1;
-  p = avs_nullable_doubles<4, 13>(base, p, xrow);
+  p = avs_nullable_doubles<4, 13, XS>(base, p, xrow);
   if (p < 0) return -1;
-  p = avs_nullable_ints<1, 17>(base, p, xrow);
+  p = avs_nullable_ints<1, 17, XS>(base, p, xrow);
   if (p < 0) return -1;
   // ["null", string] label: tag, one-byte length, bytes
   const uint32_t w = lds_u32_unaligned(base, p);
@@ -588,19 +594,25 @@ __device__ __forceinline__ int avro_walk_schema_b(const uint8_t* __restrict__ ba
 
 // ---- the kernel --------------------------------------------------------------------------------------------------
 // MODE 0: decode only (runtime n_out);  MODE 1: fused decode + score for the D-14-7-7-D autoencoder.
-// Every WARP is an independent worker: it owns a byte stage, a 32-row float tile and an mbarrier in shared memory and walks
-// chunks of 32 consecutive records (chunk = global warp index, + total warps, …).  Lane i owns record i of the chunk from its
-// offsets to its results; there is no block-wide barrier anywhere, so a warp that hits slow records, a wrap of the line or
+// Every WARP is an independent worker: it owns a byte stage, a float tile and an mbarrier in shared memory and walks chunks of
+// 32·R consecutive records (chunk = global warp index, + total warps, …).  Lane i owns records i, i+32, … of the chunk from their
+// offsets to their results; there is no block-wide barrier anywhere, so a warp that hits slow records, a wrap of the line or
 // the end of its range never holds up the other warps of the SM.  Per item (the records of the chunk whose bytes fit the stage —
-// normally all 32): wait for the bulk copy, decode, then — the stage being free again — plan the next item and issue its
+// normally all of them): wait for the bulk copy, decode, then — the stage being free again — plan the next item and issue its
 // copy so that it flies under this item's score phase, then score and store.
-template <int D, int MODE, bool FT, int FMT>
-__global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ DecodeArgs<D> a) {
+// R = 2 (fused Avro): a lane decodes two records into an element-interleaved row pair and scores both in one pass over the
+// weights (ae_forward_pair): a quarter of the weight fetches per record, half the planning work per record.
+template <int D, int MODE, bool FT, int FMT, int R>
+__device__ __forceinline__ void decode_body(const DecodeArgs<D>& a) {
+  static_assert(R == 1 || (R == 2 && MODE == 1), "two records per lane only in the fused mode");
   extern __shared__ __align__(128) uint8_t smem[];
   constexpr unsigned FULL = 0xffffffffu;
+  constexpr int CH = 32 * R;  // records per chunk
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int xt_stride = MODE == 1 ? D : a.n_out;
-  // per warp: [16-byte apron | stage (stage_cap) | 16 spare | xt 32 rows | mbarrier]
+  // floats of the tile per lane: MODE 0 one row of n_out; MODE 1 R = 1 one row of D; R = 2 D + 1 interleaved pairs (the odd
+  // pair count keeps the lanes' 64-bit accesses on distinct banks)
+  const int xt_stride = MODE == 1 ? (R == 2 ? 2 * (D + 1) : D) : a.n_out;
+  // per warp: [16-byte apron | stage (stage_cap) | 16 spare | float tile | mbarrier]
   uint8_t* wbase = smem + (size_t)warp * a.warp_bytes;
   uint8_t* stage = wbase + 16;  // apron in front: the token-tail load may start up to 3 bytes before the first token
   float* xt = reinterpret_cast<float*>(wbase + 32 + a.stage_cap);
@@ -614,7 +626,7 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
   unsigned flagged = 0, n_ok = 0, n_err = 0;
   unsigned long long n_bytes = 0;
   const bool list_mode = a.list_mode != 0;
-  const long long n_chunks = list_mode ? (long long)min(a.over_list[0], B2_OVERSIZE_CAP) : (a.n + 31) / 32;
+  const long long n_chunks = list_mode ? (long long)min(a.over_list[0], B2_OVERSIZE_CAP) : (a.n + CH - 1) / CH;
   const int warps_per_cta = blockDim.x >> 5;  // the launch picks 8, 4 or 2 warps per CTA: whatever packs most warps into an SM
   const long long n_workers = (long long)gridDim.x * warps_per_cta;
 
@@ -637,35 +649,60 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
     }
   };
 
-  // cursor over this warp's chunks: lane i holds the byte range [ob, oe) of record i of the current chunk
+  // cursor over this warp's chunks: lane i holds the byte ranges [ob[s], oe[s]) of records i + 32 s of the current chunk
   long long chunk = (long long)blockIdx.x * warps_per_cta + warp - n_workers, row0 = 0;
-  int rows = 0, sub = 0, ob = 0, oe = 0;
-  // plans the next item (records [sub, sub+cnt) of the cursor's chunk), issues its bulk copy and advances the cursor
-  auto next_item = [&](long long& it_row0, int& it_sub, int& it_cnt, int& it_b, int& it_e) -> bool {
+  int rows = 0, sub = 0, ob[R], oe[R];
+#pragma unroll
+  for (int s = 0; s < R; ++s) ob[s] = oe[s] = 0;
+  // record index q (0 .. CH-1) of the chunk → value held by lane q & 31 in slot q >> 5
+  auto pick = [&](const int (&v)[R], int q) -> int {
+    int r = __shfl_sync(FULL, v[0], q & 31);
+    if (R == 2) {
+      const int r1 = __shfl_sync(FULL, v[R - 1], q & 31);
+      if (q >= 32) r = r1;
+    }
+    return r;
+  };
+  // plans the next item (records [sub, sub+cnt) of the cursor's chunk), issues its bulk copy and advances the cursor;
+  // it_b / it_e receive the lane's stage offsets of its records
+  auto next_item = [&](long long& it_row0, int& it_sub, int& it_cnt, int (&it_b)[R], int (&it_e)[R]) -> bool {
     for (;;) {
       if (sub >= rows) {
         chunk += n_workers;
         if (chunk >= n_chunks) return false;
-        row0 = list_mode ? (long long)a.over_list[1 + chunk] : chunk * 32;
-        rows = list_mode ? 1 : (int)min(32ll, a.n - row0);
+        row0 = list_mode ? (long long)a.over_list[1 + chunk] : chunk * CH;
+        rows = list_mode ? 1 : (int)min((long long)CH, a.n - row0);
         sub = 0;
-        const int o = a.offs[row0 + min(lane, rows)];
-        ob = o;
-        oe = __shfl_down_sync(FULL, o, 1);
-        if (lane == 31 && rows == 32) oe = a.offs[row0 + 32];
+#pragma unroll
+        for (int s = 0; s < R; ++s) ob[s] = a.offs[row0 + min(lane + 32 * s, rows)];
+#pragma unroll
+        for (int s = 0; s < R; ++s) {
+          oe[s] = __shfl_down_sync(FULL, ob[s], 1);  // lane 31 keeps its own value here
+          if (s + 1 < R) {
+            const int wrap = __shfl_sync(FULL, ob[s + 1 < R ? s + 1 : s], 0);
+            if (lane == 31) oe[s] = wrap;
+          }
+        }
+        // end of the chunk's last possible record (a record that does not exist has ob == oe == end of the chunk)
+        if (lane == 31) oe[R - 1] = a.offs[row0 + rows];
       }
-      const int b_abs = __shfl_sync(FULL, ob, sub);
+      const int b_abs = pick(ob, sub);
       const uintptr_t p0 = reinterpret_cast<uintptr_t>(a.bytes) + (uintptr_t)(long long)b_abs;
       const uintptr_t a0 = p0 & ~(uintptr_t)15;
       const int lead = (int)(p0 - a0);
-      const bool fit = lane >= sub && lane < rows && (long long)oe - b_abs + lead <= (long long)a.stage_cap;
-      const int cnt = __popc(__ballot_sync(FULL, fit));  // record ends are monotone: the records that fit are sub .. sub+cnt-1
+      int cnt = 0;
+#pragma unroll
+      for (int s = 0; s < R; ++s) {
+        const int q = lane + 32 * s;
+        const bool fit = q >= sub && q < rows && (long long)oe[s] - b_abs + lead <= (long long)a.stage_cap;
+        cnt += __popc(__ballot_sync(FULL, fit));  // record ends are monotone: the records that fit are sub .. sub+cnt-1
+      }
       if (cnt == 0) {
         if (lane == 0) oversize(row0 + sub);
         sub += 1;
         continue;
       }
-      const int e_abs = __shfl_sync(FULL, oe, sub + cnt - 1);
+      const int e_abs = pick(oe, sub + cnt - 1);
       if (lane == 0) {
         const uint32_t nbytes = (uint32_t)(((e_abs - b_abs + lead) + 15) & ~15);
         mbar_expect_tx(full, nbytes);
@@ -676,64 +713,93 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
       it_row0 = row0;
       it_sub = sub;
       it_cnt = cnt;
-      it_b = ob + rel;
-      it_e = oe + rel;
+#pragma unroll
+      for (int s = 0; s < R; ++s) {
+        it_b[s] = ob[s] + rel;
+        it_e[s] = oe[s] + rel;
+      }
       sub += cnt;
       return true;
     }
   };
 
   long long c_row0 = 0, n_row0 = 0;
-  int c_sub = 0, c_cnt = 0, c_b = 0, c_e = 0, n_sub = 0, n_cnt = 0, n_b = 0, n_e = 0;
+  int c_sub = 0, c_cnt = 0, c_b[R], c_e[R], n_sub = 0, n_cnt = 0, n_b[R], n_e[R];
   bool have = next_item(c_row0, c_sub, c_cnt, c_b, c_e);
+  float* const xlane = xt + (size_t)lane * xt_stride;
   while (have) {
     mbar_wait(full, phase);
     phase ^= 1u;
-    const bool active = lane >= c_sub && lane < c_sub + c_cnt;
-    const long long gr = c_row0 + lane;
-    float* xrow = xt + (size_t)lane * xt_stride;
-    int st = B2_REC_OK;
-    uint8_t lab = 2;
-    if (active) {
-      if (FMT == FMT_CSV) {
-        int32_t* sp = (MODE == 0 && a.span) ? a.span + gr * a.csv.n_str * 2 : nullptr;
-        const int rel = c_b - ob;  // stage offset minus absolute offset (the cursor still sits on this item's chunk)
-        st = csv_walk(stage, c_b, c_e, a.csv, xrow, sp, rel);
-        if (st < 0) st = csv_record_careful(stage, c_b, c_e, a.csv, xrow, sp, rel);
-      } else if (FMT == FMT_JSON) {
-        for (int j = 0; j < xt_stride; ++j) xrow[j] = 0.0f;  // members that are absent or null
-        st = b2_json_record_auto(stage, c_b, c_e, a.json, xrow, &lab);
-      } else {
-        if (!a.avro.all_routed)
-          for (int j = 0; j < xt_stride; ++j) xrow[j] = 0.0f;  // columns no field routes to
-        st = -1;
-        if (a.avro.known == 1) st = avro_walk_schema_a(stage, c_b, c_e, a.avro.skip_prefix, xrow);
-        else if (a.avro.known == 2) st = avro_walk_schema_b(stage, c_b, c_e, a.avro.skip_prefix, xrow, &lab);
-        if (st < 0) {
-          lab = 2;
-          st = avro_decode_record(stage, c_b, c_e, a.avro, xrow, &lab);
+    int st[R];
+    uint8_t lab[R];
+    bool active[R];
+#pragma unroll
+    for (int s = 0; s < R; ++s) {
+      const int q = lane + 32 * s;
+      active[s] = q >= c_sub && q < c_sub + c_cnt;
+      st[s] = B2_REC_OK;
+      lab[s] = 2;
+      float* xrow = xlane + s;  // element j of this record sits at xrow[j * R]
+      if (active[s]) {
+        const long long gr = c_row0 + q;
+        if (FMT == FMT_CSV) {
+          int32_t* sp = (MODE == 0 && a.span) ? a.span + gr * a.csv.n_str * 2 : nullptr;
+          const int rel = c_b[s] - ob[s];  // stage offset minus absolute offset (the cursor still sits on this item's chunk)
+          st[s] = csv_walk<R>(stage, c_b[s], c_e[s], a.csv, xrow, sp, rel);
+          if (st[s] < 0) st[s] = csv_record_careful(stage, c_b[s], c_e[s], a.csv, xrow, R, sp, rel);
+        } else if (FMT == FMT_JSON) {
+          for (int j = 0; j < xt_stride; ++j) xrow[j] = 0.0f;  // members that are absent or null
+          st[s] = b2_json_record_auto(stage, c_b[s], c_e[s], a.json, xrow, &lab[s]);
+        } else {
+          if (!a.avro.all_routed)
+            for (int j = 0; j < (MODE == 1 ? D : a.n_out); ++j) xrow[j * R] = 0.0f;  // columns no field routes to
+          st[s] = -1;
+          if (a.avro.known == 1) st[s] = avro_walk_schema_a<R>(stage, c_b[s], c_e[s], a.avro.skip_prefix, xrow);
+          else if (a.avro.known == 2) st[s] = avro_walk_schema_b<R>(stage, c_b[s], c_e[s], a.avro.skip_prefix, xrow, &lab[s]);
+          if (st[s] < 0) {
+            lab[s] = 2;
+            st[s] = avro_decode_record(stage, c_b[s], c_e[s], a.avro, xrow, R, &lab[s]);
+          }
         }
       }
     }
     __syncwarp();  // every lane is done with the stage
     have = next_item(n_row0, n_sub, n_cnt, n_b, n_e);
     if (MODE == 1) {
-      if (active) {
-        float* const rowp[1] = {xrow};
-        float mm[1] = {0.f};
-        if (a.has_norm) ae_forward_rows<D, 1, true, false, FT>(a.w, a.nm, rowp, mm);
-        else ae_forward_rows<D, 1, false, false, FT>(a.w, a.nm, rowp, mm);
-        float m = mm[0];
-        if (st != B2_REC_OK) m = __int_as_float(0x7FC00000);
-        const bool f = m > a.threshold;
-        if (a.mse) a.mse[gr] = m;
-        if (a.flag) a.flag[gr] = f ? 1 : 0;
-        if (a.status) a.status[gr] = st;
-        if (a.label) a.label[gr] = FMT != FMT_CSV && st == B2_REC_OK ? lab : 2;
-        flagged += f;
-        n_ok += st == B2_REC_OK;
-        n_err += st != B2_REC_OK;
+      float mm[R];
+      if (R == 2) {
+        if (active[0] || active[R - 1]) {
+          float2* rowp = reinterpret_cast<float2*>(xlane);
+          float m2[2] = {0.f, 0.f};
+          if (a.has_norm) ae_forward_pair<D, true, FT>(a.w, a.nm, rowp, m2);
+          else ae_forward_pair<D, false, FT>(a.w, a.nm, rowp, m2);
+          mm[0] = m2[0];
+          mm[R - 1] = m2[1];
+        }
+      } else if (active[0]) {
+        float* const rowp[1] = {xlane};
+        float m1[1] = {0.f};
+        if (a.has_norm) ae_forward_rows<D, 1, true, false, FT>(a.w, a.nm, rowp, m1);
+        else ae_forward_rows<D, 1, false, false, FT>(a.w, a.nm, rowp, m1);
+        mm[0] = m1[0];
       }
+#pragma unroll
+      for (int s = 0; s < R; ++s) {
+        if (active[s]) {
+          const long long gr = c_row0 + lane + 32 * s;
+          float m = mm[s];
+          if (st[s] != B2_REC_OK) m = __int_as_float(0x7FC00000);
+          const bool f = m > a.threshold;
+          if (a.mse) a.mse[gr] = m;
+          if (a.flag) a.flag[gr] = f ? 1 : 0;
+          if (a.status) a.status[gr] = st[s];
+          if (a.label) a.label[gr] = FMT != FMT_CSV && st[s] == B2_REC_OK ? lab[s] : 2;
+          flagged += f;
+          n_ok += st[s] == B2_REC_OK;
+          n_err += st[s] != B2_REC_OK;
+        }
+      }
+      if (R == 2) __syncwarp();  // the tile is rewritten by the next item's decode (a lane only touches its own pairs, but keep the warp converged)
     } else {
       // coalesced write-out of the item's rows (they are contiguous in xt); a bad record's row becomes NaN
       const int total = c_cnt * xt_stride;
@@ -742,18 +808,21 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
       for (int i0 = 0; i0 < total; i0 += 32) {
         const int i = i0 + lane;
         const int r = min(i, total - 1) / xt_stride;
-        const int st_r = __shfl_sync(FULL, st, c_sub + r);
+        const int st_r = __shfl_sync(FULL, st[0], c_sub + r);
         if (i < total) dst[i] = st_r == B2_REC_OK ? src[i] : __int_as_float(0x7FC00000);
       }
-      if (active) {
-        if (a.status) a.status[gr] = st;
-        if (a.label) a.label[gr] = FMT != FMT_CSV && st == B2_REC_OK ? lab : 2;
-        n_ok += st == B2_REC_OK;
-        n_err += st != B2_REC_OK;
+      if (active[0]) {
+        const long long gr = c_row0 + lane;
+        if (a.status) a.status[gr] = st[0];
+        if (a.label) a.label[gr] = FMT != FMT_CSV && st[0] == B2_REC_OK ? lab[0] : 2;
+        n_ok += st[0] == B2_REC_OK;
+        n_err += st[0] != B2_REC_OK;
       }
       __syncwarp();  // xt is rewritten by the next item's decode
     }
-    c_row0 = n_row0, c_sub = n_sub, c_cnt = n_cnt, c_b = n_b, c_e = n_e;
+    c_row0 = n_row0, c_sub = n_sub, c_cnt = n_cnt;
+#pragma unroll
+    for (int s = 0; s < R; ++s) c_b[s] = n_b[s], c_e[s] = n_e[s];
   }
   if (a.counters) {
 #pragma unroll
@@ -777,6 +846,27 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
     if (tid == 0) a.over_list[0] = 0;
   }
 }
+
+// One record per lane: CTAs of up to 8 warps, registers left to ptxas (64: four CTAs per SM).  Two records per lane: CTAs of up
+// to 4 warps, MINB of them per SM bound the registers (6 → 85, 5 → 102).
+template <int D, int MODE, bool FT, int FMT, int R, int MINB>
+struct DecodeKernel;
+template <int D, int MODE, bool FT, int FMT>
+__global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ DecodeArgs<D> a) {
+  decode_body<D, MODE, FT, FMT, 1>(a);
+}
+template <int D, int MODE, bool FT, int FMT, int MINB>
+__global__ void __launch_bounds__(DEC_NT_R2, MINB) decode_kernel_r2(const __grid_constant__ DecodeArgs<D> a) {
+  decode_body<D, MODE, FT, FMT, (MODE == 1 ? 2 : 1)>(a);
+}
+template <int D, int MODE, bool FT, int FMT, int MINB>
+struct DecodeKernel<D, MODE, FT, FMT, 1, MINB> {
+  static auto get() { return decode_kernel<D, MODE, FT, FMT>; }
+};
+template <int D, int MODE, bool FT, int FMT, int MINB>
+struct DecodeKernel<D, MODE, FT, FMT, 2, MINB> {
+  static auto get() { return decode_kernel_r2<D, MODE, FT, FMT, MINB>; }
+};
 
 // ---- host side ----------------------------------------------------------------------------------------------------
 static int fill_csv(const b2_csv_spec* s, CsvP& c) {
@@ -861,14 +951,14 @@ static int align16i(int v) { return (v + 15) & ~15; }
 // Bytes one warp stages per item.  Avro without strings: 32 records of the schema's maximum size.  Otherwise an estimate of 32
 // typical records (a chunk whose bytes do not fit is simply split into several items, at the price of idle lanes):
 // `hint` = the caller's average record size if known, else ~10 bytes per CSV field / the fixed part + 16 bytes per Avro string.
-static int choose_stage_cap(int fmt, const CsvP& csv, const AvroP& avro, const JsonP& json, int hint) {
+static int choose_stage_cap(int fmt, const CsvP& csv, const AvroP& avro, const JsonP& json, int hint, int ch /* records per chunk */) {
   int per_rec;
   if (fmt == FMT_JSON) {
     per_rec = 2;
     for (int k = 0; k < json.n_keys; ++k) per_rec += json.len[k] + 14;  // "name":value,
   } else if (fmt == FMT_AVRO) {
     const int mx = avro_max_record_bytes(avro);
-    if (mx > 0) return min(STAGE_CAP_MAX, align16i(mx * 32 + 32));
+    if (mx > 0) return min(STAGE_CAP_MAX, align16i(mx * ch + 32));
     per_rec = avro.skip_prefix;
     for (int i = 0; i < avro.n_fields; ++i) {
       per_rec += avro.f[i].nullable ? 1 : 0;
@@ -887,22 +977,22 @@ static int choose_stage_cap(int fmt, const CsvP& csv, const AvroP& avro, const J
   }
   if (hint > 0) per_rec = hint;
   // a known average gets 6 % head-room (32 records rarely sum to more), an estimate none: the stage also sets how many CTAs fit
-  return max(2048, min(STAGE_CAP_MAX, align16i(per_rec * 32 + (hint > 0 ? per_rec * 2 : 0) + 48)));
+  return max(2048, min(STAGE_CAP_MAX, align16i(per_rec * ch + (hint > 0 ? per_rec * (ch / 16) : 0) + 48)));
 }
 
-template <int D, int MODE, bool FT, int FMT>
-static int launch_decode_fmt(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stream) {
-  const int xt_stride = MODE == 1 ? D : args.n_out;
-  args.stage_cap = choose_stage_cap(args.fmt, args.csv, args.avro, args.json, ctx->record_bytes_hint);
+template <int D, int MODE, bool FT, int FMT, int R, int MINB>
+static int launch_decode_r(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stream) {
+  const int xt_stride = MODE == 1 ? (R == 2 ? 2 * (D + 1) : D) : args.n_out;
+  args.stage_cap = choose_stage_cap(args.fmt, args.csv, args.avro, args.json, ctx->record_bytes_hint, 32 * R);
   args.warp_bytes = 16 + args.stage_cap + 16 + align16i(32 * xt_stride * 4) + 16;
-  auto kern = decode_kernel<D, MODE, FT, FMT>;
+  auto kern = DecodeKernel<D, MODE, FT, FMT, R, MINB>::get();
   // no block-wide synchronisation in the kernel, so the CTA size is free: take the one that packs most warps into an SM.
   // The choice depends only on (instantiation, device, bytes per warp): remembered, a launch is then one driver call.
   struct Cfg {
     int device, warp_bytes, threads, occ;
   };
   static thread_local Cfg cached = {-1, 0, 0, 0};
-  int threads = DEC_NT, occ = 0;
+  int threads = R == 2 ? DEC_NT_R2 : DEC_NT, occ = 0;
   if (cached.device == ctx->device && cached.warp_bytes == args.warp_bytes) {
     threads = cached.threads;
     occ = cached.occ;
@@ -911,7 +1001,7 @@ static int launch_decode_fmt(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stre
     B2_REQUIRE((size_t)args.warp_bytes * 2 <= (size_t)ctx->smem_optin, "decode: a warp's stage needs %d bytes of shared memory (max %d per CTA)",
                args.warp_bytes, ctx->smem_optin / 2);
     B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->smem_optin));
-    for (int w = DEC_WARPS; w >= 2; w >>= 1) {
+    for (int w = (R == 2 ? DEC_NT_R2 / 32 : DEC_WARPS); w >= 2; w >>= 1) {
       const size_t sm = (size_t)args.warp_bytes * w;
       if (sm > (size_t)ctx->smem_optin) continue;
       int o = 0;
@@ -923,7 +1013,7 @@ static int launch_decode_fmt(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stre
   const size_t smem = (size_t)args.warp_bytes * (threads / 32);
   B2_REQUIRE(occ >= 1, "decode: kernel does not fit on an SM");
   const int wpc = threads / 32;
-  const long long n_chunks = (args.n + 31) / 32;
+  const long long n_chunks = (args.n + 32 * R - 1) / (32 * R);
   long long grid = (long long)ctx->sm_count * occ;
   const long long need = (n_chunks + wpc - 1) / wpc;
   if (grid > need) grid = need;
@@ -948,6 +1038,22 @@ static int launch_decode_fmt(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stre
     B2_CUDA(cudaGetLastError());
   }
   return B2_OK;
+}
+
+// Records per lane and item.  Default: ONE.  Two records per lane (row-packed FFMA2, ae_forward_pair) were built to cut the weight
+// fetches — 12.5 % fewer executed instructions on Avro-A — and measured SLOWER on B200 (2.3e10 vs 2.6e10 records/s): the loop body
+// no longer fits the instruction cache (ncu: no_instruction becomes the top stall, issue slots 52 % busy at 19 warps/SM;
+// profiles/round2_notes.md).  The variant stays selectable for fused Avro (results are bit-identical, tests compare them):
+// context option "decode_r2" = 2 (registers capped at 85: 6 CTAs of 4 warps per SM) or 3 (102 registers, 5 CTAs); 0 / -1 = one.
+template <int D, int MODE, bool FT, int FMT>
+static int launch_decode_fmt(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stream) {
+  if (MODE == 1 && FMT == FMT_AVRO) {
+    constexpr int R2 = (MODE == 1 && FMT == FMT_AVRO) ? 2 : 1;  // keeps the other instantiations free of R = 2 code
+    const int k = ctx->knobs.decode_r2;
+    if (k == 3) return launch_decode_r<D, MODE, FT, FMT, R2, 5>(ctx, args, stream);
+    if (k == 2) return launch_decode_r<D, MODE, FT, FMT, R2, 6>(ctx, args, stream);
+  }
+  return launch_decode_r<D, MODE, FT, FMT, 1, 1>(ctx, args, stream);
 }
 
 // the record format is a template parameter: each instantiation carries only its own decoder (fewer registers, smaller code)

@@ -104,8 +104,8 @@ int  b2_ae_score(b2_ae* ae, const float* x_dev, int64_t n, const b2_norm* norm, 
 /* normalize_fn as a stand-alone operator (cardata-v1.py:40-131; LSTM-TensorFlow-IO-Kafka/cardata-v1.py:53-143):
  * out[r][j] = (x[r][j] - lo[j]) / range[j] * 2.0 - 1.0 (B2_NORM_SCALE), 0.0 (B2_NORM_ZERO) or x[r][j], x_dev / out_dev f32[n, d]
  * row-major, in binary32 with the reference's operation order — the device function the fused kernels apply, bit-identical
- * to an IEEE division for every input as long as range[j] and 1 / range[j] are both normal float32 numbers
- * (1.2e-38 < |range| < 8.5e37; the reference's table uses 1 … 7500).  b2_selftest_normalize proves that on the device: for every float32 bit pattern in
+ * to an IEEE division for every input as long as 2^-64 <= |range[j]| <= 2^64 (the reference's table uses 1 … 7500; outside
+ * that span the correction step's residual can leave the normal range and the last bit may differ).  b2_selftest_normalize proves that on the device: for every float32 bit pattern in
  * [first_bits, first_bits + count) and every feature of the table it compares that function with sub → IEEE div → fma and
  * adds the number of differences to out_dev[0] (u64[2], zeroed by the caller; [1] = feature << 32 | bits of one of them). */
 int  b2_normalize(b2_ctx* ctx, const float* x_dev, int64_t n, int d, const b2_norm* norm, float* out_dev, void* stream);

@@ -341,3 +341,37 @@ def test_full_size_decode_score_properties(cuda_device, fmt):
     ref = orc.score(xs, m.get_flat_weights(), [18, 14, 7, 7, 18], ACTS, norm=schemas.norm_arrays(), dtype=np.float64)[0]
     got = mse.cpu().numpy()[idx].astype(np.float64)
     assert (np.abs(got - ref) <= np.maximum(1e-5 * ref, 1e-7)).all()
+
+
+@pytest.mark.parametrize("fmt", ["avro_a", "avro_b"])
+def test_two_records_per_lane_variant_is_bit_identical(cuda_device, fmt):
+    """The row-packed two-records-per-lane form of the fused Avro kernel (context option decode_r2 = 2 / 3; not the default: it is
+    slower on B200) must give the same bits as one record per lane — values, flags, labels, statuses, counters — on ragged
+    batches with damaged records."""
+    x = synth.sensor_rows(70_001, seed=33)
+    x[::97, 9] = 20000.0
+    if fmt == "avro_a":
+        data, offs = synth.avro_a_batch(x)
+        sch = schemas.schema_a_json()
+    else:
+        data, offs, _ = synth.avro_b_batch(x, null_frac=0.02, seed=5, label_probs=(0.9, 0.05, 0.05))
+        sch = schemas.schema_b_json()
+    data, offs, bad = synth.corrupt_batch(data, offs, fmt, 1e-3, seed=9)
+    m = _model18()
+    res = {}
+    try:
+        for mode in (0, 2, 3):
+            bs.keras.set_option("decode_r2", mode)
+            for n in (70_001, 63, 64, 65, 1):
+                rb = dec.RecordBatch(data[: offs[n]], offs[: n + 1], skip_prefix=5)
+                cnt = torch.zeros(4, dtype=torch.int64, device="cuda")
+                mse, flag, label, status = dec.decode_score(m, rb, avro_schema=sch, counters=cnt)
+                res[(mode, n)] = (_bits(mse.cpu().numpy()), flag.cpu().numpy(), label.cpu().numpy(), status.cpu().numpy(), cnt.cpu().tolist())
+    finally:
+        bs.keras.set_option("decode_r2", 0)
+    assert (res[(0, 70_001)][3] != 0).sum() == len(bad)
+    for mode in (2, 3):
+        for n in (70_001, 63, 64, 65, 1):
+            for a, b in zip(res[(0, n)][:4], res[(mode, n)][:4]):
+                np.testing.assert_array_equal(a, b)
+            assert res[(0, n)][4] == res[(mode, n)][4]

@@ -50,12 +50,12 @@ def test_normalize_odd_width_and_identity(cuda_device):
 
 def test_division_free_form_equals_ieee_division_for_every_float32(cuda_device):
     """All 2^32 bit patterns x all 18 features of the reference's table, plus a table of awkward ranges (tiny, huge, non
-    power-of-two, reciprocal inexact; all inside the documented domain: range and 1/range are normal float32 numbers): zero
+    power-of-two, reciprocal inexact; all inside the documented domain 2^-64 <= |range| <= 2^64): zero
     differences between norm_pair_fast and sub -> IEEE div -> fma on the device."""
     l, ctx = _ffi.lib(), bs.keras.get_ctx(0)
     tables = [bs.schemas.norm_arrays(),
-              (np.full(8, 2, np.int32), np.array([0, -1e30, 3, 1e-30, 0.1, -7, 123456.7, 0], np.float32),
-               np.array([3.0, 1e30, 1e-30, 2e-38, 0.7, 1.0000001, 3.3333333e7, 8e37], np.float32))]
+              (np.full(8, 2, np.int32), np.array([0, -1e18, 3, 1e-18, 0.1, -7, 123456.7, 0], np.float32),
+               np.array([3.0, 1e18, 1e-18, 3e-18, 0.7, 1.0000001, 3.3333333e7, 1.8e19], np.float32))]
     for kind, lo, rng in tables:
         nm = _ffi.make_norm(kind, lo, rng)
         out = torch.zeros(2, dtype=torch.int64, device="cuda")

@@ -43,8 +43,8 @@ def test_csv_one_8kb_record_among_100_byte_records(cuda_device, where):
     lines2[other] = huge
     rb = dec.RecordBatch.from_messages(lines2)
     kinds = [0, 0] + [1] * 18
-    out, status = dec.decode_csv_matrix(rb, kinds, raise_on_error=False)[:2]
-    ref, _ = dec.decode_csv_matrix(dec.RecordBatch.from_messages(lines), kinds)[:2]
+    out, _, status = dec.decode_csv_matrix(rb, kinds, raise_on_error=False)
+    ref = dec.decode_csv_matrix(dec.RecordBatch.from_messages(lines), kinds)[0]
     st = status.cpu().numpy()
     assert st[where] == 0 and st[other] == 7 and (np.delete(st, other) == 0).all()
     keep = np.arange(10_000) != other
@@ -59,7 +59,7 @@ def test_csv_one_8kb_record_among_100_byte_records(cuda_device, where):
     assert torch.equal(mse[k], mse_ref[k]) and bool(torch.isnan(mse[other]))
     assert st2.cpu().numpy()[other] == 7 and cnt.cpu().tolist()[:3] == [9_999, int(flag.sum()), 1]
     # and again on the same stream: the retry list was left empty
-    out2, status2 = dec.decode_csv_matrix(rb, kinds, raise_on_error=False)[:2]
+    out2, _, status2 = dec.decode_csv_matrix(rb, kinds, raise_on_error=False)
     assert torch.equal(status2, status) and torch.equal(torch.nan_to_num(out2), torch.nan_to_num(out))
 
 
@@ -97,5 +97,5 @@ def test_many_oversize_records_and_every_stream_gets_its_own_list(cuda_device):
         with torch.cuda.stream(s):
             outs.append(dec.decode_csv_matrix(rb, kinds, raise_on_error=False))
     torch.cuda.synchronize()
-    for out, status in (o[:2] for o in outs):
+    for out, _, status in outs:
         assert not status.any() and torch.equal(out, ref)
