@@ -111,6 +111,9 @@ _PROTOTYPES = {
     "b2_lstm_destroy": (None, [_P]),
     "b2_lstm_param_count": (C.c_int, [_P]),
     "b2_lstm_forward": (C.c_int, [_P, _P, C.c_int64, C.c_int, _P, _P]),
+    "b2_lstm_fit_scratch_bytes": (C.c_int64, [C.POINTER(LstmDesc), C.c_int, C.c_int]),
+    "b2_lstm_fit_steps": (C.c_int, [_P, C.POINTER(LstmDesc), _P, _P, _P, _P, C.c_int64, _P, C.c_int64, C.c_int64, C.c_int, C.c_int,
+                                    C.POINTER(Adam), _P, _P, _P, C.c_int64, _P]),
     "b2_format_rows_bound": (C.c_int64, [C.c_int]),
     "b2_format_rows": (C.c_int, [_P, _P, C.c_int64, C.c_int, C.c_int, _P, C.c_int64, _P, _P, _P, _P]),
     "b2_kafka_index_records": (C.c_int, [_P, _P, C.c_int64, _P, _P, C.c_int64, C.c_int, _P, _P, _P, _P]),

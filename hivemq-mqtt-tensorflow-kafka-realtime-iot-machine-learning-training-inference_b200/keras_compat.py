@@ -562,10 +562,10 @@ class Model:
         ``batch_size`` = per-rank batch), run the grid-wide gradient kernel, ONE all-reduce of the P+3 floats and the Adam
         kernel per step."""
         self._ensure_built()
-        if self.kind != "dense":
-            raise NotImplementedError("fit is implemented for the Dense autoencoder (LSTM training is out of scope, SURVEY §8f.4)")
         if not self._compiled:
             raise RuntimeError("You must compile your model before training/testing. Use `model.compile(optimizer, loss)`.")
+        if self.kind != "dense":
+            return self._fit_lstm(x, y, epochs, batch_size, shuffle, verbose, callbacks, seed)
         if y is not None and y is not x:
             if np.shape(y) != np.shape(x) or not np.array_equal(np.asarray(y), np.asarray(x)):
                 raise NotImplementedError("autoencoder training only: y must be x")
@@ -613,6 +613,91 @@ class Model:
             for cb in callbacks or []:
                 cb.on_epoch_end(ep, logs)
         self._adam["iter"] = int(adam.iter)
+        self.history = hist
+        return hist
+
+    def _fit_lstm(self, x, y, epochs, batch_size, shuffle, verbose, callbacks, seed):
+        """``model.fit(zip((dataset_x, dataset_y)).batch(batch_size), epochs=…)`` of the LSTM script (LSTM-…/cardata-v1.py:191-194):
+        back-propagation through time + Adam, every step of an epoch inside one launch (``b2_lstm_fit_steps``).
+
+        ``x``: ``[N, T, F]`` array / tensor with targets ``y`` of the same shape (``[N, F]`` is accepted for ``T == 1``), or a
+        :class:`Windows` view with ``look_back == 1`` and ``y=None`` — then the targets are the script's ``dataset.skip(look_back)``
+        and both are read in place from the row stream.  Batches are consecutive (a ``tf.data`` pipeline is not shuffled by
+        ``fit``); ``shuffle=True`` permutes the sequences per epoch."""
+        dev = torch.device("cuda", self._device_index())
+        F, T = self.features, None
+        if isinstance(x, Windows):
+            if y is not None:
+                raise ValueError("Windows input brings its own targets (dataset.skip(look_back)); pass y=None")
+            if x.look_back != 1:
+                raise NotImplementedError("training on sliding windows is implemented for look_back = 1 (the reference's setting); "
+                                          "pass materialised [N, T, F] inputs and targets for longer windows")
+            rows = _to_device_f32(x.rows, dev)
+            n = min(len(x), max(int(rows.shape[0]) - 1, 0))  # Dataset.zip stops at the shorter side (Windows.targets())
+            T = 1
+            xd, yd = rows, rows[1:]
+            xs, ys = x.shift, 1  # window i starts at row i * shift; target i is row 1 + i (dataset.skip(look_back))
+        else:
+            xd = _to_device_f32(x, dev)
+            if xd.dim() != 3 or xd.shape[2] != F:
+                raise ValueError(f"expected input of shape (N, T, {F}), got {tuple(xd.shape)}")
+            n, T = int(xd.shape[0]), int(xd.shape[1])
+            if y is None:
+                raise ValueError("LSTM training needs targets y")
+            yd = _to_device_f32(y, dev)
+            if yd.dim() == 2 and T == 1:
+                yd = yd[:, None, :]
+            if tuple(yd.shape) != tuple(xd.shape):
+                raise ValueError(f"targets must have the model's output shape {tuple(xd.shape)}, got {tuple(yd.shape)}")
+            xs = ys = T
+        if n < 1:
+            raise ValueError("no training sequences")
+        l = _ffi.lib()
+        d = _ffi.LstmDesc()
+        d.features = F
+        for i, u in enumerate(self.units):
+            d.units[i] = u
+        P = self.n_params
+        w = torch.from_numpy(self.get_flat_weights().copy()).to(dev)
+        st = getattr(self, "_lstm_adam", None)
+        if st is None or st[0].numel() != P or st[0].device != dev:
+            st = self._lstm_adam = (torch.zeros(P, dtype=torch.float32, device=dev), torch.zeros(P, dtype=torch.float32, device=dev))
+        m, v = st
+        batch_size = int(batch_size)
+        steps = (n + batch_size - 1) // batch_size
+        sb = int(l.b2_lstm_fit_scratch_bytes(C.byref(d), T, min(batch_size, n)))
+        scratch = torch.empty(sb, dtype=torch.uint8, device=dev)
+        loss_d = torch.empty(steps, dtype=torch.float32, device=dev)
+        acc_d = torch.empty(steps, dtype=torch.float32, device=dev)
+        adam = _ffi.Adam(self._adam["lr"], self._adam["beta1"], self._adam["beta2"], self._adam["eps"], self._adam["iter"])
+        hist = History()
+        hist.history = {"loss": [], "accuracy": []} if "accuracy" in getattr(self, "_metrics", []) else {"loss": []}
+        g = np.random.Generator(np.random.PCG64(self._seed if seed is None else seed))
+        sizes = np.full(steps, batch_size, dtype=np.float64)
+        sizes[-1] = n - batch_size * (steps - 1)
+        for ep in range(epochs):
+            xe, ye, xse, yse = xd, yd, xs, ys
+            if shuffle:
+                perm = torch.from_numpy(g.permutation(n)).to(dev)
+                if isinstance(x, Windows):
+                    xe, ye, xse, yse = xd[perm * xs].contiguous(), yd[perm * ys].contiguous(), 1, 1
+                else:
+                    xe, ye = xd[perm].contiguous(), yd[perm].contiguous()
+            _ffi.check(l.b2_lstm_fit_steps(get_ctx(dev.index), C.byref(d), _ffi.ptr(w), _ffi.ptr(m), _ffi.ptr(v), _ffi.ptr(xe), xse,
+                                           _ffi.ptr(ye), yse, n, T, min(batch_size, n), C.byref(adam), _ffi.ptr(loss_d), _ffi.ptr(acc_d),
+                                           _ffi.ptr(scratch), sb, _stream_ptr()), "b2_lstm_fit_steps")
+            lo = loss_d.cpu().numpy().astype(np.float64)
+            logs = {"loss": float((lo * sizes).sum() / n)}
+            if "accuracy" in hist.history:
+                logs["accuracy"] = float((acc_d.cpu().numpy().astype(np.float64) * sizes).sum() / n)
+            for k, val in logs.items():
+                hist.history.setdefault(k, []).append(val)
+            if verbose:
+                print(f"Epoch {ep + 1}/{epochs} - " + " - ".join(f"{k}: {val:.4f}" for k, val in logs.items()))
+            for cb in callbacks or []:
+                cb.on_epoch_end(ep, logs)
+        self._adam["iter"] = int(adam.iter)
+        self.set_flat_weights(w.cpu().numpy())  # the forward kernels repack the weights on their next use
         self.history = hist
         return hist
 

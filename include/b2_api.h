@@ -255,6 +255,20 @@ int  b2_lstm_forward(b2_lstm* m, const float* x_dev, int64_t batch, int timestep
 int64_t b2_lstm_window_count(int64_t n_rows, int look_back, int shift);
 int  b2_lstm_forward_windows(b2_lstm* m, const float* rows_dev, int64_t n_rows, int look_back, int shift, float* y_dev, void* stream);
 
+/* Training of the same stack (LSTM-TensorFlow-IO-Kafka/cardata-v1.py:178 compile(mean_squared_error, adam, ['accuracy']) and
+ * :191-194 fit(zip((dataset_x, dataset_y)).batch(batch_size).take(1000), epochs=5)): consecutive batches of `batch` sequences,
+ * one Adam step each, all inside ONE launch (one persistent CTA: the reference's batch_size 1 x look_back 1 makes this a chain of
+ * dependent steps).  Sequence s, step t reads x_dev + (s * x_seq_stride + t) * F and is compared with y_dev + (s * y_seq_stride
+ * + t) * F (strides in rows: `timesteps` for dense [n, T, F] tensors; 1 / 1 with y_dev = rows + F for the script's sliding
+ * windows of look_back 1).  w_dev / m_dev / v_dev f32[P] (Keras flat weight order: kernel, recurrent_kernel, bias per LSTM, then
+ * the Dense kernel and bias) are updated in place, adam->iter advances by the number of steps; loss_dev / acc_dev f32[steps]
+ * (NULL to skip) receive each step's loss and accuracy.  scratch_dev: b2_lstm_fit_scratch_bytes(desc, timesteps, batch) bytes.
+ * Afterwards build a new b2_lstm from the trained weights to run the forward kernels. */
+int64_t b2_lstm_fit_scratch_bytes(const b2_lstm_desc* desc, int timesteps, int batch);
+int  b2_lstm_fit_steps(b2_ctx* ctx, const b2_lstm_desc* desc, float* w_dev, float* m_dev, float* v_dev, const float* x_dev,
+                       int64_t x_seq_stride, const float* y_dev, int64_t y_seq_stride, int64_t n_seq, int timesteps, int batch,
+                       b2_adam* adam, float* loss_dev, float* acc_dev, void* scratch_dev, int64_t scratch_bytes, void* stream);
+
 /* ---- result sink: rows → text ------------------------------------------------------------------------------
  * Replaces the formatting half of OutputCallback.on_predict_batch_end (cardata-v1.py:218-224:
  * `message = np.array2string(output)` per reconstructed row, then KafkaOutputSequence.setitem(index, message)).

@@ -458,6 +458,104 @@ def lstm_forward(x: np.ndarray, weights: np.ndarray, features: int = 18, units=(
 
 
 # ----------------------------------------------------------------------------------------------
+# LSTM stack training step — python-scripts/LSTM-TensorFlow-IO-Kafka/cardata-v1.py:178 (compile: mean_squared_error, adam,
+# metrics=['accuracy']) and :191-194 (zip((dataset_x, dataset_y)).batch(1).take(1000); fit(epochs=5)): back-propagation
+# through time of the stack above.  Gradients are checked against torch autograd in tests/test_oracle_golden.py.
+# ----------------------------------------------------------------------------------------------
+def _lstm_layer_fwd_cache(x, W, U, b):
+    """Forward of one layer keeping what BPTT needs: gates after their activations, cell states, outputs."""
+    B, T, _ = x.shape
+    u = U.shape[0]
+    h = np.zeros((B, u), dtype=x.dtype)
+    c = np.zeros((B, u), dtype=x.dtype)
+    cache = dict(x=x, i=[], f=[], g=[], o=[], c=[], h=[], W=W, U=U)
+    for t in range(T):
+        z = x[:, t] @ W + h @ U + b
+        i, f, g, o = _sigmoid(z[:, :u]), _sigmoid(z[:, u:2 * u]), np.maximum(z[:, 2 * u:3 * u], 0), _sigmoid(z[:, 3 * u:])
+        c = f * c + i * g
+        h = o * np.maximum(c, 0)
+        for k, v in zip("ifgoch", (i, f, g, o, c, h)):
+            cache[k].append(v)
+    return np.stack(cache["h"], axis=1), cache
+
+
+def _lstm_layer_bwd(dh_seq, cache):
+    """dh_seq [B,T,u]: loss gradient w.r.t. every output h_t → (dx [B,T,in], dW, dU, db)."""
+    x, W, U = cache["x"], cache["W"], cache["U"]
+    B, T, _ = x.shape
+    u = U.shape[0]
+    dW, dU, db = np.zeros_like(W), np.zeros_like(U), np.zeros(4 * u, dtype=x.dtype)
+    dx = np.zeros_like(x)
+    dh_next = np.zeros((B, u), dtype=x.dtype)
+    dc_next = np.zeros((B, u), dtype=x.dtype)
+    for t in range(T - 1, -1, -1):
+        i, f, g, o, c = (cache[k][t] for k in "ifgoc")
+        c_prev = cache["c"][t - 1] if t > 0 else np.zeros_like(c)
+        h_prev = cache["h"][t - 1] if t > 0 else np.zeros_like(c)
+        dh = dh_seq[:, t] + dh_next
+        do = dh * np.maximum(c, 0)
+        dc = dh * o * (c > 0) + dc_next
+        dz = np.concatenate([dc * g * i * (1 - i), dc * c_prev * f * (1 - f), dc * i * (g > 0), do * o * (1 - o)], axis=1)
+        dW += x[:, t].T @ dz
+        dU += h_prev.T @ dz
+        db += dz.sum(axis=0)
+        dx[:, t] = dz @ W.T
+        dh_next = dz @ U.T
+        dc_next = dc * f
+    return dx, dW, dU, db
+
+
+def lstm_loss_and_grads(x, y, weights, features: int = 18, units=(32, 16, 16, 32), dtype=np.float64):
+    """Mean-squared-error loss of the stack on (x [B,T,F], y [B,T,F]) and its gradient (flat, Keras weight order), plus the
+    'accuracy' Keras reports for this compile() call (argmax over the feature axis, averaged over batch and time)."""
+    ws = lstm_unflatten(np.asarray(weights, dtype=dtype), features, units)
+    x, y = np.asarray(x, dtype=dtype), np.asarray(y, dtype=dtype)
+    B, T, _ = x.shape
+    h1, c1 = _lstm_layer_fwd_cache(x, *ws[0:3])
+    h2seq, c2 = _lstm_layer_fwd_cache(h1, *ws[3:6])
+    rep = np.repeat(h2seq[:, -1:, :], T, axis=1)  # return_sequences=False → RepeatVector(T)
+    h3, c3 = _lstm_layer_fwd_cache(rep, *ws[6:9])
+    h4, c4 = _lstm_layer_fwd_cache(h3, *ws[9:12])
+    out = h4 @ ws[12] + ws[13]
+    diff = out - y
+    loss = float(np.mean(diff * diff))
+    acc = float(np.mean(np.argmax(out, axis=-1) == np.argmax(y, axis=-1)))
+    dout = 2.0 * diff / diff.size
+    dWd = h4.reshape(-1, h4.shape[-1]).T @ dout.reshape(-1, features)
+    dbd = dout.reshape(-1, features).sum(axis=0)
+    dh4 = dout @ ws[12].T
+    dh3, dW4, dU4, db4 = _lstm_layer_bwd(dh4, c4)
+    drep, dW3, dU3, db3 = _lstm_layer_bwd(dh3, c3)
+    dh2 = np.zeros_like(h2seq)
+    dh2[:, -1] = drep.sum(axis=1)
+    dh1, dW2, dU2, db2 = _lstm_layer_bwd(dh2, c2)
+    _, dW1, dU1, db1 = _lstm_layer_bwd(dh1, c1)
+    grads = np.concatenate([a.ravel() for a in (dW1, dU1, db1, dW2, dU2, db2, dW3, dU3, db3, dW4, dU4, db4, dWd, dbd)])
+    return loss, grads, acc, out
+
+
+def lstm_fit(x, y, weights, batch: int = 1, epochs: int = 1, features: int = 18, units=(32, 16, 16, 32), adam=None, iter0: int = 0,
+             dtype=np.float64):
+    """Mini-batch Adam over consecutive (unshuffled) batches, like model.fit(dataset.batch(batch_size)) on a tf.data pipeline;
+    → (weights, m, v, per-epoch mean loss, per-epoch accuracy, iter)."""
+    w = np.asarray(weights, dtype=dtype).copy()
+    m, v = (np.zeros_like(w), np.zeros_like(w)) if adam is None else (np.asarray(adam[0], dtype=dtype).copy(), np.asarray(adam[1], dtype=dtype).copy())
+    t = iter0
+    n = x.shape[0]
+    losses, accs = [], []
+    for _ in range(epochs):
+        ls, ac, k = 0.0, 0.0, 0
+        for s in range(0, n, batch):
+            loss, g, acc, _ = lstm_loss_and_grads(x[s:s + batch], y[s:s + batch], w, features, units, dtype=dtype)
+            t += 1
+            w, m, v = adam_step(w, m, v, g, t, dtype=dtype)
+            ls, ac, k = ls + loss, ac + acc, k + 1
+        losses.append(ls / k)
+        accs.append(ac / k)
+    return w, m, v, losses, accs, t
+
+
+# ----------------------------------------------------------------------------------------------
 # Keras-style initialisers (model_config: GlorotUniform kernels, zero biases, orthogonal recurrent, unit_forget_bias)
 # ----------------------------------------------------------------------------------------------
 def glorot_uniform(rng: np.random.Generator, shape) -> np.ndarray:

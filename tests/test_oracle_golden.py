@@ -213,3 +213,44 @@ def test_fit_oracle_decreases_loss():
     w0 = kc.init_dense_weights([18, 14, 7, 7, 18], seed=314)
     w, m, v, t, losses, accs = orc.fit(x, w0, [18, 14, 7, 7, 18], ACTS, 1e-7, batch=32, epochs=3)
     assert t == 48 and losses[-16:].mean() < losses[:16].mean()
+
+
+def test_lstm_bptt_gradients_match_torch_autograd():
+    """oracle.lstm_loss_and_grads (the float64 BPTT the CUDA training kernel is compared with) against torch autograd."""
+    import torch
+
+    F, units = 18, (32, 16, 16, 32)
+    g = np.random.default_rng(0)
+    w = orc.init_lstm_weights(F, units, seed=3).astype(np.float64) + g.normal(size=18642) * 0.05
+    for B, T in ((1, 1), (3, 4), (5, 2)):
+        x, y = g.uniform(-1, 1, (B, T, F)), g.uniform(-1, 1, (B, T, F))
+        loss, grads, acc, out = orc.lstm_loss_and_grads(x, y, w)
+        tw = torch.tensor(w, dtype=torch.float64, requires_grad=True)
+        ws, p = [], 0
+        for shp in orc.lstm_param_shapes(F, units):
+            n = int(np.prod(shp))
+            ws.append(tw[p:p + n].reshape(shp))
+            p += n
+
+        def layer(xx, W, U, b, seq):
+            u = U.shape[0]
+            h = torch.zeros(xx.shape[0], u, dtype=torch.float64)
+            c = torch.zeros_like(h)
+            hs = []
+            for t in range(xx.shape[1]):
+                z = xx[:, t] @ W + h @ U + b
+                i, f, gg, o = torch.sigmoid(z[:, :u]), torch.sigmoid(z[:, u:2 * u]), torch.relu(z[:, 2 * u:3 * u]), torch.sigmoid(z[:, 3 * u:])
+                c = f * c + i * gg
+                h = o * torch.relu(c)
+                hs.append(h)
+            return torch.stack(hs, 1) if seq else h
+
+        h = layer(torch.tensor(x), *ws[0:3], True)
+        h = layer(h, *ws[3:6], False)
+        h = layer(h[:, None, :].repeat(1, T, 1), *ws[6:9], True)
+        h = layer(h, *ws[9:12], True)
+        o = h @ ws[12] + ws[13]
+        L = ((o - torch.tensor(y)) ** 2).mean()
+        L.backward()
+        assert abs(loss - L.item()) < 1e-14 and np.abs(grads - tw.grad.numpy()).max() < 1e-14
+        np.testing.assert_allclose(out, orc.lstm_forward(x, w, dtype=np.float64), rtol=0, atol=1e-15)
