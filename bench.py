@@ -561,6 +561,35 @@ def aux_lstm(dev, T):
 
 # records per step are sized so that a step lasts ~0.1 s and the default 20 timed steps ~2 s (clocks and power reach their
 # sustained state inside the timed region); the batches of one pass always exceed the L2
+def aux_lstm_fit(dev):
+    """SURVEY §8 f.4 / LSTM-TensorFlow-IO-Kafka/cardata-v1.py:191-194: fit(zip(window(1), skip(1)).batch(1).take(1000), epochs=5)
+    — 5 000 dependent Adam steps of the 18 642-parameter stack; one persistent-CTA launch per epoch."""
+    import torch
+
+    import b200_sensor as bs
+
+    k = bs.keras
+    m = k.models.Sequential()
+    m.add(k.layers.LSTM(32, activation="relu", input_shape=(1, 18), return_sequences=True))
+    m.add(k.layers.LSTM(16, activation="relu", return_sequences=False))
+    m.add(k.layers.RepeatVector(1))
+    m.add(k.layers.LSTM(16, activation="relu", return_sequences=True))
+    m.add(k.layers.LSTM(32, activation="relu", return_sequences=True))
+    m.add(k.layers.TimeDistributed(k.layers.Dense(18)))
+    m.compile(metrics=["accuracy"], loss="mean_squared_error", optimizer="adam")
+    rows = k.normalize_fn(torch.from_numpy(bs.synth.sensor_rows(1001, seed=314, outlier_frac=0.0)).to(dev), *bs.schemas.norm_arrays())
+    win = k.Windows(rows, 1, 1)
+    m.fit(win, epochs=1, batch_size=1, shuffle=False)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    h = m.fit(win, epochs=5, batch_size=1, shuffle=False)
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    return {"value": 5000 / dt, "unit": "steps/s", "us_per_step": dt / 5000 * 1e6, "batch": 1, "look_back": 1, "epochs": 5,
+            "steps_per_epoch": 1000, "loss_first_last": [h.history["loss"][0], h.history["loss"][-1]],
+            "kernel": "lstm_fit_kernel (one persistent CTA per epoch: BPTT + Adam)"}
+
+
 WORKLOADS = {
     "score30": lambda: ScoreWorkload(30, 27, 22, repeat=24),
     "score18": lambda: ScoreWorkload(18, 27, 22, repeat=24),
@@ -842,6 +871,7 @@ def main():
             gc.collect()
             torch.cuda.empty_cache()
             also["fit_d30_batch128"] = aux_fit(dev)
+            also["lstm_fit_batch1_lookback1"] = aux_lstm_fit(dev)
             also["lstm_forward_T1"] = aux_lstm(dev, 1)
             also["lstm_forward_T16"] = aux_lstm(dev, 16)
             also["format_rows_d18"] = aux_format_rows(dev)

@@ -104,6 +104,10 @@ _PROTOTYPES = {
     "b2_ae_grad_scratch_bytes": (C.c_int64, [_P, C.c_int64]),
     "b2_ae_grad": (C.c_int, [_P, _P, C.c_int64, C.POINTER(Norm), _P, _P, C.c_int64, _P]),
     "b2_ae_apply": (C.c_int, [_P, _P, C.POINTER(Adam), _P, _P]),
+    "b2_ae_step_scratch_bytes": (C.c_int64, [_P, C.c_int64]),
+    "b2_ae_exchange_bytes": (C.c_int64, []),
+    "b2_ae_step_fused": (C.c_int, [_P, _P, C.c_int64, C.POINTER(Norm), C.POINTER(Adam), _P, C.c_int64, C.c_int64, C.POINTER(C.c_uint64),
+                                   C.c_int, C.c_int, C.c_uint32, _P, _P]),
     "b2_ae_grad_noalloc": (C.c_int, [_P, _P, C.c_int64, C.POINTER(Norm), _P, _P]),
     "b2_ae_get_adam": (C.c_int, [_P, _P, _P]),
     "b2_ae_set_adam": (C.c_int, [_P, _P, _P]),

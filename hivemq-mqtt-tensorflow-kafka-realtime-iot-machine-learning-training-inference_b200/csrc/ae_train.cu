@@ -345,6 +345,105 @@ __global__ void __launch_bounds__(FIT_NT, 1) ae_fit_kernel(const __grid_constant
 }
 
 // ---- large batch / data parallel -----------------------------------------------------------------------------------
+// One data-parallel step as ONE kernel (b2_ae_step_fused).  The CTA that finishes its tiles last folds the per-CTA partial sums
+// (fixed order), then — with more than one GPU — stores its 840-float vector straight into every peer's exchange buffer over
+// NVLink (plain peer stores into symmetric memory: the cudaMalloc'ed buffer of each rank mapped into every process), raises
+// a flag there, waits for the peers' flags in its own buffer, adds the `world` vectors in rank order (so every GPU forms the
+// identical sum) and applies the Adam update.  No NCCL call, no extra launch, no host round trip per step.
+constexpr int EXCH_W = 840;              // floats per exchange slot (>= P + 3 for D = 30)
+constexpr int EXCH_MAX_WORLD = 8;
+constexpr int EXCH_FLAGS_OFF = 2 * EXCH_MAX_WORLD * EXCH_W;   // uint32 flags[world] behind the two parities of slots
+constexpr int EXCH_FLOATS = EXCH_FLAGS_OFF + 32;
+
+struct StepTail {
+  int enabled;
+  int* ticket;            // device counter, zero before the first launch; the last CTA resets it
+  float* w;               // same buffer as GradArgs::w, writable
+  float* m;
+  float* v;
+  float lr, beta1, beta2, eps;
+  long long iter;         // value before this step
+  long long total_rows;   // rows of the GLOBAL batch (all ranks)
+  float* stats;           // [2] mean loss, accuracy of the global batch, or NULL
+  int world, rank;
+  unsigned seq;           // exchange sequence number of this step (1, 2, 3, … on every rank alike)
+  float* peer[EXCH_MAX_WORLD];  // exchange buffers of all ranks as mapped here; peer[rank] is this GPU's own
+};
+
+__device__ __forceinline__ void st_release_sys_u32(unsigned* p, unsigned v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned ld_acquire_sys_u32(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float ld_relaxed_sys_f32(const float* p) {
+  float v;
+  asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// executed by the last CTA of the launch; gl = at least EXCH_W floats of shared memory
+__device__ void step_tail(const StepTail& t, const float* scratch, int n_parts, int P, float* gl, int tid) {
+  const int W = P + 3;
+  __threadfence();
+  for (int j = tid; j < W; j += FIT_NT) {
+    float s = 0.f;
+    for (int c = 0; c < n_parts; ++c) s += __ldcg(scratch + (size_t)c * W + j);
+    gl[j] = s;
+  }
+  __syncthreads();
+  bool ok = true;
+  if (t.world > 1) {
+    const int par = (int)(t.seq & 1u);
+    for (int p = 0; p < t.world; ++p) {
+      float* dst = t.peer[p] + (size_t)(par * t.world + t.rank) * EXCH_W;
+      for (int j = tid; j < W; j += FIT_NT) dst[j] = gl[j];
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (tid < t.world) {
+      st_release_sys_u32(reinterpret_cast<unsigned*>(t.peer[tid] + EXCH_FLAGS_OFF) + t.rank, t.seq);
+      const unsigned* mine = reinterpret_cast<const unsigned*>(t.peer[t.rank] + EXCH_FLAGS_OFF) + tid;
+      const long long t0 = clock64();
+      while ((int)(ld_acquire_sys_u32(mine) - t.seq) < 0) {
+        if (clock64() - t0 > 8000000000ll) {  // a peer never showed up (~4 s): give up instead of hanging the GPU
+          ok = false;
+          break;
+        }
+      }
+    }
+    ok = __syncthreads_and(ok);
+    const float* my = t.peer[t.rank] + (size_t)(par * t.world) * EXCH_W;
+    for (int j = tid; j < W; j += FIT_NT) {
+      float s = 0.f;
+      for (int q = 0; q < t.world; ++q) s += ld_relaxed_sys_f32(my + (size_t)q * EXCH_W + j);  // rank order: same sum everywhere
+      gl[j] = s;
+    }
+    __syncthreads();
+  }
+  const float rows = (float)t.total_rows;
+  if (tid == 0 && t.stats) {
+    t.stats[0] = ok ? gl[P] / rows : __int_as_float(0x7FC00000);
+    t.stats[1] = ok ? gl[P + 1] / rows : __int_as_float(0x7FC00000);
+  }
+  if (ok) {
+    const double tt = (double)(t.iter + 1);
+    const float alpha = (float)((double)t.lr * sqrt(1.0 - pow((double)t.beta2, tt)) / (1.0 - pow((double)t.beta1, tt)));
+    for (int p = tid; p < P; p += FIT_NT) {
+      const float g = gl[p] / rows;
+      float m = t.m[p], v = t.v[p];
+      m = fmaf(1.0f - t.beta1, g - m, m);
+      v = fmaf(1.0f - t.beta2, g * g - v, v);
+      t.m[p] = m;
+      t.v[p] = v;
+      t.w[p] = t.w[p] - alpha * m / (sqrtf(v) + t.eps);
+    }
+  }
+  if (tid == 0) *t.ticket = 0;
+}
+
 template <int D>
 struct GradArgs {
   const float* x;
@@ -354,6 +453,7 @@ struct GradArgs {
   float l1;
   const float* w;   // device, Keras flat order
   float* scratch;   // [gridDim.x][P+3] partial sums
+  StepTail tail;    // fused step (b2_ae_step_fused): fold + cross-GPU exchange + Adam in the CTA that finishes last
 };
 
 template <int D>
@@ -431,6 +531,14 @@ __global__ void __launch_bounds__(FIT_NT, 1) ae_grad_kernel(const __grid_constan
     long long mine = 0;
     for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) mine += min((long long)FIT_NT, a.n - tile * FIT_NT);
     out[L::P + 2] = (float)mine;
+  }
+  if (a.tail.enabled) {  // fused step: whoever finishes last does the fold, the exchange and the update
+    __shared__ int s_last;
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) s_last = atomicAdd(a.tail.ticket, 1) == (int)gridDim.x - 1;
+    __syncthreads();
+    if (s_last) step_tail(a.tail, a.scratch, (int)gridDim.x, L::P, arena, tid);
   }
 }
 
@@ -557,6 +665,7 @@ static int grad_spec(b2_ae* ae, const float* x, int64_t n, const b2_norm* norm, 
   a.l1 = ae->desc.l1_activity;
   a.w = ae->d_w;
   a.scratch = scratch;
+  memset(&a.tail, 0, sizeof(a.tail));
   const size_t smem = train_smem<D>();
   const int grid = grad_grid(ae, n);
   B2_CUDA(cudaFuncSetAttribute(ae_grad_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -604,6 +713,68 @@ extern "C" int b2_ae_apply(b2_ae* ae, const float* grads_dev, b2_adam* adam, flo
   ae->host_stale = true;
   ae->tc_valid = false;
   return B2_OK;
+}
+
+// ---- one data-parallel step in one launch ---------------------------------------------------------------------------------
+template <int D>
+static int step_fused_spec(b2_ae* ae, const float* x, int64_t n, const b2_norm* norm, b2_adam* adam, float* scratch, int64_t total_rows,
+                           const uint64_t* peers, int world, int rank, unsigned seq, float* stats, cudaStream_t stream) {
+  GradArgs<D> a;
+  a.x = x;
+  a.n = n;
+  fill_norm<D>(norm, a.nm, a.has_norm);
+  a.l1 = ae->desc.l1_activity;
+  a.w = ae->d_w;
+  a.scratch = scratch;
+  const int grid = grad_grid(ae, n);
+  memset(&a.tail, 0, sizeof(a.tail));
+  a.tail.enabled = 1;
+  a.tail.ticket = reinterpret_cast<int*>(scratch + (size_t)grid * (ae->n_params + 3));
+  a.tail.w = ae->d_w, a.tail.m = ae->d_m, a.tail.v = ae->d_v;
+  a.tail.lr = adam->lr, a.tail.beta1 = adam->beta1, a.tail.beta2 = adam->beta2, a.tail.eps = adam->eps;
+  a.tail.iter = adam->iter;
+  a.tail.total_rows = total_rows;
+  a.tail.stats = stats;
+  a.tail.world = world, a.tail.rank = rank, a.tail.seq = seq;
+  for (int p = 0; p < world && peers; ++p) a.tail.peer[p] = reinterpret_cast<float*>((uintptr_t)peers[p]);
+  const size_t smem = train_smem<D>();
+  B2_CUDA(cudaFuncSetAttribute(ae_grad_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  ae_grad_kernel<D><<<grid, FIT_NT, smem, stream>>>(a);
+  B2_CUDA(cudaGetLastError());
+  adam->iter += 1;
+  ae->host_stale = true;
+  ae->tc_valid = false;
+  return B2_OK;
+}
+
+extern "C" int64_t b2_ae_step_scratch_bytes(const b2_ae* ae, int64_t n) {
+  if (!ae || n < 0) return 0;
+  return b2_ae_grad_scratch_bytes(ae, n) + 64;  // + the ticket counter
+}
+extern "C" int64_t b2_ae_exchange_bytes(void) { return (int64_t)sizeof(float) * EXCH_FLOATS; }
+
+extern "C" int b2_ae_step_fused(b2_ae* ae, const float* x_dev, int64_t n, const b2_norm* norm, b2_adam* adam, void* scratch_dev,
+                                int64_t scratch_bytes, int64_t total_rows, const uint64_t* peer_bufs, int world, int rank, uint32_t seq,
+                                float* stats_dev, void* stream) {
+  B2_REQUIRE(ae && x_dev && adam && scratch_dev, "b2_ae_step_fused: NULL argument");
+  B2_REQUIRE(n >= 1 && total_rows >= n, "b2_ae_step_fused: n=%lld total_rows=%lld", (long long)n, (long long)total_rows);
+  B2_REQUIRE(((uintptr_t)x_dev & 7) == 0, "b2_ae_step_fused: x_dev must be 8-byte aligned");
+  B2_REQUIRE(scratch_bytes >= b2_ae_step_scratch_bytes(ae, n), "b2_ae_step_fused: scratch of %lld bytes is smaller than the %lld needed",
+             (long long)scratch_bytes, (long long)b2_ae_step_scratch_bytes(ae, n));
+  B2_REQUIRE(world >= 1 && world <= EXCH_MAX_WORLD && rank >= 0 && rank < world, "b2_ae_step_fused: world=%d rank=%d", world, rank);
+  B2_REQUIRE(world == 1 || (peer_bufs != nullptr && seq != 0), "b2_ae_step_fused: %d ranks need the exchange buffers and a sequence number >= 1", world);
+  B2_REQUIRE(!norm || norm->n == 0 || norm->n == ae->desc.widths[0], "b2_ae_step_fused: norm table size mismatch");
+  if (ae->spec_d == 0) {
+    b2_set_error("b2_ae_step_fused: training is implemented for the D-14-7-7-D autoencoder with D in {18, 30}");
+    return B2_EUNSUPPORTED;
+  }
+  DeviceGuard g(ae->ctx->device);
+  int rc = b2_ae_ensure_adam(ae);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (ae->spec_d == 18)
+    return step_fused_spec<18>(ae, x_dev, n, norm, adam, (float*)scratch_dev, total_rows, peer_bufs, world, rank, seq, stats_dev, st);
+  return step_fused_spec<30>(ae, x_dev, n, norm, adam, (float*)scratch_dev, total_rows, peer_bufs, world, rank, seq, stats_dev, st);
 }
 
 // ---- gradient sums without any allocation ------------------------------------------------------------------------------

@@ -18,6 +18,7 @@ from __future__ import annotations
 import ctypes as C
 import json
 import math
+import os
 from typing import Dict, List, Optional, Sequence
 
 import numpy as np
@@ -723,7 +724,43 @@ class Model:
             _ffi.check(_ffi.lib().b2_ae_set_adam(self._ae, m.ctypes.data, v.ctypes.data), "b2_ae_set_adam")
         self._h5_optimizer = None
 
+    def _exchange_buffers(self, dev):
+        """Symmetric-memory exchange buffers for the fused data-parallel step (one per model and process group, kept): every
+        rank's buffer mapped into every process, so the training kernel stores its gradient vector straight into its peers'
+        memory over NVLink.  Returns None when symmetric memory is unavailable on ANY rank (then NCCL all-reduce is used)."""
+        import torch.distributed as dist
+
+        ex = getattr(self, "_exch", None)
+        if ex is not None:
+            return ex or None
+        world, ok = dist.get_world_size(), 1
+        try:
+            import torch.distributed._symmetric_memory as symm
+
+            if os.environ.get("B2_DP_NCCL") == "1" or world > 8:
+                raise RuntimeError("fused exchange disabled")
+            nfl = int(_ffi.lib().b2_ae_exchange_bytes()) // 4
+            buf = symm.empty(nfl, dtype=torch.float32, device=dev)
+            buf.zero_()
+            hdl = symm.rendezvous(buf, dist.group.WORLD.group_name)
+            ptrs = (C.c_uint64 * world)(*[int(p) for p in hdl.buffer_ptrs])
+            torch.cuda.synchronize()
+        except Exception as e:  # noqa: BLE001 — any failure means "no symmetric memory here"
+            ok, buf, hdl, ptrs = 0, None, None, None
+            self._exch_error = repr(e)
+        flag = torch.tensor([ok], dtype=torch.int32, device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag.item()) == 0:
+            self._exch = False
+            return None
+        dist.barrier()
+        self._exch = {"buf": buf, "hdl": hdl, "ptrs": ptrs, "seq": 0, "rank": dist.get_rank(), "world": world}
+        return self._exch
+
     def _fit_large(self, xd, epochs, batch_size, shuffle, validation_data, verbose, callbacks, seed, data_parallel):
+        """Large-batch / data-parallel training: ONE kernel per step (``b2_ae_step_fused``) — per-CTA gradient sums, fold, the
+        cross-GPU sum over symmetric memory (peer stores + flags inside the kernel) and Adam.  Falls back to gradient kernel →
+        NCCL all-reduce → Adam kernel when symmetric memory cannot be set up (``self.dp_path`` says which ran)."""
         import torch.distributed as dist
 
         dp = data_parallel and dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
@@ -731,9 +768,18 @@ class Model:
         P = self.n_params
         nm = self._norm_struct()
         adam = _ffi.Adam(self._adam["lr"], self._adam["beta1"], self._adam["beta2"], self._adam["eps"], self._adam["iter"])
-        scratch_bytes = int(l.b2_ae_grad_scratch_bytes(h, min(batch_size, n)))
-        scratch = torch.empty(scratch_bytes, dtype=torch.uint8, device=dev)
-        grads = torch.empty(P + 3, dtype=torch.float32, device=dev)
+        ex = self._exchange_buffers(dev) if dp else None
+        fused = (not dp) or ex is not None
+        self.dp_path = ("fused step kernel, peer stores over symmetric memory" if ex is not None else
+                        "fused step kernel (single GPU)" if fused else "b2_ae_grad + NCCL all-reduce + b2_ae_apply")
+        world = dist.get_world_size() if dp else 1
+        if fused:
+            scratch_bytes = int(l.b2_ae_step_scratch_bytes(h, min(batch_size, n)))
+            scratch = torch.zeros(scratch_bytes, dtype=torch.uint8, device=dev)
+        else:
+            scratch_bytes = int(l.b2_ae_grad_scratch_bytes(h, min(batch_size, n)))
+            scratch = torch.empty(scratch_bytes, dtype=torch.uint8, device=dev)
+            grads = torch.empty(P + 3, dtype=torch.float32, device=dev)
         steps = (n + batch_size - 1) // batch_size
         stats = torch.empty((steps, 2), dtype=torch.float32, device=dev)
         hist = History()
@@ -746,12 +792,22 @@ class Model:
             xs = xd[torch.from_numpy(g.permutation(n)).to(dev)].contiguous() if shuffle else xd
             for s in range(steps):
                 xb = xs[s * batch_size:(s + 1) * batch_size]
+                if fused:
+                    if ex is not None:
+                        ex["seq"] += 1
+                    _ffi.check(l.b2_ae_step_fused(h, _ffi.ptr(xb), xb.shape[0], C.byref(nm), C.byref(adam), _ffi.ptr(scratch), scratch_bytes,
+                                                  int(xb.shape[0]) * world, None if ex is None else ex["ptrs"], world,
+                                                  0 if ex is None else ex["rank"], 0 if ex is None else ex["seq"], _ffi.ptr(stats[s]),
+                                                  _stream_ptr()), "b2_ae_step_fused")
+                    continue
                 _ffi.check(l.b2_ae_grad(h, _ffi.ptr(xb), xb.shape[0], C.byref(nm), _ffi.ptr(grads), _ffi.ptr(scratch), scratch_bytes,
                                         _stream_ptr()), "b2_ae_grad")
                 if dp:
                     dist.all_reduce(grads)  # NCCL over NVLink: P+3 floats (gradient sums, loss sum, correct, rows)
                 _ffi.check(l.b2_ae_apply(h, _ffi.ptr(grads), C.byref(adam), _ffi.ptr(stats[s]), _stream_ptr()), "b2_ae_apply")
             st = stats.cpu().numpy().astype(np.float64)
+            if not np.isfinite(st).all():
+                raise RuntimeError("data-parallel step: a peer GPU did not arrive at the exchange (step skipped); see b2_ae_step_fused")
             sizes = np.full(steps, batch_size, dtype=np.float64)
             sizes[-1] = n - batch_size * (steps - 1)
             logs = {"loss": float((st[:, 0] * sizes).sum() / n)}

@@ -216,6 +216,21 @@ int  b2_ae_grad(b2_ae* ae, const float* x_dev, int64_t n, const b2_norm* norm, f
                 void* scratch_dev, int64_t scratch_bytes, void* stream);
 int  b2_ae_apply(b2_ae* ae, const float* grads_dev, b2_adam* adam, float* loss_out_dev, void* stream);
 
+/* The same step as ONE launch (model.fit of cardata-v3.py:220-222 run data-parallel): gradient sums of this rank's n rows, the
+ * cross-GPU sum and the Adam update all happen inside the gradient kernel — its last CTA folds the partial sums, writes the
+ * 840-float vector into every peer's exchange buffer with plain peer stores over NVLink, waits for the peers' flags and applies
+ * the update from the rank-ordered sum (bit-identical weights on every GPU).  total_rows = rows of the global batch.
+ * world == 1: no exchange (peer_bufs may be NULL).  Otherwise peer_bufs[world] are the device addresses, as mapped in THIS
+ * process, of every rank's exchange buffer of b2_ae_exchange_bytes() bytes (symmetric memory, zero-filled once), and seq is the
+ * step's sequence number — 1, 2, 3, … on all ranks alike.  scratch_dev: b2_ae_step_scratch_bytes(ae, n) bytes, zero-filled
+ * once before the first step.  stats_dev f32[2] (or NULL): mean loss and accuracy of the global batch; NaN if a peer failed
+ * to arrive within ~4 s (the step is then skipped rather than hanging the GPU).  Every rank must launch the step. */
+int64_t b2_ae_step_scratch_bytes(const b2_ae* ae, int64_t n);
+int64_t b2_ae_exchange_bytes(void);
+int  b2_ae_step_fused(b2_ae* ae, const float* x_dev, int64_t n, const b2_norm* norm, b2_adam* adam, void* scratch_dev,
+                      int64_t scratch_bytes, int64_t total_rows, const uint64_t* peer_bufs, int world, int rank, uint32_t seq,
+                      float* stats_dev, void* stream);
+
 /* No counterpart in the reference.  Same result as b2_ae_grad for callers that may not allocate device memory while
  * running (pre-budgeted memory pools, real-time loops that must stay off the allocator lock, hosts whose cudaMalloc is
  * owned by another component): the per-CTA partial sums go to a fixed buffer inside the library image instead of a

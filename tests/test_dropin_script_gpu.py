@@ -17,3 +17,12 @@ def test_cardata_v1_flow(cuda_device, tmp_path):
     assert len(history["loss"]) == 5 and history["loss"][-1] < history["loss"][0]
     assert predict.shape == (3200, 18) and sorted(seq) == list(range(3200))
     assert seq[0].startswith("[") and np.isfinite(mse).all() and flag.dtype == np.uint8
+
+
+def test_lstm_cardata_v1_flow(cuda_device):
+    spec = importlib.util.spec_from_file_location("lstm_cardata_v1_b200", os.path.join(ROOT, "scripts", "lstm_cardata_v1_b200.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    history, predict, seq = mod.main(700, take=400, predict_take=200, verbose=0)
+    assert len(history["loss"]) == 5 and history["loss"][-1] < history["loss"][0] and "accuracy" in history
+    assert predict.shape == (200, 1, 18) and sorted(seq) == list(range(200)) and seq[0].startswith("[")

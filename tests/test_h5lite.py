@@ -67,6 +67,12 @@ def test_reference_files_match_survey_anchors(have_reference, fn, first, iter_):
     assert int(it.read()) == iter_
     tc = json.loads(f.attrs["training_config"])
     assert tc["optimizer_config"]["class_name"] == "Adam" and tc["loss"] == "mean_squared_error"
+    # the list Keras' loader walks: iter, then slot m of (kernel, bias) per Dense layer, then slot v — what Model.save() writes too
+    wn = [str(s) for s in np.atleast_1d(f["optimizer_weights"].attrs["weight_names"])]
+    prefix = wn[0].rsplit("/", 1)[0]
+    dense = [w.split("/")[2] for w in wn[1:9:2]]  # the optimizer's own names of the four Dense layers (e.g. dense_4_1 in the second file)
+    assert len(set(dense)) == 4
+    assert wn == [prefix + "/iter:0"] + [f"{prefix}/{n}/{k}/{slot}:0" for slot in ("m", "v") for n in dense for k in ("kernel", "bias")]
 
 
 def test_reference_offsets(have_reference):

@@ -1,8 +1,9 @@
 """Data-parallel training check (run under torchrun, one rank per GPU):
-    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 tools/dp_fit_check.py
-Every rank computes gradient sums on ITS slice of each global batch (b2_ae_grad), the P+3 floats are all-reduced over NCCL,
-every rank applies the same Adam step (b2_ae_apply).  Checks: weights identical on all ranks, and equal (to float32 reduction
-order) to a single-GPU run over the full global batches.  Prints one JSON line on rank 0."""
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 tools/dp_fit_check.py [global_batch] [steps]
+Every rank computes gradient sums on ITS slice of each global batch; the sum over GPUs and the Adam update happen inside the same
+kernel (b2_ae_step_fused: peer stores into symmetric memory), or — B2_DP_NCCL=1, or no symmetric memory — as gradient kernel,
+NCCL all-reduce of the P+3 floats, Adam kernel.  Checks: weights identical on all ranks, and equal (to float32 reduction order)
+to a single-GPU run over the full global batches.  Prints one JSON line on rank 0."""
 import json
 import os
 import sys
@@ -28,23 +29,29 @@ def main():
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    global_batch, steps = 65536, 12
+    global_batch = int(sys.argv[1]) if len(sys.argv) > 1 else 65536
+    steps = int(sys.argv[2]) if len(sys.argv) > 2 else 12
     x = bs.synth.credit_rows(global_batch * steps, seed=314, outlier_frac=0.0)
     per = global_batch // world
     # rank r owns rows [r*per, (r+1)*per) of every global batch
     xs = x.reshape(steps, world, per, 30)[:, rank].reshape(steps * per, 30)
     m = model()
+    xs_d = torch.from_numpy(np.ascontiguousarray(xs)).cuda()
+    warm = model()
+    warm.fit(xs_d[: 2 * per], epochs=1, batch_size=per, shuffle=False, data_parallel=True)  # symmetric-memory set-up, first launches
+    m._exch = getattr(warm, "_exch", None)  # same exchange buffers (sequence numbers continue)
     dist.barrier()
     torch.cuda.synchronize()
     t0 = time.perf_counter()
-    h = m.fit(torch.from_numpy(np.ascontiguousarray(xs)).cuda(), epochs=1, batch_size=per, shuffle=False, data_parallel=True)
+    h = m.fit(xs_d, epochs=1, batch_size=per, shuffle=False, data_parallel=True)
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
     w = torch.from_numpy(m.get_flat_weights()).cuda()
     ws = [torch.empty_like(w) for _ in range(world)]
     dist.all_gather(ws, w)
     same = all(torch.equal(ws[0], t) for t in ws)
-    out = {"world": world, "global_batch": global_batch, "steps": steps, "identical_on_all_ranks": bool(same),
+    out = {"world": world, "global_batch": global_batch, "steps": steps, "identical_on_all_ranks": bool(same), "path": m.dp_path,
+           "symmetric_memory_error": getattr(warm, "_exch_error", None),
            "s_per_step": dt / steps, "samples_per_s": global_batch * steps / dt, "loss": h.history["loss"][-1]}
     if rank == 0:
         ref = model()
