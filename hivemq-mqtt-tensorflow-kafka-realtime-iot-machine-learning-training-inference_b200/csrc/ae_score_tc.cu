@@ -9,6 +9,7 @@
 
 template <int D>
 struct ScoreTcArgs {
+  AeW<D> w;             // FP32 copy of the weights: the two middle layers run in registers (MID_FP32)
   NormP<D> nm;
   const float* panels;  // device: TcShape<D>::TOTAL floats
   const float* x;
@@ -20,7 +21,7 @@ struct ScoreTcArgs {
   int use_bulk;
 };
 
-template <int D, bool NORM, bool FT>
+template <int D, bool NORM, bool FT, bool MID>
 __global__ void __launch_bounds__(TCS_ROWS, 512 / TcShape<D>::TMEM_COLS > 6 ? 6 : 512 / TcShape<D>::TMEM_COLS) ae_score_tc_kernel(const __grid_constant__ ScoreTcArgs<D> a) {
   constexpr int STAGES = 2;
   constexpr uint32_t TILE_BYTES = TCS_ROWS * D * 4;
@@ -77,7 +78,7 @@ __global__ void __launch_bounds__(TCS_ROWS, 512 / TcShape<D>::TMEM_COLS > 6 ? 6 
     }
     // the stage is free once every thread has its row in registers: the first barrier inside tcs_score_row orders that, and
     // thread 0 refills it right after issuing layer 1 … simpler and just as good: refill after the row's score
-    const float m = tcs_score_row<D, FT>(c, x, tid);
+    const float m = tcs_score_row<D, FT, MID>(c, a.w, x, tid);
     if (tid == 0) issue(tile + (long long)STAGES * gridDim.x, s);
     const bool f = m > a.threshold;  // strict, nb2.0:1163
     if (live) {
@@ -120,10 +121,10 @@ int b2_ae_tc_panels(b2_ae* ae, const float** out) {
   return B2_OK;
 }
 
-template <int D, bool NORM, bool FT>
+template <int D, bool NORM, bool FT, bool MID>
 static int launch_score_tc(b2_ae* ae, const ScoreTcArgs<D>& args, cudaStream_t stream) {
   constexpr size_t smem = (size_t)2 * TCS_ROWS * D * 4 + sizeof(float) * TcShape<D>::TOTAL;
-  auto kern = ae_score_tc_kernel<D, NORM, FT>;
+  auto kern = ae_score_tc_kernel<D, NORM, FT, MID>;
   static bool attr_set[16] = {false};
   const int dev = ae->ctx->device;
   if (!attr_set[dev & 15]) {
@@ -168,13 +169,19 @@ static int score_tc_spec(b2_ae* ae, const float* x, int64_t n, const b2_norm* no
   args.n = n;
   args.threshold = threshold;
   args.use_bulk = (((uintptr_t)x & 15) == 0) && !ae->ctx->knobs.no_bulk;
+  ae_pack_weights<D>(ae->h_w.data(), args.w);
   const bool ft = ae->ctx->knobs.fast_tanh != 0;
-  if (has_norm) {
-    if (ft) return launch_score_tc<D, true, true>(ae, args, stream);
-    return launch_score_tc<D, true, false>(ae, args, stream);
+  const bool mid = ae->ctx->knobs.score_tc != 2;  // score_tc = 2: all four layers on the tensor cores (four round trips per tile)
+  if (!ft) {  // the ≤ 4-ulp tanh is a debugging aid: one configuration is enough
+    if (has_norm) return launch_score_tc<D, true, false, true>(ae, args, stream);
+    return launch_score_tc<D, false, false, true>(ae, args, stream);
   }
-  if (ft) return launch_score_tc<D, false, true>(ae, args, stream);
-  return launch_score_tc<D, false, false>(ae, args, stream);
+  if (has_norm) {
+    if (mid) return launch_score_tc<D, true, true, true>(ae, args, stream);
+    return launch_score_tc<D, true, true, false>(ae, args, stream);
+  }
+  if (mid) return launch_score_tc<D, false, true, true>(ae, args, stream);
+  return launch_score_tc<D, false, true, false>(ae, args, stream);
 }
 
 // called by b2_ae_score when the context option "score_tc" is set and no reconstruction rows are requested

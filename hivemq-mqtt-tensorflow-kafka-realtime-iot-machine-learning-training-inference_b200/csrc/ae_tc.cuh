@@ -194,8 +194,12 @@ __device__ __forceinline__ void tcs_run_layer(TcCtx& c, int w_off_floats, int ti
 
 // Forward pass + reconstruction error of ONE row per thread, 128 rows per CTA in lock-step (every thread of the CTA must call
 // this together; rows that do not exist pass zeros).  x[] holds the (already normalised) input row and is left unchanged.
-template <int D, bool FAST_TANH>
-__device__ __forceinline__ float tcs_score_row(TcCtx& c, const float (&x)[D], int tid) {
+// MID_FP32: the two small middle layers (14→7→7: 147 of the 525 multiply-adds) run as FFMA2 in registers, weights from the
+// kernel parameters (`w`), so a tile makes TWO tensor-core round trips (layer 1, layer 4) instead of four.  The round trip —
+// tcgen05.st, fence, barrier, issue, commit, mbarrier wait, tcgen05.ld — costs ≈ 950 cycles and is what bounds this kernel,
+// not the instruction count (ncu, profiles/round2_notes.md).
+template <int D, bool FAST_TANH, bool MID_FP32>
+__device__ __forceinline__ float tcs_score_row(TcCtx& c, const AeW<D>& w, const float (&x)[D], int tid) {
   using S = TcShape<D>;
   {  // layer 1 panel: [x | 1 | 0…]
     float a[S::K1];
@@ -204,46 +208,86 @@ __device__ __forceinline__ float tcs_score_row(TcCtx& c, const float (&x)[D], in
     tcs_a_store<S::K1, S::ALO>(c.lane_base, a);
   }
   tcs_run_layer<S::N1, S::K1, S::ALO, S::ACC>(c, S::OFF1, tid);
-  {  // h1 = tanh(z1) → layer 2 panel [h1(14) | 1 | 0]
+  if (MID_FP32) {
     uint32_t z[16];
     tcs_ld16(c.lane_base + S::ACC, z);
     tcs_wait_ld();
-    float a[16];
+    float2 h1[AE_H1 / 2];
 #pragma unroll
-    for (int q = 0; q < AE_H1 / 2; ++q) {
-      const float2 t = tanh2_sel<FAST_TANH>(make_float2(__uint_as_float(z[2 * q]), __uint_as_float(z[2 * q + 1])));
+    for (int q = 0; q < AE_H1 / 2; ++q)
+      h1[q] = tanh2_sel<FAST_TANH>(make_float2(__uint_as_float(z[2 * q]), __uint_as_float(z[2 * q + 1])));
+    constexpr int Q2 = AE_P2 / 2, Q3 = AE_P3 / 2;
+    float2 h2[Q2];  // 7 units padded to 8 (pad lane stays 0: zero weights, zero bias, relu)
+#pragma unroll
+    for (int q = 0; q < Q2; ++q) h2[q] = make_float2(w.b2[2 * q], w.b2[2 * q + 1]);
+#pragma unroll
+    for (int i = 0; i < AE_H1; ++i) {
+      const float xi = (i & 1) ? h1[i / 2].y : h1[i / 2].x;
+#pragma unroll
+      for (int q = 0; q < Q2; ++q) h2[q] = fma2(splat(xi), make_float2(w.k2[i][2 * q], w.k2[i][2 * q + 1]), h2[q]);
+    }
+#pragma unroll
+    for (int q = 0; q < Q2; ++q) h2[q] = relu2(h2[q]);
+    float2 h3[Q3];
+#pragma unroll
+    for (int q = 0; q < Q3; ++q) h3[q] = make_float2(w.b3[2 * q], w.b3[2 * q + 1]);
+#pragma unroll
+    for (int i = 0; i < AE_H2; ++i) {
+      const float xi = (i & 1) ? h2[i / 2].y : h2[i / 2].x;
+#pragma unroll
+      for (int q = 0; q < Q3; ++q) h3[q] = fma2(splat(xi), make_float2(w.k3[i][2 * q], w.k3[i][2 * q + 1]), h3[q]);
+    }
+    float a[8];
+#pragma unroll
+    for (int q = 0; q < Q3; ++q) {
+      const float2 t = tanh2_sel<FAST_TANH>(h3[q]);
       a[2 * q] = t.x;
       a[2 * q + 1] = t.y;
     }
-    a[14] = 1.0f;
-    a[15] = 0.0f;
-    tcs_a_store<16, S::ALO>(c.lane_base, a);
-  }
-  tcs_run_layer<S::N2, S::K2, S::ALO, S::ACC>(c, S::OFF2, tid);
-  {  // h2 = relu(z2) → layer 3 panel [h2(7) | 1]
-    uint32_t z[8];
-    tcs_ld8(c.lane_base + S::ACC, z);
-    tcs_wait_ld();
-    float a[8];
-#pragma unroll
-    for (int i = 0; i < 7; ++i) a[i] = fmaxf(__uint_as_float(z[i]), 0.0f);
-    a[7] = 1.0f;
+    a[7] = 1.0f;  // (the pad unit's tanh(0) = 0 is replaced by the bias-1 column)
     tcs_a_store<8, S::ALO>(c.lane_base, a);
-  }
-  tcs_run_layer<S::N3, S::K3, S::ALO, S::ACC>(c, S::OFF3, tid);
-  {  // h3 = tanh(z3) → layer 4 panel [h3(7) | 1]
-    uint32_t z[8];
-    tcs_ld8(c.lane_base + S::ACC, z);
-    tcs_wait_ld();
-    float a[8];
+  } else {
+    {  // h1 = tanh(z1) → layer 2 panel [h1(14) | 1 | 0]
+      uint32_t z[16];
+      tcs_ld16(c.lane_base + S::ACC, z);
+      tcs_wait_ld();
+      float a[16];
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const float2 t = tanh2_sel<FAST_TANH>(make_float2(__uint_as_float(z[2 * q]), __uint_as_float(z[2 * q + 1])));
-      a[2 * q] = t.x;
-      a[2 * q + 1] = t.y;
+      for (int q = 0; q < AE_H1 / 2; ++q) {
+        const float2 t = tanh2_sel<FAST_TANH>(make_float2(__uint_as_float(z[2 * q]), __uint_as_float(z[2 * q + 1])));
+        a[2 * q] = t.x;
+        a[2 * q + 1] = t.y;
+      }
+      a[14] = 1.0f;
+      a[15] = 0.0f;
+      tcs_a_store<16, S::ALO>(c.lane_base, a);
     }
-    a[7] = 1.0f;
-    tcs_a_store<8, S::ALO>(c.lane_base, a);
+    tcs_run_layer<S::N2, S::K2, S::ALO, S::ACC>(c, S::OFF2, tid);
+    {  // h2 = relu(z2) → layer 3 panel [h2(7) | 1]
+      uint32_t z[8];
+      tcs_ld8(c.lane_base + S::ACC, z);
+      tcs_wait_ld();
+      float a[8];
+#pragma unroll
+      for (int i = 0; i < 7; ++i) a[i] = fmaxf(__uint_as_float(z[i]), 0.0f);
+      a[7] = 1.0f;
+      tcs_a_store<8, S::ALO>(c.lane_base, a);
+    }
+    tcs_run_layer<S::N3, S::K3, S::ALO, S::ACC>(c, S::OFF3, tid);
+    {  // h3 = tanh(z3) → layer 4 panel [h3(7) | 1]
+      uint32_t z[8];
+      tcs_ld8(c.lane_base + S::ACC, z);
+      tcs_wait_ld();
+      float a[8];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float2 t = tanh2_sel<FAST_TANH>(make_float2(__uint_as_float(z[2 * q]), __uint_as_float(z[2 * q + 1])));
+        a[2 * q] = t.x;
+        a[2 * q + 1] = t.y;
+      }
+      a[7] = 1.0f;
+      tcs_a_store<8, S::ALO>(c.lane_base, a);
+    }
   }
   tcs_run_layer<S::N4, S::K4, S::ALO, S::ACC4>(c, S::OFF4, tid);
   float2 se = make_float2(0.f, 0.f);
