@@ -1,0 +1,37 @@
+"""profiles/r2_ncu_full_summary.json → profiles/instr_per_record.json + profiles/traffic.json (what bench.py reads).
+The records of each profiled launch are those of tools/prof_all.py."""
+import json, os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+rows = json.load(open(os.path.join(ROOT, "profiles", "r2_ncu_full_summary.json")))
+RECORDS = {  # kernel-name fragment → (key, records of that launch)
+    "ae_score_tc_kernel<30": ("ae_score_d30", 1 << 22),
+    "ae_score_kernel<18": ("ae_score_d18", 1 << 22),
+    "decode_kernel<18, 1, true, 0>": ("decode_score_csv", 1 << 20),
+    "decode_kernel<18, 1, true, 1>": ("decode_score_avro_a", 1 << 20),   # first Avro launch = avro_a (prof_all order)
+    "decode_kernel<18, 1, true, 2>": ("decode_score_json", 1 << 19),
+}
+instr, traffic, seen = {}, {}, {}
+def num(d, k):
+    v = d.get(k)
+    return None if v is None else float(str(v[0]).replace(",", ""))
+def to_bytes(v, unit):
+    return v * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(unit, 1)
+for d in rows:
+    for frag, (key, n) in RECORDS.items():
+        if frag in d["kernel"]:
+            if key == "decode_score_avro_a" and key in seen:
+                key = "decode_score_avro_b"   # second fused Avro launch
+            if key in seen and key != "decode_score_avro_b":
+                continue
+            if key in instr:
+                continue
+            seen[key] = True
+            ie = num(d, "smsp__inst_executed.sum")
+            if ie:
+                instr[key] = ie / n
+            rd, wr = d.get("dram__bytes_read.sum"), d.get("dram__bytes_write.sum")
+            if rd and wr:
+                traffic[key] = (to_bytes(float(rd[0]), rd[1]) + to_bytes(float(wr[0]), wr[1])) / n
+json.dump(instr, open(os.path.join(ROOT, "profiles", "instr_per_record.json"), "w"), indent=1)
+json.dump(traffic, open(os.path.join(ROOT, "profiles", "traffic.json"), "w"), indent=1)
+print(instr, traffic)

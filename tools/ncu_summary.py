@@ -13,7 +13,11 @@ KEYS = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum
         "launch__block_size", "launch__occupancy_limit_shared_mem", "launch__occupancy_limit_registers",
         "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum",
         "l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed", "smsp__thread_inst_executed_per_inst_executed.ratio",
-        "launch__shared_mem_per_block_dynamic", "sm__inst_executed_pipe_tensor.sum", "lts__t_sector_hit_rate.pct"]
+        "launch__shared_mem_per_block_dynamic", "lts__t_sector_hit_rate.pct",
+        # tensor path (sm_100: the tcgen05 pipe shows up under these names)
+        "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active", "sm__pipe_tensor_subpipe_hmma_cycles_active.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_tmem.avg.pct_of_peak_sustained_active", "smsp__sass_inst_executed_op_tmem_ldt.sum",
+        "smsp__sass_inst_executed_op_tmem_stt.sum", "sm__inst_executed_pipe_tensor_subpipe_hmma.avg.pct_of_peak_sustained_active"]
 out = []
 for r in rows[2:]:
     d = {"kernel": r[hdr.index("Kernel Name")]}
