@@ -15,7 +15,7 @@
 //   (then the next item is planned and its copy issued, so that it flies under the score phase)
 //   score    lane-per-record   fused normalise → Dense stack → MSE → flag (ae_math.cuh), or a coalesced write-out of the rows
 // Algorithmic bytes/record: payload + 4 (offset) read, 5 written (fused) or 4*F + 4 written (decode only).
-#include "ae_math.cuh"
+#include "ae_tc.cuh"
 #include "float_parse.cuh"
 #include "json_walk.cuh"
 
@@ -76,6 +76,7 @@ struct DecodeArgs {
   // the retry launch (list_mode = 1: one CTA, one record per chunk, STAGE_CAP_MAX bytes of stage) reads them back
   int32_t* over_list;
   int list_mode;
+  const float* panels;  // tcgen05 score phase (decode_kernel_tc): packed (hi, lo) weight panels, see ae_tc.cuh
 };
 
 // ---- CSV, careful path step 1: field boundaries of one record (RFC-4180 quotes) ---------------------------------------------
@@ -602,9 +603,13 @@ __device__ __forceinline__ int avro_walk_schema_b(const uint8_t* __restrict__ ba
 // copy so that it flies under this item's score phase, then score and store.
 // R = 2 (fused Avro): a lane decodes two records into an element-interleaved row pair and scores both in one pass over the
 // weights (ae_forward_pair): a quarter of the weight fetches per record, half the planning work per record.
-template <int D, int MODE, bool FT, int FMT, int R>
+// TC (fused mode, R = 1, CTAs of exactly 4 warps): the score phase runs on the tensor cores (ae_tc.cuh) — the CTA's four warps
+// still fetch, plan and decode independently, but score their 4 x 32 records together as one 128-row tile, so the item loop runs
+// in lock-step across the CTA (a warp that has run out of chunks contributes empty rows until all four are done).
+template <int D, int MODE, bool FT, int FMT, int R, bool TC = false>
 __device__ __forceinline__ void decode_body(const DecodeArgs<D>& a) {
   static_assert(R == 1 || (R == 2 && MODE == 1), "two records per lane only in the fused mode");
+  static_assert(!TC || (MODE == 1 && R == 1), "tensor-core scoring: fused mode, one record per lane");
   extern __shared__ __align__(128) uint8_t smem[];
   constexpr unsigned FULL = 0xffffffffu;
   constexpr int CH = 32 * R;  // records per chunk
@@ -625,6 +630,10 @@ __device__ __forceinline__ void decode_body(const DecodeArgs<D>& a) {
   uint32_t phase = 0;
   unsigned flagged = 0, n_ok = 0, n_err = 0;
   unsigned long long n_bytes = 0;
+  __shared__ uint32_t s_tmem;
+  __shared__ __align__(8) uint64_t mma_bar;
+  TcCtx tc;
+  if (TC) tcs_setup<D>(tc, a.panels, reinterpret_cast<float*>(smem + (size_t)(blockDim.x >> 5) * a.warp_bytes), &s_tmem, &mma_bar, tid);
   const bool list_mode = a.list_mode != 0;
   const long long n_chunks = list_mode ? (long long)min(a.over_list[0], B2_OVERSIZE_CAP) : (a.n + CH - 1) / CH;
   const int warps_per_cta = blockDim.x >> 5;  // the launch picks 8, 4 or 2 warps per CTA: whatever packs most warps into an SM
@@ -727,16 +736,19 @@ __device__ __forceinline__ void decode_body(const DecodeArgs<D>& a) {
   int c_sub = 0, c_cnt = 0, c_b[R], c_e[R], n_sub = 0, n_cnt = 0, n_b[R], n_e[R];
   bool have = next_item(c_row0, c_sub, c_cnt, c_b, c_e);
   float* const xlane = xt + (size_t)lane * xt_stride;
-  while (have) {
-    mbar_wait(full, phase);
-    phase ^= 1u;
+  bool cur = have;  // TC: this warp holds a current item (the loop itself runs while ANY warp of the CTA does)
+  while (TC ? __syncthreads_or(cur) != 0 : have) {
+    if (!TC || cur) {
+      mbar_wait(full, phase);
+      phase ^= 1u;
+    }
     int st[R];
     uint8_t lab[R];
     bool active[R];
 #pragma unroll
     for (int s = 0; s < R; ++s) {
       const int q = lane + 32 * s;
-      active[s] = q >= c_sub && q < c_sub + c_cnt;
+      active[s] = (!TC || cur) && q >= c_sub && q < c_sub + c_cnt;
       st[s] = B2_REC_OK;
       lab[s] = 2;
       float* xrow = xlane + s;  // element j of this record sits at xrow[j * R]
@@ -764,10 +776,21 @@ __device__ __forceinline__ void decode_body(const DecodeArgs<D>& a) {
       }
     }
     __syncwarp();  // every lane is done with the stage
-    have = next_item(n_row0, n_sub, n_cnt, n_b, n_e);
+    if (!TC || cur) have = next_item(n_row0, n_sub, n_cnt, n_b, n_e);
     if (MODE == 1) {
       float mm[R];
-      if (R == 2) {
+      if (TC) {
+        // the lane's row → registers (normalised), then the 128-row tile of the whole CTA through the tensor cores
+        float x[D];
+#pragma unroll
+        for (int i = 0; i < D; i += 2) {
+          float2 v = active[0] ? *reinterpret_cast<const float2*>(xlane + i) : make_float2(0.f, 0.f);
+          if (a.has_norm) v = norm_pair_fast<D>(v, a.nm, i);
+          x[i] = v.x;
+          x[i + 1] = v.y;
+        }
+        mm[0] = tcs_score_row<D, FT, true>(tc, a.w, x, tid);
+      } else if (R == 2) {
         if (active[0] || active[R - 1]) {
           float2* rowp = reinterpret_cast<float2*>(xlane);
           float m2[2] = {0.f, 0.f};
@@ -823,7 +846,9 @@ __device__ __forceinline__ void decode_body(const DecodeArgs<D>& a) {
     c_row0 = n_row0, c_sub = n_sub, c_cnt = n_cnt;
 #pragma unroll
     for (int s = 0; s < R; ++s) c_b[s] = n_b[s], c_e[s] = n_e[s];
+    if (TC) cur = cur && have;
   }
+  if (TC) tcs_teardown<D>(tc, tid);
   if (a.counters) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -858,6 +883,11 @@ __global__ void __launch_bounds__(DEC_NT) decode_kernel(const __grid_constant__ 
 template <int D, int MODE, bool FT, int FMT, int MINB>
 __global__ void __launch_bounds__(DEC_NT_R2, MINB) decode_kernel_r2(const __grid_constant__ DecodeArgs<D> a) {
   decode_body<D, MODE, FT, FMT, (MODE == 1 ? 2 : 1)>(a);
+}
+// tensor-core score phase: CTAs of exactly 4 warps = one 128-row TMEM tile; 512 / TMEM columns of them fit an SM (registers: 5)
+template <int D, bool FT, int FMT>
+__global__ void __launch_bounds__(TCS_ROWS, 512 / TcShape<D>::TMEM_COLS > 5 ? 5 : 512 / TcShape<D>::TMEM_COLS) decode_kernel_tc(const __grid_constant__ DecodeArgs<D> a) {
+  decode_body<D, 1, FT, FMT, 1, true>(a);
 }
 template <int D, int MODE, bool FT, int FMT, int MINB>
 struct DecodeKernel<D, MODE, FT, FMT, 1, MINB> {
@@ -1040,6 +1070,53 @@ static int launch_decode_r(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stream
   return B2_OK;
 }
 
+// Fused decode + score with the score phase on the tensor cores (decode_kernel_tc): CTAs of exactly 4 warps, as many per SM as
+// TMEM columns, registers and shared memory allow; the oversize retry pass runs through the FFMA2 kernel.
+template <int D, bool FT, int FMT>
+static int launch_decode_tc(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stream) {
+  args.stage_cap = choose_stage_cap(args.fmt, args.csv, args.avro, args.json, ctx->record_bytes_hint, 32);
+  args.warp_bytes = 16 + args.stage_cap + 16 + align16i(32 * D * 4) + 16;
+  auto kern = decode_kernel_tc<D, FT, FMT>;
+  auto retry = decode_kernel<D, 1, FT, FMT>;
+  const size_t smem = (size_t)args.warp_bytes * 4 + sizeof(float) * TcShape<D>::TOTAL;
+  const int dyn_max = ctx->smem_optin - 1024;  // the kernel also has a few static words (TMEM base, MMA mbarrier)
+  B2_REQUIRE(smem <= (size_t)dyn_max, "decode (tensor-core score): a CTA needs %zu bytes of shared memory", smem);
+  static thread_local int regs[16] = {0};
+  if (regs[ctx->device & 15] == 0) {
+    B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_max));
+    B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    B2_CUDA(cudaFuncSetAttribute(retry, cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->smem_optin));
+    cudaFuncAttributes fa;
+    B2_CUDA(cudaFuncGetAttributes(&fa, kern));
+    regs[ctx->device & 15] = fa.numRegs > 0 ? fa.numRegs : 128;
+  }
+  int ctas = 512 / TcShape<D>::TMEM_COLS;
+  ctas = min(ctas, 65536 / (((regs[ctx->device & 15] + 7) & ~7) * TCS_ROWS));
+  ctas = min(ctas, (int)((size_t)(228 * 1024 - 1024) / (smem + 1024)));
+  if (ctx->knobs.tc_ctas > 0) ctas = min(ctas, ctx->knobs.tc_ctas);
+  B2_REQUIRE(ctas >= 1, "decode (tensor-core score): kernel does not fit on an SM");
+  const long long n_chunks = (args.n + 31) / 32;
+  long long grid = (long long)ctx->sm_count * ctas;
+  const long long need = (n_chunks + 3) / 4;
+  if (grid > need) grid = need;
+  const bool may_overflow = args.stage_cap < STAGE_CAP_MAX && !(args.fmt == FMT_AVRO && avro_max_record_bytes(args.avro) > 0);
+  args.list_mode = 0;
+  args.over_list = may_overflow ? b2_ctx_oversize_slot(ctx, stream) : nullptr;
+  kern<<<(unsigned)grid, TCS_ROWS, smem, stream>>>(args);
+  B2_CUDA(cudaGetLastError());
+  if (may_overflow) {
+    DecodeArgs<D> r = args;
+    r.list_mode = 1;
+    r.stage_cap = STAGE_CAP_MAX;
+    r.warp_bytes = 16 + r.stage_cap + 16 + align16i(32 * D * 4) + 16;
+    int rw = 4;
+    while (rw > 1 && (size_t)r.warp_bytes * rw > (size_t)ctx->smem_optin) rw >>= 1;
+    retry<<<1, rw * 32, (size_t)r.warp_bytes * rw, stream>>>(r);
+    B2_CUDA(cudaGetLastError());
+  }
+  return B2_OK;
+}
+
 // Records per lane and item.  Default: ONE.  Two records per lane (row-packed FFMA2, ae_forward_pair) were built to cut the weight
 // fetches — 12.5 % fewer executed instructions on Avro-A — and measured SLOWER on B200 (2.3e10 vs 2.6e10 records/s): the loop body
 // no longer fits the instruction cache (ncu: no_instruction becomes the top stall, issue slots 52 % busy at 19 warps/SM;
@@ -1047,6 +1124,9 @@ static int launch_decode_r(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stream
 // context option "decode_r2" = 2 (registers capped at 85: 6 CTAs of 4 warps per SM) or 3 (102 registers, 5 CTAs); 0 / -1 = one.
 template <int D, int MODE, bool FT, int FMT>
 static int launch_decode_fmt(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stream) {
+  if (MODE == 1 && FT && args.panels != nullptr) {  // context option decode_tc: score phase on tcgen05
+    if (MODE == 1) return launch_decode_tc<D, true, FMT>(ctx, args, stream);  // (only the fast-tanh form is instantiated)
+  }
   if (MODE == 1 && FMT == FMT_AVRO) {
     constexpr int R2 = (MODE == 1 && FMT == FMT_AVRO) ? 2 : 1;  // keeps the other instantiations free of R = 2 code
     const int k = ctx->knobs.decode_r2;
@@ -1192,6 +1272,10 @@ static int decode_score_spec(b2_ae* ae, const uint8_t* bytes, const int32_t* off
   args.mse = mse;
   args.flag = flag;
   args.counters = counters;
+  if (ae->ctx->knobs.decode_tc && ae->ctx->knobs.fast_tanh) {
+    rc = b2_ae_tc_panels(ae, &args.panels);
+    if (rc) return rc;
+  }
   if (ae->ctx->knobs.fast_tanh) return launch_decode<D, 1, true>(ae->ctx, args, stream);
   return launch_decode<D, 1, false>(ae->ctx, args, stream);
 }

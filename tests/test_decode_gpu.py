@@ -375,3 +375,37 @@ def test_two_records_per_lane_variant_is_bit_identical(cuda_device, fmt):
             for a, b in zip(res[(0, n)][:4], res[(mode, n)][:4]):
                 np.testing.assert_array_equal(a, b)
             assert res[(0, n)][4] == res[(mode, n)][4]
+
+
+@pytest.mark.parametrize("fmt", ["avro_a", "csv"])
+def test_tensor_core_score_phase_variant_agrees(cuda_device, fmt):
+    """decode_kernel_tc (context option decode_tc = 1; not the default: slower than the FFMA2 score phase on B200): the same
+    statuses, labels and counters, scores within the parity tolerance of the default kernel's, flags equal away from the threshold."""
+    x = synth.sensor_rows(50_003, seed=41)
+    if fmt == "avro_a":
+        data, offs = synth.avro_a_batch(x)
+        kw, skip = dict(avro_schema=schemas.schema_a_json()), 5
+    else:
+        data, offs = synth.csv_batch(x, seed=41)
+        kw, skip = dict(csv_kinds=SENSOR_KINDS), 0
+    data, offs, bad = synth.corrupt_batch(data, offs, fmt, 1e-3, seed=2)
+    m = _model18()
+    res = {}
+    try:
+        for tc in (0, 1):
+            bs.keras.set_option("decode_tc", tc)
+            for n in (50_003, 127, 129, 1):
+                rb = dec.RecordBatch(data[: offs[n]], offs[: n + 1], skip_prefix=skip)
+                cnt = torch.zeros(4, dtype=torch.int64, device="cuda")
+                mse, flag, label, status = dec.decode_score(m, rb, counters=cnt, **kw)
+                res[(tc, n)] = (mse.cpu().numpy().astype(np.float64), flag.cpu().numpy(), status.cpu().numpy(), cnt.cpu().tolist())
+    finally:
+        bs.keras.set_option("decode_tc", 0)
+    for n in (50_003, 127, 129, 1):
+        a, b = res[(0, n)], res[(1, n)]
+        np.testing.assert_array_equal(a[2], b[2])
+        ok = a[2] == 0
+        assert np.array_equal(np.isnan(a[0]), np.isnan(b[0])) and (np.abs(a[0][ok] - b[0][ok]) <= np.maximum(1e-5 * a[0][ok], 1e-7)).all()
+        safe = ok & (np.abs(a[0] - 5.0) > 1e-4)
+        np.testing.assert_array_equal(a[1][safe], b[1][safe])
+        assert a[3][0] == b[3][0] and a[3][2] == b[3][2] and a[3][3] == b[3][3]

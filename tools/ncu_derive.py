@@ -6,9 +6,9 @@ rows = json.load(open(os.path.join(ROOT, "profiles", "r2_ncu_full_summary.json")
 RECORDS = {  # kernel-name fragment → (key, records of that launch)
     "ae_score_tc_kernel<30": ("ae_score_d30", 1 << 22),
     "ae_score_kernel<18": ("ae_score_d18", 1 << 22),
-    "decode_kernel<18, 1, true, 0>": ("decode_score_csv", 1 << 20),
-    "decode_kernel<18, 1, true, 1>": ("decode_score_avro_a", 1 << 20),   # first Avro launch = avro_a (prof_all order)
-    "decode_kernel<18, 1, true, 2>": ("decode_score_json", 1 << 19),
+    "decode_kernel<18, 1, 1, 0>": ("decode_score_csv", 1 << 20),
+    "decode_kernel<18, 1, 1, 1>": ("decode_score_avro_a", 1 << 20),   # first Avro launch = avro_a (prof_all order)
+    "decode_kernel<18, 1, 1, 2>": ("decode_score_json", 1 << 19),
 }
 instr, traffic, seen = {}, {}, {}
 def num(d, k):
@@ -17,6 +17,8 @@ def num(d, k):
 def to_bytes(v, unit):
     return v * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(unit, 1)
 for d in rows:
+    if "retry" in str(d.get("note", "")):
+        continue
     for frag, (key, n) in RECORDS.items():
         if frag in d["kernel"]:
             if key == "decode_score_avro_a" and key in seen:
