@@ -35,7 +35,37 @@ struct NormP {             // normalize_fn table; kind: B2_NORM_*
   float lo[D];
   float range[D];
   float rinv[D];           // RN(1 / range), filled by the host
+  // Branch-free form for the packed paths (norm_pair_fast / norm_rows_fast): the three kinds become constants of ONE instruction
+  // sequence, so a feature costs no compare / select on its kind —  out = fma(q, m2, a2) with q = (v & mask - flo) / frange:
+  //   SCALE     mask ~0, flo lo, frange range, frinv = fcorr = 1/range, m2 2, a2 -1
+  //   IDENTITY  mask ~0, flo 0,  frange 1,     frinv 1, fcorr -0 (keeps the sign of a zero), m2 1, a2 -0      → v
+  //   ZERO      mask 0,  flo 0,  frange 1,     frinv 1, fcorr 1,  m2 0, a2 +0                                 → +0
+  uint32_t mask[D];
+  float flo[D], frange[D], frinv[D], fcorr[D], m2[D], a2[D];
 };
+
+// b2_norm (C ABI) → NormP<D>; returns whether a table was given
+template <int D>
+static inline int norm_fill(const b2_norm* norm, NormP<D>& nm, int n = D) {
+  memset(&nm, 0, sizeof(nm));
+  if (!norm || norm->n <= 0) return 0;
+  for (int j = 0; j < n; ++j) {
+    const int k = norm->kind[j];
+    nm.kind[j] = k;
+    nm.lo[j] = norm->lo[j];
+    nm.range[j] = norm->range[j];
+    nm.rinv[j] = 1.0f / norm->range[j];
+    const bool sc = k == B2_NORM_SCALE, zero = k == B2_NORM_ZERO;
+    nm.mask[j] = zero ? 0u : 0xFFFFFFFFu;
+    nm.flo[j] = sc ? nm.lo[j] : 0.0f;
+    nm.frange[j] = sc ? nm.range[j] : 1.0f;
+    nm.frinv[j] = sc ? nm.rinv[j] : 1.0f;
+    nm.fcorr[j] = sc ? nm.rinv[j] : (zero ? 1.0f : -0.0f);
+    nm.m2[j] = sc ? 2.0f : (zero ? 0.0f : 1.0f);
+    nm.a2[j] = sc ? -1.0f : (zero ? 0.0f : -0.0f);
+  }
+  return 1;
+}
 
 // Pack Keras flat order (kernel0[in,out], bias0, kernel1, ...) into AeW<D>.
 template <int D>
@@ -124,24 +154,23 @@ __device__ __forceinline__ float norm_feature(float v, int kind, float lo, float
 // correctly rounded quotient t/range (Markstein's theorem) for every finite t whose quotient neither overflows nor
 // lands in the subnormal range.  A subnormal-range slip is absorbed by the final `*2 - 1` (|q| < 2^-25 gives -1 either
 // way); an infinite t or an overflowing quotient shows up as q0 = ±inf, which is then the IEEE result and is selected
-// explicitly (the correction step would turn it into NaN).  NaN propagates.  Hence bit-identical to norm_feature() for
+// explicitly (the correction step would turn it into NaN).  NaN propagates.  The other two kinds run through the same
+// instructions with neutral constants (see NormP).  Hence bit-identical to norm_feature() for
 // 2^-64 <= |range| <= 2^64 (beyond that the residual r itself can go subnormal); checked exhaustively on the device over all
 // 2^32 inputs by b2_selftest_normalize (tests/test_normalize_gpu.py).
 template <int D>
 __device__ __forceinline__ float2 norm_pair_fast(float2 v, const NormP<D>& nm, int i) {
-  const float2 lo = make_float2(nm.lo[i], nm.lo[i + 1]);
-  const float2 rg = make_float2(nm.range[i], nm.range[i + 1]);
-  const float2 ri = make_float2(nm.rinv[i], nm.rinv[i + 1]);
-  const float2 t = fma2(lo, splat(-1.0f), v);  // v - lo (exactly one rounding, like the reference's subtraction)
+  const float2 vm = make_float2(__uint_as_float(__float_as_uint(v.x) & nm.mask[i]), __uint_as_float(__float_as_uint(v.y) & nm.mask[i + 1]));
+  const float2 lo = make_float2(nm.flo[i], nm.flo[i + 1]);
+  const float2 rg = make_float2(nm.frange[i], nm.frange[i + 1]);
+  const float2 ri = make_float2(nm.frinv[i], nm.frinv[i + 1]);
+  const float2 t = fma2(lo, splat(-1.0f), vm);  // v - lo (exactly one rounding, like the reference's subtraction)
   const float2 q0 = mul2(t, ri);
   const float2 r = fma2(make_float2(-q0.x, -q0.y), rg, t);
-  float2 q = fma2(r, ri, q0);
+  float2 q = fma2(r, make_float2(nm.fcorr[i], nm.fcorr[i + 1]), q0);
   if (fabsf(q0.x) == __int_as_float(0x7F800000)) q.x = q0.x;
   if (fabsf(q0.y) == __int_as_float(0x7F800000)) q.y = q0.y;
-  float2 o = fma2(q, splat(2.0f), splat(-1.0f));
-  if (nm.kind[i] != B2_NORM_SCALE) o.x = nm.kind[i] == B2_NORM_ZERO ? 0.0f : v.x;
-  if (nm.kind[i + 1] != B2_NORM_SCALE) o.y = nm.kind[i + 1] == B2_NORM_ZERO ? 0.0f : v.y;
-  return o;
+  return fma2(q, make_float2(nm.m2[i], nm.m2[i + 1]), make_float2(nm.a2[i], nm.a2[i + 1]));
 }
 
 // Forward pass for R records living in shared-memory rows row[r] (D floats each, 8-byte aligned).
@@ -251,16 +280,15 @@ __device__ __forceinline__ void ae_forward_rows(const AeW<D>& w, const NormP<D>&
 // partial sums, so both forms give the same bits.
 template <int D>
 __device__ __forceinline__ float2 norm_rows_fast(float2 v, const NormP<D>& nm, int i) {  // feature i of two records
-  const int kind = nm.kind[i];
-  if (kind == B2_NORM_ZERO) return make_float2(0.0f, 0.0f);
-  if (kind != B2_NORM_SCALE) return v;
-  const float2 t = fma2(splat(nm.lo[i]), splat(-1.0f), v);  // v - lo, one rounding
-  const float2 q0 = mul2(t, splat(nm.rinv[i]));
-  const float2 r = fma2(make_float2(-q0.x, -q0.y), splat(nm.range[i]), t);
-  float2 q = fma2(r, splat(nm.rinv[i]), q0);
+  const uint32_t mk = nm.mask[i];
+  const float2 vm = make_float2(__uint_as_float(__float_as_uint(v.x) & mk), __uint_as_float(__float_as_uint(v.y) & mk));
+  const float2 t = fma2(splat(nm.flo[i]), splat(-1.0f), vm);  // v - lo, one rounding
+  const float2 q0 = mul2(t, splat(nm.frinv[i]));
+  const float2 r = fma2(make_float2(-q0.x, -q0.y), splat(nm.frange[i]), t);
+  float2 q = fma2(r, splat(nm.fcorr[i]), q0);
   if (fabsf(q0.x) == __int_as_float(0x7F800000)) q.x = q0.x;
   if (fabsf(q0.y) == __int_as_float(0x7F800000)) q.y = q0.y;
-  return fma2(q, splat(2.0f), splat(-1.0f));
+  return fma2(q, splat(nm.m2[i]), splat(nm.a2[i]));
 }
 
 template <int D, bool NORM, bool FAST_TANH>

@@ -216,16 +216,7 @@ static int score_spec(b2_ae* ae, const float* x, int64_t n, const b2_norm* norm,
                       float* recon, unsigned long long* counters, cudaStream_t stream) {
   ScoreArgs<D> args;
   ae_pack_weights<D>(ae->h_w.data(), args.w);
-  memset(&args.nm, 0, sizeof(args.nm));
-  const bool has_norm = norm && norm->n > 0;
-  if (has_norm) {
-    for (int j = 0; j < D; ++j) {
-      args.nm.kind[j] = norm->kind[j];
-      args.nm.lo[j] = norm->lo[j];
-      args.nm.range[j] = norm->range[j];
-      args.nm.rinv[j] = 1.0f / norm->range[j];
-    }
-  }
+  const bool has_norm = norm_fill<D>(norm, args.nm) != 0;
   args.x = x;
   args.mse = mse;
   args.flag = flag;

@@ -151,15 +151,7 @@ template <int D>
 static int score_tc_spec(b2_ae* ae, const float* x, int64_t n, const b2_norm* norm, float threshold, float* mse, uint8_t* flag,
                          unsigned long long* counters, cudaStream_t stream) {
   ScoreTcArgs<D> args;
-  memset(&args.nm, 0, sizeof(args.nm));
-  const bool has_norm = norm && norm->n > 0;
-  if (has_norm)
-    for (int j = 0; j < D; ++j) {
-      args.nm.kind[j] = norm->kind[j];
-      args.nm.lo[j] = norm->lo[j];
-      args.nm.range[j] = norm->range[j];
-      args.nm.rinv[j] = 1.0f / norm->range[j];
-    }
+  const bool has_norm = norm_fill<D>(norm, args.nm) != 0;
   int rc = b2_ae_tc_panels(ae, &args.panels);
   if (rc) return rc;
   args.x = x;

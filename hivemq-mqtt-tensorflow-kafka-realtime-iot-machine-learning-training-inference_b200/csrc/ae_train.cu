@@ -584,15 +584,7 @@ __global__ void ae_apply_kernel(const ApplyArgs a) {
 // ---- host side -------------------------------------------------------------------------------------------------------
 template <int D>
 static void fill_norm(const b2_norm* norm, NormP<D>& nm, int& has_norm) {
-  memset(&nm, 0, sizeof(nm));
-  has_norm = norm && norm->n > 0;
-  if (has_norm)
-    for (int j = 0; j < D; ++j) {
-      nm.kind[j] = norm->kind[j];
-      nm.lo[j] = norm->lo[j];
-      nm.range[j] = norm->range[j];
-      nm.rinv[j] = 1.0f / norm->range[j];
-    }
+  has_norm = norm_fill<D>(norm, nm);
 }
 
 template <int D>

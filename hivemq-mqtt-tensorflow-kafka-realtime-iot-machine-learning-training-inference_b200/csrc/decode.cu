@@ -1259,15 +1259,7 @@ static int decode_score_spec(b2_ae* ae, const uint8_t* bytes, const int32_t* off
   args.status = status;
   args.label = label;
   ae_pack_weights<D>(ae->h_w.data(), args.w);
-  args.has_norm = norm && norm->n > 0;
-  if (args.has_norm) {
-    for (int j = 0; j < D; ++j) {
-      args.nm.kind[j] = norm->kind[j];
-      args.nm.lo[j] = norm->lo[j];
-      args.nm.range[j] = norm->range[j];
-      args.nm.rinv[j] = 1.0f / norm->range[j];
-    }
-  }
+  args.has_norm = norm_fill<D>(norm, args.nm);
   args.threshold = threshold;
   args.mse = mse;
   args.flag = flag;

@@ -68,14 +68,9 @@ __global__ void __launch_bounds__(256) normalize_selftest_kernel(const __grid_co
 
 int fill(const b2_norm* norm, int d, NormMax& nm) {
   B2_REQUIRE(norm && norm->n == d && d >= 1 && d <= B2_MAX_WIDTH, "normalize: table has %d features, rows have %d", norm ? norm->n : 0, d);
-  memset(&nm, 0, sizeof(nm));
-  for (int j = 0; j < d; ++j) {
+  for (int j = 0; j < d; ++j)
     B2_REQUIRE(norm->kind[j] >= B2_NORM_IDENTITY && norm->kind[j] <= B2_NORM_SCALE, "normalize: kind[%d]=%d unknown", j, norm->kind[j]);
-    nm.kind[j] = norm->kind[j];
-    nm.lo[j] = norm->lo[j];
-    nm.range[j] = norm->range[j];
-    nm.rinv[j] = 1.0f / norm->range[j];
-  }
+  norm_fill<B2_MAX_WIDTH>(norm, nm, d);
   return B2_OK;
 }
 

@@ -1,6 +1,6 @@
 """GPU diagnostic: error of the fused score kernel against the float64 oracle (accurate vs fast tanh)."""
 import os, sys, numpy as np
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import b200_sensor as bs
 from oracle import cpu_oracle as orc
 A = [1, 2, 1, 2]

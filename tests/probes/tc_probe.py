@@ -1,6 +1,6 @@
 """K1t probe: the tcgen05 score kernel against the float64 oracle and against the FP32 kernel (error statistics, throughput)."""
 import os, sys, time
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np, torch
 import b200_sensor as bs
 from oracle import cpu_oracle as orc

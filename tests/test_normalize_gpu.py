@@ -54,8 +54,8 @@ def test_division_free_form_equals_ieee_division_for_every_float32(cuda_device):
     differences between norm_pair_fast and sub -> IEEE div -> fma on the device."""
     l, ctx = _ffi.lib(), bs.keras.get_ctx(0)
     tables = [bs.schemas.norm_arrays(),
-              (np.full(8, 2, np.int32), np.array([0, -1e18, 3, 1e-18, 0.1, -7, 123456.7, 0], np.float32),
-               np.array([3.0, 1e18, 1e-18, 3e-18, 0.7, 1.0000001, 3.3333333e7, 1.8e19], np.float32))]
+              (np.array([2, 2, 2, 2, 2, 2, 2, 2, 0, 1], np.int32), np.array([0, -1e18, 3, 1e-18, 0.1, -7, 123456.7, 0, 5, 5], np.float32),
+               np.array([3.0, 1e18, 1e-18, 3e-18, 0.7, 1.0000001, 3.3333333e7, 1.8e19, 9, 9], np.float32))]  # + identity, zero kinds
     for kind, lo, rng in tables:
         nm = _ffi.make_norm(kind, lo, rng)
         out = torch.zeros(2, dtype=torch.int64, device="cuda")
