@@ -121,6 +121,8 @@ _PROTOTYPES = {
     "b2_format_rows_bound": (C.c_int64, [C.c_int]),
     "b2_format_rows": (C.c_int, [_P, _P, C.c_int64, C.c_int, C.c_int, _P, C.c_int64, _P, _P, _P, _P]),
     "b2_kafka_index_records": (C.c_int, [_P, _P, C.c_int64, _P, _P, C.c_int64, C.c_int, _P, _P, _P, _P]),
+    "b2_kafka_inflate_sizes": (C.c_int, [_P, _P, C.c_int64, _P, C.c_int64, C.c_int, _P, _P, _P]),
+    "b2_kafka_inflate": (C.c_int, [_P, _P, C.c_int64, _P, C.c_int64, _P, _P, _P, _P, C.c_int64, _P]),
     "b2_kafka_gather_values": (C.c_int, [_P, _P, _P, _P, C.c_int64, _P, _P, _P]),
     "b2_threshold_sweep_scratch_bytes": (C.c_int64, [C.c_int64]),
     "b2_threshold_sweep": (C.c_int, [_P, _P, _P, C.c_int64, _P, _P, _P, _P, _P, C.c_int64, _P]),

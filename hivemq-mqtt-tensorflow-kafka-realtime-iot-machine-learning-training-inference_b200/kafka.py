@@ -1,7 +1,8 @@
 """Kafka record-batch (message format v2) framing: broker bytes → the ``RecordBatch`` of message values the decoders take.
 
 In the reference this is tensorflow-io's ``KafkaDataset`` / librdkafka (cardata-v1.py:10).  ``scan_batches`` walks the batch
-chain on the host (12 bytes per batch), ``values_from_segment`` lets the GPU check every batch's CRC-32C, walk its records
+chain on the host (12 bytes per batch), ``values_from_segment`` lets the GPU inflate compressed batches (gzip / Snappy / LZ4;
+``b2_kafka_inflate_sizes`` + ``b2_kafka_inflate``), check every batch's CRC-32C, walk its records
 (``b2_kafka_index_records``) and pack the values back to back (``b2_kafka_gather_values``).  ``write_segment`` is the inverse,
 host side, for tests and synthetic input (Kafka itself is replaced offline by in-memory bytes, BASELINE.json).
 """
@@ -54,9 +55,37 @@ def _varint(v: int) -> bytes:
     return bytes(out)
 
 
+_CODECS = {None: 0, "none": 0, "gzip": 1, "snappy": 2, "snappy-xerial": 2, "lz4": 3}
+
+
+def _compress(records: bytes, compression) -> bytes:
+    """The records section of a batch under ``compression.type`` (test / synthetic input only: gzip from the standard library,
+    Snappy and LZ4 frames from pyarrow; "snappy-xerial" adds the Java client's SnappyOutputStream framing)."""
+    if compression in (None, "none"):
+        return records
+    if compression == "gzip":
+        import gzip
+
+        return gzip.compress(records)
+    import pyarrow as pa
+
+    if compression == "snappy":
+        return pa.compress(records, codec="snappy", asbytes=True)
+    if compression == "snappy-xerial":
+        out = b"\x82SNAPPY\x00" + struct.pack(">ii", 1, 1)
+        for i in range(0, len(records), 32768):
+            z = pa.compress(records[i:i + 32768], codec="snappy", asbytes=True)
+            out += struct.pack(">i", len(z)) + z
+        return out
+    if compression == "lz4":
+        return pa.compress(records, codec="lz4", asbytes=True)
+    raise ValueError(f"unknown compression {compression!r}")
+
+
 def write_segment(values: Sequence[bytes], records_per_batch: int = 500, keys: Optional[Sequence[Optional[bytes]]] = None,
-                  base_offset: int = 0, headers: bool = False) -> bytes:
-    """Message values → log-segment bytes: uncompressed v2 record batches of ``records_per_batch`` records each."""
+                  base_offset: int = 0, headers: bool = False, compression=None) -> bytes:
+    """Message values → log-segment bytes: v2 record batches of ``records_per_batch`` records each, their records sections
+    compressed as a whole when ``compression`` is "gzip" / "snappy" / "snappy-xerial" / "lz4" (a list gives one per batch)."""
     out = bytearray()
     n = len(values)
     for b0 in range(0, n, records_per_batch):
@@ -73,7 +102,8 @@ def write_segment(values: Sequence[bytes], records_per_batch: int = 500, keys: O
             else:
                 body += _varint(0)
             recs += _varint(len(body)) + body
-        after_crc = struct.pack(">hiqqqhii", 0, cnt - 1, 1567606196000, 1567606196000 + 3 * cnt, -1, -1, -1, cnt) + bytes(recs)
+        comp = compression[(b0 // records_per_batch) % len(compression)] if isinstance(compression, (list, tuple)) else compression
+        after_crc = struct.pack(">hiqqqhii", _CODECS[comp], cnt - 1, 1567606196000, 1567606196000 + 3 * cnt, -1, -1, -1, cnt) + _compress(bytes(recs), comp)
         batch_len = 4 + 1 + 4 + len(after_crc)                               # leader epoch, magic, crc, rest
         out += struct.pack(">qiib", base_offset + b0, batch_len, 0, 2) + struct.pack(">I", crc32c(after_crc)) + after_crc
     return bytes(out)
@@ -116,15 +146,41 @@ def values_from_segment(segment, verify_crc: bool = True, device: Optional[torch
     if nb:
         np.cumsum(cnt[:-1], out=base[1:])
     d = seg_t.to(dev).contiguous()
+    lib, ctx = _ffi.lib(), get_ctx(dev.index)
+    pre_status = None
+    hb = host.numpy()
+    if nb and (hb[pos + 22] & 7).any():
+        # compressed batches: inflate into a rebuilt, uncompressed copy of the segment (two passes, one thread per batch), then go on
+        with torch.cuda.device(dev):
+            pos_d = torch.from_numpy(pos).to(dev)
+            sizes = torch.zeros(nb, dtype=torch.int64, device=dev)
+            pre_status = torch.zeros(nb, dtype=torch.int32, device=dev)
+            _ffi.check(lib.b2_kafka_inflate_sizes(ctx, _ffi.ptr(d), int(d.numel()), _ffi.ptr(pos_d), nb, 1 if verify_crc else 0, _ffi.ptr(sizes),
+                                                  _ffi.ptr(pre_status), _stream_ptr()), "b2_kafka_inflate_sizes")
+            out_pos = torch.zeros(nb + 1, dtype=torch.int64, device=dev)
+            torch.cumsum(sizes + _HEADER, 0, out=out_pos[1:])
+            total_out = int(out_pos[-1])
+            if total_out >= 2 ** 31:
+                raise ValueError("inflated segment exceeds int32 offsets")
+            rebuilt = torch.zeros(max(total_out, 1), dtype=torch.uint8, device=dev)
+            _ffi.check(lib.b2_kafka_inflate(ctx, _ffi.ptr(d), int(d.numel()), _ffi.ptr(pos_d), nb, _ffi.ptr(sizes), _ffi.ptr(out_pos),
+                                            _ffi.ptr(pre_status), _ffi.ptr(rebuilt), total_out, _stream_ptr()), "b2_kafka_inflate")
+            d, pos, verify_crc = rebuilt[:max(total_out, 1)], out_pos[:nb].cpu().numpy(), False
     begin = torch.zeros(max(n, 1), dtype=torch.int32, device=dev)
     end = torch.zeros(max(n, 1), dtype=torch.int32, device=dev)
     status = torch.zeros(max(nb, 1), dtype=torch.int32, device=dev)
-    lib, ctx = _ffi.lib(), get_ctx(dev.index)
     with torch.cuda.device(dev):
-        pos_d, base_d = torch.from_numpy(pos).to(dev), torch.from_numpy(base).to(dev)
+        pos_d, base_d = torch.from_numpy(np.ascontiguousarray(pos)).to(dev), torch.from_numpy(base).to(dev)
         _ffi.check(lib.b2_kafka_index_records(ctx, _ffi.ptr(d), int(d.numel()), _ffi.ptr(pos_d), _ffi.ptr(base_d), nb, 1 if verify_crc else 0,
                                               _ffi.ptr(begin), _ffi.ptr(end), _ffi.ptr(status), _stream_ptr()), "b2_kafka_index_records")
         status = status[:nb]
+        if pre_status is not None:  # a batch refused before / while inflating: its status wins and its records are blanked
+            refused = pre_status != 0
+            status = torch.where(refused, pre_status, status)
+            if n and bool(refused.any()):
+                rec_bad = torch.repeat_interleave(refused, torch.from_numpy(cnt).to(dev))
+                begin[:n][rec_bad] = 0
+                end[:n][rec_bad] = 0
         if raise_on_error and nb:
             bad = torch.nonzero(status).flatten()
             if bad.numel():

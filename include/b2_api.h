@@ -312,12 +312,26 @@ int  b2_format_rows(b2_ctx* ctx, const float* x_dev, int64_t n, int n_cols, int 
 #define B2_FRAME_BAD_MAGIC  1  /* not message format v2 */
 #define B2_FRAME_BAD_CRC    2
 #define B2_FRAME_TRUNCATED  3  /* batch or record runs past its container */
-#define B2_FRAME_COMPRESSED 4  /* gzip / snappy / lz4 / zstd batch: not inflated here */
+#define B2_FRAME_COMPRESSED 4  /* compressed batch handed to b2_kafka_index_records (inflate it first), or a zstd batch (no decoder here) */
 #define B2_FRAME_CONTROL    5  /* control batch (attributes bit 5: transaction markers); consumers never see its records */
 int  b2_kafka_index_records(b2_ctx* ctx, const uint8_t* bytes_dev, int64_t n_bytes, const int64_t* batch_pos_dev, const int64_t* rec_base_dev,
                             int64_t n_batches, int verify_crc, int32_t* begin_dev, int32_t* end_dev, int32_t* status_dev, void* stream);
 int  b2_kafka_gather_values(b2_ctx* ctx, const uint8_t* bytes_dev, const int32_t* begin_dev, const int32_t* end_dev, int64_t n,
                             const int32_t* out_offs_dev, uint8_t* out_bytes_dev, void* stream);
+/* Compressed batches (attributes & 7: 1 gzip, 2 Snappy — raw or the Java client's xerial framing —, 3 LZ4 frame): what librdkafka
+ * inflates underneath KafkaDataset whatever the producer's compression.type was (cardata-v1.py:10).  Two passes, one thread per
+ * batch.  b2_kafka_inflate_sizes: status_dev int32[n_batches] (header checks, CRC-32C over the bytes as stored when verify_crc;
+ * zstd → B2_FRAME_COMPRESSED, a damaged stream → B2_FRAME_TRUNCATED) and sizes_dev int64[n_batches] = bytes of each batch's
+ * records section once inflated (as stored for an uncompressed batch, 0 for a refused one).  The caller lays the rebuilt segment
+ * out: out_pos[b+1] = out_pos[b] + 61 + sizes[b].  b2_kafka_inflate writes every batch there as an UNCOMPRESSED batch (header
+ * copied, codec bits cleared, batchLength adjusted, records inflated); the result goes through b2_kafka_index_records with
+ * verify_crc = 0 (the stored CRC belongs to the compressed bytes and was checked in the first pass) — blank the records of the
+ * batches whose first-pass status is not B2_FRAME_OK. */
+int  b2_kafka_inflate_sizes(b2_ctx* ctx, const uint8_t* bytes_dev, int64_t n_bytes, const int64_t* batch_pos_dev, int64_t n_batches,
+                            int verify_crc, int64_t* sizes_dev, int32_t* status_dev, void* stream);
+int  b2_kafka_inflate(b2_ctx* ctx, const uint8_t* bytes_dev, int64_t n_bytes, const int64_t* batch_pos_dev, int64_t n_batches,
+                      const int64_t* sizes_dev, const int64_t* out_pos_dev, int32_t* status_dev, uint8_t* out_dev, int64_t out_bytes,
+                      void* stream);
 
 /* ---- evaluation metrics ----------------------------------------------------------------------
  * The threshold sweep behind sklearn.metrics.roc_curve / precision_recall_curve as the notebooks call them on the

@@ -31,11 +31,12 @@ def test_bad_batches_are_refused_not_fatal(cuda_device):
     seg = bytearray(bs.kafka.write_segment(vals, records_per_batch=100))
     pos, _ = bs.kafka.scan_batches(bytes(seg))
     seg[pos[1] + 80] ^= 0x01      # payload bit flip → CRC mismatch
-    seg[pos[2] + 22] |= 0x02      # attributes: snappy
+    seg[pos[2] + 22] |= 0x04      # attributes: zstd (no decoder here); the stored CRC no longer matches either
     with pytest.raises(bs.kafka.FrameError):
         bs.kafka.values_from_segment(bytes(seg))
     rb, st = bs.kafka.values_from_segment(bytes(seg), raise_on_error=False)
-    assert st.cpu().tolist() == [0, 2, 4]
+    assert st.cpu().tolist() == [0, 2, 2]
+    assert bs.kafka.values_from_segment(bytes(seg), raise_on_error=False, verify_crc=False)[1].cpu().tolist() == [0, 0, 4]
     d, o = rb.data.cpu().numpy().tobytes(), rb.offsets.cpu().numpy()
     got = [d[o[i]:o[i + 1]] for i in range(300)]
     assert got[:100] == vals[:100] and all(g == b"" for g in got[100:])
@@ -97,3 +98,37 @@ def test_hostile_lengths_are_truncation_not_a_fault(cuda_device):
     torch.cuda.synchronize()
     rb, st = bs.kafka.values_from_segment(bs.kafka.write_segment([b"still", b"alive"]))
     assert rb.n == 2 and not st.any()
+
+
+@pytest.mark.parametrize("compression", ["gzip", "snappy", "snappy-xerial", "lz4", ["gzip", None, "lz4", "snappy"]])
+def test_compressed_batches_are_inflated(cuda_device, compression):
+    """Producer-side compression.type (records section compressed as a whole): the values come out as from the uncompressed
+    segment, CRC-32C is checked over the bytes as stored, a damaged stream / zstd batch is refused without touching the others."""
+    g = np.random.default_rng(3)
+    rows = synth.sensor_rows(3000, seed=8)
+    data, offs = synth.avro_a_batch(rows)
+    vals = [data[offs[i]:offs[i + 1]].tobytes() for i in range(3000)]
+    vals[17], vals[18] = None, b""
+    keys = [None if i % 5 else b"car%d" % i for i in range(3000)]
+    seg = bs.kafka.write_segment(vals, records_per_batch=250, keys=keys, headers=True, compression=compression)
+    plain = bs.kafka.write_segment(vals, records_per_batch=250, keys=keys, headers=True)
+    rb, st = bs.kafka.values_from_segment(seg)
+    ref, _ = bs.kafka.values_from_segment(plain)
+    assert not st.any() and torch.equal(rb.offsets, ref.offsets) and torch.equal(rb.data, ref.data)
+    # damage: flip a byte inside the compressed payload of batch 1 (CRC mismatch), then with the CRC check off (stream error or
+    # different bytes — either way the batch must not take the others down)
+    pos, _ = bs.kafka.scan_batches(seg)
+    bad = bytearray(seg)
+    bad[pos[1] + 61 + 20] ^= 0x5A
+    rb2, st2 = bs.kafka.values_from_segment(bytes(bad), raise_on_error=False)
+    s2 = st2.cpu().tolist()
+    assert s2[1] == 2 and s2[0] == 0 and all(v == 0 for v in s2[2:])
+    o, o2 = ref.offsets.cpu().numpy(), rb2.offsets.cpu().numpy()
+    assert (np.diff(o2)[250:500] == 0).all() and np.array_equal(np.diff(o2)[:250], np.diff(o)[:250]) and np.array_equal(np.diff(o2)[500:], np.diff(o)[500:])
+    rb3, st3 = bs.kafka.values_from_segment(bytes(bad), raise_on_error=False, verify_crc=False)
+    assert st3.cpu().tolist()[0] == 0 and rb3.n == 3000
+    # zstd (codec 4) is reported, not inflated
+    z = bytearray(seg)
+    z[pos[2] + 22] = (z[pos[2] + 22] & ~7) | 4
+    _, st4 = bs.kafka.values_from_segment(bytes(z), raise_on_error=False, verify_crc=False)
+    assert st4.cpu().tolist()[2] == 4
