@@ -40,7 +40,7 @@ struct b2_knobs {
   int no_bulk = 0;        // B2_NO_BULK       1: plain loads instead of bulk async copies in ae_score
   int force_generic = 0;  // B2_FORCE_GENERIC 1: generic Dense-stack kernel even for D-14-7-7-D
   int avro_generic = 0;   // B2_AVRO_GENERIC  1: interpreted Avro walk even for the two known schemas
-  int lstm_tc = 1;        // B2_LSTM_TC       0: FP32 FMA LSTM kernel instead of the tcgen05 one
+  int lstm_tc = 2;        // B2_LSTM_TC       LSTM forward: 2 tcgen05 kernel, two tiles per CTA when the batch is large (default), 3 always two, 1 one tile, 0 FP32 FMA kernel
   int score_tc = -1;      // B2_SCORE_TC      pre-decoded scoring: -1 auto (tcgen05 kernel K1t for D = 30, FFMA2 for D = 18), 0 FFMA2, 1 K1t, 2 K1t with all four layers on tcgen05
   int decode_r2 = 0;      // B2_DECODE_R2     fused Avro decode: 0 one record per lane (default), 2 / 3 two (85 / 102 registers)
   int decode_tc = 0;      // B2_DECODE_TC     fused decode + score: 1 = score phase on tcgen05 (decode_kernel_tc)

@@ -16,12 +16,20 @@
 //     columns (= 8 units × 4 gates, columns are gate-interleaved) at a time, applies the gates with c in registers, and
 //     writes h_new straight back into the TMEM A columns.
 // Algorithmic bytes per record-step: 4F read + 4F written; weights are read once per CTA.
+//
+// Two tiles per CTA (G = 2, the default): ncu shows the threads of the one-tile kernel parked on the MMA-done mbarrier for ≈ 45 %
+// of their time while the tensor pipe is 20 % busy — the per-layer chain issue → MMA → commit → read-back → gates is serial.  The
+// weights fill 174 KB of shared memory, so a second CTA cannot share the SM; instead one CTA of 512 threads runs TWO 128-sequence
+// tiles, one per group of 256 threads, each with its own A panel in TMEM (2 x 160 columns) and ONE accumulator (128 columns)
+// that the groups take in turns: a group pulls its whole accumulator into registers right after its MMAs complete and hands the
+// accumulator to the other group, whose MMAs then run under this group's gate arithmetic.  TMEM: 320 + 128 = 448 of 512 columns.
 #include "lstm_tc.h"
 
-constexpr int TC_NT = 128;      // sequences per CTA = TMEM lanes
-constexpr int TC_THREADS = 256; // two threads per sequence: thread t and t + 128 share TMEM lane t and split the units between them
-constexpr int TC_ALO = 80;    // TMEM column of the "lo" copy of the A panel (hi copy at 0); the panel is 80 columns wide
-constexpr int TC_D = 256;     // TMEM column of the accumulator (≤ 128 columns)
+constexpr int TC_NT = 128;      // sequences per tile = TMEM lanes
+constexpr int TC_THREADS = 256; // threads per tile: thread t and t + 128 share TMEM lane t and split the units between them
+constexpr int TC_ALO = 80;    // TMEM column of the "lo" copy of a tile's A panel (hi copy at 0); the panel is 80 columns wide
+constexpr int TC_PANEL = 160; // TMEM columns of one tile's A panel (hi + lo); tile g's panel starts at column g * TC_PANEL
+constexpr int TC_D = 320;     // TMEM column of the accumulator (≤ 128 columns), shared by the tiles of a CTA
 constexpr int TC_TMEM_COLS = 512;
 
 struct LstmTcArgs {
@@ -112,8 +120,9 @@ __device__ __forceinline__ float sigmoid_fast(float x) {
   return r;
 }
 
-// thread 0: D = A_hi·B_hi + A_lo·B_hi + A_hi·B_lo for one layer, then commit
-__device__ __forceinline__ void issue_layer(const TcLayer& L, uint32_t tbase, const float* wsm, uint64_t* bar) {
+// one thread: D = A_hi·B_hi + A_lo·B_hi + A_hi·B_lo for one layer, then commit (pbase = TMEM address of the tile's panel, dacc = of
+// the accumulator)
+__device__ __forceinline__ void issue_layer(const TcLayer& L, uint32_t pbase, uint32_t dacc, const float* wsm, uint64_t* bar) {
   tc_fence_after();
   const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(L.N >> 3) << 17) | ((128u >> 4) << 24);
   const uint32_t b_hi = smem_u32(wsm + L.w_off), b_lo = b_hi + (uint32_t)(L.N * L.K * 4);
@@ -121,11 +130,11 @@ __device__ __forceinline__ void issue_layer(const TcLayer& L, uint32_t tbase, co
   uint32_t acc = 0;
 #pragma unroll 1
   for (int pass = 0; pass < 3; ++pass) {
-    const uint32_t a0 = tbase + L.a_col + (pass == 1 ? TC_ALO : 0);
+    const uint32_t a0 = pbase + L.a_col + (pass == 1 ? TC_ALO : 0);
     const uint32_t b0 = pass == 2 ? b_lo : b_hi;
 #pragma unroll 1
     for (int j = 0; j < L.K / 8; ++j) {
-      tc_mma(tbase + TC_D, a0 + 8 * j, tc_bdesc(b0 + j * 2 * chunk, chunk, 128), idesc, acc);
+      tc_mma(dacc, a0 + 8 * j, tc_bdesc(b0 + j * 2 * chunk, chunk, 128), idesc, acc);
       acc = 1;
     }
   }
@@ -133,14 +142,20 @@ __device__ __forceinline__ void issue_layer(const TcLayer& L, uint32_t tbase, co
 }
 
 // LSTM epilogue for this thread's UH units (half of the layer's; the other half belongs to the thread 128 above / below on the
-// same TMEM lane): pull the gate pre-activations of 8 units at a time, update c (registers), write h into the A panel
-template <int UH>
-__device__ __forceinline__ void lstm_epilogue(uint32_t lane_base, int half, int h_col, float (&c)[UH], float* h_out /* UH or nullptr */) {
+// same TMEM lane): gate pre-activations of 8 units at a time, update c (registers), write h into the A panel.
+// PULLED: the thread's 4·UH accumulator columns are already in z_all (the accumulator itself may belong to the other tile by now);
+// otherwise they are read from TMEM chunk by chunk.
+template <int UH, bool PULLED>
+__device__ __forceinline__ void lstm_epilogue(uint32_t lane_panel, uint32_t lane_acc, int half, int h_col, float (&c)[UH], float* h_out /* UH or nullptr */,
+                                              const uint32_t* z_all) {
 #pragma unroll
   for (int ch = 0; ch < UH / 8; ++ch) {
-    uint32_t z[32];
-    tmem_ld32(lane_base + TC_D + (half * (UH / 8) + ch) * 32, z);
-    tc_wait_ld();
+    uint32_t zl[32];
+    if (!PULLED) {
+      tmem_ld32(lane_acc + (half * (UH / 8) + ch) * 32, zl);
+      tc_wait_ld();
+    }
+    const uint32_t* z = PULLED ? z_all + ch * 32 : zl;
     float h[8];
 #pragma unroll
     for (int q = 0; q < 8; ++q) {
@@ -153,48 +168,95 @@ __device__ __forceinline__ void lstm_epilogue(uint32_t lane_base, int half, int 
       h[q] = og * fmaxf(c[u], 0.f);
       if (h_out) h_out[u] = h[q];
     }
-    a_store<8>(lane_base, h_col + half * UH + ch * 8, h);
+    a_store<8>(lane_panel, h_col + half * UH + ch * 8, h);
   }
 }
 
-__global__ void __launch_bounds__(TC_THREADS, 1) lstm_forward_tc_kernel(const __grid_constant__ LstmTcArgs a) {
+template <int NCOL>
+__device__ __forceinline__ void pull_cols(uint32_t taddr, uint32_t (&z)[NCOL]) {  // NCOL (32 or 64) accumulator columns of this lane → registers
+#pragma unroll
+  for (int c0 = 0; c0 < NCOL; c0 += 32) {
+    uint32_t t32[32];
+    tmem_ld32(taddr + c0, t32);
+#pragma unroll
+    for (int i = 0; i < 32; ++i) z[c0 + i] = t32[i];
+  }
+  tc_wait_ld();
+}
+
+__device__ __forceinline__ void group_barrier(int g, int G) {  // all 256 threads of tile g (named barrier; the whole CTA when G == 1)
+  if (G == 1) __syncthreads();
+  else asm volatile("bar.sync %0, %1;" ::"r"(1 + g), "r"(TC_THREADS) : "memory");
+}
+
+template <int G>
+__global__ void __launch_bounds__(TC_THREADS * G, 1) lstm_forward_tc_kernel(const __grid_constant__ LstmTcArgs a) {
   extern __shared__ __align__(128) float wsm[];
   __shared__ uint32_t s_tmem;
-  __shared__ __align__(8) uint64_t bar;
-  const int tid = threadIdx.x, warp = tid >> 5;
+  __shared__ __align__(8) uint64_t bar[2];   // MMA-done, one per tile
+  __shared__ __align__(8) uint64_t tok[2];   // G == 2: "the accumulator is yours", one per tile
+  const int tid_cta = threadIdx.x;
+  const int g = G == 1 ? 0 : tid_cta / TC_THREADS;   // tile (group) of this thread
+  const int tid = tid_cta - g * TC_THREADS, warp = tid >> 5;
   const int F = a.F;
-  if (warp == 0) {
+  if (tid_cta < 32) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(TC_TMEM_COLS));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
   }
-  if (tid == 0) {
-    mbar_init(&bar, 1);
+  if (tid_cta == 0) {
+    mbar_init(&bar[0], 1);
+    mbar_init(&bar[1], 1);
+    mbar_init(&tok[0], 1);
+    mbar_init(&tok[1], 1);
     mbar_fence_init();
   }
-  for (int i = tid; i < a.packed_floats; i += TC_THREADS) wsm[i] = a.packed[i];
+  for (int i = tid_cta; i < a.packed_floats; i += TC_THREADS * G) wsm[i] = a.packed[i];
   fence_proxy_async();  // generic-proxy writes of the weights → visible to the tensor core's async-proxy reads
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tbase = s_tmem;
-  const int half = tid >> 7, row = tid & (TC_NT - 1);  // warps w and w + 4 address the same 32 TMEM lanes
-  const uint32_t lane_base = tbase + ((uint32_t)((warp & 3) * 32) << 16);
-  uint32_t parity = 0;
+  const int half = tid >> 7, row = tid & (TC_NT - 1);  // warps w and w + 4 of a group address the same 32 TMEM lanes
+  const uint32_t lane_off = (uint32_t)((warp & 3) * 32) << 16;
+  const uint32_t pbase = tbase + (uint32_t)(g * TC_PANEL);     // this tile's A panel
+  const uint32_t lane_base = pbase + lane_off;
+  const uint32_t dacc = tbase + TC_D, lane_acc = dacc + lane_off;
+  uint32_t parity = 0, tok_parity = 0;
+  // Token protocol (G == 2): tile 0 owns the accumulator first.  Before issuing a layer the tile's issuing thread waits for its
+  // token; after the tile has pulled its accumulator into registers one thread passes the token on.  Both tiles run the same
+  // number of layers (a tile beyond the end of the batch computes on zeros), so the hand-over never stalls for good.
+  if (G == 2 && tid_cta == 0) mbar_arrive(&tok[0]);
 
-  auto run_layer = [&](int l) {  // all threads: previous A-panel writes are complete → issue → wait for the accumulator
+  // all threads of the tile: previous A-panel writes are complete → issue → wait for the accumulator
+  auto run_layer = [&](int l) {
     tc_wait_st();
     tc_fence_before();
-    __syncthreads();
-    if (tid == 0) issue_layer(a.layer[l], tbase, wsm, &bar);
-    mbar_wait(&bar, parity);
+    group_barrier(g, G);
+    if (tid == 0) {
+      if (G == 2) {
+        mbar_wait(&tok[g], tok_parity);
+        tc_fence_after();
+      }
+      issue_layer(a.layer[l], pbase, dacc, wsm, &bar[g]);
+    }
+    if (G == 2) tok_parity ^= 1u;
+    mbar_wait(&bar[g], parity);
     parity ^= 1u;
     tc_fence_after();
   };
+  // G == 2: once every thread of the tile has its accumulator columns in registers, the accumulator goes to the other tile
+  auto release_acc = [&]() {
+    tc_fence_before();
+    group_barrier(g, G);
+    if (tid == 0) mbar_arrive(&tok[1 - g]);
+  };
 
   const long long n_tiles = (a.batch + TC_NT - 1) / TC_NT;
-  for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+  const long long n_rounds = (n_tiles + (long long)gridDim.x * G - 1) / ((long long)gridDim.x * G);
+  for (long long r = 0; r < n_rounds; ++r) {
+    const long long tile = (r * gridDim.x + blockIdx.x) * G + g;
     const long long seq = tile * TC_NT + row;
-    const bool live = seq < a.batch;
+    const bool live = tile < n_tiles && seq < a.batch;
     float c1[16], c2[8], c3[8], c4[16], h2[8];  // this thread's half of every layer's units
 #pragma unroll
     for (int i = 0; i < 16; ++i) c1[i] = c4[i] = 0.f;
@@ -210,7 +272,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) lstm_forward_tc_kernel(const __
       for (int i = 0; i < 16; ++i) first[i] = 0.f;
       first[0] = 1.0f;
       a_store<16>(lane_base, 0, first);   // cols 0..15 (bias-1 at 0; x fills 6.. later)
-      a_store<16>(lane_base, 16, z16);    // 16..31
+      a_store<8>(lane_base, 24, z16);     // 24..31 (cols 16..23 belong to the other half of the thread pair: it writes x there every
+                                          // step, and nothing orders its store against one made here)
       a_store<16>(lane_base, 32, z16);    // 32..47
       a_store<16>(lane_base, 48, z16);    // 48..63
       float last[16];
@@ -242,9 +305,23 @@ __global__ void __launch_bounds__(TC_THREADS, 1) lstm_forward_tc_kernel(const __
         a_store<8>(lane_base, 16, xv);
       }
       run_layer(0);                                        // L1: cols [0,56) → 128 gate columns
-      lstm_epilogue<16>(lane_base, half, 24, c1, nullptr);  // h1 → cols 24..55
+      if (G == 2) {
+        uint32_t z[64];
+        pull_cols<64>(lane_acc + half * 64, z);
+        release_acc();
+        lstm_epilogue<16, true>(lane_base, lane_acc, half, 24, c1, nullptr, z);
+      } else {
+        lstm_epilogue<16, false>(lane_base, lane_acc, half, 24, c1, nullptr, nullptr);  // h1 → cols 24..55
+      }
       run_layer(1);                                        // L2: cols [24,80) → 64 gate columns
-      lstm_epilogue<8>(lane_base, half, 56, c2, h2);        // h2 → cols 56..71 (kept in registers for phase 2)
+      if (G == 2) {
+        uint32_t z[32];
+        pull_cols<32>(lane_acc + half * 32, z);
+        release_acc();
+        lstm_epilogue<8, true>(lane_base, lane_acc, half, 56, c2, h2, z);
+      } else {
+        lstm_epilogue<8, false>(lane_base, lane_acc, half, 56, c2, h2, nullptr);        // h2 → cols 56..71 (kept in registers for phase 2)
+      }
     }
     // ---- phase 2 panel: [1, 0×7, h2_final(16), h3(16), h4(32), 1, 0×7] ----
     {
@@ -267,26 +344,47 @@ __global__ void __launch_bounds__(TC_THREADS, 1) lstm_forward_tc_kernel(const __
     }
     for (int t = 0; t < a.T; ++t) {
       run_layer(2);                                        // L3: cols [0,40)
-      lstm_epilogue<8>(lane_base, half, 24, c3, nullptr);   // h3 → cols 24..39
-      run_layer(3);                                        // L4: cols [24,80)
-      lstm_epilogue<16>(lane_base, half, 40, c4, nullptr);  // h4 → cols 40..71
-      run_layer(4);                                        // TimeDistributed(Dense): cols [40,80) → 32 columns
-      if (half == 0) {  // the 18 output columns are one 32-column read: one thread per sequence writes the row
+      if (G == 2) {
         uint32_t z[32];
-        tmem_ld32(lane_base + TC_D, z);
-        tc_wait_ld();
-        if (live) {
+        pull_cols<32>(lane_acc + half * 32, z);
+        release_acc();
+        lstm_epilogue<8, true>(lane_base, lane_acc, half, 24, c3, nullptr, z);
+      } else {
+        lstm_epilogue<8, false>(lane_base, lane_acc, half, 24, c3, nullptr, nullptr);   // h3 → cols 24..39
+      }
+      run_layer(3);                                        // L4: cols [24,80)
+      if (G == 2) {
+        uint32_t z[64];
+        pull_cols<64>(lane_acc + half * 64, z);
+        release_acc();
+        lstm_epilogue<16, true>(lane_base, lane_acc, half, 40, c4, nullptr, z);
+      } else {
+        lstm_epilogue<16, false>(lane_base, lane_acc, half, 40, c4, nullptr, nullptr);  // h4 → cols 40..71
+      }
+      run_layer(4);                                        // TimeDistributed(Dense): cols [40,80) → 32 columns
+      {
+        uint32_t z[32];
+        if (G == 2) {
+          pull_cols<32>(lane_acc, z);  // both halves read the row (only half 0 writes it): the hand-over needs every thread's arrival
+          release_acc();
+        } else if (half == 0) {
+          tmem_ld32(lane_acc, z);
+          tc_wait_ld();
+        }
+        if (half == 0 && live) {  // the 18 output columns are one 32-column read: one thread per sequence writes the row
           float* yp = a.y + (seq * a.T + t) * F;
           for (int f = 0; f < F; ++f) yp[f] = __uint_as_float(z[f]);
         }
       }
     }
-    tc_fence_before();
-    __syncthreads();  // accumulator reads done before the next tile's first MMA overwrites it
+    if (G == 1) {
+      tc_fence_before();
+      __syncthreads();  // accumulator reads done before the next tile's first MMA overwrites it
+    }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tbase), "r"(TC_TMEM_COLS));
+  if (tid_cta < 32) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tbase), "r"(TC_TMEM_COLS));
 }
 
 // ---- host side ----------------------------------------------------------------------------------------------------
@@ -369,11 +467,20 @@ int b2_lstm_tc_launch(b2_ctx* ctx, const float* d_packed, int packed_floats, con
   for (int l = 0; l < 5; ++l) a.layer[l] = layers[l];
   const size_t smem = sizeof(float) * (size_t)packed_floats + 128;
   B2_REQUIRE(smem <= (size_t)ctx->smem_optin, "lstm_tc: weights need %zu bytes of shared memory", smem);
-  B2_CUDA(cudaFuncSetAttribute(lstm_forward_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  long long tiles = (batch + TC_NT - 1) / TC_NT;
-  long long grid = ctx->sm_count;
-  if (grid > tiles) grid = tiles;
-  lstm_forward_tc_kernel<<<(unsigned)grid, TC_THREADS, smem, stream>>>(a);
+  const long long tiles = (batch + TC_NT - 1) / TC_NT;
+  // context option lstm_tc: 2 (default) two tiles per CTA once there is more than one tile per SM, 3 always two, 1 always one
+  const bool two = ctx->knobs.lstm_tc == 3 || (ctx->knobs.lstm_tc == 2 && tiles > ctx->sm_count);
+  if (two) {
+    B2_CUDA(cudaFuncSetAttribute(lstm_forward_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    long long grid = ctx->sm_count;
+    if (grid > (tiles + 1) / 2) grid = (tiles + 1) / 2;
+    lstm_forward_tc_kernel<2><<<(unsigned)grid, TC_THREADS * 2, smem, stream>>>(a);
+  } else {
+    B2_CUDA(cudaFuncSetAttribute(lstm_forward_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    long long grid = ctx->sm_count;
+    if (grid > tiles) grid = tiles;
+    lstm_forward_tc_kernel<1><<<(unsigned)grid, TC_THREADS, smem, stream>>>(a);
+  }
   B2_CUDA(cudaGetLastError());
   return B2_OK;
 }

@@ -56,12 +56,12 @@ def cuda_device():
 
 @pytest.fixture
 def lstm_path(cuda_device):
-    """Select the LSTM kernel for one test ("tcgen05" = the default tensor-core kernel, "fp32" = the FMA one) through the
-    context option; the default is restored afterwards."""
+    """Select the LSTM kernel for one test ("tcgen05" = the tensor-core kernel with one tile per CTA, "tcgen05x2" = its two-tile
+    form forced on whatever the batch size, "fp32" = the FMA one) through the context option; the default is restored afterwards."""
     import b200_sensor as bs
 
     def pick(path):
-        bs.keras.set_option("lstm_tc", 1 if path == "tcgen05" else 0)
+        bs.keras.set_option("lstm_tc", {"tcgen05": 1, "tcgen05x2": 3, "fp32": 0}[path])
 
     yield pick
-    bs.keras.set_option("lstm_tc", 1)
+    bs.keras.set_option("lstm_tc", 2)

@@ -20,7 +20,7 @@ def _lstm_model(look_back, features=18, seed=314):
     return m
 
 
-@pytest.mark.parametrize("path", ["tcgen05", "fp32"])
+@pytest.mark.parametrize("path", ["tcgen05", "tcgen05x2", "fp32"])
 @pytest.mark.parametrize("batch,T", [(1, 1), (200, 1), (127, 4), (129, 16), (5000, 3)])
 def test_lstm_forward_matches_oracle(cuda_device, lstm_path, batch, T, path):
     """Both kernels: the default tensor-core one (tcgen05.mma kind::tf32, split precision) and the FP32 FMA one."""
@@ -70,7 +70,7 @@ def test_lstm_rejects_other_stacks(cuda_device):
         m.predict(np.zeros((2, 1, 18), np.float32))
 
 
-@pytest.mark.parametrize("path", ["tcgen05", "fp32"])
+@pytest.mark.parametrize("path", ["tcgen05", "tcgen05x2", "fp32"])
 @pytest.mark.parametrize("n_rows,look_back,shift", [(1200, 1, 1), (777, 4, 1), (1000, 16, 3), (5, 8, 1)])
 def test_lstm_sliding_windows_read_in_place(cuda_device, lstm_path, n_rows, look_back, shift, path):
     """dataset.window(look_back, shift, drop_remainder=True) fused into the forward pass (LSTM-…/cardata-v1.py:184-185): the
@@ -96,3 +96,20 @@ def test_lstm_sliding_windows_read_in_place(cuda_device, lstm_path, n_rows, look
     assert t.shape[0] == min(n_rows - look_back, n_win) and t.shape[1:] == (1, 18)
     if shift == 1 and t.shape[0]:
         np.testing.assert_array_equal(t[0, 0], rows[look_back])
+
+
+def test_lstm_two_tiles_per_cta_equals_one_tile_on_a_large_batch(cuda_device, lstm_path):
+    """More tiles than SMs (the default then runs two tiles per CTA, taking turns at one TMEM accumulator): bit-identical to the
+    one-tile kernel — the arithmetic per sequence is the same — including an odd tile count and a ragged last tile."""
+    m = _lstm_model(2)
+    g = np.random.default_rng(9)
+    x = g.uniform(-1, 1, size=(148 * 128 * 2 + 128 * 3 + 57, 2, 18)).astype(np.float32)
+    idx = np.concatenate([np.arange(0, x.shape[0], 997), np.arange(x.shape[0] - 700, x.shape[0])])  # incl. the last round's tiles
+    ref = orc.lstm_forward(x[idx], m.get_flat_weights(), dtype=np.float64)
+    lstm_path("tcgen05")
+    y1 = m.predict(x)
+    assert np.abs(y1[idx] - ref).max() < 1e-4, "one tile per CTA"
+    bs.keras.set_option("lstm_tc", 2)
+    y2 = m.predict(x)
+    assert np.abs(y2[idx] - ref).max() < 1e-4, "two tiles per CTA"
+    np.testing.assert_array_equal(y1, y2)

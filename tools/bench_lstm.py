@@ -4,7 +4,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import bench, b200_sensor as bs
 dev = torch.device("cuda", 0)
-for tc in ("1", "0"):
+for tc in ("2", "1", "0"):
     bs.keras.set_option("lstm_tc", int(tc))
     for T in (1, 4, 16):
         r = bench.aux_lstm(dev, T)

@@ -35,7 +35,7 @@ m.fit(bs.synth.credit_rows(1 << 18, seed=2), epochs=1, batch_size=1 << 18, shuff
 print(bench.aux_lstm(dev, 4)["value"])
 k.set_option("lstm_tc", 0)
 print(bench.aux_lstm(dev, 4)["value"])
-k.set_option("lstm_tc", 1)
+k.set_option("lstm_tc", 2)
 ml = k.models.Sequential()
 ml.add(k.layers.LSTM(32, activation="relu", input_shape=(1, 18), return_sequences=True))
 ml.add(k.layers.LSTM(16, activation="relu", return_sequences=False))

@@ -58,7 +58,7 @@ for tcl in (1, 0):
     ml.add(k.layers.TimeDistributed(k.layers.Dense(18)))
     xl = np.random.default_rng(0).uniform(-1, 1, (150, 3, 18)).astype(np.float32)
     ml.predict(xl)
-k.set_option("lstm_tc", 1)
+k.set_option("lstm_tc", 2)
 ml.compile(metrics=["accuracy"], loss="mean_squared_error", optimizer="adam")
 ml.fit(xl[:20], xl[:20], epochs=1, batch_size=4, shuffle=False)
 bs.sink.format_rows(m30.predict(x30[:200]))
