@@ -23,6 +23,8 @@
 // tiles, one per group of 256 threads, each with its own A panel in TMEM (2 x 160 columns) and ONE accumulator (128 columns)
 // that the groups take in turns: a group pulls its whole accumulator into registers right after its MMAs complete and hands the
 // accumulator to the other group, whose MMAs then run under this group's gate arithmetic.  TMEM: 320 + 128 = 448 of 512 columns.
+#include <type_traits>
+
 #include "lstm_tc.h"
 
 constexpr int TC_NT = 128;      // sequences per tile = TMEM lanes
@@ -91,8 +93,10 @@ __device__ __forceinline__ void tc_commit(uint64_t* bar) {
 }
 
 // split one fp32 into a TF32-exact head (round to nearest) and the remainder
+// (integer rounding: cvt.rna.tf32.f32 expands to five SASS instructions on sm_100a, this is three; it differs only where the
+// rounding carries out of the largest binade, |v| > 3.4e38 · (1 - 2^-12))
 __device__ __forceinline__ void tf32_split(float v, uint32_t& hi, uint32_t& lo) {
-  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi) : "f"(v));
+  hi = (__float_as_uint(v) + 0x1000u) & 0xFFFFE000u;
   lo = __float_as_uint(v - __uint_as_float(hi));
 }
 // store n (8 or 16) consecutive A-panel values of this thread's lane as (hi, lo)
@@ -120,22 +124,33 @@ __device__ __forceinline__ float sigmoid_fast(float x) {
   return r;
 }
 
-// one thread: D = A_hi·B_hi + A_lo·B_hi + A_hi·B_lo for one layer, then commit (pbase = TMEM address of the tile's panel, dacc = of
-// the accumulator)
-__device__ __forceinline__ void issue_layer(const TcLayer& L, uint32_t pbase, uint32_t dacc, const float* wsm, uint64_t* bar) {
+// The five GEMMs of the reference stack (the only one b2_lstm_tc_pack accepts): shapes, panel columns and weight offsets are
+// compile-time constants, so the issuing thread's loop is fully unrolled and a descriptor is "base + constant".
+template <int L> struct TcL;
+template <> struct TcL<0> { static constexpr int N = 128, K = 56, A = 0,  W = 0; };
+template <> struct TcL<1> { static constexpr int N = 64,  K = 56, A = 24, W = TcL<0>::W + 2 * TcL<0>::N * TcL<0>::K; };
+template <> struct TcL<2> { static constexpr int N = 64,  K = 40, A = 0,  W = TcL<1>::W + 2 * TcL<1>::N * TcL<1>::K; };
+template <> struct TcL<3> { static constexpr int N = 128, K = 56, A = 24, W = TcL<2>::W + 2 * TcL<2>::N * TcL<2>::K; };
+template <> struct TcL<4> { static constexpr int N = 32,  K = 40, A = 40, W = TcL<3>::W + 2 * TcL<3>::N * TcL<3>::K; };
+
+// one thread: D = A_hi·B_hi + A_lo·B_hi + A_hi·B_lo for layer L, then commit (pbase = TMEM address of the tile's panel, dacc = of
+// the accumulator, wbase = shared-memory address of the packed weights)
+template <int L>
+__device__ __forceinline__ void issue_layer(uint32_t pbase, uint32_t dacc, uint32_t wbase, uint64_t* bar) {
+  using T = TcL<L>;
   tc_fence_after();
-  const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(L.N >> 3) << 17) | ((128u >> 4) << 24);
-  const uint32_t b_hi = smem_u32(wsm + L.w_off), b_lo = b_hi + (uint32_t)(L.N * L.K * 4);
-  const int chunk = L.N * 16;  // bytes between consecutive 16-byte K-chunks (LBO); rows 8 apart are 128 B apart (SBO)
-  uint32_t acc = 0;
-#pragma unroll 1
+  constexpr uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(T::N >> 3) << 17) | ((128u >> 4) << 24);
+  constexpr int chunk = T::N * 16;  // bytes between consecutive 16-byte K-chunks (LBO); rows 8 apart are 128 B apart (SBO)
+  const uint32_t b_hi = wbase + (uint32_t)T::W * 4u, b_lo = b_hi + (uint32_t)(T::N * T::K * 4);
+  // descriptor of (b_hi, chunk 0); the start-address field counts 16-byte units, so later descriptors are this one plus a constant
+  const uint64_t d_hi = tc_bdesc(b_hi, chunk, 128), d_lo = tc_bdesc(b_lo, chunk, 128);
+#pragma unroll
   for (int pass = 0; pass < 3; ++pass) {
-    const uint32_t a0 = pbase + L.a_col + (pass == 1 ? TC_ALO : 0);
-    const uint32_t b0 = pass == 2 ? b_lo : b_hi;
-#pragma unroll 1
-    for (int j = 0; j < L.K / 8; ++j) {
-      tc_mma(dacc, a0 + 8 * j, tc_bdesc(b0 + j * 2 * chunk, chunk, 128), idesc, acc);
-      acc = 1;
+    const uint32_t a0 = pbase + T::A + (pass == 1 ? TC_ALO : 0);
+#pragma unroll
+    for (int j = 0; j < T::K / 8; ++j) {
+      const uint64_t bd = (pass == 2 ? d_lo : d_hi) + (uint64_t)((j * 2 * chunk) >> 4);
+      tc_mma(dacc, a0 + 8 * j, bd, idesc, (pass | j) != 0 ? 1u : 0u);
     }
   }
   tc_commit(bar);
@@ -228,7 +243,9 @@ __global__ void __launch_bounds__(TC_THREADS * G, 1) lstm_forward_tc_kernel(cons
   if (G == 2 && tid_cta == 0) mbar_arrive(&tok[0]);
 
   // all threads of the tile: previous A-panel writes are complete → issue → wait for the accumulator
-  auto run_layer = [&](int l) {
+  const uint32_t wbase = smem_u32(wsm);
+  auto run_layer = [&](auto layer_tag) {
+    constexpr int L = decltype(layer_tag)::value;
     tc_wait_st();
     tc_fence_before();
     group_barrier(g, G);
@@ -237,7 +254,7 @@ __global__ void __launch_bounds__(TC_THREADS * G, 1) lstm_forward_tc_kernel(cons
         mbar_wait(&tok[g], tok_parity);
         tc_fence_after();
       }
-      issue_layer(a.layer[l], pbase, dacc, wsm, &bar[g]);
+      issue_layer<L>(pbase, dacc, wbase, &bar[g]);
     }
     if (G == 2) tok_parity ^= 1u;
     mbar_wait(&bar[g], parity);
@@ -304,7 +321,7 @@ __global__ void __launch_bounds__(TC_THREADS * G, 1) lstm_forward_tc_kernel(cons
         }
         a_store<8>(lane_base, 16, xv);
       }
-      run_layer(0);                                        // L1: cols [0,56) → 128 gate columns
+      run_layer(std::integral_constant<int, 0>{});                                        // L1: cols [0,56) → 128 gate columns
       if (G == 2) {
         uint32_t z[64];
         pull_cols<64>(lane_acc + half * 64, z);
@@ -313,7 +330,7 @@ __global__ void __launch_bounds__(TC_THREADS * G, 1) lstm_forward_tc_kernel(cons
       } else {
         lstm_epilogue<16, false>(lane_base, lane_acc, half, 24, c1, nullptr, nullptr);  // h1 → cols 24..55
       }
-      run_layer(1);                                        // L2: cols [24,80) → 64 gate columns
+      run_layer(std::integral_constant<int, 1>{});                                        // L2: cols [24,80) → 64 gate columns
       if (G == 2) {
         uint32_t z[32];
         pull_cols<32>(lane_acc + half * 32, z);
@@ -343,7 +360,7 @@ __global__ void __launch_bounds__(TC_THREADS * G, 1) lstm_forward_tc_kernel(cons
       // cols 72..79 still hold [1, 0×7] from phase 1
     }
     for (int t = 0; t < a.T; ++t) {
-      run_layer(2);                                        // L3: cols [0,40)
+      run_layer(std::integral_constant<int, 2>{});                                        // L3: cols [0,40)
       if (G == 2) {
         uint32_t z[32];
         pull_cols<32>(lane_acc + half * 32, z);
@@ -352,7 +369,7 @@ __global__ void __launch_bounds__(TC_THREADS * G, 1) lstm_forward_tc_kernel(cons
       } else {
         lstm_epilogue<8, false>(lane_base, lane_acc, half, 24, c3, nullptr, nullptr);   // h3 → cols 24..39
       }
-      run_layer(3);                                        // L4: cols [24,80)
+      run_layer(std::integral_constant<int, 3>{});                                        // L4: cols [24,80)
       if (G == 2) {
         uint32_t z[64];
         pull_cols<64>(lane_acc + half * 64, z);
@@ -361,7 +378,7 @@ __global__ void __launch_bounds__(TC_THREADS * G, 1) lstm_forward_tc_kernel(cons
       } else {
         lstm_epilogue<16, false>(lane_base, lane_acc, half, 40, c4, nullptr, nullptr);  // h4 → cols 40..71
       }
-      run_layer(4);                                        // TimeDistributed(Dense): cols [40,80) → 32 columns
+      run_layer(std::integral_constant<int, 4>{});                                        // TimeDistributed(Dense): cols [40,80) → 32 columns
       {
         uint32_t z[32];
         if (G == 2) {
