@@ -214,6 +214,7 @@ __global__ void __launch_bounds__(TC_THREADS * G, 1) lstm_forward_tc_kernel(cons
   const int g = G == 1 ? 0 : tid_cta / TC_THREADS;   // tile (group) of this thread
   const int tid = tid_cta - g * TC_THREADS, warp = tid >> 5;
   const int F = a.F;
+  const bool vec18 = F == 18 && ((reinterpret_cast<uintptr_t>(a.x) | reinterpret_cast<uintptr_t>(a.y)) & 7) == 0;  // 8-byte row accesses
   if (tid_cta < 32) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(TC_TMEM_COLS));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
@@ -308,7 +309,16 @@ __global__ void __launch_bounds__(TC_THREADS * G, 1) lstm_forward_tc_kernel(cons
         xv[0] = 1.0f;
         if (live) {
           const float* xp = a.x + (seq * a.seq_stride + t) * F;
-          for (int f = 0; f < min(F, 10); ++f) xv[6 + f] = __ldg(xp + f);
+          if (vec18) {  // the reference's width: rows are 72 bytes apart, so 8-byte loads are aligned; everything stays in registers
+#pragma unroll
+            for (int f = 0; f < 10; f += 2) {
+              const float2 v = __ldg(reinterpret_cast<const float2*>(xp + f));
+              xv[6 + f] = v.x;
+              xv[7 + f] = v.y;
+            }
+          } else {
+            for (int f = 0; f < min(F, 10); ++f) xv[6 + f] = __ldg(xp + f);
+          }
         }
         a_store<16>(lane_base, 0, xv);
       } else {
@@ -317,7 +327,16 @@ __global__ void __launch_bounds__(TC_THREADS * G, 1) lstm_forward_tc_kernel(cons
         for (int i = 0; i < 8; ++i) xv[i] = 0.f;
         if (live) {
           const float* xp = a.x + (seq * a.seq_stride + t) * F;
-          for (int f = 10; f < F; ++f) xv[f - 10] = __ldg(xp + f);
+          if (vec18) {
+#pragma unroll
+            for (int f = 0; f < 8; f += 2) {
+              const float2 v = __ldg(reinterpret_cast<const float2*>(xp + 10 + f));
+              xv[f] = v.x;
+              xv[f + 1] = v.y;
+            }
+          } else {
+            for (int f = 10; f < F; ++f) xv[f - 10] = __ldg(xp + f);
+          }
         }
         a_store<8>(lane_base, 16, xv);
       }
@@ -390,7 +409,13 @@ __global__ void __launch_bounds__(TC_THREADS * G, 1) lstm_forward_tc_kernel(cons
         }
         if (half == 0 && live) {  // the 18 output columns are one 32-column read: one thread per sequence writes the row
           float* yp = a.y + (seq * a.T + t) * F;
-          for (int f = 0; f < F; ++f) yp[f] = __uint_as_float(z[f]);
+          if (vec18) {
+#pragma unroll
+            for (int f = 0; f < 18; f += 2)
+              *reinterpret_cast<float2*>(yp + f) = make_float2(__uint_as_float(z[f]), __uint_as_float(z[f + 1]));
+          } else {
+            for (int f = 0; f < F; ++f) yp[f] = __uint_as_float(z[f]);
+          }
         }
       }
     }
