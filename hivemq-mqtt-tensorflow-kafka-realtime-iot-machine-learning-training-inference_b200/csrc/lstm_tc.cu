@@ -301,44 +301,54 @@ __global__ void __launch_bounds__(TC_THREADS * G, 1) lstm_forward_tc_kernel(cons
       a_store<16>(lane_base, 64, last);   // 64..79
     }
     for (int t = 0; t < a.T; ++t) {
-      // cols 0..23 of the panel: [1, 0, 0, 0, 0, 0, x0..x17]; half 0 writes cols 0..15, half 1 cols 16..23
-      if (half == 0) {
-        float xv[16];
+      // cols 0..23 of the panel: [1, 0, 0, 0, 0, 0, x0..x17]; half 0 writes cols 0..15, half 1 cols 16..23.  The reference's width
+      // (F = 18, rows 72 bytes apart: aligned 8-byte accesses) has its own branch with its own arrays so that those stay in
+      // registers; the generic branch indexes at run time and lives in local memory.
+      const float* xp = a.x + (seq * a.seq_stride + t) * F;
+      if (vec18) {
+        if (half == 0) {
+          float xv[16];
 #pragma unroll
-        for (int i = 0; i < 16; ++i) xv[i] = 0.f;
-        xv[0] = 1.0f;
-        if (live) {
-          const float* xp = a.x + (seq * a.seq_stride + t) * F;
-          if (vec18) {  // the reference's width: rows are 72 bytes apart, so 8-byte loads are aligned; everything stays in registers
+          for (int i = 0; i < 16; ++i) xv[i] = 0.f;
+          xv[0] = 1.0f;
+          if (live) {
 #pragma unroll
             for (int f = 0; f < 10; f += 2) {
               const float2 v = __ldg(reinterpret_cast<const float2*>(xp + f));
               xv[6 + f] = v.x;
               xv[7 + f] = v.y;
             }
-          } else {
-            for (int f = 0; f < min(F, 10); ++f) xv[6 + f] = __ldg(xp + f);
           }
-        }
-        a_store<16>(lane_base, 0, xv);
-      } else {
-        float xv[8];
+          a_store<16>(lane_base, 0, xv);
+        } else {
+          float xv[8];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) xv[i] = 0.f;
-        if (live) {
-          const float* xp = a.x + (seq * a.seq_stride + t) * F;
-          if (vec18) {
+          for (int i = 0; i < 8; ++i) xv[i] = 0.f;
+          if (live) {
 #pragma unroll
             for (int f = 0; f < 8; f += 2) {
               const float2 v = __ldg(reinterpret_cast<const float2*>(xp + 10 + f));
               xv[f] = v.x;
               xv[f + 1] = v.y;
             }
-          } else {
-            for (int f = 10; f < F; ++f) xv[f - 10] = __ldg(xp + f);
           }
+          a_store<8>(lane_base, 16, xv);
         }
-        a_store<8>(lane_base, 16, xv);
+      } else if (half == 0) {
+        float xg[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) xg[i] = 0.f;
+        xg[0] = 1.0f;
+        if (live)
+          for (int f = 0; f < min(F, 10); ++f) xg[6 + f] = __ldg(xp + f);
+        a_store<16>(lane_base, 0, xg);
+      } else {
+        float xg[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) xg[i] = 0.f;
+        if (live)
+          for (int f = 10; f < F; ++f) xg[f - 10] = __ldg(xp + f);
+        a_store<8>(lane_base, 16, xg);
       }
       run_layer(std::integral_constant<int, 0>{});                                        // L1: cols [0,56) → 128 gate columns
       if (G == 2) {
@@ -414,7 +424,9 @@ __global__ void __launch_bounds__(TC_THREADS * G, 1) lstm_forward_tc_kernel(cons
             for (int f = 0; f < 18; f += 2)
               *reinterpret_cast<float2*>(yp + f) = make_float2(__uint_as_float(z[f]), __uint_as_float(z[f + 1]));
           } else {
-            for (int f = 0; f < F; ++f) yp[f] = __uint_as_float(z[f]);
+#pragma unroll
+            for (int f = 0; f < 32; ++f)   // static register indices, predicated stores
+              if (f < F) yp[f] = __uint_as_float(z[f]);
           }
         }
       }
