@@ -189,7 +189,9 @@ __device__ __forceinline__ bool csv_fast_token(const uint8_t* __restrict__ st, i
 // One record per thread; all lanes of a warp are at field f of their own record, so the field's kind / column / default are
 // uniform constant-bank reads.  A numeric field is parsed straight from the 16 bytes at the cursor (b2_csv_num16: the same byte
 // classification finds the field's end, so there is no separate delimiter scan); a skipped / string field is stepped over by
-// a delimiter search.  Returns B2_REC_OK, or -1 as soon as anything is not the plain grammar (quotes, blanks, '+', long tokens,
+// a delimiter search.  (Round 2 tried a plain digit loop — LDS.U8, subtract, compare, branch, multiply-add per character, one
+// 32-bit significand — in its place: 156 instead of 169 executed instructions per field, but a chain of dependent shared-memory
+// loads; 5.55e9 against 5.8e9 records/s.  profiles/round2_notes.md §7.)  Returns B2_REC_OK, or -1 as soon as anything is not the plain grammar (quotes, blanks, '+', long tokens,
 // missing or surplus fields, an empty field without default): the caller then runs csv_record_careful on the record.
 template <int XS>
 __device__ __forceinline__ int csv_walk(const uint8_t* __restrict__ stage, int b, int e, const CsvP& c, float* __restrict__ xrow,
@@ -751,28 +753,45 @@ __device__ __forceinline__ void decode_body(const DecodeArgs<D>& a) {
       active[s] = (!TC || cur) && q >= c_sub && q < c_sub + c_cnt;
       st[s] = B2_REC_OK;
       lab[s] = 2;
+    }
+    // one record of the item: slot s of this lane, stage bytes [cb, ce), absolute offset ab of its first byte
+    auto decode_one = [&](int s, int cb, int ce, int ab, int& st_s, uint8_t& lab_s) {
+      const int q = lane + 32 * s;
       float* xrow = xlane + s;  // element j of this record sits at xrow[j * R]
-      if (active[s]) {
-        const long long gr = c_row0 + q;
-        if (FMT == FMT_CSV) {
-          int32_t* sp = (MODE == 0 && a.span) ? a.span + gr * a.csv.n_str * 2 : nullptr;
-          const int rel = c_b[s] - ob[s];  // stage offset minus absolute offset (the cursor still sits on this item's chunk)
-          st[s] = csv_walk<R>(stage, c_b[s], c_e[s], a.csv, xrow, sp, rel);
-          if (st[s] < 0) st[s] = csv_record_careful(stage, c_b[s], c_e[s], a.csv, xrow, R, sp, rel);
-        } else if (FMT == FMT_JSON) {
-          for (int j = 0; j < xt_stride; ++j) xrow[j] = 0.0f;  // members that are absent or null
-          st[s] = b2_json_record_auto(stage, c_b[s], c_e[s], a.json, xrow, &lab[s]);
-        } else {
-          if (!a.avro.all_routed)
-            for (int j = 0; j < (MODE == 1 ? D : a.n_out); ++j) xrow[j * R] = 0.0f;  // columns no field routes to
-          st[s] = -1;
-          if (a.avro.known == 1) st[s] = avro_walk_schema_a<R>(stage, c_b[s], c_e[s], a.avro.skip_prefix, xrow);
-          else if (a.avro.known == 2) st[s] = avro_walk_schema_b<R>(stage, c_b[s], c_e[s], a.avro.skip_prefix, xrow, &lab[s]);
-          if (st[s] < 0) {
-            lab[s] = 2;
-            st[s] = avro_decode_record(stage, c_b[s], c_e[s], a.avro, xrow, R, &lab[s]);
-          }
+      const long long gr = c_row0 + q;
+      if (FMT == FMT_CSV) {
+        int32_t* sp = (MODE == 0 && a.span) ? a.span + gr * a.csv.n_str * 2 : nullptr;
+        const int rel = cb - ab;  // stage offset minus absolute offset (the cursor still sits on this item's chunk)
+        st_s = csv_walk<R>(stage, cb, ce, a.csv, xrow, sp, rel);
+        if (st_s < 0) st_s = csv_record_careful(stage, cb, ce, a.csv, xrow, R, sp, rel);
+      } else if (FMT == FMT_JSON) {
+        for (int j = 0; j < xt_stride; ++j) xrow[j] = 0.0f;  // members that are absent or null
+        st_s = b2_json_record_auto(stage, cb, ce, a.json, xrow, &lab_s);
+      } else {
+        if (!a.avro.all_routed)
+          for (int j = 0; j < (MODE == 1 ? D : a.n_out); ++j) xrow[j * R] = 0.0f;  // columns no field routes to
+        st_s = -1;
+        if (a.avro.known == 1) st_s = avro_walk_schema_a<R>(stage, cb, ce, a.avro.skip_prefix, xrow);
+        else if (a.avro.known == 2) st_s = avro_walk_schema_b<R>(stage, cb, ce, a.avro.skip_prefix, xrow, &lab_s);
+        if (st_s < 0) {
+          lab_s = 2;
+          st_s = avro_decode_record(stage, cb, ce, a.avro, xrow, R, &lab_s);
         }
+      }
+    };
+    if (R == 1) {
+      if (active[0]) decode_one(0, c_b[0], c_e[0], ob[0], st[0], lab[0]);
+    } else {
+      // the two records run through ONE copy of the decoder (a rolled loop): the straight-line code of the item loop has to stay
+      // inside the 32 KB instruction cache, and two inlined decoders + the pair forward pass do not
+#pragma unroll 1
+      for (int s = 0; s < 2; ++s) {
+        const bool act = s ? active[R - 1] : active[0];
+        int st_s = B2_REC_OK;
+        uint8_t lab_s = 2;
+        if (act) decode_one(s, s ? c_b[R - 1] : c_b[0], s ? c_e[R - 1] : c_e[0], s ? ob[R - 1] : ob[0], st_s, lab_s);
+        if (s) st[R - 1] = st_s, lab[R - 1] = lab_s;
+        else st[0] = st_s, lab[0] = lab_s;
       }
     }
     __syncwarp();  // every lane is done with the stage
