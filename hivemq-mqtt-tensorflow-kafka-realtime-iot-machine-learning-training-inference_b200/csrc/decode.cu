@@ -50,6 +50,7 @@ template <int D>
 struct DecodeArgs {
   const uint8_t* bytes;
   const int32_t* offs;
+  const int32_t* ends;  // NULL: record i is [offs[i], offs[i+1]); else [offs[i], ends[i]) — ascending ranges with gaps (Kafka framing)
   long long n;
   int fmt;
   int n_out;            // floats per record produced by the decode (== D when scoring)
@@ -684,18 +685,30 @@ __device__ __forceinline__ void decode_body(const DecodeArgs<D>& a) {
         row0 = list_mode ? (long long)a.over_list[1 + chunk] : chunk * CH;
         rows = list_mode ? 1 : (int)min((long long)CH, a.n - row0);
         sub = 0;
+        if (a.ends) {
+          // ranges with gaps between them (the values inside a Kafka segment): an item's bulk copy simply brings the bytes
+          // in between along
 #pragma unroll
-        for (int s = 0; s < R; ++s) ob[s] = a.offs[row0 + min(lane + 32 * s, rows)];
-#pragma unroll
-        for (int s = 0; s < R; ++s) {
-          oe[s] = __shfl_down_sync(FULL, ob[s], 1);  // lane 31 keeps its own value here
-          if (s + 1 < R) {
-            const int wrap = __shfl_sync(FULL, ob[s + 1 < R ? s + 1 : s], 0);
-            if (lane == 31) oe[s] = wrap;
+          for (int s = 0; s < R; ++s) {
+            const int q = min(lane + 32 * s, rows - 1);
+            ob[s] = a.offs[row0 + q];
+            oe[s] = a.ends[row0 + q];
+            if (lane + 32 * s >= rows) ob[s] = oe[s];  // a record that does not exist: empty, at the end of the chunk
           }
+        } else {
+#pragma unroll
+          for (int s = 0; s < R; ++s) ob[s] = a.offs[row0 + min(lane + 32 * s, rows)];
+#pragma unroll
+          for (int s = 0; s < R; ++s) {
+            oe[s] = __shfl_down_sync(FULL, ob[s], 1);  // lane 31 keeps its own value here
+            if (s + 1 < R) {
+              const int wrap = __shfl_sync(FULL, ob[s + 1 < R ? s + 1 : s], 0);
+              if (lane == 31) oe[s] = wrap;
+            }
+          }
+          // end of the chunk's last possible record (a record that does not exist has ob == oe == end of the chunk)
+          if (lane == 31) oe[R - 1] = a.offs[row0 + rows];
         }
-        // end of the chunk's last possible record (a record that does not exist has ob == oe == end of the chunk)
-        if (lane == 31) oe[R - 1] = a.offs[row0 + rows];
       }
       const int b_abs = pick(ob, sub);
       const uintptr_t p0 = reinterpret_cast<uintptr_t>(a.bytes) + (uintptr_t)(long long)b_abs;
@@ -1249,7 +1262,7 @@ extern "C" int b2_decode_json(b2_ctx* ctx, const uint8_t* bytes_dev, const int32
 }
 
 template <int D>
-static int decode_score_spec(b2_ae* ae, const uint8_t* bytes, const int32_t* offs, int64_t n, const b2_csv_spec* csv,
+static int decode_score_spec(b2_ae* ae, const uint8_t* bytes, const int32_t* offs, const int32_t* ends, int64_t n, const b2_csv_spec* csv,
                              const b2_avro_prog* avro, const b2_json_spec* json, int skip_prefix, const b2_norm* norm, float threshold, float* mse, uint8_t* flag,
                              uint8_t* label, int32_t* status, unsigned long long* counters, cudaStream_t stream) {
   DecodeArgs<D> args;
@@ -1273,6 +1286,7 @@ static int decode_score_spec(b2_ae* ae, const uint8_t* bytes, const int32_t* off
   }
   args.bytes = bytes;
   args.offs = offs;
+  args.ends = ends;
   args.n = n;
   args.n_out = D;
   args.status = status;
@@ -1291,7 +1305,8 @@ static int decode_score_spec(b2_ae* ae, const uint8_t* bytes, const int32_t* off
   return launch_decode<D, 1, false>(ae->ctx, args, stream);
 }
 
-static int decode_score_any(const char* who, b2_ae* ae, const uint8_t* bytes_dev, const int32_t* offs_dev, int64_t n, const b2_csv_spec* csv,
+static int decode_score_any(const char* who, b2_ae* ae, const uint8_t* bytes_dev, const int32_t* offs_dev, const int32_t* ends_dev, int64_t n,
+                            const b2_csv_spec* csv,
                             const b2_avro_prog* avro, const b2_json_spec* json, int skip_prefix, const b2_norm* norm, float threshold,
                             float* mse_dev, uint8_t* flag_dev, uint8_t* label_dev, int32_t* status_dev, unsigned long long* counters_dev,
                             void* stream) {
@@ -1306,10 +1321,10 @@ static int decode_score_any(const char* who, b2_ae* ae, const uint8_t* bytes_dev
   if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   if (ae->spec_d == 18)
-    return decode_score_spec<18>(ae, bytes_dev, offs_dev, n, csv, avro, json, skip_prefix, norm, threshold, mse_dev, flag_dev, label_dev,
+    return decode_score_spec<18>(ae, bytes_dev, offs_dev, ends_dev, n, csv, avro, json, skip_prefix, norm, threshold, mse_dev, flag_dev, label_dev,
                                  status_dev, counters_dev, st);
   if (ae->spec_d == 30)
-    return decode_score_spec<30>(ae, bytes_dev, offs_dev, n, csv, avro, json, skip_prefix, norm, threshold, mse_dev, flag_dev, label_dev,
+    return decode_score_spec<30>(ae, bytes_dev, offs_dev, ends_dev, n, csv, avro, json, skip_prefix, norm, threshold, mse_dev, flag_dev, label_dev,
                                  status_dev, counters_dev, st);
   b2_set_error("%s: fused path needs the D-14-7-7-D autoencoder with D in {18, 30}; decode and score separately", who);
   return B2_EUNSUPPORTED;
@@ -1320,7 +1335,7 @@ extern "C" int b2_decode_score(b2_ae* ae, const uint8_t* bytes_dev, const int32_
                                uint8_t* flag_dev, uint8_t* label_dev, int32_t* status_dev, unsigned long long* counters_dev,
                                void* stream) {
   B2_REQUIRE((csv != nullptr) != (avro != nullptr), "b2_decode_score: exactly one of csv / avro must be given");
-  return decode_score_any("b2_decode_score", ae, bytes_dev, offs_dev, n, csv, avro, nullptr, skip_prefix, norm, threshold, mse_dev, flag_dev,
+  return decode_score_any("b2_decode_score", ae, bytes_dev, offs_dev, nullptr, n, csv, avro, nullptr, skip_prefix, norm, threshold, mse_dev, flag_dev,
                           label_dev, status_dev, counters_dev, stream);
 }
 
@@ -1328,6 +1343,19 @@ extern "C" int b2_decode_score_json(b2_ae* ae, const uint8_t* bytes_dev, const i
                                     const b2_norm* norm, float threshold, float* mse_dev, uint8_t* flag_dev, uint8_t* label_dev,
                                     int32_t* status_dev, unsigned long long* counters_dev, void* stream) {
   B2_REQUIRE(json != nullptr, "b2_decode_score_json: spec is NULL");
-  return decode_score_any("b2_decode_score_json", ae, bytes_dev, offs_dev, n, nullptr, nullptr, json, 0, norm, threshold, mse_dev, flag_dev,
+  return decode_score_any("b2_decode_score_json", ae, bytes_dev, offs_dev, nullptr, n, nullptr, nullptr, json, 0, norm, threshold, mse_dev, flag_dev,
                           label_dev, status_dev, counters_dev, stream);
+}
+
+// The same fused pass over records given as byte RANGES [begin[i], end[i]) of bytes_dev: ascending, end[i] >= begin[i], gaps
+// allowed — what b2_kafka_index_records writes, so that a Kafka segment is decoded and scored where it lies (no packed copy of the
+// values).  Exactly one of csv / avro / json.
+extern "C" int b2_decode_score_spans(b2_ae* ae, const uint8_t* bytes_dev, const int32_t* begin_dev, const int32_t* end_dev, int64_t n,
+                                     const b2_csv_spec* csv, const b2_avro_prog* avro, const b2_json_spec* json, int skip_prefix,
+                                     const b2_norm* norm, float threshold, float* mse_dev, uint8_t* flag_dev, uint8_t* label_dev,
+                                     int32_t* status_dev, unsigned long long* counters_dev, void* stream) {
+  B2_REQUIRE((csv != nullptr) + (avro != nullptr) + (json != nullptr) == 1, "b2_decode_score_spans: exactly one of csv / avro / json must be given");
+  B2_REQUIRE(n == 0 || end_dev != nullptr, "b2_decode_score_spans: end_dev is NULL");
+  return decode_score_any("b2_decode_score_spans", ae, bytes_dev, begin_dev, end_dev, n, csv, avro, json, json ? 0 : skip_prefix, norm,
+                          threshold, mse_dev, flag_dev, label_dev, status_dev, counters_dev, stream);
 }

@@ -7,13 +7,16 @@
 // baseSequence i32 | recordCount i32 | records…, all big-endian; a record = length varint | attributes i8 | timestampDelta
 // varlong | offsetDelta varint | keyLength varint | key | valueLength varint | value | headerCount varint | headers.
 //
-// The caller walks the batch chain on the host (one length field per batch) and hands over the batch positions and the running
-// record count; here one thread per batch verifies the CRC-32C (slicing-by-4 tables in shared memory) and walks its records,
-// writing each value's [begin, end) — then a warp-per-32-records gather packs the values back to back so that the result is the
-// (bytes, offsets) batch every decode entry point consumes.
+// The caller walks the batch chain on the host (one length field per batch: b2_kafka_scan_batches) and hands over the batch
+// positions and the running record count; here one WARP per batch verifies the CRC-32C (coalesced, 32 interleaved lane states
+// folded at the end) and walks its records (length chain in lock-step, record fields one record per lane), writing each value's
+// [begin, end).  The decode entry points take those ranges as they are (b2_decode_score_spans: the segment is the input, nothing
+// is copied); b2_kafka_gather_values packs the values back to back for callers that want a (bytes, offsets) batch.
 // Compressed batches (attributes & 7: gzip, Snappy, LZ4) are inflated first — b2_kafka_inflate_sizes / b2_kafka_inflate, one thread
 // per batch running the sequential decoders of inflate.cuh — into a rebuilt, uncompressed copy of the segment that then takes
 // the path above; zstd batches are reported (B2_FRAME_COMPRESSED) and skipped.
+#include <mutex>
+
 #include "common.cuh"
 #include "inflate.cuh"
 
@@ -40,6 +43,27 @@ __device__ __forceinline__ bool read_varint(const uint8_t* __restrict__ s, long 
   return false;
 }
 
+// The same, for the index kernel: the four bytes at p arrive as ONE round trip (two aligned words, funnel shift) instead of a chain
+// of dependent byte loads; a varint of up to four bytes (every length below 2^27) is taken from the register.  Near the end of
+// its container and for longer varints the byte loop decides.
+__device__ __forceinline__ bool read_varint_w(const uint8_t* __restrict__ s, long long& p, long long e, long long* v) {
+  if (p + 8 <= e) {
+    const uintptr_t at = reinterpret_cast<uintptr_t>(s + p);
+    const uint32_t* wp = reinterpret_cast<const uint32_t*>(at & ~(uintptr_t)3);
+    uint32_t x = __funnelshift_r(wp[0], wp[1], (int)(at & 3u) * 8);
+    const uint32_t stop = ~x & 0x80808080u;  // the first byte without a continuation bit ends the varint
+    if (stop) {
+      const int nb = __ffs((int)stop) >> 3;  // 1..4 bytes
+      if (nb < 4) x &= (1u << (8 * nb)) - 1u;
+      const uint32_t u = (x & 0x7Fu) | ((x >> 1) & 0x3F80u) | ((x >> 2) & 0x1FC000u) | ((x >> 3) & 0xFE00000u);
+      *v = (long long)(u >> 1) ^ -(long long)(u & 1u);
+      p += nb;
+      return true;
+    }
+  }
+  return read_varint(s, p, e, v);
+}
+
 struct FrameArgs {
   const uint8_t* bytes;
   long long n_bytes;
@@ -52,82 +76,234 @@ struct FrameArgs {
   int32_t* status;             // [nb]
 };
 
-__global__ void __launch_bounds__(KF_NT) kafka_index_kernel(const FrameArgs a) {
-  __shared__ uint32_t tab[4][256];
-  for (int i = threadIdx.x; i < 256; i += KF_NT) {  // CRC-32C (Castagnoli, reflected 0x82F63B78), slicing-by-4
-    uint32_t c = (uint32_t)i;
-    for (int k = 0; k < 8; ++k) c = (c >> 1) ^ ((c & 1u) ? 0x82F63B78u : 0u);
-    tab[0][i] = c;
+// CRC-32C tables: tab[k] = the slicing-by-4 set (advance the state over one byte / four bytes); far[k] = the same state advanced
+// over 128 zero bytes (a 32 x 32 matrix over GF(2) laid out as four 256-entry tables, one per state byte).  Built once on the
+// host, uploaded once per device.
+struct CrcTabs {
+  uint32_t tab[4][256];
+  uint32_t far[4][256];
+};
+__device__ CrcTabs g_crc_tabs;
+
+const CrcTabs& host_crc_tabs() {
+  static CrcTabs t;
+  static bool built = false;
+  if (!built) {
+    for (uint32_t i = 0; i < 256; ++i) {
+      uint32_t c = i;
+      for (int k = 0; k < 8; ++k) c = (c >> 1) ^ ((c & 1u) ? 0x82F63B78u : 0u);
+      t.tab[0][i] = c;
+    }
+    for (uint32_t i = 0; i < 256; ++i) {
+      uint32_t c = t.tab[0][i];
+      for (int k = 1; k < 4; ++k) {
+        c = t.tab[0][c & 0xFFu] ^ (c >> 8);
+        t.tab[k][i] = c;
+      }
+    }
+    for (int k = 0; k < 4; ++k)
+      for (uint32_t i = 0; i < 256; ++i) {
+        uint32_t c = i << (8 * k);
+        for (int z = 0; z < 128; ++z) c = t.tab[0][c & 0xFFu] ^ (c >> 8);
+        t.far[k][i] = c;
+      }
+    built = true;
+  }
+  return t;
+}
+
+std::mutex g_crc_mutex;
+bool g_crc_uploaded[64];
+cudaError_t upload_crc_tabs(int device, cudaStream_t stream) {
+  std::lock_guard<std::mutex> lock(g_crc_mutex);
+  if (device >= 0 && device < 64 && g_crc_uploaded[device]) return cudaSuccess;
+  const CrcTabs& t = host_crc_tabs();
+  // stream-ordered in front of the first kernel that reads it; the host copy is static, so the async copy's source stays valid
+  cudaError_t e = cudaMemcpyToSymbolAsync(g_crc_tabs, &t, sizeof(CrcTabs), 0, cudaMemcpyHostToDevice, stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+  if (e == cudaSuccess && device >= 0 && device < 64) g_crc_uploaded[device] = true;
+  return e;
+}
+
+constexpr int KF_WARPS = 8;        // batches in flight per CTA: one warp each
+constexpr int KF_TILE_ROWS = 32;   // CRC rows (of 128 bytes) between two stretches of the record walk: 4 KB stays in L1
+
+// One WARP per record batch.
+//  * CRC-32C: the checked bytes are taken as rows of 32 little-endian words, lane l owning word l of every row — coalesced loads —
+//    with the lane's running state advanced over the 128 bytes of a row by the `far` tables (c = far(c) ^ word: the four lookups
+//    of slicing-by-4, different tables).  The stream is padded IN FRONT with zero bytes to a whole number of rows (leading zeros
+//    leave a zero state alone), the initial 0xFFFFFFFF becomes an XOR onto the first four real bytes, and the 32 lane states are
+//    folded by one more slicing pass over them.
+//  * Record walk: the chain of record lengths is followed by all lanes in lock-step (same address in every lane: one broadcast
+//    load), 32 records at a time, lane k keeping record k's bounds; then the lanes read their own record's varints in parallel and
+//    store 32 value ranges coalesced.  The walk runs in stretches right behind the CRC rows of the same 4 KB, so that it finds
+//    its bytes in L1.
+__global__ void __launch_bounds__(KF_WARPS * 32) kafka_index_kernel(const FrameArgs a) {
+  __shared__ CrcTabs t;
+  {
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(&g_crc_tabs);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(&t);
+    for (int i = threadIdx.x; i < (int)(sizeof(CrcTabs) / 4); i += KF_WARPS * 32) dst[i] = src[i];
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < 256; i += KF_NT) {
-    uint32_t c = tab[0][i];
-    for (int t = 1; t < 4; ++t) {
-      c = tab[0][c & 0xFFu] ^ (c >> 8);
-      tab[t][i] = c;
+  constexpr unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const long long n_warps = (long long)gridDim.x * KF_WARPS;
+  const uint8_t* __restrict__ s = a.bytes;
+  for (long long b = (long long)blockIdx.x * KF_WARPS + (threadIdx.x >> 5); b < a.nb; b += n_warps) {
+    const long long pos = a.batch_pos[b];
+    int st = B2_FRAME_OK;
+    long long n_rec = 0, endb = 0;
+    bool control = false;
+    if (pos < 0 || pos + KF_HEADER > a.n_bytes) {
+      st = B2_FRAME_TRUNCATED;
+    } else {
+      const long long blen = (long long)(int32_t)be32(s + pos + 8);
+      endb = pos + 12 + blen;
+      n_rec = (long long)(int32_t)be32(s + pos + 57);
+      if (s[pos + 16] != 2) st = B2_FRAME_BAD_MAGIC;
+      else if (blen < KF_HEADER - 12 || endb > a.n_bytes || n_rec < 0) st = B2_FRAME_TRUNCATED;
+      else if ((s[pos + 22] & 7u) != 0) st = B2_FRAME_COMPRESSED;  // low 3 bits of attributes = codec
+      else control = (s[pos + 22] & 0x20u) != 0;                   // attributes bit 5: transaction markers, never delivered
     }
-  }
-  __syncthreads();
-  const long long b = (long long)blockIdx.x * KF_NT + threadIdx.x;
-  if (b >= a.nb) return;
-  const long long pos = a.batch_pos[b];
-  const uint8_t* s = a.bytes;
-  int st = B2_FRAME_OK;
-  long long n_rec = 0, endb = 0;
-  if (pos < 0 || pos + KF_HEADER > a.n_bytes) {
-    st = B2_FRAME_TRUNCATED;
-  } else {
-    const long long blen = (long long)(int32_t)be32(s + pos + 8);
-    endb = pos + 12 + blen;
-    n_rec = (long long)(int32_t)be32(s + pos + 57);
-    if (s[pos + 16] != 2) st = B2_FRAME_BAD_MAGIC;
-    else if (blen < KF_HEADER - 12 || endb > a.n_bytes || n_rec < 0) st = B2_FRAME_TRUNCATED;
-    else if ((s[pos + 22] & 7u) != 0) st = B2_FRAME_COMPRESSED;  // low 3 bits of attributes = codec
-  }
-  if (st == B2_FRAME_OK && a.verify_crc) {
-    uint32_t c = 0xFFFFFFFFu;
-    long long p = pos + 21;
-    for (; p + 4 <= endb; p += 4) {
-      c ^= (uint32_t)s[p] | ((uint32_t)s[p + 1] << 8) | ((uint32_t)s[p + 2] << 16) | ((uint32_t)s[p + 3] << 24);
-      c = tab[3][c & 0xFFu] ^ tab[2][(c >> 8) & 0xFFu] ^ tab[1][(c >> 16) & 0xFFu] ^ tab[0][c >> 24];
+    const long long r0 = a.rec_base[b];
+    if (n_rec < 0) n_rec = 0;
+    if (st == B2_FRAME_OK) {
+      // the checked stream [S, endb), n bytes, padded in front to whole rows
+      const long long S = pos + 21, n = endb - S;
+      const int pad = (int)((128 - (n & 127)) & 127);
+      const long long rows = (n + pad) >> 7;
+      const int sh = (int)((reinterpret_cast<uintptr_t>(s) + (uintptr_t)(S - pad + 4ll * lane)) & 3u) * 8;  // same in every lane
+      uint32_t c = 0;
+      long long p = pos + KF_HEADER, r = 0;  // record walk: next record's first byte, records done
+      bool bad = false, guess = true;
+      const bool walk = !control;
+      for (long long row0 = 0; row0 < rows; row0 += KF_TILE_ROWS) {
+        const long long row1 = min(rows, row0 + KF_TILE_ROWS);
+        // the padding, the initial value (rows 0 and 1) and the stream's last bytes (its last row) byte by byte; every other row
+        // with aligned word loads, eight rows' loads in flight in front of the eight dependent table steps
+        auto slow_word = [&](long long row) -> uint32_t {
+          const long long o = (row << 7) + 4 * lane - pad;  // real offset of this lane's word
+          uint32_t w = 0;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const long long ro = o + j;
+            if (ro >= 0 && ro < n) w |= ((uint32_t)s[S + ro] ^ (ro < 4 ? 0xFFu : 0u)) << (8 * j);
+          }
+          return w;
+        };
+        auto fast_word = [&](long long row) -> uint32_t {
+          const long long o = (row << 7) + 4 * lane - pad;
+          const uint32_t* wp = reinterpret_cast<const uint32_t*>(reinterpret_cast<uintptr_t>(s + S + o) & ~(uintptr_t)3);
+          uint32_t w = wp[0];
+          if (sh) w = __funnelshift_r(w, wp[1], sh);
+          return w;
+        };
+        auto step = [&](uint32_t w) { c = t.far[0][c & 0xFFu] ^ t.far[1][(c >> 8) & 0xFFu] ^ t.far[2][(c >> 16) & 0xFFu] ^ t.far[3][c >> 24] ^ w; };
+        long long row = row0;
+        for (; row < row1 && row < 2; ++row) step(slow_word(row));
+        const long long fast_end = min(row1, rows - 1);
+        for (; row + 8 <= fast_end; row += 8) {
+          uint32_t w[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) w[j] = fast_word(row + j);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) step(w[j]);
+        }
+        for (; row < fast_end; ++row) step(fast_word(row));
+        if (row < row1) step(slow_word(row));  // the stream's last row
+        if (!walk || bad) continue;
+        const long long g_hi = row1 == rows ? endb : S + (row1 << 7) - pad;  // bytes below g_hi have been read
+        while (r < n_rec && p < g_hi && !bad) {
+          // every length is untrusted: compare it with the bytes that are left instead of adding it to the cursor (a crafted
+          // varint near 2^63 would wrap the sum negative and slip past a `>` test)
+          long long ms = 0, me = 0;
+          int cnt = 0;
+          const int want = (int)min(32ll, n_rec - r);
+          if (guess) {
+            // Sensor records mostly have ONE length: take the stride from the record at p, let lane l read the length at
+            // p + l * stride; the leading lanes whose record has exactly that length prove the next lane's start — 32 record
+            // starts for the price of two, however long the chain.
+            long long q0 = p, len0;
+            if (!read_varint_w(s, q0, endb, &len0) || len0 < 0 || len0 > endb - q0) {
+              bad = true;
+              break;
+            }
+            const long long stride = q0 - p + len0;  // >= 1
+            long long tot = -1;
+            if (lane < want && (lane == 0 || stride <= (endb - p - 1) / lane)) {  // the guessed start lies inside the batch
+              long long q = p + lane * stride, len;
+              const long long at = q;
+              if (read_varint_w(s, q, endb, &len) && len >= 0 && len <= endb - q) ms = q, me = q + len, tot = me - at;
+            }
+            const unsigned eq = __ballot_sync(FULL, tot == stride);  // lane 0 is always in
+            const int m = eq == FULL ? 32 : __ffs((int)~eq) - 1;      // lanes 0 .. m-1 have the stride: lanes 0 .. m start a record
+            const long long tot_m = __shfl_sync(FULL, tot, m & 31);
+            cnt = m;
+            if (m < want) {
+              if (tot_m >= 0) cnt = m + 1;  // the first record of another length: known too
+              else bad = true;              // a record that must exist cannot be read
+            }
+            p = __shfl_sync(FULL, me, cnt - 1);  // cnt >= 1: end of the last record taken
+            guess = cnt >= 4;                    // lengths vary (text values): follow the chain one by one for a round
+          } else {
+            for (int k = 0; k < want && p < g_hi; ++k) {
+              long long len;
+              if (!read_varint_w(s, p, endb, &len) || len < 0 || len > endb - p) {
+                bad = true;
+                break;
+              }
+              if (k == lane) ms = p, me = p + len;
+              p += len;
+              ++cnt;
+            }
+            guess = true;
+          }
+          int32_t vb = 0, ve = 0;
+          bool ok = true;
+          if (lane < cnt) {
+            long long q = ms + 1, v, klen, vlen;  // attributes
+            ok = q <= me && read_varint_w(s, q, me, &v) && read_varint_w(s, q, me, &v) && read_varint_w(s, q, me, &klen) && klen >= -1 &&
+                 klen <= me - q;
+            if (ok) {
+              if (klen > 0) q += klen;
+              ok = read_varint_w(s, q, me, &vlen) && vlen >= -1 && vlen <= me - q;
+              vb = (int32_t)q;                               // a null value (length -1) is an empty record
+              ve = (int32_t)(q + (vlen > 0 ? vlen : 0));     // headers are skipped with the record length
+            }
+          }
+          if (__any_sync(FULL, !ok)) bad = true;
+          if (lane < cnt && !bad) {
+            a.begin[r0 + r + lane] = vb;
+            a.end[r0 + r + lane] = ve;
+          }
+          r += cnt;
+        }
+      }
+      if (a.verify_crc) {
+        // fold the lane states: lane l's words sit 4 (31 - l) bytes in front of the stream's end
+        uint32_t f = 0;
+        for (int l = 0; l < 32; ++l) {
+          f ^= __shfl_sync(FULL, c, l);
+          f = t.tab[3][f & 0xFFu] ^ t.tab[2][(f >> 8) & 0xFFu] ^ t.tab[1][(f >> 16) & 0xFFu] ^ t.tab[0][f >> 24];
+        }
+        if ((f ^ 0xFFFFFFFFu) != be32(s + pos + 17)) st = B2_FRAME_BAD_CRC;
+      }
+      if (st == B2_FRAME_OK) {
+        if (control) st = B2_FRAME_CONTROL;
+        else if (bad || r < n_rec) st = B2_FRAME_TRUNCATED;
+      }
     }
-    for (; p < endb; ++p) c = tab[0][(c ^ s[p]) & 0xFFu] ^ (c >> 8);
-    if ((c ^ 0xFFFFFFFFu) != be32(s + pos + 17)) st = B2_FRAME_BAD_CRC;
-  }
-  const long long r0 = a.rec_base[b];
-  if (st == B2_FRAME_OK && (s[pos + 22] & 0x20u)) st = B2_FRAME_CONTROL;  // attributes bit 5: transaction markers, never delivered
-  if (st == B2_FRAME_OK) {
-    long long p = pos + KF_HEADER;
-    for (long long r = 0; r < n_rec; ++r) {
-      // every length is untrusted: compare it with the bytes that are left instead of adding it to the cursor (a crafted
-      // varint near 2^63 would wrap the sum negative and slip past a `>` test)
-      long long len, v, klen, vlen;
-      if (!read_varint(s, p, endb, &len) || len < 0 || len > endb - p) {
-        st = B2_FRAME_TRUNCATED;
-        break;
-      }
-      const long long rec_end = p + len;
-      p += 1;                                                     // attributes
-      if (p > rec_end || !read_varint(s, p, rec_end, &v) || !read_varint(s, p, rec_end, &v) || !read_varint(s, p, rec_end, &klen) ||
-          klen < -1 || klen > rec_end - p) {
-        st = B2_FRAME_TRUNCATED;
-        break;
-      }
-      if (klen > 0) p += klen;
-      if (!read_varint(s, p, rec_end, &vlen) || vlen < -1 || vlen > rec_end - p) {
-        st = B2_FRAME_TRUNCATED;
-        break;
-      }
-      a.begin[r0 + r] = (int32_t)p;                               // a null value (length -1) is an empty record
-      a.end[r0 + r] = (int32_t)(p + (vlen > 0 ? vlen : 0));
-      p = rec_end;                                                // headers are skipped with the record length
+    // a refused batch yields an EMPTY range for each of the records its header announces (the caller sized begin / end from
+    // those same counts) — also when the record walk itself ran into a truncation: ranges written before are withdrawn.  The
+    // empty range sits at the batch's position, so that the ranges of a segment stay in ascending order.
+    if (st != B2_FRAME_OK) {
+      const int32_t at = (int32_t)max(0ll, min(pos, a.n_bytes));
+      for (long long i = lane; i < n_rec; i += 32) a.begin[r0 + i] = a.end[r0 + i] = at;
     }
+    if (lane == 0) a.status[b] = st;
+    __syncwarp();
   }
-  // a refused batch yields the empty range [0, 0) for each of the records its header announces (the caller sized begin / end
-  // from those same counts) — also when the record walk itself ran into a truncation: ranges written before the break are withdrawn
-  if (st != B2_FRAME_OK)
-    for (long long r = 0; r < n_rec; ++r) a.begin[r0 + r] = a.end[r0 + r] = 0;
-  a.status[b] = st;
 }
 
 // values [begin[i], end[i]) → packed at out_offs[i] (the caller scanned the lengths); one warp per 32 records
@@ -304,7 +480,10 @@ extern "C" int b2_kafka_index_records(b2_ctx* ctx, const uint8_t* bytes_dev, int
   a.begin = begin_dev;
   a.end = end_dev;
   a.status = status_dev;
-  kafka_index_kernel<<<(unsigned)((n_batches + KF_NT - 1) / KF_NT), KF_NT, 0, (cudaStream_t)stream>>>(a);
+  B2_CUDA(upload_crc_tabs(ctx->device, (cudaStream_t)stream));
+  long long grid = (n_batches + KF_WARPS - 1) / KF_WARPS;
+  if (grid > (long long)ctx->sm_count * 4) grid = (long long)ctx->sm_count * 4;
+  kafka_index_kernel<<<(unsigned)grid, KF_WARPS * 32, 0, (cudaStream_t)stream>>>(a);
   B2_CUDA(cudaGetLastError());
   return B2_OK;
 }
@@ -321,4 +500,29 @@ extern "C" int b2_kafka_gather_values(b2_ctx* ctx, const uint8_t* bytes_dev, con
   kafka_gather_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(bytes_dev, begin_dev, end_dev, n, out_offs_dev, out_bytes_dev);
   B2_CUDA(cudaGetLastError());
   return B2_OK;
+}
+
+// Host walk of the batch chain of a log segment / fetch response held in HOST memory: batch b starts at batch_pos[b] and announces
+// rec_count[b] records (clamped at 0).  Stops at the first header that does not fit or announces a batch running past the end (a
+// fetch response may end in a partial batch; consumers drop it).  Returns the number of batches found; only the first `cap` are
+// written, so a first call with cap = 0 sizes the arrays.
+extern "C" int64_t b2_kafka_scan_batches(const uint8_t* bytes_host, int64_t n_bytes, int64_t* batch_pos, int64_t* rec_count, int64_t cap) {
+  if (!bytes_host || n_bytes < 0 || (cap > 0 && (!batch_pos || !rec_count))) return -1;
+  auto be32h = [&](int64_t at) -> int64_t {
+    return (int64_t)(int32_t)(((uint32_t)bytes_host[at] << 24) | ((uint32_t)bytes_host[at + 1] << 16) | ((uint32_t)bytes_host[at + 2] << 8) |
+                              (uint32_t)bytes_host[at + 3]);
+  };
+  int64_t pos = 0, nb = 0;
+  while (pos + KF_HEADER <= n_bytes) {
+    const int64_t blen = be32h(pos + 8);
+    if (blen < KF_HEADER - 12 || blen > n_bytes - pos - 12) break;
+    if (nb < cap) {
+      const int64_t cnt = be32h(pos + 57);
+      batch_pos[nb] = pos;
+      rec_count[nb] = cnt > 0 ? cnt : 0;
+    }
+    ++nb;
+    pos += 12 + blen;
+  }
+  return nb;
 }

@@ -59,6 +59,26 @@ class RecordBatch:
         return rb
 
 
+class RecordSpans:
+    """Records given as byte ranges ``[begin[i], end[i])`` of one device buffer — ascending, gaps allowed: the message values of a
+    Kafka segment where they lie (``kafka.index_segment``).  :func:`decode_score` takes it like a :class:`RecordBatch`; nothing
+    is copied."""
+
+    def __init__(self, data: torch.Tensor, begin: torch.Tensor, end: torch.Tensor, n: int, skip_prefix: int = 0):
+        if data.dtype != torch.uint8 or begin.dtype != torch.int32 or end.dtype != torch.int32 or not data.is_cuda:
+            raise TypeError("RecordSpans wants a CUDA uint8 buffer and int32 begin / end")
+        self.data, self.begin, self.end, self.n, self.skip_prefix = data, begin, end, int(n), int(skip_prefix)
+
+    @property
+    def nbytes(self) -> int:
+        return int(self.data.numel())
+
+    def substr(self, pos: int, length: int = -1) -> "RecordSpans":
+        if length != -1:
+            raise NotImplementedError("only substr(e, pos, -1) (drop a fixed prefix) is used by the reference")
+        return RecordSpans(self.data, self.begin, self.end, self.n, self.skip_prefix + int(pos))
+
+
 def substr(records: RecordBatch, pos: int, length: int = -1) -> RecordBatch:
     """``tf.strings.substr(e, 5, -1)``: strip the Confluent framing (magic byte + 4-byte schema id), cardata-v1.py:13."""
     return records.substr(pos, length)
@@ -305,7 +325,8 @@ def decode_score(model, records, csv_kinds=None, csv_defaults=None, avro_schema=
                  status: Optional[torch.Tensor] = None, counters: Optional[torch.Tensor] = None, field_delim=",", use_quote_delim=True):
     """The streaming scoring loop of cardata-v1.py:176-231 in ONE kernel: decode → normalize_fn → Dense AE → MSE → flag.
     Everything stays on the device; returns (mse, flag, label, status) tensors.  Bad records get mse = NaN, flag = 0."""
-    rb = _as_batch(records)
+    spans = records if isinstance(records, RecordSpans) else None
+    rb = spans or _as_batch(records)
     dev = rb.data.device
     if mse is None:
         mse = torch.empty(rb.n, dtype=torch.float32, device=dev)
@@ -316,6 +337,22 @@ def decode_score(model, records, csv_kinds=None, csv_defaults=None, avro_schema=
     if (csv_kinds is not None) + (avro_schema is not None) + (json_keys is not None) != 1:
         raise ValueError("give exactly one of csv_kinds / avro_schema / json_keys")
     spec = p = None
+    if spans is not None:  # byte ranges inside a larger buffer (a Kafka segment): same kernel, no packed copy of the values
+        js = _json_spec_struct(json_keys, json_label) if json_keys is not None else None
+        if csv_kinds is not None:
+            spec = _csv_spec_struct(csv_kinds, csv_defaults, field_delim, use_quote_delim)
+        elif avro_schema is not None:
+            prog, p = _avro_prog_struct(avro_schema)
+        if label is None and csv_kinds is None:
+            label = torch.empty(rb.n, dtype=torch.uint8, device=dev)
+        nm = model._norm_struct()
+        _size_hint(rb)
+        _ffi.check(_ffi.lib().b2_decode_score_spans(model._handle(), _ffi.ptr(rb.data), _ffi.ptr(rb.begin), _ffi.ptr(rb.end), rb.n,
+                                                    C.byref(spec) if spec is not None else None, C.byref(p) if p is not None else None,
+                                                    C.byref(js) if js is not None else None, rb.skip_prefix, C.byref(nm), float(threshold),
+                                                    _ffi.ptr(mse), _ffi.ptr(flag), _ffi.ptr(label), _ffi.ptr(status), _ffi.ptr(counters),
+                                                    _stream_ptr()), "b2_decode_score_spans")
+        return mse, flag, label, status
     if json_keys is not None:
         js = _json_spec_struct(json_keys, json_label)
         if label is None:

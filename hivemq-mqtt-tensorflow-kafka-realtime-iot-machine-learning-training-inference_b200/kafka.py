@@ -1,10 +1,12 @@
 """Kafka record-batch (message format v2) framing: broker bytes → the ``RecordBatch`` of message values the decoders take.
 
 In the reference this is tensorflow-io's ``KafkaDataset`` / librdkafka (cardata-v1.py:10).  ``scan_batches`` walks the batch
-chain on the host (12 bytes per batch), ``values_from_segment`` lets the GPU inflate compressed batches (gzip / Snappy / LZ4;
-``b2_kafka_inflate_sizes`` + ``b2_kafka_inflate``), check every batch's CRC-32C, walk its records
-(``b2_kafka_index_records``) and pack the values back to back (``b2_kafka_gather_values``).  ``write_segment`` is the inverse,
-host side, for tests and synthetic input (Kafka itself is replaced offline by in-memory bytes, BASELINE.json).
+chain on the host (12 bytes per batch; ``b2_kafka_scan_batches``), ``index_segment`` lets the GPU inflate compressed batches
+(gzip / Snappy / LZ4; ``b2_kafka_inflate_sizes`` + ``b2_kafka_inflate``), check every batch's CRC-32C and walk its records
+(``b2_kafka_index_records``, one warp per batch) and returns the values as ``RecordSpans`` — byte ranges inside the segment, which
+``decode.decode_score`` consumes where they lie.  ``values_from_segment`` additionally packs the values back to back
+(``b2_kafka_gather_values``) into a ``RecordBatch`` for the other decoders.  ``write_segment`` / ``write_segment_uniform`` are the
+inverse, host side, for tests and synthetic input (Kafka itself is replaced offline by in-memory bytes, BASELINE.json).
 """
 from __future__ import annotations
 
@@ -15,7 +17,7 @@ import numpy as np
 import torch
 
 from . import _ffi
-from .decode import RecordBatch
+from .decode import RecordBatch, RecordSpans
 from .keras_compat import _stream_ptr, get_ctx
 
 FRAME_STATUS = {0: "ok", 1: "not message format v2", 2: "CRC-32C mismatch", 3: "truncated", 4: "compressed batch", 5: "control batch"}
@@ -112,26 +114,55 @@ def write_segment(values: Sequence[bytes], records_per_batch: int = 500, keys: O
 def scan_batches(segment) -> Tuple[np.ndarray, np.ndarray]:
     """Host walk of the batch chain → (batch_pos int64[nb], record_count int64[nb]).  A trailing partial batch (a fetch response
     may end in one) is ignored, like consumers do."""
-    buf = memoryview(segment.numpy() if isinstance(segment, torch.Tensor) else segment).cast("B")
-    n, pos = len(buf), 0
-    bp: List[int] = []
-    rc: List[int] = []
-    while pos + _HEADER <= n:
-        (blen,) = struct.unpack_from(">i", buf, pos + 8)
-        if blen < _HEADER - 12 or pos + 12 + blen > n:
-            break
-        (cnt,) = struct.unpack_from(">i", buf, pos + 57)
-        bp.append(pos)
-        rc.append(max(cnt, 0))
-        pos += 12 + blen
-    return np.asarray(bp, dtype=np.int64), np.asarray(rc, dtype=np.int64)
+    buf = segment.numpy() if isinstance(segment, torch.Tensor) else np.frombuffer(memoryview(segment).cast("B"), dtype=np.uint8)
+    buf = np.ascontiguousarray(buf, dtype=np.uint8)
+    lib = _ffi.lib()
+    p = buf.ctypes.data if buf.size else 0
+    if not buf.size:
+        return np.zeros(0, dtype=np.int64), np.zeros(0, dtype=np.int64)
+    nb = int(lib.b2_kafka_scan_batches(p, int(buf.size), None, None, 0))
+    if nb < 0:
+        raise ValueError("b2_kafka_scan_batches refused its arguments")
+    bp, rc = np.zeros(nb, dtype=np.int64), np.zeros(nb, dtype=np.int64)
+    if nb:
+        lib.b2_kafka_scan_batches(p, int(buf.size), bp.ctypes.data, rc.ctypes.data, nb)
+    return bp, rc
 
 
-def values_from_segment(segment, verify_crc: bool = True, device: Optional[torch.device] = None, skip_prefix: int = 0,
-                        raise_on_error: bool = True):
-    """Log-segment / fetch-response bytes (``bytes``, NumPy uint8, or a CPU / CUDA uint8 tensor; the batch chain is walked on
-    the host copy) → ``(RecordBatch of the message values, batch status int32[nb] on the device)``.  Records of a refused batch
-    come out empty; with ``raise_on_error`` a refused batch raises :class:`FrameError` instead."""
+def write_segment_uniform(values: np.ndarray, records_per_batch: int = 256, base_offset: int = 0) -> np.ndarray:
+    """Vectorised ``write_segment`` for n values of one length (uint8[n, L]; n a multiple of ``records_per_batch``): uncompressed
+    batches, null keys, no headers.  Every batch then has the same layout, so one batch is laid out in Python and the rest is NumPy
+    (the CRC-32C of all batches advances together, one byte position per step).  Returns the segment as uint8[...]."""
+    values = np.ascontiguousarray(values, dtype=np.uint8)
+    n, L = values.shape
+    if n == 0 or n % records_per_batch:
+        raise ValueError("write_segment_uniform wants a whole number of batches")
+    nb = n // records_per_batch
+    recs, vpos = bytearray(), []
+    for i in range(records_per_batch):
+        body = b"\x00" + _varint(3 * i) + _varint(i) + _varint(-1) + _varint(L)
+        recs += _varint(len(body) + L + 1) + body
+        vpos.append(len(recs))
+        recs += bytes(L) + _varint(0)
+    cnt = records_per_batch
+    after_crc = struct.pack(">hiqqqhii", 0, cnt - 1, 1567606196000, 1567606196000 + 3 * cnt, -1, -1, -1, cnt) + bytes(recs)
+    blen = 4 + 1 + 4 + len(after_crc)
+    one = np.frombuffer(struct.pack(">qiib", 0, blen, 0, 2) + b"\0\0\0\0" + after_crc, dtype=np.uint8)
+    seg = np.tile(one, (nb, 1))
+    cols = (np.asarray(vpos, dtype=np.int64) + _HEADER)[:, None] + np.arange(L, dtype=np.int64)[None, :]  # value bytes inside a batch
+    seg[:, cols.reshape(-1)] = values.reshape(nb, records_per_batch * L)
+    offs = (base_offset + np.arange(nb, dtype=np.int64) * records_per_batch).astype(">i8")
+    seg[:, 0:8] = offs.view(np.uint8).reshape(nb, 8)
+    tab = _crc32c_table()
+    c = np.full(nb, 0xFFFFFFFF, dtype=np.uint32)
+    for j in range(21, seg.shape[1]):
+        c = tab[(c ^ seg[:, j]) & 0xFF] ^ (c >> 8)
+    seg[:, 17:21] = (c ^ 0xFFFFFFFF).astype(">u4").view(np.uint8).reshape(nb, 4)
+    return seg.reshape(-1)
+
+
+def _index(segment, verify_crc: bool, device: Optional[torch.device], raise_on_error: bool):
+    """Shared front half: host chain walk, inflate if needed, CRC + record walk → (segment on the device, begin, end, n, status)."""
     if isinstance(segment, torch.Tensor):
         host = segment.cpu() if segment.is_cuda else segment
         seg_t = segment
@@ -178,15 +209,39 @@ def values_from_segment(segment, verify_crc: bool = True, device: Optional[torch
             refused = pre_status != 0
             status = torch.where(refused, pre_status, status)
             if n and bool(refused.any()):
-                rec_bad = torch.repeat_interleave(refused, torch.from_numpy(cnt).to(dev))
-                begin[:n][rec_bad] = 0
-                end[:n][rec_bad] = 0
+                cnt_d = torch.from_numpy(cnt).to(dev)
+                rec_bad = torch.repeat_interleave(refused, cnt_d)
+                at = torch.repeat_interleave(pos_d.to(torch.int32), cnt_d)  # empty, at the batch's position: the ranges stay ascending
+                begin[:n] = torch.where(rec_bad, at, begin[:n])
+                end[:n] = torch.where(rec_bad, at, end[:n])
         if raise_on_error and nb:
             bad = torch.nonzero(status).flatten()
             if bad.numel():
                 b = int(bad[0])
                 raise FrameError(f"record batch {b} at byte {int(pos[b])}: {FRAME_STATUS.get(int(status[b]), '?')} "
                                  f"({bad.numel()} of {nb} batches refused)")
+    return d, begin, end, n, status
+
+
+def index_segment(segment, verify_crc: bool = True, device: Optional[torch.device] = None, skip_prefix: int = 0,
+                  raise_on_error: bool = True):
+    """Log-segment / fetch-response bytes → ``(RecordSpans, batch status int32[nb] on the device)``: the message values as byte
+    ranges inside the segment (inside its inflated copy when batches were compressed).  Records of a refused batch are empty."""
+    d, begin, end, n, status = _index(segment, verify_crc, device, raise_on_error)
+    spans = RecordSpans(d, begin, end, n, skip_prefix=skip_prefix)
+    spans.avg_record_bytes = (int(d.numel()) + max(n, 1) - 1) // max(n, 1)
+    return spans, status
+
+
+def values_from_segment(segment, verify_crc: bool = True, device: Optional[torch.device] = None, skip_prefix: int = 0,
+                        raise_on_error: bool = True):
+    """Log-segment / fetch-response bytes (``bytes``, NumPy uint8, or a CPU / CUDA uint8 tensor; the batch chain is walked on
+    the host copy) → ``(RecordBatch of the message values, batch status int32[nb] on the device)``.  Records of a refused batch
+    come out empty; with ``raise_on_error`` a refused batch raises :class:`FrameError` instead."""
+    d, begin, end, n, status = _index(segment, verify_crc, device, raise_on_error)
+    dev = d.device
+    lib, ctx = _ffi.lib(), get_ctx(dev.index)
+    with torch.cuda.device(dev):
         offs = torch.zeros(n + 1, dtype=torch.int64, device=dev)
         if n:
             torch.cumsum((end[:n] - begin[:n]).to(torch.int64), 0, out=offs[1:])

@@ -170,6 +170,16 @@ int  b2_decode_json(b2_ctx* ctx, const uint8_t* bytes_dev, const int32_t* offs_d
 int  b2_decode_score_json(b2_ae* ae, const uint8_t* bytes_dev, const int32_t* offs_dev, int64_t n, const b2_json_spec* json,
                           const b2_norm* norm, float threshold, float* mse_dev, uint8_t* flag_dev, uint8_t* label_dev,
                           int32_t* status_dev, unsigned long long* counters_dev, void* stream);
+/* The same fused pass over records given as byte RANGES of bytes_dev: record i = [begin_dev[i], end_dev[i]), ranges ascending,
+ * end >= begin, gaps between them allowed (a warp's bulk copy brings the bytes in between along; counters_dev[3] counts them).
+ * That is what b2_kafka_index_records writes: the reference's KafkaDataset hands the scripts one string per message
+ * (cardata-v1.py:10-16); here the segment's bytes are decoded and scored where they lie, with no packed copy of the values.
+ * Exactly one of csv / avro / json; skip_prefix as in b2_decode_score (ignored for JSON).  Same input contract as offs_dev
+ * otherwise (16 readable bytes behind the last record, a record of more than 24 KB is refused). */
+int  b2_decode_score_spans(b2_ae* ae, const uint8_t* bytes_dev, const int32_t* begin_dev, const int32_t* end_dev, int64_t n,
+                           const b2_csv_spec* csv, const b2_avro_prog* avro, const b2_json_spec* json, int skip_prefix,
+                           const b2_norm* norm, float threshold, float* mse_dev, uint8_t* flag_dev, uint8_t* label_dev,
+                           int32_t* status_dev, unsigned long long* counters_dev, void* stream);
 
 /* ---- Avro encoder (inverse of b2_decode_avro) -------------------------------------------------------------------
  * Rows x_dev f32[n, prog->n_out] (+ label_dev u8[n]: 0 "false", 1 "true", else null; NULL = all null) → Avro binary records
@@ -301,19 +311,24 @@ int  b2_format_rows(b2_ctx* ctx, const float* x_dev, int64_t n, int n_cols, int 
 /* ---- Kafka record-batch framing (message format v2) ------------------------------------------
  * What tensorflow-io's KafkaDataset / librdkafka does in front of the reference's scripts (cardata-v1.py:10): fetch-response or
  * log-segment bytes → message values.  The caller walks the batch chain on the host (baseOffset i64, batchLength i32: the next
- * batch starts 12 + batchLength bytes on; recordCount i32 at byte 57) and passes batch_pos_dev int64[n_batches] and rec_base_dev
- * int64[n_batches] (records in the batches before each one).  One thread per batch checks magic == 2, the CRC-32C (verify_crc)
- * and walks the records: begin_dev / end_dev int32[n_records] receive each value's byte range inside bytes_dev, status_dev
- * int32[n_batches] a B2_FRAME_* code (every record a refused batch's header announces gets the empty range [0, 0); record, key and
- * value lengths are untrusted input and are checked against the bytes that remain).
- * b2_kafka_gather_values then packs the values back to back at out_offs_dev int32[n] (the caller's scan of end - begin), giving
- * the (bytes, offsets) batch every decode entry point takes. */
+ * batch starts 12 + batchLength bytes on; recordCount i32 at byte 57 — b2_kafka_scan_batches does it on a host copy of the bytes:
+ * returns the number of batches, writes the first `cap` positions / record counts, so cap = 0 sizes the arrays; a trailing partial
+ * batch is dropped like consumers do) and passes batch_pos_dev int64[n_batches] and rec_base_dev int64[n_batches] (records in the
+ * batches before each one).  One warp per batch checks magic == 2, the CRC-32C (verify_crc) and walks the records: begin_dev /
+ * end_dev int32[n_records] receive each value's byte range inside bytes_dev, status_dev int32[n_batches] a B2_FRAME_* code (every
+ * record a refused batch's header announces gets an EMPTY range placed at the batch's position, so the ranges of a segment whose
+ * batch positions ascend are in ascending order; record, key and value lengths are untrusted input and are checked against the
+ * bytes that remain).
+ * Those ranges go straight into b2_decode_score_spans (below): the segment itself is the decode input and no value is copied.
+ * b2_kafka_gather_values instead packs the values back to back at out_offs_dev int32[n] (the caller's scan of end - begin),
+ * giving the (bytes, offsets) batch every other decode entry point takes. */
 #define B2_FRAME_OK         0
 #define B2_FRAME_BAD_MAGIC  1  /* not message format v2 */
 #define B2_FRAME_BAD_CRC    2
 #define B2_FRAME_TRUNCATED  3  /* batch or record runs past its container */
 #define B2_FRAME_COMPRESSED 4  /* compressed batch handed to b2_kafka_index_records (inflate it first), or a zstd batch (no decoder here) */
 #define B2_FRAME_CONTROL    5  /* control batch (attributes bit 5: transaction markers); consumers never see its records */
+int64_t b2_kafka_scan_batches(const uint8_t* bytes_host, int64_t n_bytes, int64_t* batch_pos, int64_t* rec_count, int64_t cap);
 int  b2_kafka_index_records(b2_ctx* ctx, const uint8_t* bytes_dev, int64_t n_bytes, const int64_t* batch_pos_dev, const int64_t* rec_base_dev,
                             int64_t n_batches, int verify_crc, int32_t* begin_dev, int32_t* end_dev, int32_t* status_dev, void* stream);
 int  b2_kafka_gather_values(b2_ctx* ctx, const uint8_t* bytes_dev, const int32_t* begin_dev, const int32_t* end_dev, int64_t n,

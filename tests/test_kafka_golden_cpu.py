@@ -99,3 +99,40 @@ def test_write_segment_reads_back_with_the_independent_walker():
     assert [v for _, recs in batches for _, v, _ in recs] == vals
     assert [k for _, recs in batches for k, _, _ in recs] == keys
     assert struct.unpack_from(">q", seg, 0)[0] == 77
+
+
+def test_scan_batches_and_uniform_writer_cpu():
+    """The C chain walk (b2_kafka_scan_batches) against a struct.unpack walk, incl. a trailing partial batch and an empty buffer;
+    the vectorised segment writer against the record-by-record one."""
+    import struct
+
+    import b200_sensor as bs
+
+    rng = np.random.default_rng(5)
+    vals = [bytes(rng.integers(0, 256, int(rng.integers(0, 300)), dtype=np.uint8)) for _ in range(700)]
+    seg = bs.kafka.write_segment(vals, records_per_batch=97, headers=True)
+
+    def walk(buf):
+        pos, out = 0, []
+        while pos + 61 <= len(buf):
+            (blen,) = struct.unpack_from(">i", buf, pos + 8)
+            if blen < 49 or pos + 12 + blen > len(buf):
+                break
+            out.append((pos, max(struct.unpack_from(">i", buf, pos + 57)[0], 0)))
+            pos += 12 + blen
+        return out
+
+    for cut in (0, 1, 30, 61, 500):
+        buf = seg[:len(seg) - cut]
+        bp, rc = bs.kafka.scan_batches(buf)
+        assert list(zip(bp.tolist(), rc.tolist())) == walk(buf), cut
+    bp, rc = bs.kafka.scan_batches(b"")
+    assert bp.size == 0 and rc.size == 0
+    bad = bytearray(seg)
+    bad[8:12] = struct.pack(">i", -5)  # a negative batch length ends the walk at once
+    assert bs.kafka.scan_batches(bytes(bad))[0].size == 0
+
+    fixed = rng.integers(0, 256, (512, 63), dtype=np.uint8)
+    a = bs.kafka.write_segment_uniform(fixed, records_per_batch=128, base_offset=11)
+    b = bs.kafka.write_segment([bytes(v) for v in fixed], records_per_batch=128, base_offset=11)
+    assert bytes(a) == b

@@ -132,3 +132,97 @@ def test_compressed_batches_are_inflated(cuda_device, compression):
     z[pos[2] + 22] = (z[pos[2] + 22] & ~7) | 4
     _, st4 = bs.kafka.values_from_segment(bytes(z), raise_on_error=False, verify_crc=False)
     assert st4.cpu().tolist()[2] == 4
+
+
+def _ae18():
+    k = bs.keras
+    inp = k.layers.Input(shape=(18,))
+    h = k.layers.Dense(14, activation="tanh")(inp)
+    h = k.layers.Dense(7, activation="relu")(h)
+    h = k.layers.Dense(7, activation="tanh")(h)
+    return k.models.Model(inputs=inp, outputs=k.layers.Dense(18, activation="relu")(h))
+
+
+@pytest.mark.parametrize("per_batch", [1, 31, 32, 33, 700, 20_000])
+def test_warp_per_batch_walk_all_batch_shapes(cuda_device, per_batch):
+    """One warp per batch, 32 records per round, 4 KB stretches between CRC rows: batch sizes around every one of those edges,
+    values from 0 to 600 bytes (records longer than a CRC row and shorter than a word), keys and headers in between."""
+    g = np.random.default_rng(per_batch)
+    n = 20_000 if per_batch > 33 else 40 * per_batch + 7
+    vals = [bytes(g.integers(0, 256, int(g.integers(0, 600 if i % 50 == 0 else 90)), dtype=np.uint8)) for i in range(n)]
+    keys = [None if i % 5 else b"k" * (i % 200) for i in range(n)]
+    seg = bs.kafka.write_segment(vals, records_per_batch=per_batch, keys=keys, headers=True)
+    rb, st = bs.kafka.values_from_segment(seg)
+    assert rb.n == n and not st.any()
+    d, o = rb.data.cpu().numpy().tobytes(), rb.offsets.cpu().numpy()
+    assert [d[o[i]:o[i + 1]] for i in range(n)] == vals
+    spans, st2 = bs.kafka.index_segment(seg)
+    b, e = spans.begin.cpu().numpy()[:n], spans.end.cpu().numpy()[:n]
+    assert (b[1:] >= e[:-1]).all() and (e >= b).all()
+    assert [seg[b[i]:e[i]] for i in range(0, n, 17)] == vals[::17]
+
+
+def test_crc_flags_a_flip_anywhere_in_the_checked_bytes(cuda_device):
+    """The lane-interleaved CRC-32C: one flipped bit at the first checked byte, inside the front padding row, at row and tile
+    borders, in the middle and at the very last byte must each turn exactly that batch into BAD_CRC; the two bytes in front of the
+    checked range (magic is checked on its own, the epoch is not covered) must not."""
+    g = np.random.default_rng(9)
+    vals = [bytes(g.integers(0, 256, 63, dtype=np.uint8)) for _ in range(1000)]
+    seg0 = bs.kafka.write_segment(vals, records_per_batch=250)
+    pos, _ = bs.kafka.scan_batches(seg0)
+    blen = int(pos[1] - pos[0])
+    assert blen > 3 * 4096
+    for b in (0, 2):
+        for off in (21, 22, 24, 25, 60, 61, 21 + 127, 21 + 128, 21 + 129, 21 + 4095, 21 + 4096, 21 + 4097, blen // 2, blen - 5, blen - 4, blen - 1):
+            seg = bytearray(seg0)
+            seg[pos[b] + off] ^= 0x10
+            st = bs.kafka.index_segment(bytes(seg), raise_on_error=False)[1].cpu().tolist()
+            want = [0, 0, 0, 0]
+            want[b] = 2
+            if off == 22:
+                assert st[b] != 0, off          # attributes: the codec bits change the verdict before the CRC is looked at
+            else:
+                assert st == want, (b, off, st)
+    seg = bytearray(seg0)
+    seg[pos[1] + 13] ^= 0x01                     # partitionLeaderEpoch: in front of the CRC'd range
+    assert bs.kafka.index_segment(bytes(seg))[1].cpu().tolist() == [0, 0, 0, 0]
+
+
+@pytest.mark.parametrize("fmt", ["avro_a", "csv", "json"])
+def test_scores_straight_from_the_segment_equal_scores_of_the_packed_values(cuda_device, fmt):
+    """index_segment → decode_score on the byte ranges inside the segment (no gather) == values_from_segment → decode_score, bit for
+    bit, with a refused batch in the middle (its records are empty in both) and malformed records."""
+    n = 30_000
+    rows = synth.sensor_rows(n, seed=21)
+    if fmt == "avro_a":
+        data, offs = synth.avro_a_batch(rows)
+        kw, skip = dict(avro_schema=schemas.schema_a_json()), 5
+    elif fmt == "csv":
+        data, offs = synth.csv_batch(rows, seed=21)
+        kw, skip = dict(csv_kinds=[0, 0] + [1] * 18), 0
+    else:
+        data, offs = synth.json_batch(rows, labels=(np.arange(n) % 64 == 0))
+        kw, skip = dict(json_keys=list(schemas.FEATURE_NAMES), json_label="failure_occurred"), 0
+    data, offs, _ = synth.corrupt_batch(data, offs, fmt, 1e-3, seed=4)
+    vals = [data[offs[i]:offs[i + 1]].tobytes() for i in range(n)]
+    seg = bytearray(bs.kafka.write_segment(vals, records_per_batch=333))
+    pos, _ = bs.kafka.scan_batches(bytes(seg))
+    seg[pos[7] + 200] ^= 0x40
+    seg = bytes(seg)
+    m = _ae18()
+    m.set_normalization(*schemas.norm_arrays())
+    spans, st = bs.kafka.index_segment(seg, skip_prefix=skip, raise_on_error=False)
+    rb, st2 = bs.kafka.values_from_segment(seg, skip_prefix=skip, raise_on_error=False)
+    assert st.cpu().tolist() == st2.cpu().tolist() and st[7] == 2 and int((st != 0).sum()) == 1
+    ca, cb = torch.zeros(4, dtype=torch.int64, device="cuda"), torch.zeros(4, dtype=torch.int64, device="cuda")
+    a = dec.decode_score(m, spans, counters=ca, **kw)
+    b = dec.decode_score(m, rb, counters=cb, **kw)
+    torch.cuda.synchronize()
+    for x, y in zip(a, b):
+        if x is None or y is None:
+            assert x is None and y is None
+            continue
+        assert np.array_equal(x.cpu().numpy().view(np.uint8), y.cpu().numpy().view(np.uint8))
+    assert ca[:3].tolist() == cb[:3].tolist() and int(ca[0]) > n * 0.98
+    bad = a[3].cpu().numpy()
+    assert (bad[7 * 333:8 * 333] != 0).all()
