@@ -590,6 +590,62 @@ def aux_lstm_fit(dev):
             "kernel": "lstm_fit_kernel (one persistent CTA per epoch: BPTT + Adam)"}
 
 
+def aux_kafka_ingest(dev):
+    """what KafkaDataset / librdkafka does in front of cardata-v1.py:10 — record-batch (v2) bytes of one
+    partition segment → CRC-32C check + record walk (one warp per batch) → fused decode + score on the value ranges inside the
+    segment (no packed copy).  2^20 Avro-A records in 4 096 uncompressed batches of 256; CUDA-event timed."""
+    import torch
+
+    import b200_sensor as bs
+    from b200_sensor import _ffi, decode as dec
+    from b200_sensor.keras_compat import _stream_ptr, get_ctx
+
+    n, per = 1 << 20, 256
+    data, offs = bs.synth.avro_a_batch(bs.synth.sensor_rows(n, seed=314 + 99))
+    L = int(offs[1] - offs[0])
+    seg = bs.kafka.write_segment_uniform(data.reshape(n, L), records_per_batch=per)
+    d = torch.from_numpy(seg).to(dev)
+    pos, cnt = bs.kafka.scan_batches(seg)
+    nb = len(pos)
+    base = np.zeros(nb, dtype=np.int64)
+    np.cumsum(cnt[:-1], out=base[1:])
+    pos_d, base_d = torch.from_numpy(pos).to(dev), torch.from_numpy(base).to(dev)
+    begin, end = torch.zeros(n, dtype=torch.int32, device=dev), torch.zeros(n, dtype=torch.int32, device=dev)
+    status = torch.zeros(nb, dtype=torch.int32, device=dev)
+    lib, ctx = _ffi.lib(), get_ctx(dev.index)
+    m = ScoreWorkload(18, 20, 20).model()
+    spans = dec.RecordSpans(d, begin, end, n, skip_prefix=5)
+    spans.avg_record_bytes = (int(d.numel()) + n - 1) // n
+    out = dict(mse=torch.empty(n, dtype=torch.float32, device=dev), flag=torch.empty(n, dtype=torch.uint8, device=dev),
+               label=torch.empty(n, dtype=torch.uint8, device=dev), status=torch.empty(n, dtype=torch.int32, device=dev))
+
+    def index():
+        _ffi.check(lib.b2_kafka_index_records(ctx, _ffi.ptr(d), int(d.numel()), _ffi.ptr(pos_d), _ffi.ptr(base_d), nb, 1, _ffi.ptr(begin),
+                                              _ffi.ptr(end), _ffi.ptr(status), _stream_ptr()), "b2_kafka_index_records")
+
+    def chain():
+        index()
+        dec.decode_score(m, spans, avro_schema=bs.schemas.schema_a_json(), threshold=THRESHOLD, **out)
+
+    def timed(fn, iters=30):
+        for _ in range(3):
+            fn()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        a.record()
+        for _ in range(iters):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / iters * 1e-3
+
+    t_idx, t_chain = timed(index), timed(chain)
+    assert not bool(status.any()) and int((out["status"] != 0).sum()) == 0
+    return {"value": n / t_chain, "unit": UNIT, "records": n, "batches": nb, "segment_bytes": int(d.numel()),
+            "index_us": t_idx * 1e6, "index_gbs": d.numel() / t_idx / 1e9, "segment_to_scores_us": t_chain * 1e6,
+            "kernels": "kafka_index_kernel (one warp per batch) + decode_kernel<18,1,1,1> on ranges inside the segment"}
+
+
 WORKLOADS = {
     "score30": lambda: ScoreWorkload(30, 27, 22, repeat=24),
     "score18": lambda: ScoreWorkload(18, 27, 22, repeat=24),
@@ -876,6 +932,7 @@ def main():
             also["lstm_forward_T16"] = aux_lstm(dev, 16)
             also["format_rows_d18"] = aux_format_rows(dev)
             also["metrics_threshold_sweep"] = aux_metrics(dev)
+            also["kafka_segment_to_scores_avro_a"] = aux_kafka_ingest(dev)
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
                 "data": "synthetic", "config": config, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,

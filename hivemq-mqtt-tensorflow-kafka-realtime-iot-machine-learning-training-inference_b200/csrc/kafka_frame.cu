@@ -247,29 +247,107 @@ __global__ void __launch_bounds__(KF_WARPS * 32) kafka_index_kernel(const FrameA
             p = __shfl_sync(FULL, me, cnt - 1);  // cnt >= 1: end of the last record taken
             guess = cnt >= 4;                    // lengths vary (text values): follow the chain one by one for a round
           } else {
-            for (int k = 0; k < want && p < g_hi; ++k) {
-              long long len;
-              if (!read_varint_w(s, p, endb, &len) || len < 0 || len > endb - p) {
+            // the chain one record at a time, in 32-bit offsets from the batch's first byte: per record one round trip for the
+            // four bytes at the cursor and a dozen dependent integer instructions
+            const uint8_t* sb = s + pos;
+            const uint32_t endr = (uint32_t)(endb - pos);
+            uint32_t pp = (uint32_t)(p - pos), ms32 = 0, me32 = 0;
+            for (int k = 0; k < want; ++k) {
+              uint32_t nb = 0, len = 0;
+              if (pp + 8u <= endr) {
+                const uintptr_t at = reinterpret_cast<uintptr_t>(sb + pp);
+                const uint32_t* wp = reinterpret_cast<const uint32_t*>(at & ~(uintptr_t)3);
+                uint32_t x = __funnelshift_r(wp[0], wp[1], (int)(at & 3u) * 8);
+                const uint32_t stop = ~x & 0x80808080u;
+                if (stop) {
+                  nb = (uint32_t)__ffs((int)stop) >> 3;
+                  x &= 0xFFFFFFFFu >> (32u - 8u * nb);
+                  const uint32_t u = (x & 0x7Fu) | ((x >> 1) & 0x3F80u) | ((x >> 2) & 0x1FC000u) | ((x >> 3) & 0xFE00000u);
+                  if (u & 1u) {  // a negative length
+                    bad = true;
+                    break;
+                  }
+                  len = u >> 1;
+                }
+              }
+              if (nb == 0) {  // the batch's last bytes, or a length of 2^27 and more: the byte loop decides
+                long long q = pos + pp, l64;
+                if (!read_varint(s, q, endb, &l64) || l64 < 0 || l64 > endb - q) {
+                  bad = true;
+                  break;
+                }
+                nb = (uint32_t)(q - pos) - pp;
+                len = (uint32_t)l64;
+              } else if (len > endr - pp - nb) {
                 bad = true;
                 break;
               }
-              if (k == lane) ms = p, me = p + len;
-              p += len;
+              if (k == lane) ms32 = pp + nb, me32 = pp + nb + len;
+              pp += nb + len;
               ++cnt;
             }
+            p = pos + pp;
+            ms = pos + ms32;
+            me = pos + me32;
             guess = true;
           }
           int32_t vb = 0, ve = 0;
           bool ok = true;
           if (lane < cnt) {
-            long long q = ms + 1, v, klen, vlen;  // attributes
-            ok = q <= me && read_varint_w(s, q, me, &v) && read_varint_w(s, q, me, &v) && read_varint_w(s, q, me, &klen) && klen >= -1 &&
-                 klen <= me - q;
-            if (ok) {
-              if (klen > 0) q += klen;
-              ok = read_varint_w(s, q, me, &vlen) && vlen >= -1 && vlen <= me - q;
-              vb = (int32_t)q;                               // a null value (length -1) is an empty record
-              ve = (int32_t)(q + (vlen > 0 ? vlen : 0));     // headers are skipped with the record length
+            bool done = false;
+            if (me - ms >= 20) {
+              // the common record — attributes, three short varints, a null key, the value length — sits in its first 16 bytes:
+              // one round trip (five aligned words), then the varints come out of registers
+              const uintptr_t at = reinterpret_cast<uintptr_t>(s + ms);
+              const uint32_t* wp = reinterpret_cast<const uint32_t*>(at & ~(uintptr_t)3);
+              const int sh0 = (int)(at & 3u) * 8;
+              const uint32_t a0 = wp[0], a1 = wp[1], a2 = wp[2], a3 = wp[3], a4 = wp[4];
+              uint32_t w0 = __funnelshift_r(a0, a1, sh0), w1 = __funnelshift_r(a1, a2, sh0), w2 = __funnelshift_r(a2, a3, sh0),
+                       w3 = __funnelshift_r(a3, a4, sh0);
+              int used = 0;
+              bool short4 = true;
+              auto drop = [&](int nbytes) {  // the window moves on by 1..4 bytes
+                const int b = nbytes * 8;
+                w0 = __funnelshift_rc(w0, w1, b), w1 = __funnelshift_rc(w1, w2, b), w2 = __funnelshift_rc(w2, w3, b), w3 = __funnelshift_rc(w3, 0u, b);
+                used += nbytes;
+              };
+              auto take = [&]() -> int {  // zig-zag varint of up to four bytes at the window's front
+                const uint32_t stop = ~w0 & 0x80808080u;
+                if (!stop) {
+                  short4 = false;
+                  return 0;
+                }
+                const int nb = __ffs((int)stop) >> 3;
+                const uint32_t x = nb < 4 ? w0 & ((1u << (8 * nb)) - 1u) : w0;
+                const uint32_t u = (x & 0x7Fu) | ((x >> 1) & 0x3F80u) | ((x >> 2) & 0x1FC000u) | ((x >> 3) & 0xFE00000u);
+                drop(nb);
+                return (int)(u >> 1) ^ -(int)(u & 1u);
+              };
+              drop(1);  // attributes
+              take();   // timestampDelta
+              take();   // offsetDelta
+              const int klen = take();
+              if (short4 && klen <= 0 && klen >= -1) {
+                const int vlen = take();
+                if (short4 && used <= 16) {  // everything read lay inside the 16 bytes
+                  const long long q = ms + used;
+                  ok = vlen >= -1 && vlen <= me - q;
+                  vb = (int32_t)q;
+                  ve = (int32_t)(q + (vlen > 0 ? vlen : 0));
+                  done = true;
+                }
+              }
+            }
+            if (!done) {  // keys, long varints, records of a few bytes: field by field
+              long long q = ms + 1, v, klen, vlen;  // attributes
+              ok = q <= me && read_varint_w(s, q, me, &v) && read_varint_w(s, q, me, &v) && read_varint_w(s, q, me, &klen) && klen >= -1 &&
+                   klen <= me - q;
+              if (ok) {
+                if (klen > 0) q += klen;
+                ok = read_varint_w(s, q, me, &vlen) && vlen >= -1 && vlen <= me - q;
+                vb = (int32_t)q;                               // a null value (length -1) is an empty record
+                ve = (int32_t)(q + (vlen > 0 ? vlen : 0));     // headers are skipped with the record length
+              }
             }
           }
           if (__any_sync(FULL, !ok)) bad = true;
