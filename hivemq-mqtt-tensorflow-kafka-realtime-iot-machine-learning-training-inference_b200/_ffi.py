@@ -120,6 +120,7 @@ _PROTOTYPES = {
                                     C.POINTER(Adam), _P, _P, _P, C.c_int64, _P]),
     "b2_format_rows_bound": (C.c_int64, [C.c_int]),
     "b2_format_rows": (C.c_int, [_P, _P, C.c_int64, C.c_int, C.c_int, _P, C.c_int64, _P, _P, _P, _P]),
+    "b2_decode_spans": (C.c_int, [_P, _P, _P, _P, C.c_int64, C.POINTER(CsvSpec), C.POINTER(AvroProg), C.POINTER(JsonSpec), C.c_int, _P, _P, _P, _P, _P]),
     "b2_decode_score_spans": (C.c_int, [_P, _P, _P, _P, C.c_int64, C.POINTER(CsvSpec), C.POINTER(AvroProg), C.POINTER(JsonSpec), C.c_int,
                                         C.POINTER(Norm), C.c_float, _P, _P, _P, _P, _P, _P]),
     "b2_kafka_scan_batches": (C.c_int64, [_P, C.c_int64, _P, _P, C.c_int64]),

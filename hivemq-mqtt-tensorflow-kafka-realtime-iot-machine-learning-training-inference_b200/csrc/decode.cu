@@ -1261,6 +1261,45 @@ extern "C" int b2_decode_json(b2_ctx* ctx, const uint8_t* bytes_dev, const int32
   return launch_decode<18, 0, false>(ctx, args, (cudaStream_t)stream);
 }
 
+// Decode only, records given as byte ranges (see b2_decode_score_spans): the three decoders behind one entry point.
+extern "C" int b2_decode_spans(b2_ctx* ctx, const uint8_t* bytes_dev, const int32_t* begin_dev, const int32_t* end_dev, int64_t n,
+                               const b2_csv_spec* csv, const b2_avro_prog* avro, const b2_json_spec* json, int skip_prefix, float* out_dev,
+                               uint8_t* label_dev, int32_t* span_dev, int32_t* status_dev, void* stream) {
+  B2_REQUIRE(ctx, "b2_decode_spans: NULL context");
+  B2_REQUIRE((csv != nullptr) + (avro != nullptr) + (json != nullptr) == 1, "b2_decode_spans: exactly one of csv / avro / json must be given");
+  B2_REQUIRE(n >= 0, "b2_decode_spans: n < 0");
+  if (n == 0) return B2_OK;
+  B2_REQUIRE(bytes_dev && begin_dev && end_dev && out_dev, "b2_decode_spans: NULL device pointer");
+  DeviceGuard g(ctx->device);
+  DecodeArgs<18> args;  // D is irrelevant in MODE 0
+  memset(&args, 0, sizeof(args));
+  int rc;
+  if (csv) {
+    rc = fill_csv(csv, args.csv);
+    args.fmt = FMT_CSV;
+    args.n_out = args.csv.n_float;
+    args.span = span_dev;
+  } else if (avro) {
+    rc = fill_avro(ctx, avro, skip_prefix, args.avro);
+    args.fmt = FMT_AVRO;
+    args.n_out = avro->n_out;
+    args.label = label_dev;
+  } else {
+    rc = fill_json(json, args.json);
+    args.fmt = FMT_JSON;
+    args.n_out = json->n_out;
+    args.label = label_dev;
+  }
+  if (rc) return rc;
+  args.bytes = bytes_dev;
+  args.offs = begin_dev;
+  args.ends = end_dev;
+  args.n = n;
+  args.out = out_dev;
+  args.status = status_dev;
+  return launch_decode<18, 0, false>(ctx, args, (cudaStream_t)stream);
+}
+
 template <int D>
 static int decode_score_spec(b2_ae* ae, const uint8_t* bytes, const int32_t* offs, const int32_t* ends, int64_t n, const b2_csv_spec* csv,
                              const b2_avro_prog* avro, const b2_json_spec* json, int skip_prefix, const b2_norm* norm, float threshold, float* mse, uint8_t* flag,

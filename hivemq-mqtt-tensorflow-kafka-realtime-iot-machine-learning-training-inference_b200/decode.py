@@ -84,8 +84,16 @@ def substr(records: RecordBatch, pos: int, length: int = -1) -> RecordBatch:
     return records.substr(pos, length)
 
 
-def _as_batch(records) -> RecordBatch:
-    return records if isinstance(records, RecordBatch) else RecordBatch.from_messages(records)
+def _as_batch(records):
+    return records if isinstance(records, (RecordBatch, RecordSpans)) else RecordBatch.from_messages(records)
+
+
+def _decode_spans(rb: "RecordSpans", csv=None, avro=None, js=None, skip=0, out=None, label=None, span=None, status=None):
+    """The decode-only kernels on byte ranges inside a larger buffer (b2_decode_spans)."""
+    _ffi.check(_ffi.lib().b2_decode_spans(get_ctx(rb.data.device.index), _ffi.ptr(rb.data), _ffi.ptr(rb.begin), _ffi.ptr(rb.end), rb.n,
+                                          C.byref(csv) if csv is not None else None, C.byref(avro) if avro is not None else None,
+                                          C.byref(js) if js is not None else None, int(skip), _ffi.ptr(out), _ffi.ptr(label), _ffi.ptr(span),
+                                          _ffi.ptr(status), _stream_ptr()), "b2_decode_spans")
 
 
 # Host-side structs are built once per distinct schema / spec and reused: at 10^10 records/s a launch lasts tens of
@@ -172,8 +180,11 @@ def decode_csv_matrix(records, kinds, defaults=None, field_delim=",", use_quote_
     span = torch.zeros((rb.n, max(ns, 1), 2), dtype=torch.int32, device=rb.data.device) if ns else None
     status = torch.empty(rb.n, dtype=torch.int32, device=rb.data.device)
     _size_hint(rb)
-    _ffi.check(_ffi.lib().b2_decode_csv(get_ctx(rb.data.device.index), _ffi.ptr(rb.data), _ffi.ptr(rb.offsets), rb.n, C.byref(spec),
-                                        _ffi.ptr(out), _ffi.ptr(span), _ffi.ptr(status), _stream_ptr()), "b2_decode_csv")
+    if isinstance(rb, RecordSpans):
+        _decode_spans(rb, csv=spec, out=out, span=span, status=status)
+    else:
+        _ffi.check(_ffi.lib().b2_decode_csv(get_ctx(rb.data.device.index), _ffi.ptr(rb.data), _ffi.ptr(rb.offsets), rb.n, C.byref(spec),
+                                            _ffi.ptr(out), _ffi.ptr(span), _ffi.ptr(status), _stream_ptr()), "b2_decode_csv")
     if raise_on_error:
         _raise_on_status(status, "decode_csv")
     return out, span, status
@@ -217,8 +228,11 @@ def decode_avro_matrix(records, schema, skip_prefix: Optional[int] = None, raise
     status = torch.empty(rb.n, dtype=torch.int32, device=rb.data.device)
     skip = rb.skip_prefix if skip_prefix is None else skip_prefix
     _size_hint(rb)
-    _ffi.check(_ffi.lib().b2_decode_avro(get_ctx(rb.data.device.index), _ffi.ptr(rb.data), _ffi.ptr(rb.offsets), rb.n, skip, C.byref(p),
-                                         _ffi.ptr(out), _ffi.ptr(label), _ffi.ptr(status), _stream_ptr()), "b2_decode_avro")
+    if isinstance(rb, RecordSpans):
+        _decode_spans(rb, avro=p, skip=skip, out=out, label=label, status=status)
+    else:
+        _ffi.check(_ffi.lib().b2_decode_avro(get_ctx(rb.data.device.index), _ffi.ptr(rb.data), _ffi.ptr(rb.offsets), rb.n, skip, C.byref(p),
+                                             _ffi.ptr(out), _ffi.ptr(label), _ffi.ptr(status), _stream_ptr()), "b2_decode_avro")
     if raise_on_error:
         _raise_on_status(status, "decode_avro")
     return out, label, status, prog
@@ -312,8 +326,11 @@ def decode_json_matrix(records, keys, label_key: Optional[str] = None, raise_on_
     if rb.skip_prefix:
         raise ValueError("JSON records carry no framing prefix")
     _size_hint(rb)
-    _ffi.check(_ffi.lib().b2_decode_json(get_ctx(dev.index), _ffi.ptr(rb.data), _ffi.ptr(rb.offsets), rb.n, C.byref(spec), _ffi.ptr(out),
-                                         _ffi.ptr(label), _ffi.ptr(status), _stream_ptr()), "b2_decode_json")
+    if isinstance(rb, RecordSpans):
+        _decode_spans(rb, js=spec, out=out, label=label, status=status)
+    else:
+        _ffi.check(_ffi.lib().b2_decode_json(get_ctx(dev.index), _ffi.ptr(rb.data), _ffi.ptr(rb.offsets), rb.n, C.byref(spec), _ffi.ptr(out),
+                                             _ffi.ptr(label), _ffi.ptr(status), _stream_ptr()), "b2_decode_json")
     if raise_on_error:
         _raise_on_status(status, "decode_json")
     return out, label, status

@@ -176,6 +176,11 @@ int  b2_decode_score_json(b2_ae* ae, const uint8_t* bytes_dev, const int32_t* of
  * (cardata-v1.py:10-16); here the segment's bytes are decoded and scored where they lie, with no packed copy of the values.
  * Exactly one of csv / avro / json; skip_prefix as in b2_decode_score (ignored for JSON).  Same input contract as offs_dev
  * otherwise (16 readable bytes behind the last record, a record of more than 24 KB is refused). */
+/* b2_decode_spans: decode only (b2_decode_csv / _avro / _json by the spec given), same ranges; span_dev as in b2_decode_csv (string
+ * field ranges, absolute offsets into bytes_dev), label_dev as in b2_decode_avro / _json. */
+int  b2_decode_spans(b2_ctx* ctx, const uint8_t* bytes_dev, const int32_t* begin_dev, const int32_t* end_dev, int64_t n,
+                     const b2_csv_spec* csv, const b2_avro_prog* avro, const b2_json_spec* json, int skip_prefix, float* out_dev,
+                     uint8_t* label_dev, int32_t* span_dev, int32_t* status_dev, void* stream);
 int  b2_decode_score_spans(b2_ae* ae, const uint8_t* bytes_dev, const int32_t* begin_dev, const int32_t* end_dev, int64_t n,
                            const b2_csv_spec* csv, const b2_avro_prog* avro, const b2_json_spec* json, int skip_prefix,
                            const b2_norm* norm, float threshold, float* mse_dev, uint8_t* flag_dev, uint8_t* label_dev,

@@ -226,3 +226,41 @@ def test_scores_straight_from_the_segment_equal_scores_of_the_packed_values(cuda
     assert ca[:3].tolist() == cb[:3].tolist() and int(ca[0]) > n * 0.98
     bad = a[3].cpu().numpy()
     assert (bad[7 * 333:8 * 333] != 0).all()
+
+
+def test_decode_only_on_ranges_inside_the_segment(cuda_device):
+    """b2_decode_spans: the three decode-only kernels on the value ranges of a segment == the same kernels on the packed values
+    (matrix, label, status bit for bit; CSV string-field spans point at the same bytes)."""
+    n = 5_000
+    rows = synth.sensor_rows(n, seed=8)
+    for fmt in ("avro_a", "csv", "json"):
+        if fmt == "avro_a":
+            data, offs = synth.avro_a_batch(rows)
+        elif fmt == "csv":
+            data, offs = synth.csv_batch(rows, seed=8)
+        else:
+            data, offs = synth.json_batch(rows, labels=(np.arange(n) % 3 == 0))
+        data, offs, _ = synth.corrupt_batch(data, offs, fmt, 2e-3, seed=8)
+        seg = bs.kafka.write_segment([data[offs[i]:offs[i + 1]].tobytes() for i in range(n)], records_per_batch=211, headers=True)
+        skip = 5 if fmt == "avro_a" else 0
+        spans, _ = bs.kafka.index_segment(seg, skip_prefix=skip)
+        rb, _ = bs.kafka.values_from_segment(seg, skip_prefix=skip)
+        if fmt == "avro_a":
+            a = dec.decode_avro_matrix(spans, schemas.schema_a_json(), raise_on_error=False)[:3]
+            b = dec.decode_avro_matrix(rb, schemas.schema_a_json(), raise_on_error=False)[:3]
+        elif fmt == "json":
+            a = dec.decode_json_matrix(spans, list(schemas.FEATURE_NAMES), "failure_occurred", raise_on_error=False)
+            b = dec.decode_json_matrix(rb, list(schemas.FEATURE_NAMES), "failure_occurred", raise_on_error=False)
+        else:
+            kinds = [0, 2] + [1] * 18
+            oa, sa, ta = dec.decode_csv_matrix(spans, kinds, raise_on_error=False)
+            ob, sb_, tb = dec.decode_csv_matrix(rb, kinds, raise_on_error=False)
+            a, b = (oa, ta), (ob, tb)
+            good = (ta == 0).cpu().numpy()
+            sa, sb_ = sa.cpu().numpy()[good, 0], sb_.cpu().numpy()[good, 0]
+            packed = rb.data.cpu().numpy().tobytes()
+            assert [seg[x:y] for x, y in sa[::97]] == [packed[x:y] for x, y in sb_[::97]]
+            assert seg[sa[0][0]:sa[0][1]].startswith(b"car")
+        for x, y in zip(a, b):
+            assert np.array_equal(x.cpu().numpy().view(np.uint8), y.cpu().numpy().view(np.uint8)), fmt
+        assert int((a[-1] != 0).sum()) >= 5
