@@ -673,6 +673,7 @@ extern "C" int b2_ae_grad(b2_ae* ae, const float* x_dev, int64_t n, const b2_nor
                           int64_t scratch_bytes, void* stream) {
   B2_REQUIRE(ae && x_dev && grads_dev && scratch_dev, "b2_ae_grad: NULL argument");
   B2_REQUIRE(n >= 1, "b2_ae_grad: n=%lld < 1", (long long)n);
+  B2_REQUIRE(n <= (1ll << 24), "b2_ae_grad: n=%lld rows in one step (the row count travels with the gradient as a float: exact to 2^24)", (long long)n);
   B2_REQUIRE(((uintptr_t)x_dev & 7) == 0, "b2_ae_grad: x_dev must be 8-byte aligned");
   B2_REQUIRE(scratch_bytes >= b2_ae_grad_scratch_bytes(ae, n), "b2_ae_grad: scratch of %lld bytes is smaller than the %lld needed",
              (long long)scratch_bytes, (long long)b2_ae_grad_scratch_bytes(ae, n));

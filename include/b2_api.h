@@ -224,7 +224,8 @@ int  b2_ae_fit_steps(b2_ae* ae, const float* x_dev, const int32_t* order_dev, in
 
 /* Large-batch / data-parallel step, split so that a gradient all-reduce can sit between the halves:
  *   b2_ae_grad:  grads_dev f32[P+3] = Σ_rows d(loss)/dθ (un-normalised), then Σ loss, Σ correct, row count.
- *                scratch_dev must hold b2_ae_grad_scratch_bytes(ae, n) bytes.
+ *                scratch_dev must hold b2_ae_grad_scratch_bytes(ae, n) bytes.  n <= 2^24 per call: the row count is a float of
+ *                the gradient vector, and the all-reduced count must stay below 2^24 too to remain exact.
  *   b2_ae_apply: θ ← Adam(θ, grads / total_rows) using grads_dev after the caller's all-reduce. */
 int64_t b2_ae_grad_scratch_bytes(const b2_ae* ae, int64_t n);
 int  b2_ae_grad(b2_ae* ae, const float* x_dev, int64_t n, const b2_norm* norm, float* grads_dev,
