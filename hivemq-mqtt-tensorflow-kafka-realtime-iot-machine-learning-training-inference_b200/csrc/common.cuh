@@ -44,6 +44,7 @@ struct b2_knobs {
   int score_tc = -1;      // B2_SCORE_TC      pre-decoded scoring: -1 auto (tcgen05 kernel K1t for D = 30, FFMA2 for D = 18), 0 FFMA2, 1 K1t, 2 K1t with all four layers on tcgen05
   int decode_r2 = 0;      // B2_DECODE_R2     fused Avro decode: 0 one record per lane (default), 2 / 3 two (85 / 102 registers)
   int decode_tc = 0;      // B2_DECODE_TC     fused decode + score: 1 = score phase on tcgen05 (decode_kernel_tc)
+  int decode_mma = 0;     // B2_DECODE_MMA    fused decode + score: 1 = score phase as warp-level TF32 MMAs (decode_kernel_wm, ae_mma.cuh)
   int tc_ctas = 0;        // B2_TC_CTAS       CTAs per SM of the tcgen05 score kernels (0 = as many as TMEM allows)
 };
 

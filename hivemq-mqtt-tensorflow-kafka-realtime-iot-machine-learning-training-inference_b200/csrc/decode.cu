@@ -15,6 +15,7 @@
 //   (then the next item is planned and its copy issued, so that it flies under the score phase)
 //   score    lane-per-record   fused normalise → Dense stack → MSE → flag (ae_math.cuh), or a coalesced write-out of the rows
 // Algorithmic bytes/record: payload + 4 (offset) read, 5 written (fused) or 4*F + 4 written (decode only).
+#include "ae_mma.cuh"
 #include "ae_tc.cuh"
 #include "float_parse.cuh"
 #include "json_walk.cuh"
@@ -609,10 +610,12 @@ __device__ __forceinline__ int avro_walk_schema_b(const uint8_t* __restrict__ ba
 // TC (fused mode, R = 1, CTAs of exactly 4 warps): the score phase runs on the tensor cores (ae_tc.cuh) — the CTA's four warps
 // still fetch, plan and decode independently, but score their 4 x 32 records together as one 128-row tile, so the item loop runs
 // in lock-step across the CTA (a warp that has run out of chunks contributes empty rows until all four are done).
-template <int D, int MODE, bool FT, int FMT, int R, bool TC = false>
+template <int D, int MODE, bool FT, int FMT, int R, bool TC = false, bool WM = false>
 __device__ __forceinline__ void decode_body(const DecodeArgs<D>& a) {
   static_assert(R == 1 || (R == 2 && MODE == 1), "two records per lane only in the fused mode");
   static_assert(!TC || (MODE == 1 && R == 1), "tensor-core scoring: fused mode, one record per lane");
+  static_assert(!WM || (MODE == 1 && R == 1 && !TC && FMT != FMT_JSON), "warp-MMA scoring: fused mode, one record per lane, CSV / Avro");
+  constexpr int XS = WM ? 2 : R;  // distance between consecutive elements of a record in the tile (WM: rows interleaved in pairs)
   extern __shared__ __align__(128) uint8_t smem[];
   constexpr unsigned FULL = 0xffffffffu;
   constexpr int CH = 32 * R;  // records per chunk
@@ -637,6 +640,12 @@ __device__ __forceinline__ void decode_body(const DecodeArgs<D>& a) {
   __shared__ __align__(8) uint64_t mma_bar;
   TcCtx tc;
   if (TC) tcs_setup<D>(tc, a.panels, reinterpret_cast<float*>(smem + (size_t)(blockDim.x >> 5) * a.warp_bytes), &s_tmem, &mma_bar, tid);
+  // WM: the CTA's table of weight fragments behind the warps' regions (the one block-wide barrier of the kernel)
+  const uint8_t* const wm_tab = smem + (size_t)(blockDim.x >> 5) * a.warp_bytes;
+  if (WM) {
+    mma_fill_table<D>(a.w, smem + (size_t)(blockDim.x >> 5) * a.warp_bytes, tid, blockDim.x);
+    __syncthreads();
+  }
   const bool list_mode = a.list_mode != 0;
   const long long n_chunks = list_mode ? (long long)min(a.over_list[0], B2_OVERSIZE_CAP) : (a.n + CH - 1) / CH;
   const int warps_per_cta = blockDim.x >> 5;  // the launch picks 8, 4 or 2 warps per CTA: whatever packs most warps into an SM
@@ -676,7 +685,9 @@ __device__ __forceinline__ void decode_body(const DecodeArgs<D>& a) {
     return r;
   };
   // plans the next item (records [sub, sub+cnt) of the cursor's chunk), issues its bulk copy and advances the cursor;
-  // it_b / it_e receive the lane's stage offsets of its records
+  // it_b / it_e receive the lane's stage offsets of its records.  (Fetching a chunk's offsets one chunk ahead was tried: the
+  // load then stays in flight across the decode phase, whose shared-memory loads end up waiting on the same scoreboard:
+  // 2.71e10 -> 2.52e10 records/s on Avro-A.)
   auto next_item = [&](long long& it_row0, int& it_sub, int& it_cnt, int (&it_b)[R], int (&it_e)[R]) -> bool {
     for (;;) {
       if (sub >= rows) {
@@ -750,7 +761,7 @@ __device__ __forceinline__ void decode_body(const DecodeArgs<D>& a) {
   long long c_row0 = 0, n_row0 = 0;
   int c_sub = 0, c_cnt = 0, c_b[R], c_e[R], n_sub = 0, n_cnt = 0, n_b[R], n_e[R];
   bool have = next_item(c_row0, c_sub, c_cnt, c_b, c_e);
-  float* const xlane = xt + (size_t)lane * xt_stride;
+  float* const xlane = WM ? xt + mma_row_offset<D>(lane) : xt + (size_t)lane * xt_stride;
   bool cur = have;  // TC: this warp holds a current item (the loop itself runs while ANY warp of the CTA does)
   while (TC ? __syncthreads_or(cur) != 0 : have) {
     if (!TC || cur) {
@@ -770,25 +781,25 @@ __device__ __forceinline__ void decode_body(const DecodeArgs<D>& a) {
     // one record of the item: slot s of this lane, stage bytes [cb, ce), absolute offset ab of its first byte
     auto decode_one = [&](int s, int cb, int ce, int ab, int& st_s, uint8_t& lab_s) {
       const int q = lane + 32 * s;
-      float* xrow = xlane + s;  // element j of this record sits at xrow[j * R]
+      float* xrow = xlane + s;  // element j of this record sits at xrow[j * XS]
       const long long gr = c_row0 + q;
       if (FMT == FMT_CSV) {
         int32_t* sp = (MODE == 0 && a.span) ? a.span + gr * a.csv.n_str * 2 : nullptr;
         const int rel = cb - ab;  // stage offset minus absolute offset (the cursor still sits on this item's chunk)
-        st_s = csv_walk<R>(stage, cb, ce, a.csv, xrow, sp, rel);
-        if (st_s < 0) st_s = csv_record_careful(stage, cb, ce, a.csv, xrow, R, sp, rel);
+        st_s = csv_walk<XS>(stage, cb, ce, a.csv, xrow, sp, rel);
+        if (st_s < 0) st_s = csv_record_careful(stage, cb, ce, a.csv, xrow, XS, sp, rel);
       } else if (FMT == FMT_JSON) {
         for (int j = 0; j < xt_stride; ++j) xrow[j] = 0.0f;  // members that are absent or null
         st_s = b2_json_record_auto(stage, cb, ce, a.json, xrow, &lab_s);
       } else {
         if (!a.avro.all_routed)
-          for (int j = 0; j < (MODE == 1 ? D : a.n_out); ++j) xrow[j * R] = 0.0f;  // columns no field routes to
+          for (int j = 0; j < (MODE == 1 ? D : a.n_out); ++j) xrow[j * XS] = 0.0f;  // columns no field routes to
         st_s = -1;
-        if (a.avro.known == 1) st_s = avro_walk_schema_a<R>(stage, cb, ce, a.avro.skip_prefix, xrow);
-        else if (a.avro.known == 2) st_s = avro_walk_schema_b<R>(stage, cb, ce, a.avro.skip_prefix, xrow, &lab_s);
+        if (a.avro.known == 1) st_s = avro_walk_schema_a<XS>(stage, cb, ce, a.avro.skip_prefix, xrow);
+        else if (a.avro.known == 2) st_s = avro_walk_schema_b<XS>(stage, cb, ce, a.avro.skip_prefix, xrow, &lab_s);
         if (st_s < 0) {
           lab_s = 2;
-          st_s = avro_decode_record(stage, cb, ce, a.avro, xrow, R, &lab_s);
+          st_s = avro_decode_record(stage, cb, ce, a.avro, xrow, XS, &lab_s);
         }
       }
     };
@@ -822,6 +833,18 @@ __device__ __forceinline__ void decode_body(const DecodeArgs<D>& a) {
           x[i + 1] = v.y;
         }
         mm[0] = tcs_score_row<D, FT, true>(tc, a.w, x, tid);
+      } else if (WM) {
+        // every lane normalises its own row in place (uniform constants), then the warp's 32 rows run through the MMA chain
+        if (a.has_norm && active[0]) {
+#pragma unroll
+          for (int i = 0; i < D; i += 2) {
+            const float2 v = norm_pair_fast<D>(make_float2(xlane[2 * i], xlane[2 * i + 2]), a.nm, i);
+            xlane[2 * i] = v.x;
+            xlane[2 * i + 2] = v.y;
+          }
+        }
+        __syncwarp();
+        mm[0] = mma_score_warp<D, FT>(xt, wm_tab, lane);
       } else if (R == 2) {
         if (active[0] || active[R - 1]) {
           float2* rowp = reinterpret_cast<float2*>(xlane);
@@ -854,7 +877,7 @@ __device__ __forceinline__ void decode_body(const DecodeArgs<D>& a) {
           n_err += st[s] != B2_REC_OK;
         }
       }
-      if (R == 2) __syncwarp();  // the tile is rewritten by the next item's decode (a lane only touches its own pairs, but keep the warp converged)
+      if (R == 2 || WM) __syncwarp();  // the tile is rewritten by the next item's decode (WM: the lanes have read each other's rows)
     } else {
       // coalesced write-out of the item's rows (they are contiguous in xt); a bad record's row becomes NaN
       const int total = c_cnt * xt_stride;
@@ -920,6 +943,11 @@ __global__ void __launch_bounds__(DEC_NT_R2, MINB) decode_kernel_r2(const __grid
 template <int D, bool FT, int FMT>
 __global__ void __launch_bounds__(TCS_ROWS, 512 / TcShape<D>::TMEM_COLS > 5 ? 5 : 512 / TcShape<D>::TMEM_COLS) decode_kernel_tc(const __grid_constant__ DecodeArgs<D> a) {
   decode_body<D, 1, FT, FMT, 1, true>(a);
+}
+// warp-MMA score phase (ae_mma.cuh): CTA shape as for decode_kernel; registers bounded for three CTAs of 8 warps per SM
+template <int D, bool FT, int FMT>
+__global__ void __launch_bounds__(DEC_NT, 3) decode_kernel_wm(const __grid_constant__ DecodeArgs<D> a) {
+  decode_body<D, 1, FT, FMT, 1, false, true>(a);
 }
 template <int D, int MODE, bool FT, int FMT, int MINB>
 struct DecodeKernel<D, MODE, FT, FMT, 1, MINB> {
@@ -1042,12 +1070,21 @@ static int choose_stage_cap(int fmt, const CsvP& csv, const AvroP& avro, const J
   return max(2048, min(STAGE_CAP_MAX, align16i(per_rec * ch + (hint > 0 ? per_rec * (ch / 16) : 0) + 48)));
 }
 
-template <int D, int MODE, bool FT, int FMT, int R, int MINB>
+// the kernel of a launch: VAR = 1 selects the warp-MMA score phase (fused mode, one record per lane)
+template <int D, int MODE, bool FT, int FMT, int R, int MINB, int VAR>
+static auto decode_kernel_of() {
+  if constexpr (VAR == 1 && FMT != FMT_JSON) return decode_kernel_wm<D, FT, FMT>;
+  else return DecodeKernel<D, MODE, FT, FMT, R, MINB>::get();
+}
+
+template <int D, int MODE, bool FT, int FMT, int R, int MINB, int VAR = 0>
 static int launch_decode_r(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stream) {
+  static_assert(VAR == 0 || (MODE == 1 && R == 1 && FMT != FMT_JSON), "warp-MMA scoring: fused mode, one record per lane, CSV / Avro");
   const int xt_stride = MODE == 1 ? (R == 2 ? 2 * (D + 1) : D) : args.n_out;
   args.stage_cap = choose_stage_cap(args.fmt, args.csv, args.avro, args.json, ctx->record_bytes_hint, 32 * R);
   args.warp_bytes = 16 + args.stage_cap + 16 + align16i(32 * xt_stride * 4) + 16;
-  auto kern = DecodeKernel<D, MODE, FT, FMT, R, MINB>::get();
+  auto kern = decode_kernel_of<D, MODE, FT, FMT, R, MINB, VAR>();
+  constexpr size_t cta_extra = VAR == 1 ? (size_t)MmaShape<D>::BYTES : 0;  // per-CTA table of weight fragments
   // no block-wide synchronisation in the kernel, so the CTA size is free: take the one that packs most warps into an SM.
   // The choice depends only on (instantiation, device, bytes per warp): remembered, a launch is then one driver call.
   struct Cfg {
@@ -1060,11 +1097,11 @@ static int launch_decode_r(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stream
     occ = cached.occ;
   } else {
     int best_warps = 0;
-    B2_REQUIRE((size_t)args.warp_bytes * 2 <= (size_t)ctx->smem_optin, "decode: a warp's stage needs %d bytes of shared memory (max %d per CTA)",
-               args.warp_bytes, ctx->smem_optin / 2);
+    B2_REQUIRE((size_t)args.warp_bytes * 2 + cta_extra <= (size_t)ctx->smem_optin, "decode: a warp's stage needs %d bytes of shared memory (max %d per CTA)",
+               args.warp_bytes, (int)(ctx->smem_optin - cta_extra) / 2);
     B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->smem_optin));
     for (int w = (R == 2 ? DEC_NT_R2 / 32 : DEC_WARPS); w >= 2; w >>= 1) {
-      const size_t sm = (size_t)args.warp_bytes * w;
+      const size_t sm = (size_t)args.warp_bytes * w + cta_extra;
       if (sm > (size_t)ctx->smem_optin) continue;
       int o = 0;
       B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, kern, w * 32, sm));
@@ -1072,7 +1109,7 @@ static int launch_decode_r(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stream
     }
     if (occ >= 1) cached = Cfg{ctx->device, args.warp_bytes, threads, occ};
   }
-  const size_t smem = (size_t)args.warp_bytes * (threads / 32);
+  const size_t smem = (size_t)args.warp_bytes * (threads / 32) + cta_extra;
   B2_REQUIRE(occ >= 1, "decode: kernel does not fit on an SM");
   const int wpc = threads / 32;
   const long long n_chunks = (args.n + 32 * R - 1) / (32 * R);
@@ -1095,8 +1132,8 @@ static int launch_decode_r(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stream
     r.stage_cap = STAGE_CAP_MAX;
     r.warp_bytes = 16 + r.stage_cap + 16 + align16i(32 * xt_stride * 4) + 16;
     int rw = 4;
-    while (rw > 1 && (size_t)r.warp_bytes * rw > (size_t)ctx->smem_optin) rw >>= 1;
-    kern<<<1, rw * 32, (size_t)r.warp_bytes * rw, stream>>>(r);
+    while (rw > 1 && (size_t)r.warp_bytes * rw + cta_extra > (size_t)ctx->smem_optin) rw >>= 1;
+    kern<<<1, rw * 32, (size_t)r.warp_bytes * rw + cta_extra, stream>>>(r);
     B2_CUDA(cudaGetLastError());
   }
   return B2_OK;
@@ -1164,6 +1201,9 @@ static int launch_decode_fmt(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stre
     const int k = ctx->knobs.decode_r2;
     if (k == 3) return launch_decode_r<D, MODE, FT, FMT, R2, 5>(ctx, args, stream);
     if (k == 2) return launch_decode_r<D, MODE, FT, FMT, R2, 6>(ctx, args, stream);
+  }
+  if constexpr (MODE == 1 && FMT != FMT_JSON) {
+    if (ctx->knobs.decode_mma != 0) return launch_decode_r<D, MODE, FT, FMT, 1, 1, 1>(ctx, args, stream);
   }
   return launch_decode_r<D, MODE, FT, FMT, 1, 1>(ctx, args, stream);
 }
