@@ -25,8 +25,11 @@ struct AeW {  // padded, kernel-parameter resident copy of the weights
   float b2[AE_P2];
   float k3[AE_H2][AE_P3];
   float b3[AE_P3];
-  float k4[AE_H3][PD];     // [in][out]
-  float b4[PD];
+  // layer 4 per OUTPUT PAIR, the order the second pass consumes it in: (b[2p], b[2p+1], k[0][2p], k[0][2p+1], ... k[6][2p], k[6][2p+1])
+  // = 16 floats = four LDCU.128 per pair (as [in][out] rows every one of the 7 + 1 operand pairs was an LDCU.64 of its own)
+  float o4[PD / 2][2 + 2 * AE_H3];
+  __host__ __device__ float k4(int k, int j) const { return o4[j >> 1][2 + 2 * k + (j & 1)]; }
+  __host__ __device__ float b4(int j) const { return o4[j >> 1][j & 1]; }
 };
 
 template <int D>
@@ -42,6 +45,9 @@ struct NormP {             // normalize_fn table; kind: B2_NORM_*
   //   ZERO      mask 0,  flo 0,  frange 1,     frinv 1, fcorr 1,  m2 0, a2 +0                                 → +0
   uint32_t mask[D];
   float flo[D], frange[D], frinv[D], fcorr[D], m2[D], a2[D];
+  // the same constants once more, grouped per feature PAIR in the order norm_pair_fast consumes them — (flo, frinv | frange, fcorr |
+  // m2, a2 | mask), two values each: 16 words = four 16-byte constant loads per pair instead of seven 8-byte ones
+  float pk[(D + 1) / 2][16];
 };
 
 // b2_norm (C ABI) → NormP<D>; returns whether a table was given
@@ -64,6 +70,12 @@ static inline int norm_fill(const b2_norm* norm, NormP<D>& nm, int n = D) {
     nm.m2[j] = sc ? 2.0f : (zero ? 0.0f : 1.0f);
     nm.a2[j] = sc ? -1.0f : (zero ? 0.0f : -0.0f);
   }
+  for (int j = 0; j < n; ++j) {
+    float* q = nm.pk[j >> 1];
+    const int h = j & 1;
+    q[0 + h] = nm.flo[j], q[2 + h] = nm.frinv[j], q[4 + h] = nm.frange[j], q[6 + h] = nm.fcorr[j], q[8 + h] = nm.m2[j], q[10 + h] = nm.a2[j];
+    memcpy(&q[12 + h], &nm.mask[j], 4);
+  }
   return 1;
 }
 
@@ -82,8 +94,8 @@ static inline void ae_pack_weights(const float* w, AeW<D>& o) {
     for (int j = 0; j < AE_H3; ++j) o.k3[i][j] = *p++;
   for (int j = 0; j < AE_H3; ++j) o.b3[j] = *p++;
   for (int i = 0; i < AE_H3; ++i)
-    for (int j = 0; j < D; ++j) o.k4[i][j] = *p++;
-  for (int j = 0; j < D; ++j) o.b4[j] = *p++;
+    for (int j = 0; j < D; ++j) o.o4[j >> 1][2 + 2 * i + (j & 1)] = *p++;
+  for (int j = 0; j < D; ++j) o.o4[j >> 1][j & 1] = *p++;
 }
 
 #ifdef __CUDACC__
@@ -160,17 +172,15 @@ __device__ __forceinline__ float norm_feature(float v, int kind, float lo, float
 // 2^32 inputs by b2_selftest_normalize (tests/test_normalize_gpu.py).
 template <int D>
 __device__ __forceinline__ float2 norm_pair_fast(float2 v, const NormP<D>& nm, int i) {
-  const float2 vm = make_float2(__uint_as_float(__float_as_uint(v.x) & nm.mask[i]), __uint_as_float(__float_as_uint(v.y) & nm.mask[i + 1]));
-  const float2 lo = make_float2(nm.flo[i], nm.flo[i + 1]);
-  const float2 rg = make_float2(nm.frange[i], nm.frange[i + 1]);
-  const float2 ri = make_float2(nm.frinv[i], nm.frinv[i + 1]);
-  const float2 t = fma2(lo, splat(-1.0f), vm);  // v - lo (exactly one rounding, like the reference's subtraction)
-  const float2 q0 = mul2(t, ri);
-  const float2 r = fma2(make_float2(-q0.x, -q0.y), rg, t);
-  float2 q = fma2(r, make_float2(nm.fcorr[i], nm.fcorr[i + 1]), q0);
+  const float* __restrict__ c = nm.pk[i >> 1];  // i is even
+  const float2 vm = make_float2(__uint_as_float(__float_as_uint(v.x) & __float_as_uint(c[12])), __uint_as_float(__float_as_uint(v.y) & __float_as_uint(c[13])));
+  const float2 t = fma2(make_float2(c[0], c[1]), splat(-1.0f), vm);  // v - lo (exactly one rounding, like the reference's subtraction)
+  const float2 q0 = mul2(t, make_float2(c[2], c[3]));
+  const float2 r = fma2(make_float2(-q0.x, -q0.y), make_float2(c[4], c[5]), t);
+  float2 q = fma2(r, make_float2(c[6], c[7]), q0);
   if (fabsf(q0.x) == __int_as_float(0x7F800000)) q.x = q0.x;
   if (fabsf(q0.y) == __int_as_float(0x7F800000)) q.y = q0.y;
-  return fma2(q, make_float2(nm.m2[i], nm.m2[i + 1]), make_float2(nm.a2[i], nm.a2[i + 1]));
+  return fma2(q, make_float2(c[8], c[9]), make_float2(c[10], c[11]));
 }
 
 // Forward pass for R records living in shared-memory rows row[r] (D floats each, 8-byte aligned).
@@ -255,11 +265,11 @@ __device__ __forceinline__ void ae_forward_rows(const AeW<D>& w, const NormP<D>&
   for (int j = 0; j < D; j += 2) {
 #pragma unroll
     for (int r = 0; r < R; ++r) {
-      float2 y = make_float2(w.b4[j], w.b4[j + 1]);
+      float2 y = make_float2(w.o4[j / 2][0], w.o4[j / 2][1]);
 #pragma unroll
       for (int k = 0; k < AE_H3; ++k) {
         const float hk = (k & 1) ? h3[r][k / 2].y : h3[r][k / 2].x;
-        y = fma2(splat(hk), make_float2(w.k4[k][j], w.k4[k][j + 1]), y);
+        y = fma2(splat(hk), make_float2(w.o4[j / 2][2 + 2 * k], w.o4[j / 2][3 + 2 * k]), y);
       }
       y = relu2(y);
       const float2 xv = *reinterpret_cast<const float2*>(row[r] + j);
@@ -342,9 +352,9 @@ __device__ __forceinline__ void ae_forward_pair(const AeW<D>& w, const NormP<D>&
   float2 se_even = make_float2(0.f, 0.f), se_odd = make_float2(0.f, 0.f);
 #pragma unroll
   for (int j = 0; j < D; ++j) {
-    float2 y = splat(w.b4[j]);
+    float2 y = splat(w.b4(j));
 #pragma unroll
-    for (int k = 0; k < AE_H3; ++k) y = fma2(h3[k], splat(w.k4[k][j]), y);
+    for (int k = 0; k < AE_H3; ++k) y = fma2(h3[k], splat(w.k4(k, j)), y);
     y = relu2(y);
     const float2 d = fma2(y, splat(-1.0f), row[j]);
     if (j & 1) se_odd = fma2(d, d, se_odd);

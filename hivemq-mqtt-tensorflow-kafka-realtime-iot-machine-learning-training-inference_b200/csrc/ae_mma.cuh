@@ -90,8 +90,8 @@ __device__ __forceinline__ void mma_fill_table(const AeW<D>& w, uint8_t* tab, in
       }
     } else {
       if (n < D) {
-        if (u0 < AE_H3) v0 = w.k4[u0][n];
-        if (u1 < AE_H3) v1 = w.k4[u1][n];
+        if (u0 < AE_H3) v0 = w.k4(u0, n);
+        if (u1 < AE_H3) v1 = w.k4(u1, n);
       }
     }
     const float h0 = tf32_rna(v0), h1 = tf32_rna(v1);
@@ -114,8 +114,8 @@ __device__ __forceinline__ void mma_fill_table(const AeW<D>& w, uint8_t* tab, in
       if (n + 1 < AE_H3) v1 = w.b3[n + 1];
     } else {
       const int n = 8 * (b - S::B4) + 2 * t;
-      if (n < D) v0 = w.b4[n];
-      if (n + 1 < D) v1 = w.b4[n + 1];
+      if (n < D) v0 = w.b4(n);
+      if (n + 1 < D) v1 = w.b4(n + 1);
     }
     bias[e] = make_float4(v0, v1, v0, v1);
   }

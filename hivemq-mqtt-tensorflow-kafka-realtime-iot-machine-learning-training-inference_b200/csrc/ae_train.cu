@@ -46,9 +46,11 @@ __host__ __device__ inline int padded_offset(int p) {
   p -= 49, off += AE_H2 * AE_P3;
   if (p < 7) return off + p;
   p -= 7, off += AE_P3;
-  if (p < 7 * D) return off + (p / D) * PD + p % D;
-  p -= 7 * D, off += AE_H3 * PD;
-  return off + p;
+  // layer 4 is stored per output pair: (b[2q], b[2q+1], k[0][2q], k[0][2q+1], ..., k[6][2q], k[6][2q+1]), see AeW::o4
+  constexpr int PAIR = 2 + 2 * AE_H3;
+  if (p < 7 * D) return off + ((p % D) >> 1) * PAIR + 2 + 2 * (p / D) + ((p % D) & 1);
+  p -= 7 * D;
+  return off + (p >> 1) * PAIR + (p & 1);
 }
 
 // gradient of one parameter = Σ_b A[b*sa + ia] * B[b*sb + ib]   (A == nullptr → bias: Σ_b B[...])
@@ -145,9 +147,9 @@ __device__ __forceinline__ void row_fwd_bwd(const AeW<D>& w, float* __restrict__
   int yarg = 0, xarg = 0;
 #pragma unroll 2
   for (int j = 0; j < D; ++j) {
-    float y = w.b4[j];
+    float y = w.b4(j);
 #pragma unroll
-    for (int k = 0; k < AE_H3; ++k) y = fmaf(h3[k], w.k4[k][j], y);
+    for (int k = 0; k < AE_H3; ++k) y = fmaf(h3[k], w.k4(k, j), y);
     y = fmaxf(y, 0.f);
     const float xj = x[j];
     const float d = y - xj;
@@ -157,7 +159,7 @@ __device__ __forceinline__ void row_fwd_bwd(const AeW<D>& w, float* __restrict__
     const float dz = y > 0.f ? c_mse * d : 0.f;
     arena[A::Z4 + t * D + j] = dz;
 #pragma unroll
-    for (int k = 0; k < AE_H3; ++k) dh3[k] = fmaf(dz, w.k4[k][j], dh3[k]);
+    for (int k = 0; k < AE_H3; ++k) dh3[k] = fmaf(dz, w.k4(k, j), dh3[k]);
   }
   (void)PD;
   float dz3[AE_H3], dz2[AE_H2];
