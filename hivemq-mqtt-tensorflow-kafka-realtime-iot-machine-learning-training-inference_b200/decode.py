@@ -407,6 +407,8 @@ class _HostWorkspace:
     def __init__(self, dev):
         self.dev = dev
         self.side = torch.cuda.Stream(device=dev)
+        self.back = torch.cuda.Stream(device=dev)   # results D2H, chunk by chunk, under the following chunks' H2D (PCIe is full duplex)
+        self.done = [torch.cuda.Event() for _ in range(64)]
         self.cap_bytes = self.cap_n = 0
         self.d = self.o = self.res = self.status = self.label = None
         self.events = [torch.cuda.Event() for _ in range(64)]
@@ -424,13 +426,15 @@ class _HostWorkspace:
 
 
 def decode_score_host(model, data, offsets, csv_kinds=None, csv_defaults=None, avro_schema=None, threshold: float = 5.0,
-                      skip_prefix: int = 0, chunks: int = 4, reuse_output: bool = False, json_keys=None, json_label=None):
+                      skip_prefix: int = 0, chunks: int = 4, reuse_output: bool = False, json_keys=None, json_label=None,
+                      overlap_d2h: bool = True):
     """End-to-end form for HOST buffers (what a Kafka consumer hands over): ``data`` uint8 / ``offsets`` int32 as NumPy arrays
     or (ideally pinned) CPU tensors → H2D copy → fused kernel → D2H of (mse f32[n], flag u8[n]) as NumPy arrays.
 
     The batch is cut into ``chunks`` record ranges: the payload bytes of range c+1 cross PCIe on a copy stream while range c is
-    decoded + scored; the 5 B/record results come back in ONE copy at the end.  Device staging buffers, the copy stream and the
-    events are kept per device between calls.  With ``reuse_output`` the returned arrays are views of a per-size pinned buffer
+    decoded + scored, and the 5 B/record results of range c go back on a third stream under the H2D of the ranges behind it
+    (``overlap_d2h=False``: ONE copy at the end).  Device staging buffers, the streams and the events are kept per device
+    between calls.  With ``reuse_output`` the returned arrays are views of a per-size pinned buffer
     that the next call of the same size overwrites (no pinned allocation per call)."""
     dev = torch.device("cuda", torch.cuda.current_device())
     d = data if isinstance(data, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(data, dtype=np.uint8))
@@ -475,6 +479,15 @@ def decode_score_host(model, data, offsets, csv_kinds=None, csv_defaults=None, a
         decode_score(model, rb, csv_kinds=csv_kinds, csv_defaults=csv_defaults, avro_schema=avro_schema, json_keys=json_keys,
                      json_label=json_label, threshold=threshold,
                      mse=mse[c0:c1], flag=flag[c0:c1], status=status[c0:c1], label=None if label is None else label[c0:c1])
-    out.copy_(ws.res[: n * 5], non_blocking=True)
+        if overlap_d2h:
+            ws.done[k].record(main)
+            with torch.cuda.stream(ws.back):
+                ws.back.wait_event(ws.done[k])
+                out[c0 * 4: c1 * 4].copy_(ws.res[c0 * 4: c1 * 4], non_blocking=True)
+                out[n * 4 + c0: n * 4 + c1].copy_(ws.res[n * 4 + c0: n * 4 + c1], non_blocking=True)
+    if overlap_d2h:
+        main.wait_stream(ws.back)
+    else:
+        out.copy_(ws.res[: n * 5], non_blocking=True)
     main.synchronize()
     return out[: n * 4].view(torch.float32).numpy(), out[n * 4:].numpy()

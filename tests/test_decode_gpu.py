@@ -250,8 +250,9 @@ def test_host_end_to_end_path_matches_device_path(cuda_device, fmt):
         kw, skip = dict(avro_schema=schemas.schema_a_json()), 5
     mse_d, flag_d, _, _ = dec.decode_score(m, dec.RecordBatch(data, offs, skip_prefix=skip), **kw)
     hd, ho = torch.from_numpy(data).pin_memory(), torch.from_numpy(offs).pin_memory()
-    for reuse in (False, True, True):
-        mse_h, flag_h = dec.decode_score_host(m, hd, ho, skip_prefix=skip, reuse_output=reuse, **kw)
+    for reuse, overlap in ((False, True), (True, True), (True, True), (True, False), (False, False)):
+        # results copied back chunk by chunk on a third stream (default), or in one copy at the end
+        mse_h, flag_h = dec.decode_score_host(m, hd, ho, skip_prefix=skip, reuse_output=reuse, overlap_d2h=overlap, **kw)
         np.testing.assert_array_equal(mse_h, mse_d.cpu().numpy())
         np.testing.assert_array_equal(flag_h, flag_d.cpu().numpy())
     mse_h, flag_h = dec.decode_score_host(m, data[: offs[7]], offs[:8], skip_prefix=skip, chunks=16, **kw)  # more chunks than records/4
