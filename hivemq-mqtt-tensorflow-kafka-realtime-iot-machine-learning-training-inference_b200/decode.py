@@ -463,7 +463,10 @@ def decode_score_host(model, data, offsets, csv_kinds=None, csv_defaults=None, a
     o_dev.copy_(o, non_blocking=True)
     side.wait_stream(main)  # the staging buffers are reused: ordered after whatever the previous call still had in flight
     chunks = max(1, min(int(chunks), len(ws.events)))
-    bounds = sorted(set(n * c // chunks for c in range(chunks + 1)))
+    # chunk sizes fall off linearly (4 : 3 : 2 : 1 for four chunks): what is left to do once the last byte has crossed PCIe — the
+    # last chunk's kernel and the copy of its results — is what a step pays on top of the transfers
+    tot = chunks * (chunks + 1) // 2
+    bounds = sorted(set(n * (tot - (chunks - c) * (chunks - c + 1) // 2) // tot for c in range(chunks + 1)))
     with torch.cuda.stream(side):
         for k, (c0, c1) in enumerate(zip(bounds[:-1], bounds[1:])):
             b0, b1 = int(oh[c0]), int(oh[c1])
