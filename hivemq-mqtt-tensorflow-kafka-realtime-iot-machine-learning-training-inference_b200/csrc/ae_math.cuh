@@ -190,9 +190,14 @@ __device__ __forceinline__ float2 norm_pair_fast(float2 v, const NormP<D>& nm, i
 // consumed as-is, so no register shuffling is needed; R = 2 rows per thread share every LDCU.128 weight fetch.
 //   pass 1 streams x (normalising it in place when NORM) into the layer-1 accumulators,
 //   pass 2 produces one output pair at a time, accumulates (x - y)^2 and (RECON) overwrites x with y.
-template <int D, int R, bool NORM, bool RECON, bool FAST_TANH>
+// ZM (only with NORM): bit i set = the normalisation table forces feature i to +0 (kind ZERO — four of the reference's eighteen,
+// cardata-v1.py:72-87).  Such an input adds exactly nothing to layer 1 (+0 · w for finite w), so its multiply-adds, its weight
+// fetches and its share of the normalisation arithmetic are left out at compile time; the launch selects a ZM instantiation only
+// when the table's zero set matches and the skipped weights are finite, and the results are bit-identical to ZM = 0.
+template <int D, int R, bool NORM, bool RECON, bool FAST_TANH, unsigned ZM = 0u>
 __device__ __forceinline__ void ae_forward_rows(const AeW<D>& w, const NormP<D>& nm, float* const (&row)[R], float (&mse)[R]) {
   static_assert(D % 2 == 0, "feature count must be even (8-byte row alignment)");
+  static_assert(ZM == 0u || NORM, "a zero set is a property of the normalisation table");
   constexpr int Q1 = AE_H1 / 2, Q2 = AE_P2 / 2, Q3 = AE_P3 / 2;
   float2 h1[R][Q1];
 #pragma unroll
@@ -203,16 +208,24 @@ __device__ __forceinline__ void ae_forward_rows(const AeW<D>& w, const NormP<D>&
   for (int i = 0; i < D; i += 2) {
 #pragma unroll
     for (int r = 0; r < R; ++r) {
+      if (((ZM >> i) & 3u) == 3u) {  // both features forced to zero: nothing to compute, the row just receives the zeros
+        *reinterpret_cast<float2*>(row[r] + i) = make_float2(0.f, 0.f);
+        continue;
+      }
       float2 xv = *reinterpret_cast<const float2*>(row[r] + i);
       if (NORM) {
         xv = norm_pair_fast<D>(xv, nm, i);
         *reinterpret_cast<float2*>(row[r] + i) = xv;
       }
+      if (!((ZM >> i) & 1u)) {
 #pragma unroll
-      for (int q = 0; q < Q1; ++q) h1[r][q] = fma2(splat(xv.x), make_float2(w.k1[i][2 * q], w.k1[i][2 * q + 1]), h1[r][q]);
+        for (int q = 0; q < Q1; ++q) h1[r][q] = fma2(splat(xv.x), make_float2(w.k1[i][2 * q], w.k1[i][2 * q + 1]), h1[r][q]);
+      }
+      if (!((ZM >> (i + 1)) & 1u)) {
 #pragma unroll
-      for (int q = 0; q < Q1; ++q)
-        h1[r][q] = fma2(splat(xv.y), make_float2(w.k1[i + 1][2 * q], w.k1[i + 1][2 * q + 1]), h1[r][q]);
+        for (int q = 0; q < Q1; ++q)
+          h1[r][q] = fma2(splat(xv.y), make_float2(w.k1[i + 1][2 * q], w.k1[i + 1][2 * q + 1]), h1[r][q]);
+      }
     }
   }
 #pragma unroll

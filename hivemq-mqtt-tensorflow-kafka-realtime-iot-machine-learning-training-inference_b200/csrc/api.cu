@@ -40,7 +40,7 @@ const KnobName kKnobs[] = {
     {"avro_generic", "B2_AVRO_GENERIC", &b2_knobs::avro_generic}, {"lstm_tc", "B2_LSTM_TC", &b2_knobs::lstm_tc},
     {"score_tc", "B2_SCORE_TC", &b2_knobs::score_tc},          {"tc_ctas", "B2_TC_CTAS", &b2_knobs::tc_ctas},
     {"decode_r2", "B2_DECODE_R2", &b2_knobs::decode_r2},       {"decode_tc", "B2_DECODE_TC", &b2_knobs::decode_tc},
-    {"decode_mma", "B2_DECODE_MMA", &b2_knobs::decode_mma},
+    {"decode_mma", "B2_DECODE_MMA", &b2_knobs::decode_mma},   {"zero_skip", "B2_ZERO_SKIP", &b2_knobs::zero_skip},
 };
 }  // namespace
 

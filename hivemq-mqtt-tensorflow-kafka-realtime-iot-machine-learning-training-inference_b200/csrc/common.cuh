@@ -45,6 +45,7 @@ struct b2_knobs {
   int decode_r2 = 0;      // B2_DECODE_R2     fused Avro decode: 0 one record per lane (default), 2 / 3 two (85 / 102 registers)
   int decode_tc = 0;      // B2_DECODE_TC     fused decode + score: 1 = score phase on tcgen05 (decode_kernel_tc)
   int decode_mma = 0;     // B2_DECODE_MMA    fused decode + score: 1 = score phase as warp-level TF32 MMAs (decode_kernel_wm, ae_mma.cuh)
+  int zero_skip = 1;      // B2_ZERO_SKIP     fused decode + score: 1 = the instantiation that leaves out the features the reference's table forces to zero (when the table matches), 0 = always the generic one
   int tc_ctas = 0;        // B2_TC_CTAS       CTAs per SM of the tcgen05 score kernels (0 = as many as TMEM allows)
 };
 

@@ -474,7 +474,8 @@ __device__ __forceinline__ int avro_decode_record(const uint8_t* __restrict__ ba
 // emitted with constant counts and columns: no loops, no descriptor reads.  A record that is not in the common shape (an int
 // of more than two bytes, a union tag other than 0/2, a long label) returns -1 and takes the generic walk; results are
 // identical by construction and checked against each other in tests/test_decode_gpu.py.
-template <int COUNT, int OUT0, int XS>
+// ZM: bit i set = column i is overwritten with zero by the normalisation anyway (see ae_forward_rows): its value is not extracted
+template <int COUNT, int OUT0, int XS, unsigned ZM = 0u>
 __device__ __forceinline__ int avs_floats(const uint8_t* __restrict__ base, int p, float* __restrict__ xrow) {
   const uint32_t* wp = reinterpret_cast<const uint32_t*>(base + (p & ~3));
   const int sh = (p & 3) * 8;
@@ -482,7 +483,7 @@ __device__ __forceinline__ int avs_floats(const uint8_t* __restrict__ base, int 
 #pragma unroll
   for (int j = 0; j < COUNT; ++j) {
     const uint32_t w_next = wp[j + 1];
-    xrow[(OUT0 + j) * XS] = __uint_as_float(__funnelshift_r(w_prev, w_next, sh));
+    if (!((ZM >> (OUT0 + j)) & 1u)) xrow[(OUT0 + j) * XS] = __uint_as_float(__funnelshift_r(w_prev, w_next, sh));
     w_prev = w_next;
   }
   return p + 4 * COUNT;
@@ -515,13 +516,13 @@ __device__ __forceinline__ int avs_ints(const uint8_t* __restrict__ base, int p,
   }
   return p;
 }
-template <int XS>
+template <int XS, unsigned ZM = 0u>
 __device__ __forceinline__ int avro_walk_schema_a(const uint8_t* __restrict__ base, int p, int e, int skip, float* __restrict__ xrow) {
   p += skip;
-  p = avs_floats<9, 0, XS>(base, p, xrow);
+  p = avs_floats<9, 0, XS, ZM>(base, p, xrow);
   p = avs_ints<4, 9, XS>(base, p, xrow);
   if (p < 0) return -1;
-  p = avs_floats<4, 13, XS>(base, p, xrow);
+  p = avs_floats<4, 13, XS, ZM>(base, p, xrow);
   p = avs_ints<1, 17, XS>(base, p, xrow);
   if (p < 0) return -1;
   return p > e ? B2_REC_TRUNCATED : B2_REC_OK;
@@ -610,8 +611,9 @@ __device__ __forceinline__ int avro_walk_schema_b(const uint8_t* __restrict__ ba
 // TC (fused mode, R = 1, CTAs of exactly 4 warps): the score phase runs on the tensor cores (ae_tc.cuh) — the CTA's four warps
 // still fetch, plan and decode independently, but score their 4 x 32 records together as one 128-row tile, so the item loop runs
 // in lock-step across the CTA (a warp that has run out of chunks contributes empty rows until all four are done).
-template <int D, int MODE, bool FT, int FMT, int R, bool TC = false, bool WM = false>
+template <int D, int MODE, bool FT, int FMT, int R, bool TC = false, bool WM = false, unsigned ZM = 0u>
 __device__ __forceinline__ void decode_body(const DecodeArgs<D>& a) {
+  static_assert(ZM == 0u || (MODE == 1 && R == 1 && !TC && !WM), "zero-set specialisation: fused mode, FFMA2 score phase");
   static_assert(R == 1 || (R == 2 && MODE == 1), "two records per lane only in the fused mode");
   static_assert(!TC || (MODE == 1 && R == 1), "tensor-core scoring: fused mode, one record per lane");
   static_assert(!WM || (MODE == 1 && R == 1 && !TC && FMT != FMT_JSON), "warp-MMA scoring: fused mode, one record per lane, CSV / Avro");
@@ -795,7 +797,7 @@ __device__ __forceinline__ void decode_body(const DecodeArgs<D>& a) {
         if (!a.avro.all_routed)
           for (int j = 0; j < (MODE == 1 ? D : a.n_out); ++j) xrow[j * XS] = 0.0f;  // columns no field routes to
         st_s = -1;
-        if (a.avro.known == 1) st_s = avro_walk_schema_a<XS>(stage, cb, ce, a.avro.skip_prefix, xrow);
+        if (a.avro.known == 1) st_s = avro_walk_schema_a<XS, ZM>(stage, cb, ce, a.avro.skip_prefix, xrow);
         else if (a.avro.known == 2) st_s = avro_walk_schema_b<XS>(stage, cb, ce, a.avro.skip_prefix, xrow, &lab_s);
         if (st_s < 0) {
           lab_s = 2;
@@ -857,7 +859,7 @@ __device__ __forceinline__ void decode_body(const DecodeArgs<D>& a) {
       } else if (active[0]) {
         float* const rowp[1] = {xlane};
         float m1[1] = {0.f};
-        if (a.has_norm) ae_forward_rows<D, 1, true, false, FT>(a.w, a.nm, rowp, m1);
+        if (ZM != 0u || a.has_norm) ae_forward_rows<D, 1, true, false, FT, ZM>(a.w, a.nm, rowp, m1);  // (a ZM kernel is only launched with a table)
         else ae_forward_rows<D, 1, false, false, FT>(a.w, a.nm, rowp, m1);
         mm[0] = m1[0];
       }
@@ -943,6 +945,13 @@ __global__ void __launch_bounds__(DEC_NT_R2, MINB) decode_kernel_r2(const __grid
 template <int D, bool FT, int FMT>
 __global__ void __launch_bounds__(TCS_ROWS, 512 / TcShape<D>::TMEM_COLS > 5 ? 5 : 512 / TcShape<D>::TMEM_COLS) decode_kernel_tc(const __grid_constant__ DecodeArgs<D> a) {
   decode_body<D, 1, FT, FMT, 1, true>(a);
+}
+// the reference's normalisation table forces features 0, 2, 4 and 5 to zero (cardata-v1.py:72, :78, :84, :87): the instantiation
+// with that zero set compiled in (see ae_forward_rows), launched when the caller's table has exactly this zero set
+constexpr unsigned REF_ZERO_MASK = 0x35u;
+template <int D, bool FT, int FMT>
+__global__ void __launch_bounds__(DEC_NT, FMT == FMT_AVRO ? 4 : 3) decode_kernel_zs(const __grid_constant__ DecodeArgs<D> a) {
+  decode_body<D, 1, FT, FMT, 1, false, false, REF_ZERO_MASK>(a);
 }
 // warp-MMA score phase (ae_mma.cuh): CTA shape as for decode_kernel; registers bounded for three CTAs of 8 warps per SM
 template <int D, bool FT, int FMT>
@@ -1074,12 +1083,13 @@ static int choose_stage_cap(int fmt, const CsvP& csv, const AvroP& avro, const J
 template <int D, int MODE, bool FT, int FMT, int R, int MINB, int VAR>
 static auto decode_kernel_of() {
   if constexpr (VAR == 1 && FMT != FMT_JSON) return decode_kernel_wm<D, FT, FMT>;
+  else if constexpr (VAR == 2) return decode_kernel_zs<D, FT, FMT>;
   else return DecodeKernel<D, MODE, FT, FMT, R, MINB>::get();
 }
 
 template <int D, int MODE, bool FT, int FMT, int R, int MINB, int VAR = 0>
 static int launch_decode_r(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stream) {
-  static_assert(VAR == 0 || (MODE == 1 && R == 1 && FMT != FMT_JSON), "warp-MMA scoring: fused mode, one record per lane, CSV / Avro");
+  static_assert(VAR == 0 || (MODE == 1 && R == 1 && (VAR == 2 || FMT != FMT_JSON)), "score-phase variants: fused mode, one record per lane");
   const int xt_stride = MODE == 1 ? (R == 2 ? 2 * (D + 1) : D) : args.n_out;
   args.stage_cap = choose_stage_cap(args.fmt, args.csv, args.avro, args.json, ctx->record_bytes_hint, 32 * R);
   args.warp_bytes = 16 + args.stage_cap + 16 + align16i(32 * xt_stride * 4) + 16;
@@ -1204,6 +1214,19 @@ static int launch_decode_fmt(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stre
   }
   if constexpr (MODE == 1 && FMT != FMT_JSON) {
     if (ctx->knobs.decode_mma != 0) return launch_decode_r<D, MODE, FT, FMT, 1, 1, 1>(ctx, args, stream);
+  }
+  if constexpr (MODE == 1 && D == 18 && FT) {
+    // the table's zero set is the reference's and the layer-1 rows it skips are finite (+0 · w must be exactly nothing)
+    if (ctx->knobs.zero_skip != 0 && args.has_norm) {
+      unsigned zm = 0;
+      bool finite = true;
+      for (int i = 0; i < D; ++i) {
+        if (args.nm.kind[i] != B2_NORM_ZERO) continue;
+        zm |= 1u << i;
+        for (int j = 0; j < AE_H1; ++j) finite = finite && std::isfinite(args.w.k1[i][j]);
+      }
+      if (zm == REF_ZERO_MASK && finite) return launch_decode_r<D, MODE, FT, FMT, 1, 1, 2>(ctx, args, stream);
+    }
   }
   return launch_decode_r<D, MODE, FT, FMT, 1, 1>(ctx, args, stream);
 }

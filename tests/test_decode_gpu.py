@@ -410,3 +410,59 @@ def test_tensor_core_score_phase_variant_agrees(cuda_device, fmt):
         safe = ok & (np.abs(a[0] - 5.0) > 1e-4)
         np.testing.assert_array_equal(a[1][safe], b[1][safe])
         assert a[3][0] == b[3][0] and a[3][2] == b[3][2] and a[3][3] == b[3][3]
+
+
+@pytest.mark.parametrize("fmt", ["avro_a", "avro_b", "csv"])
+def test_zero_set_instantiation_is_bit_identical(cuda_device, fmt):
+    """The fused kernel compiled for the zero set of the reference's normalisation table (features 0, 2, 4, 5 are forced to 0.0 by
+    normalize_fn, cardata-v1.py:72-87: their layer-1 products are left out) must give the same bits as the generic instantiation
+    (context option zero_skip = 0) — also when the zeroed columns carry NaN / inf / huge values, and with damaged records."""
+    x = synth.sensor_rows(60_001, seed=77)
+    rng = np.random.default_rng(5)
+    for col in (0, 2, 4, 5):
+        rows = rng.choice(len(x), 300, replace=False)
+        x[rows[:100], col] = np.nan if fmt != "csv" else 1e30
+        x[rows[100:200], col] = np.inf if fmt != "csv" else -3.4e38
+        x[rows[200:], col] = -1e30
+    if fmt == "avro_a":
+        data, offs = synth.avro_a_batch(x)
+        kw, skip = dict(avro_schema=schemas.schema_a_json()), 5
+    elif fmt == "avro_b":
+        data, offs, _ = synth.avro_b_batch(x, null_frac=0.02, seed=5, label_probs=(0.9, 0.05, 0.05))
+        kw, skip = dict(avro_schema=schemas.schema_b_json()), 5
+    else:
+        data, offs = synth.csv_batch(x, seed=7)
+        kw, skip = dict(csv_kinds=SENSOR_KINDS), 0
+    data, offs, bad = synth.corrupt_batch(data, offs, fmt, 1e-3, seed=11)
+    m = _model18()
+    res = {}
+    try:
+        for zs in (1, 0):
+            bs.keras.set_option("zero_skip", zs)
+            for n in (60_001, 33, 1):
+                rb = dec.RecordBatch(data[: offs[n]], offs[: n + 1], skip_prefix=skip)
+                cnt = torch.zeros(4, dtype=torch.int64, device="cuda")
+                mse, flag, label, status = dec.decode_score(m, rb, counters=cnt, **kw)
+                res[(zs, n)] = (_bits(mse.cpu().numpy()), flag.cpu().numpy(), status.cpu().numpy(), cnt.cpu().tolist())
+    finally:
+        bs.keras.set_option("zero_skip", 1)
+    assert (res[(1, 60_001)][2] != 0).sum() == len(bad)
+    assert np.isfinite(res[(1, 60_001)][0].view(np.float32)[res[(1, 60_001)][2] == 0]).all()  # the poisoned columns never reach the score
+    for n in (60_001, 33, 1):
+        for a, b in zip(res[(1, n)][:3], res[(0, n)][:3]):
+            np.testing.assert_array_equal(a, b)
+        assert res[(1, n)][3] == res[(0, n)][3]
+    # a table with another zero set, or a non-finite weight in a skipped row, runs the generic instantiation: same answer as the oracle path
+    kind, lo, rg = schemas.norm_arrays()
+    kind2 = kind.copy()
+    kind2[1] = schemas.NORM_ZERO
+    m2 = _model18()
+    m2.set_normalization(kind2, lo, rg)
+    rb = dec.RecordBatch(data, offs, skip_prefix=skip)
+    a = dec.decode_score(m2, rb, **kw)[0].cpu().numpy()
+    bs.keras.set_option("zero_skip", 0)
+    try:
+        b = dec.decode_score(m2, rb, **kw)[0].cpu().numpy()
+    finally:
+        bs.keras.set_option("zero_skip", 1)
+    np.testing.assert_array_equal(_bits(a), _bits(b))
