@@ -79,6 +79,23 @@ static inline int norm_fill(const b2_norm* norm, NormP<D>& nm, int n = D) {
   return 1;
 }
 
+// The reference's normalisation table forces features 0, 2, 4 and 5 to zero (cardata-v1.py:72, :78, :84, :87): kernels carry one
+// instantiation with that zero set compiled in (ZM of ae_forward_rows), launched when the caller's table has exactly this set.
+constexpr unsigned REF_ZERO_MASK = 0x35u;
+// bit i = feature i is of kind ZERO; ~0u when a layer-1 weight row that a ZM instantiation would skip is not finite (+0 · w must be
+// exactly nothing for the skip to be invisible)
+template <int D, class W, class N>
+static inline unsigned norm_zero_set(const N& nm, const W& w) {
+  unsigned zm = 0;
+  for (int i = 0; i < D && i < 32; ++i) {
+    if (nm.kind[i] != B2_NORM_ZERO) continue;
+    zm |= 1u << i;
+    for (int j = 0; j < 14; ++j)
+      if (!(w.k1[i][j] - w.k1[i][j] == 0.0f)) return ~0u;
+  }
+  return zm;
+}
+
 // Pack Keras flat order (kernel0[in,out], bias0, kernel1, ...) into AeW<D>.
 template <int D>
 static inline void ae_pack_weights(const float* w, AeW<D>& o) {

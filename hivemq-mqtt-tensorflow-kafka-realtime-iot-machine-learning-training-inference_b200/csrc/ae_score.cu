@@ -28,7 +28,7 @@ struct ScoreArgs {
   int use_bulk;
 };
 
-template <int D, int NT, int STAGES, bool NORM, bool RECON, bool FT>
+template <int D, int NT, int STAGES, bool NORM, bool RECON, bool FT, unsigned ZM = 0u>
 __global__ void __launch_bounds__(NT) ae_score_kernel(const __grid_constant__ ScoreArgs<D> a) {
   constexpr int TILE = 2 * NT;
   constexpr int TILE_FLOATS = TILE * D;
@@ -77,7 +77,7 @@ __global__ void __launch_bounds__(NT) ae_score_kernel(const __grid_constant__ Sc
     // computed on but never stored
     float* const rowp[2] = {st + (size_t)tid * D, st + (size_t)(tid + NT) * D};
     float mm[2] = {0.f, 0.f};
-    if (va) ae_forward_rows<D, 2, NORM, RECON, FT>(a.w, a.nm, rowp, mm);
+    if (va) ae_forward_rows<D, 2, NORM, RECON, FT, ZM>(a.w, a.nm, rowp, mm);
     const float2 m = make_float2(mm[0], mm[1]);
     const bool fa = m.x > a.threshold, fb = m.y > a.threshold;  // strict, nb2.0:1163
     if (va) {
@@ -188,11 +188,11 @@ __global__ void __launch_bounds__(128) ae_score_generic_kernel(const __grid_cons
 int b2_ae_score_tc(b2_ae* ae, const float* x_dev, int64_t n, const b2_norm* norm, float threshold, float* mse_dev, uint8_t* flag_dev,
                    unsigned long long* counters_dev, cudaStream_t stream);
 
-template <int D, int NT, int STAGES, bool NORM, bool RECON, bool FT>
+template <int D, int NT, int STAGES, bool NORM, bool RECON, bool FT, unsigned ZM = 0u>
 static int launch_score(b2_ae* ae, const ScoreArgs<D>& args, cudaStream_t stream) {
   constexpr int TILE = 2 * NT;
   constexpr size_t smem = (size_t)STAGES * TILE * D * 4 + STAGES * sizeof(uint64_t);
-  auto kern = ae_score_kernel<D, NT, STAGES, NORM, RECON, FT>;
+  auto kern = ae_score_kernel<D, NT, STAGES, NORM, RECON, FT, ZM>;
   static int occ_cache[16] = {0};  // per device
   int dev = ae->ctx->device;
   if (occ_cache[dev & 15] == 0) {
@@ -233,6 +233,11 @@ static int score_spec(b2_ae* ae, const float* x, int64_t n, const b2_norm* norm,
   if (recon) {
     if (has_norm) return launch_score<D, 128, 2, true, true, false>(ae, args, stream);
     return launch_score<D, 128, 2, false, true, false>(ae, args, stream);
+  }
+  if constexpr (D == 18) {
+    // the default launch shape with the reference table's zero set compiled in (ae_forward_rows ZM), when the table matches
+    if (has_norm && ft && cfg == 1 && ae->ctx->knobs.zero_skip != 0 && norm_zero_set<D>(args.nm, args.w) == REF_ZERO_MASK)
+      return launch_score<D, 128, 1, true, false, true, REF_ZERO_MASK>(ae, args, stream);
   }
 #define B2_PICK(NT_, ST_)                                                                      \
   do {                                                                                         \

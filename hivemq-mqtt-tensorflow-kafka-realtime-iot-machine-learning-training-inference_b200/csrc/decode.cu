@@ -529,11 +529,17 @@ __device__ __forceinline__ int avro_walk_schema_a(const uint8_t* __restrict__ ba
 }
 
 // ["null", double]: tag 0x00 = null (→ 0), 0x02 = value; anything else bails out
-template <int COUNT, int OUT0, int XS>
+template <int COUNT, int OUT0, int XS, unsigned ZM = 0u>
 __device__ __forceinline__ int avs_nullable_doubles(const uint8_t* __restrict__ base, int p, float* __restrict__ xrow) {
   bool ok = true;
 #pragma unroll
   for (int j = 0; j < COUNT; ++j) {
+    if ((ZM >> (OUT0 + j)) & 1u) {  // a column the normalisation overwrites with zero: only the union tag is looked at
+      const uint32_t tag = base[p];
+      ok = ok && (tag == 0u || tag == 2u);
+      p += tag == 2u ? 9 : 1;
+      continue;
+    }
     // tag + 8 value bytes always sit inside three aligned words
     const uint32_t* wp = reinterpret_cast<const uint32_t*>(base + (p & ~3));
     const uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2];
@@ -563,11 +569,11 @@ __device__ __forceinline__ int avs_nullable_ints(const uint8_t* __restrict__ bas
   }
   return ok ? p : -1;
 }
-template <int XS>
+template <int XS, unsigned ZM = 0u>
 __device__ __forceinline__ int avro_walk_schema_b(const uint8_t* __restrict__ base, int p, int e, int skip, float* __restrict__ xrow,
                                                   uint8_t* label) {
   p += skip;
-  p = avs_nullable_doubles<9, 0, XS>(base, p, xrow);
+  p = avs_nullable_doubles<9, 0, XS, ZM>(base, p, xrow);
   if (p < 0) return -1;
   p = avs_nullable_ints<4, 9, XS>(base, p, xrow);
   if (p < 0) return -1;
@@ -798,7 +804,7 @@ __device__ __forceinline__ void decode_body(const DecodeArgs<D>& a) {
           for (int j = 0; j < (MODE == 1 ? D : a.n_out); ++j) xrow[j * XS] = 0.0f;  // columns no field routes to
         st_s = -1;
         if (a.avro.known == 1) st_s = avro_walk_schema_a<XS, ZM>(stage, cb, ce, a.avro.skip_prefix, xrow);
-        else if (a.avro.known == 2) st_s = avro_walk_schema_b<XS>(stage, cb, ce, a.avro.skip_prefix, xrow, &lab_s);
+        else if (a.avro.known == 2) st_s = avro_walk_schema_b<XS, ZM>(stage, cb, ce, a.avro.skip_prefix, xrow, &lab_s);
         if (st_s < 0) {
           lab_s = 2;
           st_s = avro_decode_record(stage, cb, ce, a.avro, xrow, XS, &lab_s);
@@ -946,9 +952,8 @@ template <int D, bool FT, int FMT>
 __global__ void __launch_bounds__(TCS_ROWS, 512 / TcShape<D>::TMEM_COLS > 5 ? 5 : 512 / TcShape<D>::TMEM_COLS) decode_kernel_tc(const __grid_constant__ DecodeArgs<D> a) {
   decode_body<D, 1, FT, FMT, 1, true>(a);
 }
-// the reference's normalisation table forces features 0, 2, 4 and 5 to zero (cardata-v1.py:72, :78, :84, :87): the instantiation
-// with that zero set compiled in (see ae_forward_rows), launched when the caller's table has exactly this zero set
-constexpr unsigned REF_ZERO_MASK = 0x35u;
+// the instantiation with the reference table's zero set compiled in (REF_ZERO_MASK, ae_math.cuh), launched when the caller's table
+// has exactly that zero set
 template <int D, bool FT, int FMT>
 __global__ void __launch_bounds__(DEC_NT, FMT == FMT_AVRO ? 4 : 3) decode_kernel_zs(const __grid_constant__ DecodeArgs<D> a) {
   decode_body<D, 1, FT, FMT, 1, false, false, REF_ZERO_MASK>(a);
@@ -1217,16 +1222,8 @@ static int launch_decode_fmt(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stre
   }
   if constexpr (MODE == 1 && D == 18 && FT) {
     // the table's zero set is the reference's and the layer-1 rows it skips are finite (+0 · w must be exactly nothing)
-    if (ctx->knobs.zero_skip != 0 && args.has_norm) {
-      unsigned zm = 0;
-      bool finite = true;
-      for (int i = 0; i < D; ++i) {
-        if (args.nm.kind[i] != B2_NORM_ZERO) continue;
-        zm |= 1u << i;
-        for (int j = 0; j < AE_H1; ++j) finite = finite && std::isfinite(args.w.k1[i][j]);
-      }
-      if (zm == REF_ZERO_MASK && finite) return launch_decode_r<D, MODE, FT, FMT, 1, 1, 2>(ctx, args, stream);
-    }
+    if (ctx->knobs.zero_skip != 0 && args.has_norm && norm_zero_set<D>(args.nm, args.w) == REF_ZERO_MASK)
+      return launch_decode_r<D, MODE, FT, FMT, 1, 1, 2>(ctx, args, stream);
   }
   return launch_decode_r<D, MODE, FT, FMT, 1, 1>(ctx, args, stream);
 }

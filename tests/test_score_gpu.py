@@ -102,6 +102,35 @@ def test_score18_with_fused_normalisation(cuda_device):
     assert flag.sum() > 0
 
 
+def test_score18_zero_set_instantiation_is_bit_identical(cuda_device):
+    """b2_ae_score with the reference's table runs the kernel that leaves out the four features normalize_fn forces to 0.0
+    (cardata-v1.py:72-87); context option zero_skip = 0 runs the generic one.  Same bits, also with NaN / inf in those columns,
+    and the generic kernel is taken for a table with another zero set."""
+    m = _model18()
+    kind, lo, rng = bs.schemas.norm_arrays()
+    m.set_normalization(kind, lo, rng)
+    x = bs.synth.sensor_rows(70_003, seed=12)
+    x[::7, 0] = np.nan
+    x[::11, 2] = np.inf
+    x[::13, 4] = -np.inf
+    x[::17, 5] = 3e38
+    res = {}
+    try:
+        for zs in (1, 0):
+            bs.keras.set_option("zero_skip", zs)
+            mse, flag = m.score(x)
+            res[zs] = (np.asarray(mse, dtype=np.float32).view(np.uint32).copy(), np.asarray(flag).copy())
+    finally:
+        bs.keras.set_option("zero_skip", 1)
+    np.testing.assert_array_equal(res[1][0], res[0][0])
+    np.testing.assert_array_equal(res[1][1], res[0][1])
+    assert np.isfinite(res[1][0].view(np.float32)).all()
+    w = m.get_flat_weights()
+    xn32 = orc.normalize(np.nan_to_num(x, nan=0.0, posinf=0.0, neginf=0.0), kind, lo, rng, dtype=np.float32)
+    ref = orc.score(xn32.astype(np.float64), w, [18, 14, 7, 7, 18], ACTS, dtype=np.float64)[0]
+    _check(res[1][0].view(np.float32), res[1][1], ref)
+
+
 def test_predict_matches_oracle_and_callbacks(cuda_device, ae30, golden_dir):
     m = _model30(ae30, golden_dir)
     x = bs.synth.credit_rows(3000 + 13, seed=5)
