@@ -35,6 +35,7 @@ struct CsvP {
   uint8_t kind[B2_MAX_FIELDS];       // 0 skip, 1 float, 2 string
   uint8_t has_default[B2_MAX_FIELDS];
   uint8_t col[B2_MAX_FIELDS];        // output column (float) or span slot (string) of field i
+  uint8_t nov[B2_MAX_FIELDS];        // float field whose value is not needed (the normalisation forces its column to zero): only validated
   float dflt[B2_MAX_FIELDS];
 };
 struct AvroRun {
@@ -205,7 +206,14 @@ __device__ __forceinline__ int csv_walk(const uint8_t* __restrict__ stage, int b
     int rem = e - pos;
     if (rem < 0) return -1;  // the record ended with the previous field
     const int kind = c.kind[f];
-    if (kind == 1) {
+    if (kind == 1 && c.nov[f]) {
+      // the same token grammar, value unused: the digit folding and the rounding drop out of this copy of the parser
+      const uint32_t* wp = reinterpret_cast<const uint32_t*>(stage + (pos & ~3));
+      uint32_t unused = 0;
+      const int r = b2_csv_num16(wp[0], wp[1], wp[2], wp[3], wp[4], (pos & 3) * 8, rem, delim, &unused);
+      if (r < 0 || (r == 0 && !c.has_default[f])) return -1;
+      pos += r + 1;
+    } else if (kind == 1) {
       const uint32_t* wp = reinterpret_cast<const uint32_t*>(stage + (pos & ~3));
       uint32_t bits = 0;
       const int r = b2_csv_num16(wp[0], wp[1], wp[2], wp[3], wp[4], (pos & 3) * 8, rem, delim, &bits);
@@ -1392,6 +1400,11 @@ static int decode_score_spec(b2_ae* ae, const uint8_t* bytes, const int32_t* off
   args.label = label;
   ae_pack_weights<D>(ae->h_w.data(), args.w);
   args.has_norm = norm_fill<D>(norm, args.nm);
+  if (csv && args.has_norm && ae->ctx->knobs.zero_skip != 0) {
+    // CSV float fields whose column the table forces to zero: the field walk checks the token and skips its conversion
+    for (int f = 0; f < args.csv.n_fields; ++f)
+      if (args.csv.kind[f] == 1 && args.nm.kind[args.csv.col[f]] == B2_NORM_ZERO) args.csv.nov[f] = 1;
+  }
   args.threshold = threshold;
   args.mse = mse;
   args.flag = flag;

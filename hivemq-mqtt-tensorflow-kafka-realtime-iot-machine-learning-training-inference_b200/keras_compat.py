@@ -47,7 +47,7 @@ def _stream_ptr() -> int:
 
 def set_option(name: str, value: int, device: Optional[int] = None) -> None:
     """Tuning / debugging switch of the device's context (``b2_ctx_set_option``): "fast_tanh", "score_cfg", "no_bulk",
-    "force_generic", "avro_generic", "lstm_tc", "score_tc".  The environment (B2_FAST_TANH, ...) only sets the defaults,
+    "force_generic", "avro_generic", "lstm_tc", "score_tc", "tc_ctas", "decode_r2", "decode_tc", "decode_mma", "zero_skip".  The environment (B2_FAST_TANH, ...) only sets the defaults,
     once, when the context is created."""
     _ffi.check(_ffi.lib().b2_ctx_set_option(get_ctx(device), name.encode(), int(value)), "b2_ctx_set_option")
 

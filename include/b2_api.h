@@ -60,7 +60,10 @@ int  b2_ctx_sm_count(const b2_ctx* ctx);
  * come, e.g. total payload bytes / N (0 = unknown, the default: estimated from the schema).  Each warp stages 32 records at a
  * time; a good hint makes a 32-record chunk fit its stage in one piece and lets more CTAs share an SM. */
 int  b2_ctx_set_record_bytes_hint(b2_ctx* ctx, int avg_record_bytes);
-/* Tuning / debugging switches: "fast_tanh", "score_cfg", "no_bulk", "force_generic", "avro_generic", "lstm_tc", "score_tc".
+/* Tuning / debugging switches: "fast_tanh", "score_cfg", "no_bulk", "force_generic", "avro_generic", "lstm_tc", "score_tc",
+ * "tc_ctas", "decode_r2", "decode_tc", "decode_mma" (score phase of the fused kernel as warp-level TF32 MMAs) and "zero_skip"
+ * (1, the default: a normalisation table whose zero set is the reference's — features 0, 2, 4, 5, cardata-v1.py:72-87 — runs the
+ * kernels compiled for that set; same bits as 0).
  * Their defaults come from the environment (B2_FAST_TANH, …) ONCE, when the context is created; no launch reads the
  * environment afterwards. */
 int  b2_ctx_set_option(b2_ctx* ctx, const char* name, int value);

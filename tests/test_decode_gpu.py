@@ -466,3 +466,35 @@ def test_zero_set_instantiation_is_bit_identical(cuda_device, fmt):
     finally:
         bs.keras.set_option("zero_skip", 1)
     np.testing.assert_array_equal(_bits(a), _bits(b))
+
+
+def test_csv_zeroed_columns_are_still_validated(cuda_device):
+    """A CSV float field whose column the normalisation forces to zero is not converted, but a token tf.io.decode_csv would refuse
+    there must still mark the record: same statuses (and scores) with zero_skip on and off."""
+    x = synth.sensor_rows(200, seed=5)
+    data, offs = synth.csv_batch(x, seed=5)
+    lines = [bytes(data[offs[i]:offs[i + 1]]).decode() for i in range(len(x))]
+    bad_tokens = ["abc", "", "1e", "--1", "1.2.3", "0x10", " 1", "1e400", "-", "+", "1,5"]
+    want_bad = set()
+    for k, tok in enumerate(bad_tokens * 4):
+        row, col = 3 * k + 1, (0, 2, 4, 5)[k % 4]
+        f = lines[row].split(",")
+        f[2 + col] = tok
+        lines[row] = ",".join(f)
+        if tok in ("abc", "1e", "--1", "1.2.3", "-", "+"):  # not a number under any reading
+            want_bad.add(row)
+    rb = dec.RecordBatch.from_messages(lines)
+    m = _model18()
+    res = {}
+    try:
+        for zs in (1, 0):
+            bs.keras.set_option("zero_skip", zs)
+            mse, flag, _, status = dec.decode_score(m, rb, csv_kinds=SENSOR_KINDS)
+            res[zs] = (_bits(mse.cpu().numpy()), flag.cpu().numpy(), status.cpu().numpy())
+    finally:
+        bs.keras.set_option("zero_skip", 1)
+    for a, b in zip(res[1], res[0]):
+        np.testing.assert_array_equal(a, b)
+    got_bad = set(np.nonzero(res[1][2])[0].tolist())
+    assert want_bad <= got_bad, [lines[i] for i in sorted(want_bad - got_bad)][:4]
+    assert all(i % 3 == 1 for i in got_bad)  # only rows that were touched

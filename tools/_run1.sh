@@ -1,5 +1,6 @@
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_score_gpu.py tests/test_decode_gpu.py tests/test_normalize_gpu.py tests/test_train_gpu.py -q -m gpu -x 2>&1 | tail -4
-timeout 900 python tools/mma_probe.py avro_b 1 > gpurun_out/mma_probe7.txt 2>&1; echo "probe rc $?"
-grep "decode_mma=0.*records/s" gpurun_out/mma_probe7.txt
-timeout 600 python bench.py --workload score18 --steps 5 --warmup 3 --no-cpu-baseline --no-e2e --also none 2>/dev/null | python -c "import json,sys; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('score18', d['value'], d['roofline']['frac'])"
+timeout 1200 python -m pytest tests -m gpu -x -q 2>&1 | tail -4
+timeout 600 python tools/prof_all.py > gpurun_out/prof_all_plain.log 2>&1; echo "prof_all rc $?"; tail -2 gpurun_out/prof_all_plain.log
+timeout 1500 ncu --set full --clock-control none -o gpurun_out/all_r2b -f python tools/prof_all.py > gpurun_out/prof_all_ncu.log 2>&1; echo "ncu rc $?"
+ncu -i gpurun_out/all_r2b.ncu-rep --page raw --csv > gpurun_out/all_r2b_raw.csv 2>/dev/null; ls -la gpurun_out/all_r2b*; 
+sz=$(stat -c %s gpurun_out/all_r2b.ncu-rep); if [ "$sz" -gt 40000000 ]; then rm gpurun_out/all_r2b.ncu-rep; fi

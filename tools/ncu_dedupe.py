@@ -17,7 +17,7 @@ def main(src, dst):
         grid = e.get("launch__grid_size", ["", ""])[0]
         key = (e["kernel"], grid)
         name = e["kernel"]
-        if name.startswith("void decode_kernel<18, 1, 1, 1>") and grid != "1":
+        if (name.startswith("void decode_kernel<18, 1, 1, 1>") or name.startswith("void decode_kernel_zs<18, 1, 1>")) and grid != "1":
             avro += 1
             key = (name, grid, avro)
             e["note"] = "Avro-A, 2^20 records" if avro == 1 else "Avro-B, 2^20 records"

@@ -9,6 +9,10 @@ RECORDS = {  # kernel-name fragment → (key, records of that launch)
     "decode_kernel<18, 1, 1, 0>": ("decode_score_csv", 1 << 20),
     "decode_kernel<18, 1, 1, 1>": ("decode_score_avro_a", 1 << 20),   # first Avro launch = avro_a (prof_all order)
     "decode_kernel<18, 1, 1, 2>": ("decode_score_json", 1 << 19),
+    # the instantiation for the reference table's zero set (the default with that table)
+    "decode_kernel_zs<18, 1, 0>": ("decode_score_csv", 1 << 20),
+    "decode_kernel_zs<18, 1, 1>": ("decode_score_avro_a", 1 << 20),
+    "decode_kernel_zs<18, 1, 2>": ("decode_score_json", 1 << 19),
 }
 instr, traffic, seen = {}, {}, {}
 def num(d, k):
