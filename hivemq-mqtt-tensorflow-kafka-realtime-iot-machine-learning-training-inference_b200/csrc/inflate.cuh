@@ -21,7 +21,7 @@
 #define B2_INFL_TRUNCATED (-1)   /* input ends inside a token / block */
 #define B2_INFL_CORRUPT   (-2)   /* impossible offset, bad header, bad Huffman code, length mismatch */
 #define B2_INFL_OVERFLOW  (-3)   /* output does not fit `cap` */
-#define B2_INFL_UNSUPPORTED (-4) /* a feature this decoder does not implement (LZ4 dictionary / linked-block options are fine; zstd is not here) */
+#define B2_INFL_UNSUPPORTED (-4) /* a feature this decoder does not implement (a zstd dictionary) */
 
 // ---- output cursor shared by the three decoders -------------------------------------------------------------------------
 struct B2Out {
@@ -385,10 +385,525 @@ B2_HD long long b2_gzip(const uint8_t* s, long long n, uint8_t* dst, long long c
   return o.n;
 }
 
-// codec = attributes & 7 of the batch header: 1 gzip, 2 snappy, 3 lz4, 4 zstd (not implemented)
+// ---- Zstandard (RFC 8878) -------------------------------------------------------------------------------------------------
+// Frames of raw / RLE / compressed blocks; a compressed block = literals section (raw, RLE or Huffman-coded, 1 or 4 streams) +
+// sequences section (literal length / offset / match length codes, three interleaved FSE states over one backward bit stream).
+// No dictionaries (Kafka's producers use none).  Everything a block needs lives in B2Zstd (≈ 10 KB: three FSE tables, one Huffman
+// table) — on the GPU that is the thread's local memory; the literals are decoded lazily, as the sequences consume them, so no
+// literal buffer exists.  The content checksum (xxHash64) is not verified: the Kafka batch's CRC-32C covers the compressed bytes.
+struct B2ZEntry {
+  uint16_t base;  // FSE: new state before the extra bits
+  uint8_t sym, nb;
+};
+struct B2ZFse {
+  B2ZEntry e[512];
+  int log;
+};
+// forward bit reader (LSB first) for the FSE table descriptions
+struct B2ZFwd {
+  const uint8_t* p;
+  long long n, bit;
+};
+B2_HD uint32_t b2z_peek_fwd(const B2ZFwd& r, int k) {  // k ≤ 24; bits beyond the end read as zero
+  uint32_t v = 0;
+  const long long by = r.bit >> 3;
+  for (int i = 0; i < 4; ++i)
+    if (by + i < r.n) v |= (uint32_t)r.p[by + i] << (8 * i);
+  return (v >> (r.bit & 7)) & ((1u << k) - 1u);
+}
+// backward bit stream: the last byte carries a 1 marker above the payload; bits are taken from the top down
+struct B2ZBack {
+  const uint8_t* p;
+  long long bitpos;  // bits not yet consumed; negative once more was asked for than there is
+};
+B2_HD int b2z_highbit(uint32_t v) {
+  int h = 0;
+  while (v >>= 1) ++h;
+  return h;
+}
+B2_HD bool b2z_back_init(B2ZBack& b, const uint8_t* p, long long n) {
+  if (n < 1 || p[n - 1] == 0) return false;
+  b.p = p;
+  b.bitpos = 8 * (n - 1) + b2z_highbit(p[n - 1]);
+  return true;
+}
+// bits [pos, pos + k) of the stream as a little-endian number, k ≤ 32; positions below zero read as zero
+B2_HD uint32_t b2z_bits_at(const uint8_t* p, long long pos, int k) {
+  int up = 0;  // bits of the request that lie below position zero
+  if (pos < 0) {
+    if (pos + k <= 0) return 0;
+    up = (int)(-pos);
+    k -= up;
+    pos = 0;
+  }
+  if (k == 0) return 0;
+  uint64_t v = 0;
+  const long long by = pos >> 3;
+  const int nbytes = (int)(((pos & 7) + k + 7) >> 3);
+  for (int i = 0; i < nbytes; ++i) v |= (uint64_t)p[by + i] << (8 * i);
+  return (uint32_t)((v >> (pos & 7)) & (k == 32 ? 0xFFFFFFFFull : ((1ull << k) - 1ull))) << up;
+}
+B2_HD uint32_t b2z_read_back(B2ZBack& b, int k) {
+  b.bitpos -= k;
+  return b2z_bits_at(b.p, b.bitpos, k);
+}
+
+// normalised counts of an FSE table description → *consumed bytes; returns the accuracy log or a negative error
+B2_HD int b2z_read_ncount(const uint8_t* s, long long n, int max_log, int max_sym, short* norm, int* n_sym, long long* consumed) {
+  B2ZFwd r{s, n, 0};
+  const int log = (int)b2z_peek_fwd(r, 4) + 5;
+  r.bit += 4;
+  if (log > max_log) return B2_INFL_CORRUPT;
+  int remaining = (1 << log) + 1, threshold = 1 << log, nb = log + 1, sym = 0;
+  bool prev0 = false;
+  while (remaining > 1 && sym <= max_sym) {
+    if (prev0) {
+      int n0 = sym;
+      for (;;) {
+        const uint32_t two = b2z_peek_fwd(r, 2);
+        r.bit += 2;
+        n0 += (int)two;
+        if (two != 3) break;
+        if (r.bit > 8 * n) return B2_INFL_TRUNCATED;
+      }
+      if (n0 > max_sym + 1) return B2_INFL_CORRUPT;
+      while (sym < n0) norm[sym++] = 0;
+      if (sym > max_sym) break;
+    }
+    const int mx = (2 * threshold - 1) - remaining;
+    const uint32_t bs = b2z_peek_fwd(r, nb);
+    int count;
+    if ((int)(bs & (uint32_t)(threshold - 1)) < mx) {
+      count = (int)(bs & (uint32_t)(threshold - 1));
+      r.bit += nb - 1;
+    } else {
+      count = (int)(bs & (uint32_t)(2 * threshold - 1));
+      if (count >= threshold) count -= mx;
+      r.bit += nb;
+    }
+    --count;  // -1 = "less than one": a single cell at the top of the table
+    remaining -= count < 0 ? -count : count;
+    norm[sym++] = (short)count;
+    prev0 = count == 0;
+    while (remaining < threshold) {
+      --nb;
+      threshold >>= 1;
+    }
+    if (r.bit > 8 * n) return B2_INFL_TRUNCATED;
+  }
+  if (remaining != 1 || sym > max_sym + 1) return B2_INFL_CORRUPT;
+  *n_sym = sym;
+  *consumed = (r.bit + 7) >> 3;
+  return log;
+}
+B2_HD int b2z_build_fse(B2ZFse& t, const short* norm, int n_sym, int log) {
+  const int size = 1 << log;
+  uint16_t next[64];
+  int high = size - 1;
+  for (int s = 0; s < n_sym; ++s) {
+    if (norm[s] == -1) {
+      t.e[high--].sym = (uint8_t)s;
+      next[s] = 1;
+    } else {
+      next[s] = (uint16_t)norm[s];
+    }
+  }
+  const int step = (size >> 1) + (size >> 3) + 3, mask = size - 1;
+  int pos = 0;
+  for (int s = 0; s < n_sym; ++s)
+    for (int i = 0; i < norm[s]; ++i) {
+      t.e[pos].sym = (uint8_t)s;
+      do pos = (pos + step) & mask;
+      while (pos > high);
+    }
+  if (pos != 0) return B2_INFL_CORRUPT;
+  for (int u = 0; u < size; ++u) {
+    const int sy = t.e[u].sym;
+    const uint32_t ns = next[sy]++;
+    const int nb = log - b2z_highbit(ns);
+    t.e[u].nb = (uint8_t)nb;
+    t.e[u].base = (uint16_t)((ns << nb) - (uint32_t)size);
+  }
+  t.log = log;
+  return 0;
+}
+B2_HD void b2z_rle_fse(B2ZFse& t, int sym) {
+  t.e[0].sym = (uint8_t)sym;
+  t.e[0].nb = 0;
+  t.e[0].base = 0;
+  t.log = 0;
+}
+
+struct B2ZHuf {
+  uint8_t sym[2048], nb[2048];
+  int log;  // 0 = no table yet
+};
+// Huffman tree description → table; returns bytes consumed or a negative error
+B2_HD long long b2z_read_huf(B2ZHuf& h, const uint8_t* s, long long n) {
+  if (n < 1) return B2_INFL_TRUNCATED;
+  uint8_t w[256];
+  int nw = 0;
+  long long used;
+  const int hb = s[0];
+  if (hb >= 128) {  // weights stored directly, 4 bits each
+    nw = hb - 127;
+    used = 1 + (nw + 1) / 2;
+    if (used > n) return B2_INFL_TRUNCATED;
+    for (int i = 0; i < nw; ++i) w[i] = (i & 1) ? (s[1 + i / 2] & 15) : (s[1 + i / 2] >> 4);
+  } else {  // FSE-compressed weights: two interleaved states over a backward stream
+    used = 1 + hb;
+    if (hb < 2 || used > n) return hb < 2 ? B2_INFL_CORRUPT : B2_INFL_TRUNCATED;
+    short norm[16];
+    int ns = 0;
+    long long c = 0;
+    const int log = b2z_read_ncount(s + 1, hb, 6, 12, norm, &ns, &c);
+    if (log < 0) return log;
+    B2ZFse t;
+    if (b2z_build_fse(t, norm, ns, log) < 0) return B2_INFL_CORRUPT;
+    B2ZBack b;
+    if (c >= hb || !b2z_back_init(b, s + 1 + c, hb - c)) return B2_INFL_CORRUPT;
+    uint32_t s1 = b2z_read_back(b, log), s2 = b2z_read_back(b, log);
+    if (b.bitpos < 0) return B2_INFL_CORRUPT;
+    for (;;) {
+      if (nw > 253) return B2_INFL_CORRUPT;
+      w[nw++] = t.e[s1].sym;
+      s1 = t.e[s1].base + b2z_read_back(b, t.e[s1].nb);
+      if (b.bitpos < 0) {
+        w[nw++] = t.e[s2].sym;
+        break;
+      }
+      w[nw++] = t.e[s2].sym;
+      s2 = t.e[s2].base + b2z_read_back(b, t.e[s2].nb);
+      if (b.bitpos < 0) {
+        w[nw++] = t.e[s1].sym;
+        break;
+      }
+    }
+  }
+  // the last weight completes the sum of 2^(w-1) to a power of two
+  uint32_t sum = 0;
+  for (int i = 0; i < nw; ++i) {
+    if (w[i] > 11) return B2_INFL_CORRUPT;
+    if (w[i]) sum += 1u << (w[i] - 1);
+  }
+  if (sum == 0) return B2_INFL_CORRUPT;
+  const int log = b2z_highbit(sum) + 1;
+  if (log > 11) return B2_INFL_CORRUPT;
+  const uint32_t rest = (1u << log) - sum;
+  if (rest == 0 || (rest & (rest - 1)) != 0) return B2_INFL_CORRUPT;
+  w[nw++] = (uint8_t)(b2z_highbit(rest) + 1);
+  // cells in order of rising weight (longest codes first), symbols of one weight in rising order
+  int pos = 0;
+  for (int wt = 1; wt <= log; ++wt)
+    for (int sy = 0; sy < nw; ++sy)
+      if (w[sy] == wt) {
+        const int cells = 1 << (wt - 1);
+        for (int i = 0; i < cells; ++i) {
+          h.sym[pos + i] = (uint8_t)sy;
+          h.nb[pos + i] = (uint8_t)(log + 1 - wt);
+        }
+        pos += cells;
+      }
+  if (pos != (1 << log)) return B2_INFL_CORRUPT;
+  h.log = log;
+  return used;
+}
+
+// the literals of one block, handed out in order
+struct B2ZLit {
+  int type;             // 0 raw, 1 RLE, 2 Huffman
+  const uint8_t* raw;   // raw: next byte; RLE: the byte
+  long long left;       // literals not yet handed out
+  // Huffman: up to four streams, consumed one after the other
+  B2ZBack st[4];
+  long long st_left[4];
+  int cur, n_st;
+};
+B2_HD int b2z_lit_take(B2ZLit& l, const B2ZHuf& h, B2Out& o, long long len) {
+  if (len > l.left) return B2_INFL_CORRUPT;
+  l.left -= len;
+  if (o.dst && o.n + len > o.cap) return B2_INFL_OVERFLOW;
+  if (l.type == 0) {
+    if (o.dst)
+      for (long long i = 0; i < len; ++i) o.dst[o.n + i] = l.raw[i];
+    l.raw += len;
+  } else if (l.type == 1) {
+    if (o.dst)
+      for (long long i = 0; i < len; ++i) o.dst[o.n + i] = l.raw[0];
+  } else {
+    for (long long i = 0; i < len; ++i) {
+      while (l.cur < l.n_st && l.st_left[l.cur] == 0) {
+        if (l.st[l.cur].bitpos != 0) return B2_INFL_CORRUPT;  // a stream must end exactly on its first bit
+        ++l.cur;
+      }
+      if (l.cur >= l.n_st) return B2_INFL_CORRUPT;
+      B2ZBack& b = l.st[l.cur];
+      const uint32_t idx = b2z_bits_at(b.p, b.bitpos - h.log, h.log);
+      b.bitpos -= h.nb[idx];
+      if (b.bitpos < 0) return B2_INFL_CORRUPT;
+      --l.st_left[l.cur];
+      if (o.dst) o.dst[o.n + i] = h.sym[idx];
+    }
+  }
+  o.n += len;
+  return 0;
+}
+
+struct B2Zstd {
+  B2ZFse ll, of, ml;
+  B2ZHuf huf;
+  bool have_ll, have_of, have_ml;
+  uint32_t rep[3];
+};
+// one table of the sequences section: mode 0 predefined, 1 RLE, 2 described, 3 the previous block's
+B2_HD long long b2z_seq_table(B2ZFse& t, bool& have, int mode, const uint8_t* s, long long n, int max_log, int max_sym, const short* dflt,
+                              int dflt_n, int dflt_log) {
+  if (mode == 0) {
+    if (b2z_build_fse(t, dflt, dflt_n, dflt_log) < 0) return B2_INFL_CORRUPT;
+    have = true;
+    return 0;
+  }
+  if (mode == 1) {
+    if (n < 1) return B2_INFL_TRUNCATED;
+    if (s[0] > max_sym) return B2_INFL_CORRUPT;
+    b2z_rle_fse(t, s[0]);
+    have = true;
+    return 1;
+  }
+  if (mode == 2) {
+    short norm[64];
+    int ns = 0;
+    long long c = 0;
+    const int log = b2z_read_ncount(s, n, max_log, max_sym, norm, &ns, &c);
+    if (log < 0) return log;
+    if (b2z_build_fse(t, norm, ns, log) < 0) return B2_INFL_CORRUPT;
+    have = true;
+    return c;
+  }
+  return have ? 0 : B2_INFL_CORRUPT;
+}
+
+B2_HD int b2z_block(B2Zstd& z, const uint8_t* s, long long n, B2Out& o, long long base) {
+  // ---- literals section
+  if (n < 1) return B2_INFL_TRUNCATED;
+  B2ZLit lit;
+  lit.cur = 0, lit.n_st = 0, lit.raw = s;
+  const int ltype = s[0] & 3, sf = (s[0] >> 2) & 3;
+  long long p = 0, regen = 0;
+  if (ltype < 2) {
+    if (sf == 0 || sf == 2) regen = s[0] >> 3, p = 1;
+    else if (sf == 1) {
+      if (n < 2) return B2_INFL_TRUNCATED;
+      regen = (s[0] >> 4) | ((long long)s[1] << 4), p = 2;
+    } else {
+      if (n < 3) return B2_INFL_TRUNCATED;
+      regen = (s[0] >> 4) | ((long long)s[1] << 4) | ((long long)s[2] << 12), p = 3;
+    }
+    lit.type = ltype;
+    lit.raw = s + p;
+    const long long stored = ltype == 0 ? regen : 1;
+    if (p + stored > n) return B2_INFL_TRUNCATED;
+    p += stored;
+  } else {
+    long long comp;
+    const int hl = sf == 3 ? 5 : (sf == 2 ? 4 : 3);
+    if (n < hl) return B2_INFL_TRUNCATED;
+    unsigned long long hdr = 0;
+    for (int i = 0; i < hl; ++i) hdr |= (unsigned long long)s[i] << (8 * i);
+    if (sf < 2) regen = (hdr >> 4) & 0x3FF, comp = (hdr >> 14) & 0x3FF;
+    else if (sf == 2) regen = (hdr >> 4) & 0x3FFF, comp = (hdr >> 18) & 0x3FFF;
+    else regen = (hdr >> 4) & 0x3FFFF, comp = (hdr >> 22) & 0x3FFFF;
+    p = hl;
+    if (p + comp > n) return B2_INFL_TRUNCATED;
+    const uint8_t* c = s + p;
+    long long cn = comp;
+    if (ltype == 2) {
+      const long long u = b2z_read_huf(z.huf, c, cn);
+      if (u < 0) return (int)u;
+      c += u, cn -= u;
+    } else if (z.huf.log == 0) {
+      return B2_INFL_CORRUPT;  // "treeless" with no tree from an earlier block
+    }
+    lit.type = 2;
+    if (sf == 0) {
+      lit.n_st = 1;
+      lit.st_left[0] = regen;
+      if (!b2z_back_init(lit.st[0], c, cn)) return B2_INFL_CORRUPT;
+    } else {
+      if (cn < 6) return B2_INFL_CORRUPT;
+      const long long z1 = c[0] | (c[1] << 8), z2 = c[2] | (c[3] << 8), z3 = c[4] | (c[5] << 8), z4 = cn - 6 - z1 - z2 - z3;
+      if (z4 < 1) return B2_INFL_CORRUPT;
+      const long long per = (regen + 3) / 4;
+      if (regen < 3 * per) return B2_INFL_CORRUPT;
+      const uint8_t* q = c + 6;
+      const long long zs[4] = {z1, z2, z3, z4};
+      lit.n_st = 4;
+      for (int i = 0; i < 4; ++i) {
+        lit.st_left[i] = i < 3 ? per : regen - 3 * per;
+        if (!b2z_back_init(lit.st[i], q, zs[i])) return B2_INFL_CORRUPT;
+        q += zs[i];
+      }
+    }
+    p += comp;
+  }
+  lit.left = regen;
+  // ---- sequences section
+  if (p >= n) return B2_INFL_TRUNCATED;
+  long long nseq = s[p++];
+  if (nseq >= 128) {
+    if (nseq == 255) {
+      if (p + 2 > n) return B2_INFL_TRUNCATED;
+      nseq = s[p] + ((long long)s[p + 1] << 8) + 0x7F00;
+      p += 2;
+    } else {
+      if (p + 1 > n) return B2_INFL_TRUNCATED;
+      nseq = ((nseq - 128) << 8) + s[p];
+      p += 1;
+    }
+  }
+  if (nseq > 0) {
+    if (p >= n) return B2_INFL_TRUNCATED;
+    const int modes = s[p++];
+    if (modes & 3) return B2_INFL_CORRUPT;
+    const short ll_d[36] = {4, 3, 2, 2, 2, 2, 2, 2, 2, 2, 2, 2, 2, 1, 1, 1, 2, 2, 2, 2, 2, 2, 2, 2, 2, 3, 2, 1, 1, 1, 1, 1, -1, -1, -1, -1};
+    const short of_d[29] = {1, 1, 1, 1, 1, 1, 2, 2, 2, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, -1, -1, -1, -1, -1};
+    const short ml_d[53] = {1, 4, 3, 2, 2, 2, 2, 2, 2, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1,
+                            1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, -1, -1, -1, -1, -1, -1, -1};
+    long long u = b2z_seq_table(z.ll, z.have_ll, (modes >> 6) & 3, s + p, n - p, 9, 35, ll_d, 36, 6);
+    if (u < 0) return (int)u;
+    p += u;
+    u = b2z_seq_table(z.of, z.have_of, (modes >> 4) & 3, s + p, n - p, 8, 31, of_d, 29, 5);
+    if (u < 0) return (int)u;
+    p += u;
+    u = b2z_seq_table(z.ml, z.have_ml, (modes >> 2) & 3, s + p, n - p, 9, 52, ml_d, 53, 6);
+    if (u < 0) return (int)u;
+    p += u;
+    B2ZBack b;
+    if (p >= n || !b2z_back_init(b, s + p, n - p)) return B2_INFL_CORRUPT;
+    uint32_t sl = b2z_read_back(b, z.ll.log), so = b2z_read_back(b, z.of.log), sm = b2z_read_back(b, z.ml.log);
+    if (b.bitpos < 0) return B2_INFL_CORRUPT;
+    const uint32_t ll_base[36] = {0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16, 18, 20, 22, 24, 28, 32, 40, 48, 64, 128, 256, 512,
+                                  1024, 2048, 4096, 8192, 16384, 32768, 65536};
+    const uint8_t ll_bits[36] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 2, 2, 3, 3, 4, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16};
+    const uint32_t ml_base[53] = {3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16, 17, 18, 19, 20, 21, 22, 23, 24, 25, 26, 27, 28, 29, 30, 31, 32, 33,
+                                  34, 35, 37, 39, 41, 43, 47, 51, 59, 67, 83, 99, 131, 259, 515, 1027, 2051, 4099, 8195, 16387, 32771, 65539};
+    const uint8_t ml_bits[53] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0,
+                                 0, 0, 0, 0, 0, 1, 1, 1, 1, 2, 2, 3, 3, 4, 4, 5, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16};
+    for (long long q = 0; q < nseq; ++q) {
+      const int oc = z.of.e[so].sym, mc = z.ml.e[sm].sym, lc = z.ll.e[sl].sym;
+      if (oc > 31 || mc > 52 || lc > 35) return B2_INFL_CORRUPT;
+      const uint32_t ov = (1u << oc) + b2z_read_back(b, oc);
+      const uint32_t mlen = ml_base[mc] + b2z_read_back(b, ml_bits[mc]);
+      const uint32_t llen = ll_base[lc] + b2z_read_back(b, ll_bits[lc]);
+      if (q + 1 < nseq) {  // the states are refreshed in the order literal length, match length, offset
+        sl = z.ll.e[sl].base + b2z_read_back(b, z.ll.e[sl].nb);
+        sm = z.ml.e[sm].base + b2z_read_back(b, z.ml.e[sm].nb);
+        so = z.of.e[so].base + b2z_read_back(b, z.of.e[so].nb);
+      }
+      if (b.bitpos < 0) return B2_INFL_CORRUPT;
+      uint32_t off;
+      if (ov > 3) {
+        off = ov - 3;
+        z.rep[2] = z.rep[1], z.rep[1] = z.rep[0], z.rep[0] = off;
+      } else {
+        const uint32_t idx = ov - 1 + (llen == 0 ? 1u : 0u);  // 0..3: repeat offsets 1..3, or (idx 3) the first one minus one
+        if (idx == 0) {
+          off = z.rep[0];
+        } else {
+          off = idx == 3 ? z.rep[0] - 1 : z.rep[idx];
+          if (off == 0) return B2_INFL_CORRUPT;
+          if (idx != 1) z.rep[2] = z.rep[1];
+          z.rep[1] = z.rep[0];
+          z.rep[0] = off;
+        }
+      }
+      int rc = b2z_lit_take(lit, z.huf, o, llen);
+      if (rc) return rc;
+      rc = b2_out_match(o, off, mlen, base);
+      if (rc) return rc;
+    }
+    if (b.bitpos != 0) return B2_INFL_CORRUPT;
+  } else if (p != n) {
+    return B2_INFL_CORRUPT;
+  }
+  return b2z_lit_take(lit, z.huf, o, lit.left);  // what the sequences left over
+}
+
+// a concatenation of frames (and skippable frames); returns the regenerated size or a negative error
+B2_HD long long b2_zstd(const uint8_t* s, long long n, uint8_t* dst, long long cap) {
+  B2Out o{dst, cap, 0};
+  B2Zstd z;
+  long long p = 0;
+  if (n < 4) return B2_INFL_TRUNCATED;
+  while (p < n) {
+    if (p + 4 > n) return B2_INFL_TRUNCATED;
+    const uint32_t magic = s[p] | (s[p + 1] << 8) | (s[p + 2] << 16) | ((uint32_t)s[p + 3] << 24);
+    p += 4;
+    if ((magic & 0xFFFFFFF0u) == 0x184D2A50u) {  // skippable frame
+      if (p + 4 > n) return B2_INFL_TRUNCATED;
+      const long long sz = s[p] | (s[p + 1] << 8) | (s[p + 2] << 16) | ((long long)s[p + 3] << 24);
+      p += 4 + sz;
+      if (p > n) return B2_INFL_TRUNCATED;
+      continue;
+    }
+    if (magic != 0xFD2FB528u) return B2_INFL_CORRUPT;
+    if (p >= n) return B2_INFL_TRUNCATED;
+    const int fhd = s[p++];
+    if (fhd & 0x08) return B2_INFL_CORRUPT;  // reserved bit
+    const int fcs_flag = fhd >> 6, single = (fhd >> 5) & 1, checksum = (fhd >> 2) & 1, did_flag = fhd & 3;
+    const int did_bytes = did_flag == 3 ? 4 : did_flag;
+    const int fcs_bytes = fcs_flag == 0 ? single : (fcs_flag == 1 ? 2 : (fcs_flag == 2 ? 4 : 8));
+    if (p + (single ? 0 : 1) + did_bytes + fcs_bytes > n) return B2_INFL_TRUNCATED;
+    if (!single) ++p;  // window descriptor: the whole output is addressable here
+    unsigned long long did = 0;
+    for (int i = 0; i < did_bytes; ++i) did |= (unsigned long long)s[p + i] << (8 * i);
+    if (did != 0) return B2_INFL_UNSUPPORTED;
+    p += did_bytes + fcs_bytes;
+    const long long base = o.n;
+    z.huf.log = 0;
+    z.have_ll = z.have_of = z.have_ml = false;
+    z.rep[0] = 1, z.rep[1] = 4, z.rep[2] = 8;
+    for (;;) {
+      if (p + 3 > n) return B2_INFL_TRUNCATED;
+      const uint32_t bh = s[p] | (s[p + 1] << 8) | (s[p + 2] << 16);
+      p += 3;
+      const int last = bh & 1, type = (bh >> 1) & 3;
+      const long long bs = bh >> 3;
+      if (type == 0) {
+        if (p + bs > n) return B2_INFL_TRUNCATED;
+        if (!b2_out_lit(o, s + p, bs)) return B2_INFL_OVERFLOW;
+        p += bs;
+      } else if (type == 1) {
+        if (p + 1 > n) return B2_INFL_TRUNCATED;
+        if (o.dst) {
+          if (o.n + bs > o.cap) return B2_INFL_OVERFLOW;
+          for (long long i = 0; i < bs; ++i) o.dst[o.n + i] = s[p];
+        }
+        o.n += bs;
+        p += 1;
+      } else if (type == 2) {
+        if (p + bs > n) return B2_INFL_TRUNCATED;
+        const int rc = b2z_block(z, s + p, bs, o, base);
+        if (rc) return rc;
+        p += bs;
+      } else {
+        return B2_INFL_CORRUPT;
+      }
+      if (last) break;
+    }
+    if (checksum) {
+      if (p + 4 > n) return B2_INFL_TRUNCATED;
+      p += 4;
+    }
+  }
+  return o.n;
+}
+
+// codec = attributes & 7 of the batch header: 1 gzip, 2 snappy, 3 lz4, 4 zstd
 B2_HD long long b2_inflate_codec(int codec, const uint8_t* s, long long n, uint8_t* dst, long long cap) {
   if (codec == 1) return b2_gzip(s, n, dst, cap);
   if (codec == 2) return b2_snappy(s, n, dst, cap);
   if (codec == 3) return b2_lz4_frame(s, n, dst, cap);
+  if (codec == 4) return b2_zstd(s, n, dst, cap);
   return B2_INFL_UNSUPPORTED;
 }

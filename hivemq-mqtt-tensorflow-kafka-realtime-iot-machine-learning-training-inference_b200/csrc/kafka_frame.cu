@@ -12,9 +12,9 @@
 // folded at the end) and walks its records (length chain in lock-step, record fields one record per lane), writing each value's
 // [begin, end).  The decode entry points take those ranges as they are (b2_decode_score_spans: the segment is the input, nothing
 // is copied); b2_kafka_gather_values packs the values back to back for callers that want a (bytes, offsets) batch.
-// Compressed batches (attributes & 7: gzip, Snappy, LZ4) are inflated first — b2_kafka_inflate_sizes / b2_kafka_inflate, one thread
+// Compressed batches (attributes & 7: gzip, Snappy, LZ4, zstd) are inflated first — b2_kafka_inflate_sizes / b2_kafka_inflate, one thread
 // per batch running the sequential decoders of inflate.cuh — into a rebuilt, uncompressed copy of the segment that then takes
-// the path above; zstd batches are reported (B2_FRAME_COMPRESSED) and skipped.
+// the path above.
 #include <mutex>
 
 #include "common.cuh"
@@ -463,7 +463,7 @@ __global__ void __launch_bounds__(KF_NT) kafka_inflate_sizes_kernel(const Inflat
         size = endb - (pos + KF_HEADER);
       } else {
         const long long r = b2_inflate_codec(codec, s + pos + KF_HEADER, endb - (pos + KF_HEADER), nullptr, 0);
-        if (r == B2_INFL_UNSUPPORTED) st = B2_FRAME_COMPRESSED;   // zstd
+        if (r == B2_INFL_UNSUPPORTED) st = B2_FRAME_COMPRESSED;   // a codec number beyond zstd, a zstd dictionary
         else if (r < 0) st = B2_FRAME_TRUNCATED;                  // the compressed stream is damaged
         else size = r;
       }

@@ -57,12 +57,12 @@ def _varint(v: int) -> bytes:
     return bytes(out)
 
 
-_CODECS = {None: 0, "none": 0, "gzip": 1, "snappy": 2, "snappy-xerial": 2, "lz4": 3}
+_CODECS = {None: 0, "none": 0, "gzip": 1, "snappy": 2, "snappy-xerial": 2, "lz4": 3, "zstd": 4, "zstd-stream": 4}
 
 
 def _compress(records: bytes, compression) -> bytes:
     """The records section of a batch under ``compression.type`` (test / synthetic input only: gzip from the standard library,
-    Snappy and LZ4 frames from pyarrow; "snappy-xerial" adds the Java client's SnappyOutputStream framing)."""
+    Snappy, LZ4 frames and Zstandard from pyarrow; "snappy-xerial" adds the Java client's SnappyOutputStream framing)."""
     if compression in (None, "none"):
         return records
     if compression == "gzip":
@@ -73,6 +73,14 @@ def _compress(records: bytes, compression) -> bytes:
 
     if compression == "snappy":
         return pa.compress(records, codec="snappy", asbytes=True)
+    if compression == "zstd":          # one frame with its content size, as ZSTD_compress writes it
+        return pa.compress(records, codec="zstd", asbytes=True)
+    if compression == "zstd-stream":   # the streaming API (what the Java client's ZstdOutputStream uses): window descriptor, no content size
+        sink = pa.BufferOutputStream()
+        with pa.CompressedOutputStream(sink, "zstd") as f:
+            for i in range(0, len(records), 40_000):
+                f.write(records[i:i + 40_000])
+        return sink.getvalue().to_pybytes()
     if compression == "snappy-xerial":
         out = b"\x82SNAPPY\x00" + struct.pack(">ii", 1, 1)
         for i in range(0, len(records), 32768):
@@ -87,7 +95,7 @@ def _compress(records: bytes, compression) -> bytes:
 def write_segment(values: Sequence[bytes], records_per_batch: int = 500, keys: Optional[Sequence[Optional[bytes]]] = None,
                   base_offset: int = 0, headers: bool = False, compression=None) -> bytes:
     """Message values → log-segment bytes: v2 record batches of ``records_per_batch`` records each, their records sections
-    compressed as a whole when ``compression`` is "gzip" / "snappy" / "snappy-xerial" / "lz4" (a list gives one per batch)."""
+    compressed as a whole when ``compression`` is "gzip" / "snappy" / "snappy-xerial" / "lz4" / "zstd" / "zstd-stream" (a list gives one per batch)."""
     out = bytearray()
     n = len(values)
     for b0 in range(0, n, records_per_batch):

@@ -335,17 +335,18 @@ int  b2_format_rows(b2_ctx* ctx, const float* x_dev, int64_t n, int n_cols, int 
 #define B2_FRAME_BAD_MAGIC  1  /* not message format v2 */
 #define B2_FRAME_BAD_CRC    2
 #define B2_FRAME_TRUNCATED  3  /* batch or record runs past its container */
-#define B2_FRAME_COMPRESSED 4  /* compressed batch handed to b2_kafka_index_records (inflate it first), or a zstd batch (no decoder here) */
+#define B2_FRAME_COMPRESSED 4  /* compressed batch handed to b2_kafka_index_records (inflate it first), or a codec this library has no decoder for */
 #define B2_FRAME_CONTROL    5  /* control batch (attributes bit 5: transaction markers); consumers never see its records */
 int64_t b2_kafka_scan_batches(const uint8_t* bytes_host, int64_t n_bytes, int64_t* batch_pos, int64_t* rec_count, int64_t cap);
 int  b2_kafka_index_records(b2_ctx* ctx, const uint8_t* bytes_dev, int64_t n_bytes, const int64_t* batch_pos_dev, const int64_t* rec_base_dev,
                             int64_t n_batches, int verify_crc, int32_t* begin_dev, int32_t* end_dev, int32_t* status_dev, void* stream);
 int  b2_kafka_gather_values(b2_ctx* ctx, const uint8_t* bytes_dev, const int32_t* begin_dev, const int32_t* end_dev, int64_t n,
                             const int32_t* out_offs_dev, uint8_t* out_bytes_dev, void* stream);
-/* Compressed batches (attributes & 7: 1 gzip, 2 Snappy — raw or the Java client's xerial framing —, 3 LZ4 frame): what librdkafka
+/* Compressed batches (attributes & 7: 1 gzip, 2 Snappy — raw or the Java client's xerial framing —, 3 LZ4 frame, 4 Zstandard
+ * frames without dictionary): what librdkafka
  * inflates underneath KafkaDataset whatever the producer's compression.type was (cardata-v1.py:10).  Two passes, one thread per
  * batch.  b2_kafka_inflate_sizes: status_dev int32[n_batches] (header checks, CRC-32C over the bytes as stored when verify_crc;
- * zstd → B2_FRAME_COMPRESSED, a damaged stream → B2_FRAME_TRUNCATED) and sizes_dev int64[n_batches] = bytes of each batch's
+ * an unknown codec → B2_FRAME_COMPRESSED, a damaged stream → B2_FRAME_TRUNCATED) and sizes_dev int64[n_batches] = bytes of each batch's
  * records section once inflated (as stored for an uncompressed batch, 0 for a refused one).  The caller lays the rebuilt segment
  * out: out_pos[b+1] = out_pos[b] + 61 + sizes[b].  b2_kafka_inflate writes every batch there as an UNCOMPRESSED batch (header
  * copied, codec bits cleared, batchLength adjusted, records inflated); the result goes through b2_kafka_index_records with

@@ -31,7 +31,7 @@ def test_bad_batches_are_refused_not_fatal(cuda_device):
     seg = bytearray(bs.kafka.write_segment(vals, records_per_batch=100))
     pos, _ = bs.kafka.scan_batches(bytes(seg))
     seg[pos[1] + 80] ^= 0x01      # payload bit flip → CRC mismatch
-    seg[pos[2] + 22] |= 0x04      # attributes: zstd (no decoder here); the stored CRC no longer matches either
+    seg[pos[2] + 22] |= 0x05      # attributes: a codec nobody knows; the stored CRC no longer matches either
     with pytest.raises(bs.kafka.FrameError):
         bs.kafka.values_from_segment(bytes(seg))
     rb, st = bs.kafka.values_from_segment(bytes(seg), raise_on_error=False)
@@ -100,10 +100,10 @@ def test_hostile_lengths_are_truncation_not_a_fault(cuda_device):
     assert rb.n == 2 and not st.any()
 
 
-@pytest.mark.parametrize("compression", ["gzip", "snappy", "snappy-xerial", "lz4", ["gzip", None, "lz4", "snappy"]])
+@pytest.mark.parametrize("compression", ["gzip", "snappy", "snappy-xerial", "lz4", "zstd", "zstd-stream", ["gzip", None, "lz4", "snappy", "zstd"]])
 def test_compressed_batches_are_inflated(cuda_device, compression):
     """Producer-side compression.type (records section compressed as a whole): the values come out as from the uncompressed
-    segment, CRC-32C is checked over the bytes as stored, a damaged stream / zstd batch is refused without touching the others."""
+    segment, CRC-32C is checked over the bytes as stored, a damaged stream / a batch of an unknown codec is refused without touching the others."""
     g = np.random.default_rng(3)
     rows = synth.sensor_rows(3000, seed=8)
     data, offs = synth.avro_a_batch(rows)
@@ -127,9 +127,9 @@ def test_compressed_batches_are_inflated(cuda_device, compression):
     assert (np.diff(o2)[250:500] == 0).all() and np.array_equal(np.diff(o2)[:250], np.diff(o)[:250]) and np.array_equal(np.diff(o2)[500:], np.diff(o)[500:])
     rb3, st3 = bs.kafka.values_from_segment(bytes(bad), raise_on_error=False, verify_crc=False)
     assert st3.cpu().tolist()[0] == 0 and rb3.n == 3000
-    # zstd (codec 4) is reported, not inflated
+    # a codec number nobody knows (5) is reported, not inflated
     z = bytearray(seg)
-    z[pos[2] + 22] = (z[pos[2] + 22] & ~7) | 4
+    z[pos[2] + 22] = (z[pos[2] + 22] & ~7) | 5
     _, st4 = bs.kafka.values_from_segment(bytes(z), raise_on_error=False, verify_crc=False)
     assert st4.cpu().tolist()[2] == 4
 
