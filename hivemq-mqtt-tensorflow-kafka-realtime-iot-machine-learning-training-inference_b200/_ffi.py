@@ -30,7 +30,7 @@ class AeDesc(C.Structure):
 
 class Norm(C.Structure):
     _fields_ = [("n", C.c_int32), ("kind", C.c_int32 * MAX_WIDTH), ("lo", C.c_float * MAX_WIDTH),
-                ("range", C.c_float * MAX_WIDTH)]
+                ("range", C.c_float * MAX_WIDTH), ("order", C.c_int32)]
 
 
 class CsvSpec(C.Structure):
@@ -173,12 +173,13 @@ def ptr(t) -> Optional[int]:
     return None if t is None else t.data_ptr()
 
 
-def make_norm(kind=None, lo=None, rng=None) -> Norm:
+def make_norm(kind=None, lo=None, rng=None, order: int = 0) -> Norm:
     n = Norm()
     if kind is None:
         n.n = 0
         return n
     n.n = len(kind)
+    n.order = int(order)   # 0: float32 order (cardata-v1.py), 1: float64 order (cardata-v3.py; fused Avro calls only)
     for i in range(n.n):
         n.kind[i] = int(kind[i])
         n.lo[i] = float(lo[i])

@@ -257,6 +257,7 @@ static int score_spec(b2_ae* ae, const float* x, int64_t n, const b2_norm* norm,
 extern "C" int b2_ae_score(b2_ae* ae, const float* x_dev, int64_t n, const b2_norm* norm, float threshold, float* mse_dev,
                            uint8_t* flag_dev, float* recon_dev, unsigned long long* counters_dev, void* stream) {
   B2_REQUIRE(ae != nullptr, "b2_ae_score: ae is NULL");
+  B2_NORM_F32_ONLY(norm, "b2_ae_score");
   B2_REQUIRE(n >= 0, "b2_ae_score: n=%lld < 0", (long long)n);
   if (n == 0) return B2_OK;
   B2_REQUIRE(x_dev != nullptr, "b2_ae_score: x_dev is NULL");

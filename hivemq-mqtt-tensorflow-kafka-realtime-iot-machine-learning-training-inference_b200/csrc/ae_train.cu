@@ -620,6 +620,7 @@ static int fit_spec(b2_ae* ae, const float* x, const int32_t* order, int64_t row
 
 extern "C" int b2_ae_fit_steps(b2_ae* ae, const float* x_dev, const int32_t* order_dev, int64_t rows_total, int batch,
                                const b2_norm* norm, b2_adam* adam, float* loss_dev, float* acc_dev, void* stream) {
+  B2_NORM_F32_ONLY(norm, "b2_ae_fit_steps");
   B2_REQUIRE(ae && x_dev && adam, "b2_ae_fit_steps: NULL argument");
   B2_REQUIRE(rows_total >= 1, "b2_ae_fit_steps: rows_total=%lld < 1", (long long)rows_total);
   B2_REQUIRE(batch >= 1 && batch <= FIT_NT, "b2_ae_fit_steps: batch=%d not in 1..%d (use b2_ae_grad/b2_ae_apply for larger batches)", batch,
@@ -673,6 +674,7 @@ static int grad_spec(b2_ae* ae, const float* x, int64_t n, const b2_norm* norm, 
 
 extern "C" int b2_ae_grad(b2_ae* ae, const float* x_dev, int64_t n, const b2_norm* norm, float* grads_dev, void* scratch_dev,
                           int64_t scratch_bytes, void* stream) {
+  B2_NORM_F32_ONLY(norm, "b2_ae_grad");
   B2_REQUIRE(ae && x_dev && grads_dev && scratch_dev, "b2_ae_grad: NULL argument");
   B2_REQUIRE(n >= 1, "b2_ae_grad: n=%lld < 1", (long long)n);
   B2_REQUIRE(n <= (1ll << 24), "b2_ae_grad: n=%lld rows in one step (the row count travels with the gradient as a float: exact to 2^24)", (long long)n);
@@ -751,6 +753,7 @@ extern "C" int64_t b2_ae_exchange_bytes(void) { return (int64_t)sizeof(float) * 
 extern "C" int b2_ae_step_fused(b2_ae* ae, const float* x_dev, int64_t n, const b2_norm* norm, b2_adam* adam, void* scratch_dev,
                                 int64_t scratch_bytes, int64_t total_rows, const uint64_t* peer_bufs, int world, int rank, uint32_t seq,
                                 float* stats_dev, void* stream) {
+  B2_NORM_F32_ONLY(norm, "b2_ae_step_fused");
   B2_REQUIRE(ae && x_dev && adam && scratch_dev, "b2_ae_step_fused: NULL argument");
   B2_REQUIRE(n >= 1 && total_rows >= n, "b2_ae_step_fused: n=%lld total_rows=%lld", (long long)n, (long long)total_rows);
   B2_REQUIRE(((uintptr_t)x_dev & 7) == 0, "b2_ae_step_fused: x_dev must be 8-byte aligned");
@@ -803,6 +806,7 @@ static int noalloc_scratch_for_current_device(int device, float** out) {
 }
 
 extern "C" int b2_ae_grad_noalloc(b2_ae* ae, const float* x_dev, int64_t n, const b2_norm* norm, float* grads_dev, void* stream) {
+  B2_NORM_F32_ONLY(norm, "b2_ae_grad_noalloc");
   B2_REQUIRE(ae && x_dev && grads_dev, "b2_ae_grad_noalloc: NULL argument");
   B2_REQUIRE(n >= 1, "b2_ae_grad_noalloc: n=%lld < 1", (long long)n);
   B2_REQUIRE(((uintptr_t)x_dev & 7) == 0, "b2_ae_grad_noalloc: x_dev must be 8-byte aligned");

@@ -32,6 +32,12 @@ void b2_set_error(const char* fmt, ...);
     }                                \
   } while (0)
 
+// b2_norm.order = B2_NORM_ORDER_F64 needs float64 values: only the fused Avro decode has them (decode.cu)
+#define B2_NORM_F32_ONLY(norm, who)                                                                                        \
+  B2_REQUIRE(!(norm) || (norm)->n <= 0 || (norm)->order == B2_NORM_ORDER_F32,                                              \
+             "%s: the float64 normalisation order (cardata-v3.py) needs float64 values; only b2_decode_score / "             \
+             "b2_decode_score_spans with an Avro program take it", who)
+
 // Tuning / debugging knobs.  Read ONCE from the environment (B2_FAST_TANH, B2_SCORE_CFG, …) when the context is created — a
 // launch never calls getenv — and changed afterwards with b2_ctx_set_option().
 struct b2_knobs {

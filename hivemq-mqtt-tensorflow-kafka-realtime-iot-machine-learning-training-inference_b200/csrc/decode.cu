@@ -80,6 +80,9 @@ struct DecodeArgs {
   int32_t* over_list;
   int list_mode;
   const float* panels;  // tcgen05 score phase (decode_kernel_tc): packed (hi, lo) weight panels, see ae_tc.cuh
+  // float64 normalisation order (b2_norm.order = B2_NORM_ORDER_F64, cardata-v3.py:53-168; decode_kernel_n64): the table as doubles
+  double n64_lo[D], n64_rg[D];
+  int norm64;
 };
 
 // ---- CSV, careful path step 1: field boundaries of one record (RFC-4180 quotes) ---------------------------------------------
@@ -612,6 +615,76 @@ __device__ __forceinline__ int avro_walk_schema_b(const uint8_t* __restrict__ ba
   return B2_REC_OK;
 }
 
+// ---- Avro, float64 order (cardata-v3.py) ------------------------------------------------------------------------------------
+// cardata-v3.py decodes every numeric field as float64 (:53-74; ints via tf.cast(..., tf.float64), :98-103) and runs normalize_fn
+// on float64 (:78-168) — (v - lo) / (hi - lo) * 2.0 - 1.0 with every step rounded to binary64 — before Keras rounds the model
+// input to float32.  This walk keeps a field's value in binary64 until that last rounding: plain field-by-field loop over the
+// schema program (no run specialisation: the mode is opt-in), one IEEE double division per scaled feature.
+template <int D>
+__device__ __forceinline__ float norm64_store(const DecodeArgs<D>& a, int col, double v) {
+  const int kind = a.nm.kind[col];
+  if (kind == B2_NORM_SCALE) v = __fma_rn(__ddiv_rn(__dsub_rn(v, a.n64_lo[col]), a.n64_rg[col]), 2.0, -1.0);  // 2q is exact: one rounding, like (q * 2.0) - 1.0
+  else if (kind == B2_NORM_ZERO) v = 0.0;
+  return __double2float_rn(v);
+}
+template <int D>
+__device__ __noinline__ int avro_decode_record_f64(const uint8_t* __restrict__ base, int p, int e, const DecodeArgs<D>& a, float* __restrict__ xrow,
+                                                   int xs, uint8_t* label) {
+  const AvroP& av = a.avro;
+  uint8_t lab_out = 2;
+  p += av.skip_prefix;
+  if (p > e) return B2_REC_TRUNCATED;
+  for (int i = 0; i < av.n_fields; ++i) {
+    const int type = av.f[i].type, nullable = av.f[i].nullable, out = av.f[i].out;
+    bool present = true, wide;
+    int v32 = 0;
+    long long v64 = 0;
+    double val = 0.0;  // a null numeric field decodes as 0 ([upstream] tfio default) and is then scaled like any other value
+    uint8_t lab = 2;
+    if (nullable) {
+      p = av_varint(base, p, e, 10, &v32, &v64, &wide);
+      if (p < 0) return B2_REC_TRUNCATED;
+      if (wide || (v32 != 0 && v32 != 1)) return B2_REC_BAD_BRANCH;
+      present = v32 != (nullable == 1 ? 0 : 1);
+    }
+    if (present) {
+      if (type == AV_FLOAT) {
+        if (p + 4 > e) return B2_REC_TRUNCATED;
+        val = (double)__uint_as_float(lds_u32_unaligned(base, p));
+        p += 4;
+      } else if (type == AV_DOUBLE) {
+        if (p + 8 > e) return B2_REC_TRUNCATED;
+        const unsigned long long bits = (unsigned long long)lds_u32_unaligned(base, p) | ((unsigned long long)lds_u32_unaligned(base, p + 4) << 32);
+        val = __longlong_as_double((long long)bits);
+        p += 8;
+      } else if (type == AV_INT || type == AV_LONG) {
+        p = av_varint(base, p, e, type == AV_INT ? 5 : 10, &v32, &v64, &wide);
+        if (p < 0) return B2_REC_TRUNCATED;
+        val = !wide ? (double)v32 : (type == AV_INT ? (double)(int)v64 : __ll2double_rn(v64));
+      } else if (type == AV_BOOLEAN) {
+        if (p + 1 > e) return B2_REC_TRUNCATED;
+        val = base[p] ? 1.0 : 0.0;
+        p += 1;
+      } else if (type == AV_STRING || type == AV_BYTES) {
+        p = av_varint(base, p, e, 10, &v32, &v64, &wide);
+        if (p < 0) return B2_REC_TRUNCATED;
+        const long long L = wide ? v64 : (long long)v32;
+        if (L < 0 || (long long)p + L > e) return B2_REC_TRUNCATED;
+        const uint32_t c4 = lds_u32_unaligned(base, p);
+        if (L == 5 && c4 == 0x736C6166u && base[p + 4] == 'e') lab = 0;
+        else if (L == 4 && c4 == 0x65757274u) lab = 1;
+        else lab = L == 0 ? 2 : 3;
+        p += (int)L;
+      }
+    }
+    if (out >= 0) xrow[out * xs] = norm64_store<D>(a, out, val);
+    else if (out == -2) lab_out = lab;
+  }
+  if (p > e) return B2_REC_TRUNCATED;
+  *label = lab_out;
+  return B2_REC_OK;
+}
+
 // ---- the kernel --------------------------------------------------------------------------------------------------
 // MODE 0: decode only (runtime n_out);  MODE 1: fused decode + score for the D-14-7-7-D autoencoder.
 // Every WARP is an independent worker: it owns a byte stage, a float tile and an mbarrier in shared memory and walks chunks of
@@ -625,8 +698,9 @@ __device__ __forceinline__ int avro_walk_schema_b(const uint8_t* __restrict__ ba
 // TC (fused mode, R = 1, CTAs of exactly 4 warps): the score phase runs on the tensor cores (ae_tc.cuh) — the CTA's four warps
 // still fetch, plan and decode independently, but score their 4 x 32 records together as one 128-row tile, so the item loop runs
 // in lock-step across the CTA (a warp that has run out of chunks contributes empty rows until all four are done).
-template <int D, int MODE, bool FT, int FMT, int R, bool TC = false, bool WM = false, unsigned ZM = 0u>
+template <int D, int MODE, bool FT, int FMT, int R, bool TC = false, bool WM = false, unsigned ZM = 0u, bool N64 = false>
 __device__ __forceinline__ void decode_body(const DecodeArgs<D>& a) {
+  static_assert(!N64 || (MODE == 1 && R == 1 && !TC && !WM && ZM == 0u && FMT == FMT_AVRO), "float64 order: fused Avro, FFMA2 score phase");
   static_assert(ZM == 0u || (MODE == 1 && R == 1 && !TC && !WM), "zero-set specialisation: fused mode, FFMA2 score phase");
   static_assert(R == 1 || (R == 2 && MODE == 1), "two records per lane only in the fused mode");
   static_assert(!TC || (MODE == 1 && R == 1), "tensor-core scoring: fused mode, one record per lane");
@@ -807,6 +881,11 @@ __device__ __forceinline__ void decode_body(const DecodeArgs<D>& a) {
       } else if (FMT == FMT_JSON) {
         for (int j = 0; j < xt_stride; ++j) xrow[j] = 0.0f;  // members that are absent or null
         st_s = b2_json_record_auto(stage, cb, ce, a.json, xrow, &lab_s);
+      } else if (N64) {
+        // columns no field routes to hold a decoded 0.0, scaled like any other value
+        if (!a.avro.all_routed)
+          for (int j = 0; j < D; ++j) xrow[j * XS] = norm64_store<D>(a, j, 0.0);
+        st_s = avro_decode_record_f64<D>(stage, cb, ce, a, xrow, XS, &lab_s);
       } else {
         if (!a.avro.all_routed)
           for (int j = 0; j < (MODE == 1 ? D : a.n_out); ++j) xrow[j * XS] = 0.0f;  // columns no field routes to
@@ -873,8 +952,8 @@ __device__ __forceinline__ void decode_body(const DecodeArgs<D>& a) {
       } else if (active[0]) {
         float* const rowp[1] = {xlane};
         float m1[1] = {0.f};
-        if (ZM != 0u || a.has_norm) ae_forward_rows<D, 1, true, false, FT, ZM>(a.w, a.nm, rowp, m1);  // (a ZM kernel is only launched with a table)
-        else ae_forward_rows<D, 1, false, false, FT>(a.w, a.nm, rowp, m1);
+        if (!N64 && (ZM != 0u || a.has_norm)) ae_forward_rows<D, 1, true, false, FT, ZM>(a.w, a.nm, rowp, m1);  // (a ZM kernel is only launched with a table)
+        else ae_forward_rows<D, 1, false, false, FT>(a.w, a.nm, rowp, m1);  // (N64: the decode has normalised the row already)
         mm[0] = m1[0];
       }
 #pragma unroll
@@ -965,6 +1044,11 @@ __global__ void __launch_bounds__(TCS_ROWS, 512 / TcShape<D>::TMEM_COLS > 5 ? 5 
 template <int D, bool FT, int FMT>
 __global__ void __launch_bounds__(DEC_NT, FMT == FMT_AVRO ? 4 : 3) decode_kernel_zs(const __grid_constant__ DecodeArgs<D> a) {
   decode_body<D, 1, FT, FMT, 1, false, false, REF_ZERO_MASK>(a);
+}
+// float64 normalisation order (cardata-v3.py): the walk that keeps values in binary64 until the model's input cast
+template <int D, bool FT>
+__global__ void __launch_bounds__(DEC_NT, 3) decode_kernel_n64(const __grid_constant__ DecodeArgs<D> a) {
+  decode_body<D, 1, FT, FMT_AVRO, 1, false, false, 0u, true>(a);
 }
 // warp-MMA score phase (ae_mma.cuh): CTA shape as for decode_kernel; registers bounded for three CTAs of 8 warps per SM
 template <int D, bool FT, int FMT>
@@ -1097,12 +1181,13 @@ template <int D, int MODE, bool FT, int FMT, int R, int MINB, int VAR>
 static auto decode_kernel_of() {
   if constexpr (VAR == 1 && FMT != FMT_JSON) return decode_kernel_wm<D, FT, FMT>;
   else if constexpr (VAR == 2) return decode_kernel_zs<D, FT, FMT>;
+  else if constexpr (VAR == 3 && FMT == FMT_AVRO) return decode_kernel_n64<D, FT>;
   else return DecodeKernel<D, MODE, FT, FMT, R, MINB>::get();
 }
 
 template <int D, int MODE, bool FT, int FMT, int R, int MINB, int VAR = 0>
 static int launch_decode_r(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stream) {
-  static_assert(VAR == 0 || (MODE == 1 && R == 1 && (VAR == 2 || FMT != FMT_JSON)), "score-phase variants: fused mode, one record per lane");
+  static_assert(VAR == 0 || (MODE == 1 && R == 1 && (VAR == 2 || FMT != FMT_JSON) && (VAR != 3 || FMT == FMT_AVRO)), "kernel variants: fused mode, one record per lane");
   const int xt_stride = MODE == 1 ? (R == 2 ? 2 * (D + 1) : D) : args.n_out;
   args.stage_cap = choose_stage_cap(args.fmt, args.csv, args.avro, args.json, ctx->record_bytes_hint, 32 * R);
   args.warp_bytes = 16 + args.stage_cap + 16 + align16i(32 * xt_stride * 4) + 16;
@@ -1216,6 +1301,9 @@ static int launch_decode_tc(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t strea
 // context option "decode_r2" = 2 (registers capped at 85: 6 CTAs of 4 warps per SM) or 3 (102 registers, 5 CTAs); 0 / -1 = one.
 template <int D, int MODE, bool FT, int FMT>
 static int launch_decode_fmt(b2_ctx* ctx, DecodeArgs<D>& args, cudaStream_t stream) {
+  if constexpr (MODE == 1 && FMT == FMT_AVRO) {  // the float64 normalisation order has one kernel; the tuning options below do not apply
+    if (args.norm64) return launch_decode_r<D, MODE, FT, FMT, 1, 1, 3>(ctx, args, stream);
+  }
   if (MODE == 1 && FT && args.panels != nullptr) {  // context option decode_tc: score phase on tcgen05
     if (MODE == 1) return launch_decode_tc<D, true, FMT>(ctx, args, stream);  // (only the fast-tanh form is instantiated)
   }
@@ -1400,6 +1488,16 @@ static int decode_score_spec(b2_ae* ae, const uint8_t* bytes, const int32_t* off
   args.label = label;
   ae_pack_weights<D>(ae->h_w.data(), args.w);
   args.has_norm = norm_fill<D>(norm, args.nm);
+  if (args.has_norm && norm->order != B2_NORM_ORDER_F32) {
+    B2_REQUIRE(norm->order == B2_NORM_ORDER_F64, "b2_decode_score: b2_norm.order=%d unknown", norm->order);
+    if (!avro) {
+      b2_set_error("b2_decode_score: the float64 normalisation order is defined for Avro records (cardata-v3.py decodes Avro as float64); "
+                   "CSV and JSON values are float32 after tf.io.decode_csv / this library's JSON route");
+      return B2_EUNSUPPORTED;
+    }
+    args.norm64 = 1;
+    for (int i = 0; i < D; ++i) args.n64_lo[i] = (double)norm->lo[i], args.n64_rg[i] = (double)norm->range[i];
+  }
   if (csv && args.has_norm && ae->ctx->knobs.zero_skip != 0) {
     // CSV float fields whose column the table forces to zero: the field walk checks the token and skips its conversion
     for (int f = 0; f < args.csv.n_fields; ++f)

@@ -77,6 +77,7 @@ int fill(const b2_norm* norm, int d, NormMax& nm) {
 }  // namespace
 
 extern "C" int b2_normalize(b2_ctx* ctx, const float* x_dev, int64_t n, int d, const b2_norm* norm, float* out_dev, void* stream) {
+  B2_NORM_F32_ONLY(norm, "b2_normalize");
   B2_REQUIRE(ctx, "b2_normalize: NULL context");
   B2_REQUIRE(n >= 0, "b2_normalize: n < 0");
   NormalizeArgs a;

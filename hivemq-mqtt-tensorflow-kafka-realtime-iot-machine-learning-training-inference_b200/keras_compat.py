@@ -406,9 +406,13 @@ class Model:
             inp = u
         return s + [(self.units[-1], self.features), (self.features,)]
 
-    def set_normalization(self, kind, lo, rng):
-        """Fuse ``normalize_fn`` (cardata-v1.py:40-131) into score/predict/fit: raw rows in, normalised inside the kernel."""
-        self._norm = None if kind is None else (list(kind), list(lo), list(rng))
+    def set_normalization(self, kind, lo, rng, order: str = "f32"):
+        """Fuse ``normalize_fn`` (cardata-v1.py:40-131) into score/predict/fit: raw rows in, normalised inside the kernel.
+        ``order="f64"`` is cardata-v3.py's variant (:53-168): Avro values decoded as float64, scaled in float64, rounded to
+        float32 last — it needs float64 values, so only the fused Avro decode + score accepts it."""
+        if order not in ("f32", "f64"):
+            raise ValueError("order must be 'f32' or 'f64'")
+        self._norm = None if kind is None else (list(kind), list(lo), list(rng), 1 if order == "f64" else 0)
         self._norm_struct_key = None  # the cached C struct belongs to the previous table
         return self
 

@@ -85,7 +85,14 @@ typedef struct {
   int32_t kind[B2_MAX_WIDTH];
   float   lo[B2_MAX_WIDTH];
   float   range[B2_MAX_WIDTH];      /* hi - lo */
+  int32_t order;                    /* B2_NORM_ORDER_F32 (0): values are rounded to float32 first, then scaled in float32 —
+                                       cardata-v1.py:16-37, :61-69.  B2_NORM_ORDER_F64 (1): decoded and scaled in float64, rounded
+                                       to float32 last (Keras' input cast) — cardata-v3.py:53-74, :98-168.  The float64 order needs
+                                       float64 values, i.e. it exists for the fused Avro calls (b2_decode_score /
+                                       b2_decode_score_spans with an Avro program); every other call refuses it. */
 } b2_norm;
+#define B2_NORM_ORDER_F32 0
+#define B2_NORM_ORDER_F64 1
 
 /* Replaces tf.keras.models.load_model + model construction (cardata-v1.py:153-167,202; nb2.0:888).
  * host_weights = kernel0[in*out] (row-major [in,out], Keras layout), bias0[out], kernel1, bias1, ... */

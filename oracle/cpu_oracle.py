@@ -172,13 +172,15 @@ def _read_varint(buf: bytes, p: int, end: int, max_bytes: int) -> Tuple[Optional
 
 
 def decode_avro(data: np.ndarray, offsets: np.ndarray, prog_fields: Sequence[Tuple[int, int, int]], n_out: int,
-                skip_prefix: int = 5):
-    """prog_fields: (type, nullable, out) per schema field.  Returns (out f32[n,n_out], label u8[n], status i32[n]).
+                skip_prefix: int = 5, dtype=np.float32):
+    """prog_fields: (type, nullable, out) per schema field.  Returns (out dtype[n,n_out], label u8[n], status i32[n]).
 
-    Numeric values are converted to float32 exactly once (int → float32 like tf.cast at cardata-v1.py:61-66,
-    double → float32 round-to-nearest like Keras' input cast).  Null numeric → 0 ([upstream] tfio default)."""
+    dtype float32 (cardata-v1.py:16-37): numeric values are converted to float32 exactly once (int → float32 like tf.cast at
+    cardata-v1.py:61-66, double → float32 round-to-nearest like Keras' input cast).  dtype float64 (cardata-v3.py:53-74 decodes
+    with dtype=tf.float64 and casts the int fields to float64, :98-103): doubles as they are, ints exactly.
+    Null numeric → 0 ([upstream] tfio default)."""
     n = len(offsets) - 1
-    out = np.zeros((n, n_out), dtype=np.float32)
+    out = np.zeros((n, n_out), dtype=dtype)
     label = np.full(n, 2, dtype=np.uint8)
     status = np.zeros(n, dtype=np.int32)
     raw = data.tobytes()
@@ -211,7 +213,7 @@ def decode_avro(data: np.ndarray, offsets: np.ndarray, prog_fields: Sequence[Tup
                         break
                     if typ == T_INT:
                         v = (v + 2 ** 31) % 2 ** 32 - 2 ** 31
-                    val = np.float32(v)
+                    val = dtype(v)
                 elif typ == T_FLOAT:
                     if p + 4 > end:
                         st = REC_TRUNCATED
@@ -223,13 +225,13 @@ def decode_avro(data: np.ndarray, offsets: np.ndarray, prog_fields: Sequence[Tup
                         st = REC_TRUNCATED
                         break
                     with np.errstate(over="ignore"):
-                        val = np.float32(np.frombuffer(raw, dtype="<f8", count=1, offset=p)[0])
+                        val = dtype(np.frombuffer(raw, dtype="<f8", count=1, offset=p)[0])
                     p += 8
                 elif typ == T_BOOLEAN:
                     if p + 1 > end:
                         st = REC_TRUNCATED
                         break
-                    val = np.float32(1.0 if raw[p] else 0.0)
+                    val = dtype(1.0 if raw[p] else 0.0)
                     p += 1
                 elif typ in (T_STRING, T_BYTES):
                     ln, p = _read_varint(raw, p, end, 10)

@@ -498,3 +498,53 @@ def test_csv_zeroed_columns_are_still_validated(cuda_device):
     got_bad = set(np.nonzero(res[1][2])[0].tolist())
     assert want_bad <= got_bad, [lines[i] for i in sorted(want_bad - got_bad)][:4]
     assert all(i % 3 == 1 for i in got_bad)  # only rows that were touched
+
+
+def test_float64_normalisation_order_of_cardata_v3(cuda_device):
+    """cardata-v3.py decodes the KSQL Avro records as float64, runs normalize_fn on float64 and only then lets Keras round the
+    model input to float32 (:53-168).  With set_normalization(..., order="f64") the fused kernel follows that order: its scores
+    carry the same bits as scoring rows that NumPy decoded and normalised in float64 and rounded to float32 last — and they differ
+    from the float32 order (cardata-v1.py) in a few last bits.  Calls that have no float64 values refuse the option."""
+    from oracle import cpu_oracle as orc
+
+    rng = np.random.default_rng(21)
+    x = synth.sensor_rows(3000, seed=21).astype(np.float64)
+    x *= 1.0 + 1e-9 * rng.standard_normal(x.shape)           # not representable in float32: the two orders can differ
+    x[5, 1], x[6, 3], x[7, 6] = 1e300, -1e-300, np.nan
+    data, offs, _ = synth.avro_b_batch(x, null_frac=0.03, seed=4, label_probs=(0.9, 0.05, 0.05))
+    data, offs, bad = synth.corrupt_batch(data, offs, "avro_b", 2e-3, seed=3)
+    sch = schemas.schema_b_json()
+    prog = bs.avro_schema.compile_schema(sch)
+    kind, lo, rg = schemas.norm_arrays()
+    m64 = _model18()
+    m64.set_normalization(kind, lo, rg, order="f64")
+    rb = dec.RecordBatch(data, offs, skip_prefix=5)
+    cnt = torch.zeros(4, dtype=torch.int64, device="cuda")
+    mse64, flag64, label64, status64 = dec.decode_score(m64, rb, avro_schema=sch, counters=cnt)
+    # the reference order on the CPU: float64 decode, float64 normalize_fn, float32 cast, then the model (here: the same kernel math
+    # on pre-normalised rows, which is bit-identical to the fused kernel's score phase)
+    fields = [(f.type, f.nullable, f.out) for f in prog.fields]
+    v64, lab_ref, st_ref = orc.decode_avro(data, offs, fields, 18, skip_prefix=5, dtype=np.float64)
+    np.testing.assert_array_equal(status64.cpu().numpy(), st_ref)
+    ok = st_ref == 0
+    assert (~ok).sum() == len(bad)
+    with np.errstate(all="ignore"):
+        xn = orc.normalize(v64[ok], kind, lo.astype(np.float64), rg.astype(np.float64), dtype=np.float64).astype(np.float32)
+    plain = _model18()
+    plain.set_normalization(None, None, None)
+    ref_mse, ref_flag = plain.score_device(torch.from_numpy(xn).cuda())
+    np.testing.assert_array_equal(_bits(mse64.cpu().numpy()[ok]), _bits(ref_mse.cpu().numpy()))
+    np.testing.assert_array_equal(flag64.cpu().numpy()[ok], ref_flag.cpu().numpy())
+    np.testing.assert_array_equal(label64.cpu().numpy()[ok], lab_ref[ok])
+    assert np.isnan(mse64.cpu().numpy()[~ok]).all() and cnt.cpu().tolist()[2] == len(bad)
+    # the float32 order on the same records: close, not identical
+    m32 = _model18()
+    mse32 = dec.decode_score(m32, rb, avro_schema=sch)[0].cpu().numpy()
+    a, b = mse64.cpu().numpy()[ok], mse32[ok]
+    fin = np.isfinite(a) & np.isfinite(b)
+    assert (np.abs(a[fin] - b[fin]) <= 2e-6 * np.abs(b[fin]) + 1e-9).all() and (_bits(a[fin]) != _bits(b[fin])).any()
+    # no float64 values there: refused
+    for call in (lambda: dec.decode_score(m64, dec.RecordBatch(*synth.csv_batch(x[:10].astype(np.float32), seed=1)), csv_kinds=SENSOR_KINDS),
+                 lambda: m64.score(x[:10].astype(np.float32))):
+        with pytest.raises(Exception, match="float64"):
+            call()

@@ -46,7 +46,7 @@ def test_struct_sizes_match_header():
     # sizes implied by include/b2_api.h (ints are 4 bytes, no padding surprises)
     f = bs._ffi
     assert ctypes.sizeof(f.AeDesc) == 4 + 9 * 4 + 8 * 4 + 4
-    assert ctypes.sizeof(f.Norm) == 4 + 3 * 64 * 4
+    assert ctypes.sizeof(f.Norm) == 4 + 3 * 64 * 4 + 4   # + order
     assert ctypes.sizeof(f.CsvSpec) == 4 + 3 * 64 * 4 + 8
     assert ctypes.sizeof(f.AvroProg) == 8 + 64 * 4
     assert ctypes.sizeof(f.Adam) == 24
