@@ -187,10 +187,12 @@ __device__ __forceinline__ float norm_feature(float v, int kind, float lo, float
 // instructions with neutral constants (see NormP).  Hence bit-identical to norm_feature() for
 // 2^-64 <= |range| <= 2^64 (beyond that the residual r itself can go subnormal); checked exhaustively on the device over all
 // 2^32 inputs by b2_selftest_normalize (tests/test_normalize_gpu.py).
-template <int D>
+// MASKED = false: the caller knows that neither feature is of kind ZERO (their masks are all ones), so the two ANDs are left out
+template <int D, bool MASKED = true>
 __device__ __forceinline__ float2 norm_pair_fast(float2 v, const NormP<D>& nm, int i) {
   const float* __restrict__ c = nm.pk[i >> 1];  // i is even
-  const float2 vm = make_float2(__uint_as_float(__float_as_uint(v.x) & __float_as_uint(c[12])), __uint_as_float(__float_as_uint(v.y) & __float_as_uint(c[13])));
+  const float2 vm = MASKED ? make_float2(__uint_as_float(__float_as_uint(v.x) & __float_as_uint(c[12])), __uint_as_float(__float_as_uint(v.y) & __float_as_uint(c[13])))
+                           : v;
   const float2 t = fma2(make_float2(c[0], c[1]), splat(-1.0f), vm);  // v - lo (exactly one rounding, like the reference's subtraction)
   const float2 q0 = mul2(t, make_float2(c[2], c[3]));
   const float2 r = fma2(make_float2(-q0.x, -q0.y), make_float2(c[4], c[5]), t);
@@ -231,7 +233,8 @@ __device__ __forceinline__ void ae_forward_rows(const AeW<D>& w, const NormP<D>&
       }
       float2 xv = *reinterpret_cast<const float2*>(row[r] + i);
       if (NORM) {
-        xv = norm_pair_fast<D>(xv, nm, i);
+        // with a compiled-in zero set, a pair outside it has no ZERO feature: no masks
+        xv = (ZM != 0u && ((ZM >> i) & 3u) == 0u) ? norm_pair_fast<D, false>(xv, nm, i) : norm_pair_fast<D, true>(xv, nm, i);
         *reinterpret_cast<float2*>(row[r] + i) = xv;
       }
       if (!((ZM >> i) & 1u)) {
