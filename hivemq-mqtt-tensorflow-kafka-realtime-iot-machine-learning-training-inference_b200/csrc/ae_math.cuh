@@ -82,13 +82,15 @@ static inline int norm_fill(const b2_norm* norm, NormP<D>& nm, int n = D) {
 // The reference's normalisation table forces features 0, 2, 4 and 5 to zero (cardata-v1.py:72, :78, :84, :87): kernels carry one
 // instantiation with that zero set compiled in (ZM of ae_forward_rows), launched when the caller's table has exactly this set.
 constexpr unsigned REF_ZERO_MASK = 0x35u;
-// bit i = feature i is of kind ZERO; ~0u when a layer-1 weight row that a ZM instantiation would skip is not finite (+0 · w must be
-// exactly nothing for the skip to be invisible)
+// bit i = feature i is of kind ZERO — or ~0u when the table is not of the shape the ZM instantiations assume: every feature
+// outside the zero set of kind SCALE (as in the reference's table: the instantiation then folds "* 2 - 1" into immediates), and
+// the layer-1 weight rows it skips finite (+0 · w must be exactly nothing for the skip to be invisible)
 template <int D, class W, class N>
 static inline unsigned norm_zero_set(const N& nm, const W& w) {
   unsigned zm = 0;
   for (int i = 0; i < D && i < 32; ++i) {
-    if (nm.kind[i] != B2_NORM_ZERO) continue;
+    if (nm.kind[i] == B2_NORM_SCALE) continue;
+    if (nm.kind[i] != B2_NORM_ZERO) return ~0u;
     zm |= 1u << i;
     for (int j = 0; j < 14; ++j)
       if (!(w.k1[i][j] - w.k1[i][j] == 0.0f)) return ~0u;
@@ -187,7 +189,8 @@ __device__ __forceinline__ float norm_feature(float v, int kind, float lo, float
 // instructions with neutral constants (see NormP).  Hence bit-identical to norm_feature() for
 // 2^-64 <= |range| <= 2^64 (beyond that the residual r itself can go subnormal); checked exhaustively on the device over all
 // 2^32 inputs by b2_selftest_normalize (tests/test_normalize_gpu.py).
-// MASKED = false: the caller knows that neither feature is of kind ZERO (their masks are all ones), so the two ANDs are left out
+// MASKED = false: the caller knows that both features are of kind SCALE: no masks, the correction factor is the reciprocal itself
+// and the last step is fma(q, 2, -1) with immediates — four constants per feature instead of seven
 template <int D, bool MASKED = true>
 __device__ __forceinline__ float2 norm_pair_fast(float2 v, const NormP<D>& nm, int i) {
   const float* __restrict__ c = nm.pk[i >> 1];  // i is even
@@ -196,9 +199,10 @@ __device__ __forceinline__ float2 norm_pair_fast(float2 v, const NormP<D>& nm, i
   const float2 t = fma2(make_float2(c[0], c[1]), splat(-1.0f), vm);  // v - lo (exactly one rounding, like the reference's subtraction)
   const float2 q0 = mul2(t, make_float2(c[2], c[3]));
   const float2 r = fma2(make_float2(-q0.x, -q0.y), make_float2(c[4], c[5]), t);
-  float2 q = fma2(r, make_float2(c[6], c[7]), q0);
+  float2 q = fma2(r, MASKED ? make_float2(c[6], c[7]) : make_float2(c[2], c[3]), q0);
   if (fabsf(q0.x) == __int_as_float(0x7F800000)) q.x = q0.x;
   if (fabsf(q0.y) == __int_as_float(0x7F800000)) q.y = q0.y;
+  if (!MASKED) return fma2(q, splat(2.0f), splat(-1.0f));
   return fma2(q, make_float2(c[8], c[9]), make_float2(c[10], c[11]));
 }
 
@@ -233,7 +237,8 @@ __device__ __forceinline__ void ae_forward_rows(const AeW<D>& w, const NormP<D>&
       }
       float2 xv = *reinterpret_cast<const float2*>(row[r] + i);
       if (NORM) {
-        // with a compiled-in zero set, a pair outside it has no ZERO feature: no masks
+        // with a compiled-in zero set (launched for tables whose other features are all of kind SCALE), a pair outside it needs
+        // neither masks nor the per-kind constants
         xv = (ZM != 0u && ((ZM >> i) & 3u) == 0u) ? norm_pair_fast<D, false>(xv, nm, i) : norm_pair_fast<D, true>(xv, nm, i);
         *reinterpret_cast<float2*>(row[r] + i) = xv;
       }
