@@ -69,3 +69,32 @@ def test_confluent_framing_is_magic_zero_plus_big_endian_schema_id():
     prog = av.compile_schema(json.dumps(sv.SCHEMA_SPEC_RECORD))
     data, _ = av.encode_records(prog, {"a": np.array([27])}, 1, strings={"b": [b"foo"]}, prefix_schema_id=0x01020304)
     assert data.tobytes() == bytes([0, 1, 2, 3, 4]) + sv.h(sv.SPEC_RECORD_HEX)
+
+
+def test_float64_decode_of_cardata_v3_keeps_doubles_and_ints_exact():
+    """cardata-v3.py:53-74 decodes with dtype=tf.float64 (ints cast to float64, :98-103): the oracle's float64 mode returns a double
+    as it is stored and an int exactly, where the float32 mode (cardata-v1.py) rounds both once."""
+    import struct
+
+    schema = {"type": "record", "name": "r", "fields": [{"name": "d", "type": ["null", "double"]}, {"name": "i", "type": ["null", "int"]},
+                                                        {"name": "n", "type": ["null", "double"]}]}
+    prog = av.compile_schema(json.dumps(schema))
+    d, i = 0.1 + 2.0 ** -40, 16777217                       # neither is a float32
+    zz = (i << 1) ^ (i >> 31)
+    vi = bytearray()
+    while zz >= 0x80:
+        vi.append((zz & 0x7F) | 0x80)
+        zz >>= 7
+    vi.append(zz)
+    payload = b"\x02" + struct.pack("<d", d) + b"\x02" + bytes(vi) + b"\x00"    # union branch 1, branch 1, null
+    data, offs = np.frombuffer(payload, dtype=np.uint8), np.array([0, len(payload)], dtype=np.int32)
+    fields = [(f.type, f.nullable, f.out) for f in prog.fields]
+    o64, _, st64 = orc.decode_avro(data, offs, fields, prog.n_out, skip_prefix=0, dtype=np.float64)
+    o32, _, st32 = orc.decode_avro(data, offs, fields, prog.n_out, skip_prefix=0)
+    assert st64[0] == 0 and st32[0] == 0
+    assert o64.dtype == np.float64 and o64[0].tolist() == [d, float(i), 0.0]
+    assert o32.dtype == np.float32 and o32[0].tolist() == [float(np.float32(d)), float(np.float32(i)), 0.0]
+    # and the float64 normalize_fn differs from the float32 one exactly where a rounding step does
+    kind, lo, rg = np.array([2, 2, 1]), np.array([0.0, 0.0, 0.0]), np.array([7.0, 3.0, 1.0])
+    n64 = orc.normalize(o64, kind, lo, rg, dtype=np.float64)
+    assert n64[0, 0] == (d - 0.0) / 7.0 * 2.0 - 1.0 and n64[0, 1] == float(i) / 3.0 * 2.0 - 1.0 and n64[0, 2] == 0.0
