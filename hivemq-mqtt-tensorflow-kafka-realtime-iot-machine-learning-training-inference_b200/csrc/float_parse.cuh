@@ -505,6 +505,23 @@ B2_HD int b2_num16(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, uint32_t 
   int Lm, pd, has_dot, ex = 0, L;
   if (MODE == 0 ? (p1 >= rem || c1 == delim) : (c1 == ',' || c1 == '}')) {
     if (p1 == 0) return neg ? -1 : 0;  // empty field ("-" alone is not a number)
+    if (p1 <= 8) {
+      // an integer token of at most 8 digits (tyre pressures, firmware version, time stamps' low part …): it fits 32 bits, so ONE
+      // integer → binary32 conversion is the correctly rounded value (exact below 2^24).  The 8 bytes are shifted up so that the
+      // last digit sits in byte 7: what follows the token falls off the top, the bytes below read as leading zeros.
+      if (MODE == 1 && (p1 > rem || (p1 > 1 && (t0 & 0xFFu) == '0'))) return -1;
+      const uint64_t X = (((uint64_t)x1 << 32) | x0) << (8 * (8 - p1));
+      const uint32_t v = b2_four_digits_fast((uint32_t)X) * 10000u + b2_four_digits_fast((uint32_t)(X >> 32));
+      float f = (float)v;
+      uint32_t fb;
+#if defined(__CUDA_ARCH__)
+      fb = __float_as_uint(f);
+#else
+      __builtin_memcpy(&fb, &f, 4);
+#endif
+      *out = (neg ? 0x80000000u : 0u) | fb;
+      return p1 + neg;
+    }
     Lm = pd = L = p1;
     has_dot = 0;
   } else {

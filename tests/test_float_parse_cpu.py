@@ -18,3 +18,12 @@ def test_parse_fuzz_against_strtof(tmp_path, golden_dir):
     r = subprocess.run([exe, "300000", str(tf)], capture_output=True, text=True)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "mismatches=0" in r.stdout
+
+
+def test_integer_tokens_against_strtof(tmp_path):
+    """The at-most-8-digit integer shortcut of the CSV / JSON number parser (tyre pressures, firmware version) vs glibc strtof."""
+    exe = str(tmp_path / "int_token_fuzz")
+    subprocess.run(["g++", "-O2", "-std=c++17", "-I", os.path.join(ROOT, "include"), "-o", exe,
+                    os.path.join(ROOT, "tests", "helpers", "int_token_fuzz.cpp")], check=True)
+    r = subprocess.run([exe, "1000000"], capture_output=True, text=True)
+    assert r.returncode == 0 and "0 mismatches" in r.stdout, r.stdout[-500:]
