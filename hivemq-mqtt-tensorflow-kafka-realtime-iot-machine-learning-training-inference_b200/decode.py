@@ -494,3 +494,103 @@ def decode_score_host(model, data, offsets, csv_kinds=None, csv_defaults=None, a
         out.copy_(ws.res[: n * 5], non_blocking=True)
     main.synchronize()
     return out[: n * 4].view(torch.float32).numpy(), out[n * 4:].numpy()
+
+
+class HostScorePipeline:
+    """Streaming form of ``decode_score_host`` for a consumer loop (cardata-v1.py:176-231 polls, scores, produces, polls again):
+    ``submit(data, offsets)`` enqueues a host batch's H2D copies, kernels and D2H copies and returns a ticket at once;
+    ``result(ticket)`` waits for THAT batch only and returns ``(mse f32[n], flag u8[n])``.  Up to ``depth`` batches are in flight
+    (default 2), each in its own set of device / pinned buffers: batch k + 1 crosses PCIe while batch k's last kernel, its last
+    result copy and all of the host-side bookkeeping run, so neither the tail of a batch nor the host's speed shows in the
+    throughput.  One H2D stream and one D2H stream are shared by the slots (the batches stay in order); the kernels run on the
+    stream that is current at construction.
+
+    The returned arrays are views of the slot's pinned buffer: valid until ``depth`` more batches have been submitted."""
+
+    def __init__(self, model, depth: int = 2, chunks: int = 4, threshold: float = 5.0, skip_prefix: int = 0, csv_kinds=None,
+                 csv_defaults=None, avro_schema=None, json_keys=None, json_label=None):
+        if depth < 1:
+            raise ValueError("depth must be at least 1")
+        self.model, self.depth, self.chunks, self.threshold, self.skip_prefix = model, int(depth), int(chunks), float(threshold), skip_prefix
+        self.kw = dict(csv_kinds=csv_kinds, csv_defaults=csv_defaults, avro_schema=avro_schema, json_keys=json_keys, json_label=json_label)
+        self.dev = torch.device("cuda", torch.cuda.current_device())
+        self.main = torch.cuda.current_stream()
+        self.slots = [_HostWorkspace(self.dev) for _ in range(self.depth)]
+        self.side, self.back = self.slots[0].side, self.slots[0].back
+        self.pinned = [None] * self.depth          # per slot: pinned uint8[5 n]
+        self.fin = [torch.cuda.Event() for _ in range(self.depth)]
+        self.n_of = [0] * self.depth
+        self.ticket_of = [None] * self.depth       # ticket whose results sit in the slot and have not been collected
+        self.next_ticket = 0
+
+    def submit(self, data, offsets) -> int:
+        d = data if isinstance(data, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(data, dtype=np.uint8))
+        o = offsets if isinstance(offsets, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(offsets, dtype=np.int32))
+        n = int(o.numel()) - 1
+        t = self.next_ticket
+        self.next_ticket += 1
+        s = t % self.depth
+        if self.ticket_of[s] is not None:          # the slot's previous batch was never collected: its buffers are about to be reused
+            self.fin[s].synchronize()
+            self.ticket_of[s] = None
+        ws = self.slots[s]
+        self.n_of[s] = n
+        self.ticket_of[s] = t
+        if n <= 0:
+            self.fin[s].record(self.back)
+            return t
+        if self.pinned[s] is None or self.pinned[s].numel() < n * 5:
+            self.pinned[s] = torch.empty(n * 5, dtype=torch.uint8).pin_memory()
+        out = self.pinned[s]
+        oh = o.numpy()
+        b_first, b_last = int(oh[0]), int(oh[n])
+        ws.fit(b_last, n)
+        main, side, back = self.main, self.side, self.back
+        d_dev, o_dev = ws.d, ws.o[: n + 1]
+        mse = ws.res[: n * 4].view(torch.float32)
+        flag = ws.res[n * 4: n * 5]
+        status = ws.status[:n]
+        label = ws.label[:n] if self.kw["avro_schema"] is not None else None
+        chunks = max(1, min(self.chunks, len(ws.events)))
+        tot = chunks * (chunks + 1) // 2
+        bounds = sorted(set(n * (tot - (chunks - c) * (chunks - c + 1) // 2) // tot for c in range(chunks + 1)))
+        with torch.cuda.stream(side):
+            o_dev.copy_(o, non_blocking=True)
+            for k, (c0, c1) in enumerate(zip(bounds[:-1], bounds[1:])):
+                b0, b1 = int(oh[c0]), int(oh[c1])
+                if b1 > b0:
+                    d_dev[b0:b1].copy_(d[b0:b1], non_blocking=True)
+                ws.events[k].record(side)
+        avg = (b_last - b_first + n - 1) // max(n, 1)
+        with torch.cuda.stream(main):
+            for k, (c0, c1) in enumerate(zip(bounds[:-1], bounds[1:])):
+                main.wait_event(ws.events[k])
+                rb = RecordBatch.__new__(RecordBatch)
+                rb.data, rb.offsets, rb.n, rb.skip_prefix = d_dev, o_dev[c0:c1 + 1], c1 - c0, self.skip_prefix
+                rb.avg_record_bytes = avg
+                decode_score(self.model, rb, threshold=self.threshold, mse=mse[c0:c1], flag=flag[c0:c1], status=status[c0:c1],
+                             label=None if label is None else label[c0:c1], **self.kw)
+                ws.done[k].record(main)
+                with torch.cuda.stream(back):
+                    back.wait_event(ws.done[k])
+                    out[c0 * 4: c1 * 4].copy_(ws.res[c0 * 4: c1 * 4], non_blocking=True)
+                    out[n * 4 + c0: n * 4 + c1].copy_(ws.res[n * 4 + c0: n * 4 + c1], non_blocking=True)
+        self.fin[s].record(back)
+        return t
+
+    def result(self, ticket: int):
+        s = ticket % self.depth
+        if self.ticket_of[s] != ticket:
+            raise ValueError(f"ticket {ticket} is not in flight (collected already, or {self.depth} batches were submitted after it)")
+        self.fin[s].synchronize()
+        self.ticket_of[s] = None
+        n = self.n_of[s]
+        if n <= 0:
+            return np.zeros(0, np.float32), np.zeros(0, np.uint8)
+        out = self.pinned[s]
+        return out[: n * 4].view(torch.float32).numpy(), out[n * 4: n * 5].numpy()
+
+    def drain(self):
+        """Collect everything still in flight, oldest first → list of (ticket, mse, flag)."""
+        pend = sorted(t for t in self.ticket_of if t is not None)
+        return [(t,) + self.result(t) for t in pend]

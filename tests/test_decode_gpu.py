@@ -548,3 +548,53 @@ def test_float64_normalisation_order_of_cardata_v3(cuda_device):
                  lambda: m64.score(x[:10].astype(np.float32))):
         with pytest.raises(Exception, match="float64"):
             call()
+
+
+def test_host_score_pipeline_matches_one_batch_at_a_time(cuda_device):
+    """HostScorePipeline (submit / result, two batches in flight, per-slot buffers) returns what decode_score_host returns, batch by
+    batch — ragged sizes, an empty batch, results collected late, out of order and after the slot was about to be reused."""
+    m = _model18()
+    sch = schemas.schema_a_json()
+    batches = []
+    for i, n in enumerate((50_003, 7, 0, 1, 33_333, 64, 20_001)):
+        if n == 0:
+            batches.append((np.zeros(0, np.uint8), np.zeros(1, np.int32)))
+        else:
+            batches.append(synth.avro_a_batch(synth.sensor_rows(n, seed=100 + i)))
+    want = [dec.decode_score_host(m, d, o, avro_schema=sch, skip_prefix=5) for d, o in batches]
+    pipe = dec.HostScorePipeline(m, depth=2, avro_schema=sch, skip_prefix=5)
+    pinned = [(torch.from_numpy(d).pin_memory(), torch.from_numpy(o).pin_memory()) for d, o in batches]
+    got = {}
+    prev = None
+    for k, (d, o) in enumerate(pinned):       # the consumer loop: submit k, then collect k - 1
+        t = pipe.submit(d, o)
+        if prev is not None:
+            mse, flag = pipe.result(prev)
+            got[prev] = (mse.copy(), flag.copy())
+        prev = t
+    for t, mse, flag in pipe.drain():
+        got[t] = (mse.copy(), flag.copy())
+    assert sorted(got) == list(range(len(batches)))
+    for k, (mse, flag) in enumerate(want):
+        np.testing.assert_array_equal(_bits(got[k][0]), _bits(mse))
+        np.testing.assert_array_equal(got[k][1], flag)
+    # a ticket that was never collected is waited for when its slot comes round again; collecting it afterwards is an error
+    t0 = pipe.submit(*pinned[0])
+    t1 = pipe.submit(*pinned[4])
+    t2 = pipe.submit(*pinned[6])               # reuses t0's slot
+    with pytest.raises(ValueError):
+        pipe.result(t0)
+    m2, f2 = pipe.result(t2)
+    m1, f1 = pipe.result(t1)
+    np.testing.assert_array_equal(_bits(m2), _bits(want[6][0]))
+    np.testing.assert_array_equal(_bits(m1), _bits(want[4][0]))
+    # CSV through the same pipeline, depth 3
+    xs = synth.sensor_rows(9_000, seed=5)
+    dcsv, ocsv = synth.csv_batch(xs, seed=2)
+    p3 = dec.HostScorePipeline(m, depth=3, csv_kinds=SENSOR_KINDS)
+    ts = [p3.submit(dcsv, ocsv) for _ in range(3)]
+    ref = dec.decode_score_host(m, dcsv, ocsv, csv_kinds=SENSOR_KINDS)
+    for t in ts:
+        mse, flag = p3.result(t)
+        np.testing.assert_array_equal(_bits(mse), _bits(ref[0]))
+        np.testing.assert_array_equal(flag, ref[1])
