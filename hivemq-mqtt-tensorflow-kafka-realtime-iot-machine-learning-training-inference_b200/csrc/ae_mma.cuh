@@ -12,7 +12,7 @@
 // so with MMA k index t ↔ unit 8s+2t and t+4 ↔ unit 8s+2t+1 (the rows of B permuted to match, done once per CTA) a0..a3 =
 // c0, c2, c1, c3: the activation writes its results in that order and nothing else moves.  Layer 1 takes the same elements from the
 // tile, which therefore holds the warp's rows INTERLEAVED in pairs (rows g and g+8 of an M tile element by element:
-// tile[pair][col][slot], see mma_row_slot) so that ONE 16-byte load is an A fragment; those x values are also exactly the elements
+// tile[pair][col][slot], see mma_row_offset) so that ONE 16-byte load is an A fragment; those x values are also exactly the elements
 // the lane needs for (x - y)^2 at the end.
 // Precision: 3-pass split TF32, D = A_lo·B_hi + A_hi·B_lo + A_hi·B_hi with FP32 accumulation (A split by truncation on the fly, B
 // split with round-to-nearest once per CTA); biases are the initial accumulator, so they stay full FP32.
