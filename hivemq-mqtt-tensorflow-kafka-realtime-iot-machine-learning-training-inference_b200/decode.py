@@ -505,7 +505,8 @@ class HostScorePipeline:
     throughput.  One H2D stream and one D2H stream are shared by the slots (the batches stay in order); the kernels run on the
     stream that is current at construction.
 
-    The returned arrays are views of the slot's pinned buffer: valid until ``depth`` more batches have been submitted."""
+    The returned arrays are views of the slot's pinned buffer: valid until ``depth`` more batches have been submitted.  A PINNED
+    input buffer is read by the copy engine after ``submit`` has returned: leave it alone until that batch's ``result``."""
 
     def __init__(self, model, depth: int = 2, chunks: int = 4, threshold: float = 5.0, skip_prefix: int = 0, csv_kinds=None,
                  csv_defaults=None, avro_schema=None, json_keys=None, json_label=None):
