@@ -33,3 +33,20 @@ def test_field_program():
 def test_norm_table():
     kind, lo, rng = schemas.norm_arrays()
     assert kind.tolist().count(schemas.NORM_ZERO) == 4 and rng[1] == 25.0 and rng[13] == 7.0 and rng[9] == 15.0
+
+
+def test_reference_table_has_the_shape_the_specialised_kernels_are_compiled_for():
+    """csrc/ae_math.cuh compiles one instantiation for the reference's normalize_fn table: features 0, 2, 4, 5 forced to 0.0
+    (cardata-v1.py:72, :78, :84, :87 — REF_ZERO_MASK = 0x35), every other feature scaled.  If the table here ever changes shape, the
+    generic kernels take over silently: this test is the reminder."""
+    import os
+    import re
+
+    from b200_sensor import schemas
+
+    kind, lo, rg = schemas.norm_arrays()
+    zero = sum(1 << i for i, k in enumerate(kind) if k == schemas.NORM_ZERO)
+    assert zero == 0x35 and all(k in (schemas.NORM_ZERO, schemas.NORM_SCALE) for k in kind)
+    src = open(os.path.join(os.path.dirname(os.path.abspath(schemas.__file__)), "csrc", "ae_math.cuh")).read()
+    assert int(re.search(r"REF_ZERO_MASK = (0x[0-9a-fA-F]+)u", src).group(1), 16) == zero
+    assert (rg[kind == schemas.NORM_SCALE] >= 1.0).all()   # reciprocals ≤ 1: no overflow on the way to the quotient
