@@ -13,7 +13,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 OPS = ["UTCHMMA", "LDTM", "STTM", "UTCBAR", "UBLKCP", "SYNCS", "FFMA2", "LDCU", "MUFU", "HMMA", "DMUL", "STL", "LDL"]
 HEAD = """# SASS evidence for libb2sensor.so at HEAD (cuobjdump -sass, sm_100a): static instruction counts per kernel.
 # UTCHMMA = tcgen05.mma, LDTM / STTM = tcgen05.ld / st (TMEM), UTCBAR = tcgen05.commit, UBLKCP = cp.async.bulk (TMA engine),
-# SYNCS = mbarrier, FFMA2 = packed FP32 FMA, LDCU = uniform constant load, HMMA = legacy mma.sync (none expected),
+# SYNCS = mbarrier, FFMA2 = packed FP32 FMA, LDCU = uniform constant load, HMMA = warp-level mma.sync (only the optional decode_kernel_wm variant, §9 of the notes),
 # STL / LDL = local-memory traffic.
 """
 
