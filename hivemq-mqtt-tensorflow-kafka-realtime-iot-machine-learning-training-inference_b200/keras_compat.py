@@ -483,10 +483,56 @@ class Model:
                                           _ffi.ptr(flag), _ffi.ptr(recon), _ffi.ptr(counters), _stream_ptr()), "b2_ae_score")
         return mse, flag
 
-    def score(self, x, threshold: float = 5.0):
+    def _score_host_overlapped(self, x: torch.Tensor, threshold: float, dev, chunks: int = 4):
+        """Pinned float32 rows on the host → (mse, flag) in a pinned result buffer kept per size: the rows cross PCIe in chunks of
+        falling size on a copy stream, chunk c is scored while chunk c + 1 arrives, and its 5 B/row results go back on a third
+        stream (the same three-stream overlap as decode.decode_score_host)."""
+        n, d = x.shape
+        ws = getattr(self, "_host_ws", None)
+        if ws is None or ws["dev"] != dev:
+            ws = self._host_ws = {"dev": dev, "side": torch.cuda.Stream(device=dev), "back": torch.cuda.Stream(device=dev), "cap": 0,
+                                  "ev": [torch.cuda.Event() for _ in range(16)], "done": [torch.cuda.Event() for _ in range(16)], "out": {}}
+        if n > ws["cap"]:
+            ws["cap"] = n
+            ws["x"] = torch.empty((n, d), dtype=torch.float32, device=dev)
+            ws["res"] = torch.empty(n * 5 + 16, dtype=torch.uint8, device=dev)
+        out = ws["out"].get(n)
+        if out is None:
+            out = ws["out"][n] = torch.empty(n * 5, dtype=torch.uint8).pin_memory()
+        xd, res = ws["x"][:n], ws["res"]
+        mse, flag = res[: n * 4].view(torch.float32), res[n * 4: n * 5]
+        main, side, back = torch.cuda.current_stream(), ws["side"], ws["back"]
+        chunks = max(1, min(chunks, 16))
+        tot = chunks * (chunks + 1) // 2
+        bounds = sorted(set(n * (tot - (chunks - c) * (chunks - c + 1) // 2) // tot for c in range(chunks + 1)))
+        side.wait_stream(main)
+        with torch.cuda.stream(side):
+            for k, (c0, c1) in enumerate(zip(bounds[:-1], bounds[1:])):
+                xd[c0:c1].copy_(x[c0:c1], non_blocking=True)
+                ws["ev"][k].record(side)
+        for k, (c0, c1) in enumerate(zip(bounds[:-1], bounds[1:])):
+            main.wait_event(ws["ev"][k])
+            self.score_device(xd[c0:c1], threshold, mse=mse[c0:c1], flag=flag[c0:c1])
+            ws["done"][k].record(main)
+            with torch.cuda.stream(back):
+                back.wait_event(ws["done"][k])
+                out[c0 * 4: c1 * 4].copy_(res[c0 * 4: c1 * 4], non_blocking=True)
+                out[n * 4 + c0: n * 4 + c1].copy_(res[n * 4 + c0: n * 4 + c1], non_blocking=True)
+        main.wait_stream(back)
+        main.synchronize()
+        return out[: n * 4].view(torch.float32).numpy(), out[n * 4:].numpy()
+
+    def score(self, x, threshold: float = 5.0, reuse_output: bool = False):
         """``mse = mean((x - predict(x))**2, axis=1)`` (nb2.0:1015) and ``flag = mse > threshold`` (nb2.0:1163).
-        Returns (mse f32[N], flag u8[N]) as NumPy arrays."""
+        Returns (mse f32[N], flag u8[N]) as NumPy arrays.  With ``reuse_output`` and a pinned float32 CPU tensor the copies and the
+        kernel overlap chunk by chunk and the returned arrays are views of a pinned buffer that the next call of the same size
+        overwrites."""
         dev = torch.device("cuda", self._device_index())
+        if (reuse_output and isinstance(x, torch.Tensor) and not x.is_cuda and x.dtype == torch.float32 and x.dim() == 2
+                and x.shape[0] >= 4096 and x.is_contiguous() and x.is_pinned() and self.kind == "dense"):
+            self._ensure_built()
+            with torch.cuda.device(dev):
+                return self._score_host_overlapped(x, threshold, dev)
         xd = _to_device_f32(x, dev)
         mse, flag = self.score_device(xd, threshold)
         return mse.cpu().numpy(), flag.cpu().numpy()

@@ -211,3 +211,20 @@ def test_full_size_properties(cuda_device, ae30, golden_dir):
     sub = torch.arange(0, n, 4099, device="cuda")
     ref = orc.score(x[sub].cpu().numpy(), ae30["weights"], [30, 14, 7, 7, 30], ACTS, dtype=np.float64)[0]
     _check(mse[sub].cpu().numpy(), flag[sub].cpu().numpy(), ref)
+
+
+def test_score_host_overlapped_path_equals_plain_path(cuda_device, ae30, golden_dir):
+    """Model.score(pinned rows, reuse_output=True): chunked H2D / kernel / D2H overlap — same bits as the plain call; sizes around the
+    chunk arithmetic; the D = 18 model with its fused normalisation too."""
+    m30 = _model30(ae30, golden_dir)
+    m18 = _model18()
+    m18.set_normalization(*bs.schemas.norm_arrays())
+    for m, gen, d in ((m30, bs.synth.credit_rows, 30), (m18, bs.synth.sensor_rows, 18)):
+        for n in (4096, 4097, 65_537, 200_003):
+            x = np.ascontiguousarray(gen(n, seed=n % 97), dtype=np.float32)
+            ref_mse, ref_flag = m.score(x)
+            hx = torch.from_numpy(x).pin_memory()
+            for _ in range(2):   # second call reuses the buffers
+                mse, flag = m.score(hx, reuse_output=True)
+                np.testing.assert_array_equal(np.asarray(mse).view(np.uint32), np.asarray(ref_mse, dtype=np.float32).view(np.uint32))
+                np.testing.assert_array_equal(flag, ref_flag)
