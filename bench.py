@@ -871,7 +871,7 @@ def main():
                                      "kernel, max over ranks: what the host / PCIe side alone allows at this N"},
                "api": "Model.score(pinned host tensor, reuse_output=True) -> (mse, flag) numpy; rows in 4 chunks, H2D / kernel / D2H overlapped" if isinstance(wl, ScoreWorkload) else
                       "decode.HostScorePipeline(model).submit(pinned bytes, pinned offsets) / .result(ticket) -> (mse, flag) numpy, two "
-                      "batches in flight; per batch 4 chunks, H2D of a chunk under the kernel of the one before, results D2H chunk by "
+                      "batches in flight; per batch 2 chunks, H2D of a chunk under the kernel of the one before, results D2H chunk by "
                       "chunk on a third stream (decode.decode_score_host is the one-batch-at-a-time form of the same steps)"}
 
     if rank == 0:

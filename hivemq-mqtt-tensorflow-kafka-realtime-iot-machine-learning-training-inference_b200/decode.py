@@ -503,12 +503,13 @@ class HostScorePipeline:
     (default 2), each in its own set of device / pinned buffers: batch k + 1 crosses PCIe while batch k's last kernel, its last
     result copy and all of the host-side bookkeeping run, so neither the tail of a batch nor the host's speed shows in the
     throughput.  One H2D stream and one D2H stream are shared by the slots (the batches stay in order); the kernels run on the
-    stream that is current at construction.
+    stream that is current at construction.  ``chunks`` cuts a batch as in ``decode_score_host``; with batches overlapping each other
+    it matters little (measured 1.29 – 1.32 ms per 2^20-record batch for 1, 2 or 4 chunks), two keeps the host-side work small.
 
     The returned arrays are views of the slot's pinned buffer: valid until ``depth`` more batches have been submitted.  A PINNED
     input buffer is read by the copy engine after ``submit`` has returned: leave it alone until that batch's ``result``."""
 
-    def __init__(self, model, depth: int = 2, chunks: int = 4, threshold: float = 5.0, skip_prefix: int = 0, csv_kinds=None,
+    def __init__(self, model, depth: int = 2, chunks: int = 2, threshold: float = 5.0, skip_prefix: int = 0, csv_kinds=None,
                  csv_defaults=None, avro_schema=None, json_keys=None, json_label=None):
         if depth < 1:
             raise ValueError("depth must be at least 1")
