@@ -847,7 +847,7 @@ def main():
     e2e = None
     if not args.no_e2e:
         wl.setup_e2e(dev, rank)
-        for i in range(2):
+        for i in range(max(args.warmup, 3) * 8):   # the link and the host side have idled through the device-resident region: 24+ batches (≈ 30 ms) of warm-up
             wl.step_e2e(i)
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
